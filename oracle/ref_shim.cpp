@@ -1,0 +1,262 @@
+// ref_shim.cpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+//
+// extern "C" shim over the UNMODIFIED reference library
+// (/root/reference/libraries/hough-3d-lines/{vector3d,pointcloud,sphere,hough}.cpp),
+// which oracle/Makefile compiles in place into oracle/_ref/libhough_ref.so.
+// No reference source is copied: this file only #includes the reference headers
+// from where they lie and calls the reference classes.  It exists so that tests
+// (and tests/golden/make_golden.py) can drive the real reference through ctypes.
+//
+// The loop driver below follows lib/hough3dlines.cpp:200-317 / wrap.h:172-347 with
+// initHoughSpace(g) + the 3-arg ctor (the fork's own main() does not compile against
+// its hough.h).  orthogonal_LSQ needs Eigen, which is absent: the driver calls the
+// restatement h3do_orthogonal_lsq (oracle/h3d_oracle.c) -- parity unpinned there.
+#include "hough.h"
+#include "pointcloud.h"
+#include "sphere.h"
+#include "vector3d.h"
+
+#include "h3d_oracle.h"
+
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace {
+void to_pc(PointCloud &pc, const double *xyz, size_t n) {
+  pc.points.resize(n);
+  for (size_t i = 0; i < n; i++) pc.points[i] = Vector3d(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+}
+void from_pc(const PointCloud &pc, double *xyz) {
+  for (size_t i = 0; i < pc.points.size(); i++) {
+    xyz[3 * i] = pc.points[i].x; xyz[3 * i + 1] = pc.points[i].y; xyz[3 * i + 2] = pc.points[i].z;
+  }
+}
+int g_granularity = -1;
+}  // namespace
+
+extern "C" {
+
+// ---- sphere / initHoughSpace (lib/hough.cpp:15-20) -----------------------
+size_t ref_sphere(int g, double *xyz, size_t cap) {
+  Sphere s;
+  s.fromIcosahedron(g);
+  size_t n = s.vertices.size();
+  if (xyz) {
+    if (n > cap) return 0;
+    for (size_t i = 0; i < n; i++) { xyz[3 * i] = s.vertices[i].x; xyz[3 * i + 1] = s.vertices[i].y; xyz[3 * i + 2] = s.vertices[i].z; }
+  }
+  return n;
+}
+size_t ref_sphere_triangles(int g, unsigned *tri, size_t cap) {
+  Sphere s;
+  s.fromIcosahedron(g);
+  size_t n = s.triangles.size();
+  if (tri) {
+    if (n > cap) return 0;
+    for (size_t i = 0; i < n; i++) tri[i] = s.triangles[i];
+  }
+  return n;
+}
+void ref_init_space(int g) {
+  if (g_granularity == g) return;   // the reference leaks the old sphere; avoid redoing 15 s at g6
+  initHoughSpace((unsigned)g);
+  g_granularity = g;
+}
+
+// ---- Hough ---------------------------------------------------------------
+void *ref_hough_create(const double minP[3], const double maxP[3], double dx) {
+  try {
+    return new Hough(Vector3d(minP[0], minP[1], minP[2]), Vector3d(maxP[0], maxP[1], maxP[2]), dx);
+  } catch (...) { return nullptr; }
+}
+void ref_hough_destroy(void *h) { delete static_cast<Hough *>(h); }
+size_t ref_hough_num_x(void *h) { return static_cast<Hough *>(h)->num_x; }
+size_t ref_hough_num_b(void *h) { return static_cast<Hough *>(h)->num_b; }
+double ref_hough_dx(void *h) { return static_cast<Hough *>(h)->dx; }
+double ref_hough_max_x(void *h) { return static_cast<Hough *>(h)->max_x; }
+size_t ref_hough_cells(void *h) { return static_cast<Hough *>(h)->VotingSpace.size(); }
+const unsigned *ref_hough_votes(void *h) { return static_cast<Hough *>(h)->VotingSpace.data(); }
+void ref_hough_add(void *h, const double *xyz, size_t n) { PointCloud pc; to_pc(pc, xyz, n); static_cast<Hough *>(h)->add(pc); }
+void ref_hough_subtract(void *h, const double *xyz, size_t n) { PointCloud pc; to_pc(pc, xyz, n); static_cast<Hough *>(h)->subtract(pc); }
+unsigned ref_hough_get_line(void *hv, double a[3], double b[3], uint64_t *flat_index) {
+  Hough *h = static_cast<Hough *>(hv);
+  Vector3d va, vb;
+  unsigned votes = h->getLine(&va, &vb);
+  a[0] = va.x; a[1] = va.y; a[2] = va.z; b[0] = vb.x; b[1] = vb.y; b[2] = vb.z;
+  if (flat_index) {   // getLine does not return the index: recover it by the same first-max rule
+    uint64_t idx = 0;
+    if (votes > 0)
+      for (size_t i = 0; i < h->VotingSpace.size(); i++) if (h->VotingSpace[i] == votes) { idx = i; break; }
+    *flat_index = idx;
+  }
+  return votes;
+}
+
+// ---- PointCloud ------------------------------------------------------------
+void ref_min_max(const double *xyz, size_t n, double mn[3], double mx[3]) {
+  PointCloud pc; to_pc(pc, xyz, n);
+  Vector3d a, b; pc.getMinMax3D(&a, &b);
+  mn[0] = a.x; mn[1] = a.y; mn[2] = a.z; mx[0] = b.x; mx[1] = b.y; mx[2] = b.z;
+}
+void ref_shift_to_origin(double *xyz, size_t n, double shift[3]) {
+  PointCloud pc; to_pc(pc, xyz, n);
+  pc.shift = Vector3d(shift[0], shift[1], shift[2]);
+  pc.shiftToOrigin();
+  from_pc(pc, xyz);
+  shift[0] = pc.shift.x; shift[1] = pc.shift.y; shift[2] = pc.shift.z;
+}
+void ref_mean_value(const double *xyz, size_t n, double mean[3]) {
+  PointCloud pc; to_pc(pc, xyz, n);
+  Vector3d m = pc.meanValue();
+  mean[0] = m.x; mean[1] = m.y; mean[2] = m.z;
+}
+// returns count; idx_out = positions in the input (Y keeps input order, so a
+// two-pointer walk recovers them; equal points are all-in or all-out)
+size_t ref_points_close_to_line(const double *xyz, size_t n, const double a[3], const double b[3],
+                                double dx, uint32_t *idx_out) {
+  PointCloud pc, Y; to_pc(pc, xyz, n);
+  pc.pointsCloseToLine(Vector3d(a[0], a[1], a[2]), Vector3d(b[0], b[1], b[2]), dx, &Y);
+  size_t j = 0;
+  for (size_t i = 0; i < n && j < Y.points.size(); i++)
+    if (pc.points[i] == Y.points[j]) idx_out[j++] = (uint32_t)i;
+  return Y.points.size();
+}
+size_t ref_remove_points(double *x, size_t nx, const double *y, size_t ny) {
+  PointCloud X, Y; to_pc(X, x, nx); to_pc(Y, y, ny);
+  X.removePoints(Y);
+  from_pc(X, x);
+  return X.points.size();
+}
+// rc of readFromFile (0/1/2/3); *n receives the count, xyz (cap points) the data
+int ref_read_from_file(const char *path, char delim, double *xyz, size_t cap, size_t *n) {
+  PointCloud pc;
+  int rc = pc.readFromFile(path, delim);
+  *n = pc.points.size();
+  if (rc == 0 && xyz && pc.points.size() <= cap) from_pc(pc, xyz);
+  return rc;
+}
+
+// ---- iterative loop on the real classes --------------------------------------
+// Same record layout as h3do_hough3dlines so the two traces can be memcmp'd.
+// timing_us (optional, 6 doubles): add, subtract, getLine, closeToLine, lsq, remove.
+int ref_hough3dlines(const double *xyz_in, size_t n_in, int granularity, double opt_dx,
+                     int opt_minvotes, int opt_nlines, int mode,
+                     h3do_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                     h3do_result *res, double *timing_us) {
+  using clk = std::chrono::steady_clock;
+  auto us = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+  double tacc[6] = {0, 0, 0, 0, 0, 0};
+  std::memset(res, 0, sizeof(*res));
+  PointCloud X;
+  std::vector<uint32_t> orig;
+  for (size_t i = 0; i < n_in; i++) {                       // wrap.h:175-189
+    double x = xyz_in[3 * i], y = xyz_in[3 * i + 1], z = xyz_in[3 * i + 2];
+    if (!(std::isnan(x) || std::isinf(x)) && !(std::isnan(y) || std::isinf(y)) && !(std::isnan(z) || std::isinf(z))) {
+      X.points.push_back(Vector3d(x, y, z)); orig.push_back((uint32_t)i);
+    }
+  }
+  res->n_input = (uint32_t)X.points.size();
+  if (mode == 1) {
+    if (opt_minvotes < 2) opt_minvotes = 2;
+    if (X.points.size() < 2) { res->rc = 1; return 1; }
+  }
+  Vector3d minP, maxP, minPshifted, maxPshifted;
+  X.getMinMax3D(&minP, &maxP);
+  double d = (maxP - minP).norm();
+  res->d = d;
+  if (d == 0.0) { res->rc = 1; return 1; }
+  X.shiftToOrigin();
+  X.getMinMax3D(&minPshifted, &maxPshifted);
+  res->shift[0] = X.shift.x; res->shift[1] = X.shift.y; res->shift[2] = X.shift.z;
+  if (mode == 1 && opt_dx == 0.0) opt_dx = d / 64.0;
+  else if (opt_dx >= d) { res->rc = 1; return 1; }
+
+  ref_init_space(granularity);
+  Hough *hough;
+  try { hough = new Hough(minPshifted, maxPshifted, opt_dx); } catch (const std::exception &) { res->rc = 1; return 1; }
+  res->dx = hough->dx; res->max_x = hough->max_x; res->num_x = hough->num_x; res->num_b = hough->num_b;
+  auto t0 = clk::now();
+  hough->add(X);
+  tacc[0] += us(t0, clk::now());
+
+  PointCloud Y;
+  std::vector<uint32_t> yi;
+  double rc;
+  size_t used = 0;
+  uint32_t nlines = 0, it = 0;
+  auto record_inliers = [&](uint32_t *cnt, uint32_t *off) {
+    // Y is an ordered subset of X: recover positions, map to original numbering
+    *cnt = (uint32_t)Y.points.size(); *off = (uint32_t)used;
+    size_t j = 0;
+    for (size_t i = 0; i < X.points.size() && j < Y.points.size(); i++)
+      if (X.points[i] == Y.points[j]) { if (used < pool_cap) pool[used++] = orig[i]; j++; }
+  };
+  do {
+    Vector3d a, b;
+    h3do_iter rec; std::memset(&rec, 0, sizeof(rec));
+    t0 = clk::now(); hough->subtract(Y); tacc[1] += us(t0, clk::now());
+    t0 = clk::now(); rec.votes = hough->getLine(&a, &b); tacc[2] += us(t0, clk::now());
+    {
+      uint64_t idx = 0;
+      if (rec.votes > 0)
+        for (size_t i = 0; i < hough->VotingSpace.size(); i++) if (hough->VotingSpace[i] == rec.votes) { idx = i; break; }
+      rec.argmax = idx;
+    }
+    rec.a_raw[0] = a.x; rec.a_raw[1] = a.y; rec.a_raw[2] = a.z; rec.b_raw[0] = b.x; rec.b_raw[1] = b.y; rec.b_raw[2] = b.z;
+
+    t0 = clk::now(); X.pointsCloseToLine(a, b, opt_dx, &Y); tacc[3] += us(t0, clk::now());
+    record_inliers(&rec.n1, &rec.off1);
+    rec.off2 = (uint32_t)used;
+    {
+      std::vector<double> ybuf(Y.points.size() * 3 + 3);
+      from_pc(Y, ybuf.data());
+      double aa[3], bb[3];
+      t0 = clk::now(); rc = h3do_orthogonal_lsq(ybuf.data(), Y.points.size(), aa, bb); tacc[4] += us(t0, clk::now());
+      a = Vector3d(aa[0], aa[1], aa[2]); b = Vector3d(bb[0], bb[1], bb[2]);
+    }
+    rec.rc1 = rc; rec.a1[0] = a.x; rec.a1[1] = a.y; rec.a1[2] = a.z; rec.b1[0] = b.x; rec.b1[1] = b.y; rec.b1[2] = b.z;
+    if (rc == 0.0) { rec.status = 1; if (it < max_iters) iters[it] = rec; it++; break; }
+
+    t0 = clk::now(); X.pointsCloseToLine(a, b, opt_dx, &Y); tacc[3] += us(t0, clk::now());
+    record_inliers(&rec.n2, &rec.off2);
+    unsigned nvotes = Y.points.size();
+    if (nvotes < (unsigned int)opt_minvotes) { rec.status = 2; if (it < max_iters) iters[it] = rec; it++; break; }
+    {
+      std::vector<double> ybuf(Y.points.size() * 3 + 3);
+      from_pc(Y, ybuf.data());
+      double aa[3], bb[3];
+      t0 = clk::now(); rc = h3do_orthogonal_lsq(ybuf.data(), Y.points.size(), aa, bb); tacc[4] += us(t0, clk::now());
+      a = Vector3d(aa[0], aa[1], aa[2]); b = Vector3d(bb[0], bb[1], bb[2]);
+    }
+    rec.rc2 = rc; rec.a2[0] = a.x; rec.a2[1] = a.y; rec.a2[2] = a.z; rec.b2[0] = b.x; rec.b2[1] = b.y; rec.b2[2] = b.z;
+    if (rc == 0.0) { rec.status = 3; if (it < max_iters) iters[it] = rec; it++; break; }
+    a = a + X.shift;
+    rec.a2[0] = a.x; rec.a2[1] = a.y; rec.a2[2] = a.z;
+    nlines++;
+    if (it < max_iters) iters[it] = rec;
+    it++;
+
+    // removePoints, keeping the original numbering in step (same two-pointer rule)
+    t0 = clk::now();
+    {
+      std::vector<uint32_t> norig;
+      size_t i, j;
+      for (i = 0, j = 0; i < X.points.size() && j < Y.points.size(); i++) {
+        if (X.points[i] == Y.points[j]) j++; else norig.push_back(orig[i]);
+      }
+      for (; i < X.points.size(); i++) norig.push_back(orig[i]);
+      X.removePoints(Y);
+      orig.swap(norig);
+    }
+    tacc[5] += us(t0, clk::now());
+  } while ((X.points.size() > 1) && ((opt_nlines == 0) || (opt_nlines > (int)nlines)));
+
+  res->n_iters = it; res->n_lines = nlines; res->pool_used = used;
+  delete hough;
+  if (timing_us) std::memcpy(timing_us, tacc, sizeof(tacc));
+  return 0;
+}
+
+}  // extern "C"
