@@ -1,0 +1,183 @@
+/*
+ * h3d.h -- C-ABI of libh3d.so: the B200-native (sm_100a) iterative 3D Hough
+ * line-detection path of DJacquemont/pointcloud_segmentation.
+ *
+ * The reference has no FFI for this path: its boundary is the C++ header API of
+ * libraries/hough-3d-lines ("lib/" below), compiled straight into the ROS node
+ * (CMakeLists.txt:164-168).  The drop-in C++ classes shipped under
+ * pointcloud_segmentation_b200/include/ (Hough, PointCloud, Vector3d, Sphere,
+ * initHoughSpace, orthogonal_LSQ) are thin host code over THIS interface; each
+ * entry point cites the reference function it replaces.
+ *
+ * Conventions: plain pointers and sizes, HOST buffers unless a name ends in
+ * `_dev`; every function returns an int status (H3D_OK == 0) and never throws;
+ * h3d_last_error() gives the text of the last failure on the calling thread.
+ * Points are `double xyz[3*n]` (lib/vector3d.h:15-20 layout, AoS) unless stated.
+ * There is no CPU fallback: without a CUDA device every compute call fails with
+ * H3D_ERR_CUDA.
+ *
+ * "wrap.h" = include/pointcloud_segmentation/hough_3d_lines.h of the reference,
+ * "node.cpp" = src/pointcloud_segmentation_node.cpp.
+ */
+#ifndef H3D_H_
+#define H3D_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  H3D_OK = 0,
+  H3D_ERR_ARG = 1,       /* bad argument / not initialised                   */
+  H3D_ERR_CUDA = 2,      /* CUDA runtime failure or no device                */
+  H3D_ERR_NOMEM = 3,     /* device or host allocation failed                 */
+  H3D_ERR_RANGE = 4,     /* accumulator has >= 2^32 cells, num_x too large … */
+  H3D_ERR_DEGENERATE = 5,/* wrap.h:202-212: identical points / dx too large  */
+  H3D_ERR_NCCL = 6
+};
+
+const char *h3d_last_error(void);
+/* library / device facts: sm count, compute capability major*10+minor */
+int h3d_device_info(int *sm_count, int *cc, size_t *smem_per_block_optin);
+
+/* ---- direction sphere: lib/hough.cpp:15-20 initHoughSpace,
+ *      lib/sphere.cpp:18-330 Sphere::fromIcosahedron ----------------------- */
+/* builds (and caches) the direction table for granularity g (0..8) and makes it
+ * the current Hough space, like the reference's global `houghSpace`. */
+int h3d_init_space(unsigned granularity);
+int h3d_space_info(unsigned *granularity, size_t *num_b);
+/* Sphere::vertices / Sphere::triangles of granularity g (does not change the
+ * current space).  Pass NULL buffers to query the counts. */
+int h3d_sphere(int g, double *vertices_xyz, size_t cap_vertices, size_t *n_vertices,
+               unsigned *triangles, size_t cap_indices, size_t *n_indices);
+
+/* ---- Hough accumulator: lib/hough.h:21-46, lib/hough.cpp:26-135 ---------- */
+typedef struct h3d_hough h3d_hough;
+
+/* Hough::Hough(minP, maxP, dx) (lib/hough.cpp:26-43).  Uses the current space.
+ * The accumulator is NOT materialised in HBM: each direction's (x',y') plane
+ * lives in shared memory while it is voted and only (max votes, first max cell)
+ * per direction is kept; h3d_download_votes() rebuilds the dense array. */
+int h3d_create(const double minP[3], const double maxP[3], double dx, h3d_hough **out);
+/* direction-sharded variant: this instance owns directions
+ * [dir_begin, dir_end) of the current space; flat indices stay global. */
+int h3d_create_sharded(const double minP[3], const double maxP[3], double dx,
+                       size_t dir_begin, size_t dir_end, h3d_hough **out);
+void h3d_destroy(h3d_hough *h);                       /* Hough::~Hough */
+int h3d_info(const h3d_hough *h, size_t *num_x, size_t *num_b, double *dx, double *max_x);
+/* Hough::add (lib/hough.cpp:50-55) / Hough::subtract (lib/hough.cpp:58-63) */
+int h3d_add(h3d_hough *h, const double *xyz, size_t n);
+int h3d_subtract(h3d_hough *h, const double *xyz, size_t n);
+/* Hough::getLine (lib/hough.cpp:103-135): returns votes, anchor a, direction b
+ * and the flat accumulator index x_i*num_x*num_b + y_i*num_b + j of the winner
+ * (first maximum in flat order, like the reference's strict `>` scan). */
+int h3d_get_line(h3d_hough *h, double a[3], double b[3], unsigned *votes, uint64_t *flat_index);
+/* the winner of this instance's shard as a packed key
+ * (votes << 32) | (0xFFFFFFFF - flat_index); max over shards == global winner */
+int h3d_get_line_key(h3d_hough *h, uint64_t *key);
+/* inverse map of lib/hough.cpp:114-132 for a flat index */
+int h3d_line_from_index(const h3d_hough *h, uint64_t flat_index, double a[3], double b[3]);
+/* Hough::VotingSpace: dense num_x*num_x*num_b array in the reference layout
+ * (direction fastest, lib/hough.cpp:88-90).  cap in cells. */
+int h3d_download_votes(h3d_hough *h, unsigned *votes, size_t cap);
+
+/* ---- PointCloud: lib/pointcloud.cpp:18-128 -------------------------------- */
+int h3d_min_max(const double *xyz, size_t n, double mn[3], double mx[3]);    /* :41-59  */
+int h3d_shift_to_origin(double *xyz, size_t n, double shift_inout[3]);       /* :18-26  */
+int h3d_mean_value(const double *xyz, size_t n, double mean[3]);             /* :29-38  */
+/* pointsCloseToLine (:94-105): indices of kept points, input order */
+int h3d_points_close_to_line(const double *xyz, size_t n, const double a[3], const double b[3],
+                             double dx, uint32_t *idx_out, size_t *n_out);
+/* removePoints (:109-128): ordered set difference by exact ==, compacts x in place */
+int h3d_remove_points(double *x_xyz, size_t nx, const double *y_xyz, size_t ny, size_t *n_out);
+/* orthogonal_LSQ (wrap.h:121-150): anchor = f64 mean, direction = top eigenvector
+ * of the f32 centred scatter, *rc = top eigenvalue */
+int h3d_orthogonal_lsq(const double *xyz, size_t n, double a[3], double b[3], double *rc);
+
+/* ---- pre-filter: node.cpp:386-421 (PassThrough x,y,z + VoxelGrid) --------- */
+/* xyz_in: n points, `stride` floats apart, x,y,z first.  win = {xmin,xmax,ymin,
+ * ymax,zmin,zmax} inclusive.  out_xyz: cap*3 floats, one centroid per voxel in
+ * ascending voxel index.  *n_out may exceed cap (then only cap were written). */
+int h3d_prefilter(const float *xyz_in, size_t n, size_t stride, const float win[6], float leaf,
+                  float *out_xyz, size_t cap, size_t *n_out);
+
+/* ---- the whole iterative loop on the device: wrap.h:172-259,339-347 /
+ *      lib/hough3dlines.cpp:200-317 ---------------------------------------- */
+typedef struct {
+  uint32_t votes;      /* getLine return value                                  */
+  uint32_t status;     /* 0 = line accepted; 1 = rc1==0; 2 = < minvotes; 3 = rc2==0 */
+  uint64_t argmax;     /* flat accumulator index of the winner                  */
+  double a_raw[3], b_raw[3];    /* getLine output (centred frame)               */
+  double a1[3], b1[3], rc1;     /* first orthogonal_LSQ                         */
+  double a2[3], b2[3], rc2;     /* second orthogonal_LSQ, a2 already + X.shift  */
+  uint32_t n1, n2;     /* inlier counts of pass 1 / pass 2                      */
+  uint32_t off1, off2; /* offsets of the two inlier lists in the index pool     */
+} h3d_iter;
+
+typedef struct {
+  int rc;              /* 0 ok; 1 = degenerate cloud / dx too large             */
+  uint32_t n_iters;    /* iterations recorded (accepted + the final break)      */
+  uint32_t n_lines;    /* accepted lines                                        */
+  uint32_t n_input;    /* points after the NaN/Inf strip                        */
+  double shift[3];     /* X.shift                                               */
+  double d;            /* bbox diagonal                                         */
+  double dx;           /* effective dx                                          */
+  double max_x;
+  uint64_t num_x, num_b;
+  uint64_t pool_used;
+  uint64_t votes_cast; /* (point,direction) votes evaluated, for votes/s        */
+} h3d_result;
+
+/* mode 0 = ROS wrapper rules (wrap.h), 1 = standalone rules
+ * (lib/hough3dlines.cpp:171-173,211-213: dx==0 -> d/64, minvotes >= 2).
+ * pool receives, per iteration, the ORIGINAL indices of the pass-1 and pass-2
+ * inliers.  Uses and may change the current space (h3d_init_space(granularity)). */
+int h3d_hough3dlines(const double *xyz, size_t n, int granularity, double opt_dx,
+                     int opt_minvotes, int opt_nlines, int mode,
+                     h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                     h3d_result *res);
+
+/* ---- persistent pipeline: pre-filter + loop, buffers kept between frames --- */
+typedef struct h3d_pipeline h3d_pipeline;
+typedef struct {
+  int granularity;
+  float window[6];       /* PassThrough limits, node.cpp:394-407                */
+  float leaf;            /* VoxelGrid leaf, node.cpp:410-412                    */
+  double opt_dx;         /* node.cpp:243: sqrt(3)*leaf                          */
+  int opt_minvotes, opt_nlines;
+  size_t max_raw_points; /* capacity of one raw frame                           */
+  size_t max_iters;      /* capacity of the per-frame iteration records         */
+  int prefilter;         /* 1: raw f32 frame -> K0 -> loop; 0: input is already
+                            the filtered f32 cloud (wrap.h:175-189 widening)    */
+} h3d_pipeline_config;
+
+int h3d_pipeline_create(const h3d_pipeline_config *cfg, h3d_pipeline **out);
+void h3d_pipeline_destroy(h3d_pipeline *p);
+/* one frame, host in / host out (H2D + kernels + D2H).  raw: n points of
+ * `stride` floats (x,y,z first; sensor_msgs/PointCloud2 with point_step =
+ * 4*stride).  Inlier indices in pool refer to the FILTERED cloud. */
+int h3d_pipeline_run(h3d_pipeline *p, const float *raw, size_t n, size_t stride,
+                     h3d_iter *iters, uint32_t *pool, size_t pool_cap, h3d_result *res);
+/* same with the raw frame already resident in device memory */
+int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride,
+                         h3d_iter *iters, uint32_t *pool, size_t pool_cap, h3d_result *res);
+/* filtered cloud of the last frame (f32 xyz), for inspection */
+int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n_out);
+/* per-phase device times of the last frame, microseconds:
+ * [0] pre-filter, [1] first vote (Hough::add), [2] loop, [3] total */
+int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
+
+/* ---- measurement hooks (bench.py): raw kernel timings with CUDA events ----- */
+/* runs the vote kernel `reps` times over all directions of h and returns the
+ * mean device time per launch in microseconds.  ablate: 0 = full kernel,
+ * 1 = projection math only (no shared atomics), 2 = shared atomics only;
+ * bits 8..15 of `ablate` optionally give the directions per work item (1,2,4,8). */
+int h3d_bench_vote(h3d_hough *h, int reps, int ablate, float *us_per_launch);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* H3D_H_ */

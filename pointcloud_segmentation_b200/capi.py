@@ -1,0 +1,153 @@
+"""ctypes bindings of libh3d.so (include/h3d.h) for the test and bench harness.
+
+The product is the C-ABI library plus the C++ drop-in headers; this module only
+lets pytest / bench.py call the same entry points a C++ consumer would.  It
+raises at import of the library if libh3d.so is missing -- there is no fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libh3d.so")
+
+_lib = None
+
+
+class H3dError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"h3d error {code}: {msg}")
+        self.code = code
+
+
+class Iter(C.Structure):
+    _fields_ = [
+        ("votes", C.c_uint32), ("status", C.c_uint32), ("argmax", C.c_uint64),
+        ("a_raw", C.c_double * 3), ("b_raw", C.c_double * 3),
+        ("a1", C.c_double * 3), ("b1", C.c_double * 3), ("rc1", C.c_double),
+        ("a2", C.c_double * 3), ("b2", C.c_double * 3), ("rc2", C.c_double),
+        ("n1", C.c_uint32), ("n2", C.c_uint32), ("off1", C.c_uint32), ("off2", C.c_uint32),
+    ]
+
+
+class Result(C.Structure):
+    _fields_ = [
+        ("rc", C.c_int), ("n_iters", C.c_uint32), ("n_lines", C.c_uint32), ("n_input", C.c_uint32),
+        ("shift", C.c_double * 3), ("d", C.c_double), ("dx", C.c_double), ("max_x", C.c_double),
+        ("num_x", C.c_uint64), ("num_b", C.c_uint64), ("pool_used", C.c_uint64),
+        ("votes_cast", C.c_uint64),
+    ]
+
+
+class PipelineConfig(C.Structure):
+    _fields_ = [
+        ("granularity", C.c_int), ("window", C.c_float * 6), ("leaf", C.c_float),
+        ("opt_dx", C.c_double), ("opt_minvotes", C.c_int), ("opt_nlines", C.c_int),
+        ("max_raw_points", C.c_size_t), ("max_iters", C.c_size_t), ("prefilter", C.c_int),
+    ]
+
+
+def lib():
+    """Load libh3d.so (built in-tree by `make -C pointcloud_segmentation_b200`)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `make -C {HERE}` "
+                "(or __graft_entry__.build()); there is no CPU fallback")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.h3d_last_error.restype = C.c_char_p
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise H3dError(rc, lib().h3d_last_error().decode(errors="replace"))
+
+
+def _d3(v):
+    return (C.c_double * 3)(*[float(x) for x in v])
+
+
+def _pts(xyz):
+    a = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+    return a, a.ctypes.data_as(C.POINTER(C.c_double)), C.c_size_t(a.shape[0])
+
+
+def device_info():
+    sm, cc, smem = C.c_int(), C.c_int(), C.c_size_t()
+    check(lib().h3d_device_info(C.byref(sm), C.byref(cc), C.byref(smem)))
+    return {"sm_count": sm.value, "cc": cc.value, "smem_optin": smem.value}
+
+
+def init_space(g):
+    check(lib().h3d_init_space(C.c_uint(g)))
+
+
+def sphere(g):
+    nv, nt = C.c_size_t(), C.c_size_t()
+    check(lib().h3d_sphere(C.c_int(g), None, C.c_size_t(0), C.byref(nv), None, C.c_size_t(0), C.byref(nt)))
+    v = np.empty((nv.value, 3), dtype=np.float64)
+    t = np.empty(nt.value, dtype=np.uint32)
+    check(lib().h3d_sphere(C.c_int(g), v.ctypes.data_as(C.POINTER(C.c_double)), nv, C.byref(nv),
+                           t.ctypes.data_as(C.POINTER(C.c_uint)), nt, C.byref(nt)))
+    return v, t
+
+
+class Hough:
+    """Mirror of the reference's `Hough` class (lib/hough.h:21-46) over the C-ABI."""
+
+    def __init__(self, minP, maxP, dx, shard=None):
+        self._h = C.c_void_p()
+        if shard is None:
+            check(lib().h3d_create(_d3(minP), _d3(maxP), C.c_double(dx), C.byref(self._h)))
+        else:
+            check(lib().h3d_create_sharded(_d3(minP), _d3(maxP), C.c_double(dx), C.c_size_t(shard[0]),
+                                           C.c_size_t(shard[1]), C.byref(self._h)))
+        nx, nb, dxx, mx = C.c_size_t(), C.c_size_t(), C.c_double(), C.c_double()
+        check(lib().h3d_info(self._h, C.byref(nx), C.byref(nb), C.byref(dxx), C.byref(mx)))
+        self.num_x, self.num_b, self.dx, self.max_x = nx.value, nb.value, dxx.value, mx.value
+
+    def add(self, xyz):
+        a, p, n = _pts(xyz)
+        check(lib().h3d_add(self._h, p, n))
+
+    def subtract(self, xyz):
+        a, p, n = _pts(xyz)
+        check(lib().h3d_subtract(self._h, p, n))
+
+    def get_line(self):
+        a, b = (C.c_double * 3)(), (C.c_double * 3)()
+        votes, flat = C.c_uint(), C.c_uint64()
+        check(lib().h3d_get_line(self._h, a, b, C.byref(votes), C.byref(flat)))
+        return votes.value, np.array(a[:]), np.array(b[:]), flat.value
+
+    def get_line_key(self):
+        k = C.c_uint64()
+        check(lib().h3d_get_line_key(self._h, C.byref(k)))
+        return k.value
+
+    def votes(self):
+        cells = self.num_x * self.num_x * self.num_b
+        out = np.empty(cells, dtype=np.uint32)
+        check(lib().h3d_download_votes(self._h, out.ctypes.data_as(C.POINTER(C.c_uint)), C.c_size_t(cells)))
+        return out
+
+    def bench_vote(self, reps=10, ablate=0, D=0):
+        us = C.c_float()
+        check(lib().h3d_bench_vote(self._h, C.c_int(reps), C.c_int(ablate | (D << 8)), C.byref(us)))
+        return us.value
+
+    def close(self):
+        if self._h:
+            lib().h3d_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,543 @@
+// h3d_capi.cu -- the extern "C" boundary of libh3d.so (include/h3d.h): contexts,
+// device memory, kernel launches.  No CPU fallback: every compute entry point
+// needs a CUDA device and fails with H3D_ERR_CUDA otherwise.
+#include "../../include/h3d.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+
+#include "h3d_kernels.cuh"
+
+namespace h3d {
+
+static thread_local std::string g_error;
+void set_error(const std::string &msg) { g_error = msg; }
+
+#define H3D_CUDA(call)                                                                       \
+  do {                                                                                       \
+    cudaError_t e_ = (call);                                                                 \
+    if (e_ != cudaSuccess) {                                                                 \
+      char buf_[512];                                                                        \
+      snprintf(buf_, sizeof buf_, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      set_error(buf_);                                                                       \
+      return e_ == cudaErrorMemoryAllocation ? H3D_ERR_NOMEM : H3D_ERR_CUDA;                 \
+    }                                                                                        \
+  } while (0)
+
+#define H3D_TRY(call)             \
+  do {                            \
+    int rc_ = (call);             \
+    if (rc_ != H3D_OK) return rc_; \
+  } while (0)
+
+static int fail(int code, const char *msg) {
+  set_error(msg);
+  return code;
+}
+
+// ---- device facts -----------------------------------------------------------
+struct DeviceFacts {
+  int ok = 0, sm_count = 0, cc = 0;
+  size_t smem_optin = 0;
+};
+static int device_facts(DeviceFacts *out) {
+  static std::mutex mu;
+  static std::map<int, DeviceFacts> cache;
+  int dev = 0;
+  H3D_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(dev);
+  if (it == cache.end()) {
+    cudaDeviceProp p;
+    H3D_CUDA(cudaGetDeviceProperties(&p, dev));
+    DeviceFacts f;
+    f.ok = 1; f.sm_count = p.multiProcessorCount; f.cc = p.major * 10 + p.minor;
+    f.smem_optin = p.sharedMemPerBlockOptin;
+    it = cache.emplace(dev, f).first;
+  }
+  *out = it->second;
+  return H3D_OK;
+}
+
+// ---- direction spaces (lib/hough.cpp:15-20: one global sphere) ---------------
+static std::mutex g_space_mu;
+static std::map<std::pair<int, unsigned>, std::shared_ptr<const Space>> g_spaces;   // (device, g)
+static std::shared_ptr<const Space> g_current;
+
+int get_space(unsigned g, std::shared_ptr<const Space> *out) {
+  if (g > 8) return fail(H3D_ERR_ARG, "granularity must be 0..8");
+  int dev = 0;
+  H3D_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(g_space_mu);
+  auto key = std::make_pair(dev, g);
+  auto it = g_spaces.find(key);
+  if (it != g_spaces.end()) { *out = it->second; return H3D_OK; }
+  auto sp = std::make_shared<Space>();
+  sp->granularity = g;
+  build_sphere((int)g, sp->dirs, sp->triangles);
+  sp->num_b = sp->dirs.size() / 3;
+  std::vector<DirCoef> coef(sp->num_b);
+  for (size_t j = 0; j < sp->num_b; ++j) {
+    const double bx = sp->dirs[3 * j], by = sp->dirs[3 * j + 1], bz = sp->dirs[3 * j + 2];
+    const double beta = 1 / (1 + bz);                 // lib/hough.cpp:73
+    coef[j].c0 = 1 - (beta * (bx * bx));              // :76
+    coef[j].c1 = beta * (bx * by);                    // :77, :81
+    coef[j].c2 = 1 - (beta * (by * by));              // :82
+    coef[j].bx = bx; coef[j].by = by;
+  }
+  H3D_CUDA(cudaMalloc(&sp->coef_dev, sizeof(DirCoef) * sp->num_b));
+  H3D_CUDA(cudaMalloc(&sp->dirs_dev, sizeof(double) * 3 * sp->num_b));
+  H3D_CUDA(cudaMemcpy(sp->coef_dev, coef.data(), sizeof(DirCoef) * sp->num_b, cudaMemcpyHostToDevice));
+  H3D_CUDA(cudaMemcpy(sp->dirs_dev, sp->dirs.data(), sizeof(double) * 3 * sp->num_b, cudaMemcpyHostToDevice));
+  g_spaces[key] = sp;
+  *out = sp;
+  return H3D_OK;
+}
+
+std::shared_ptr<const Space> current_space() {
+  std::lock_guard<std::mutex> lock(g_space_mu);
+  return g_current;
+}
+
+}  // namespace h3d
+
+using namespace h3d;
+
+// ---- the handle ----------------------------------------------------------------
+struct h3d_hough {
+  std::shared_ptr<const Space> space;
+  HoughDev d{};
+  DeviceFacts dev;
+  cudaStream_t stream = nullptr;
+  size_t cap = 0;                 // point capacity
+  double *px = nullptr, *py = nullptr, *pz = nullptr;
+  int *w = nullptr;
+  double *stage = nullptr;        // AoS staging for uploads
+  size_t stage_cap = 0;           // in points
+  bool all_dirty = true;          // no usable per-direction record
+  bool has_negative = false;      // a subtract() hit no added point: planes may wrap
+  unsigned long long *keys = nullptr;   // [0] best exact, [1] best overall
+  int *list = nullptr, *count = nullptr;
+  int *idx = nullptr;             // scratch: indices of removed points
+  size_t idx_cap = 0;
+  int vote_d = 1;                 // directions per work item of the full vote
+  uint64_t votes_cast = 0;
+};
+
+extern "C" const char *h3d_last_error(void) { return g_error.c_str(); }
+
+extern "C" int h3d_device_info(int *sm_count, int *cc, size_t *smem_optin) {
+  DeviceFacts f;
+  H3D_TRY(device_facts(&f));
+  if (sm_count) *sm_count = f.sm_count;
+  if (cc) *cc = f.cc;
+  if (smem_optin) *smem_optin = f.smem_optin;
+  return H3D_OK;
+}
+
+extern "C" int h3d_init_space(unsigned granularity) {
+  std::shared_ptr<const Space> sp;
+  H3D_TRY(get_space(granularity, &sp));
+  std::lock_guard<std::mutex> lock(g_space_mu);
+  g_current = sp;
+  return H3D_OK;
+}
+
+extern "C" int h3d_space_info(unsigned *granularity, size_t *num_b) {
+  auto sp = current_space();
+  if (!sp) return fail(H3D_ERR_ARG, "h3d_init_space() has not been called");
+  if (granularity) *granularity = sp->granularity;
+  if (num_b) *num_b = sp->num_b;
+  return H3D_OK;
+}
+
+extern "C" int h3d_sphere(int g, double *vertices, size_t cap_v, size_t *n_v, unsigned *triangles,
+                          size_t cap_t, size_t *n_t) {
+  if (g < 0 || g > 8) return fail(H3D_ERR_ARG, "granularity must be 0..8");
+  std::vector<double> v;
+  std::vector<unsigned> t;
+  build_sphere(g, v, t);   // pure host geometry, no device needed
+  if (n_v) *n_v = v.size() / 3;
+  if (n_t) *n_t = t.size();
+  if (vertices) {
+    if (cap_v < v.size() / 3) return fail(H3D_ERR_ARG, "vertex buffer too small");
+    memcpy(vertices, v.data(), v.size() * sizeof(double));
+  }
+  if (triangles) {
+    if (cap_t < t.size()) return fail(H3D_ERR_ARG, "triangle buffer too small");
+    memcpy(triangles, t.data(), t.size() * sizeof(unsigned));
+  }
+  return H3D_OK;
+}
+
+// ---- Hough: lib/hough.cpp:26-135 ---------------------------------------------------
+static double round_to_nearest(double v) {   // lib/hough.cpp:22-24
+  return (v > 0.0) ? floor(v + 0.5) : ceil(v - 0.5);
+}
+
+static int ensure_points(h3d_hough *h, size_t need) {
+  if (need <= h->cap) return H3D_OK;
+  size_t cap = h->cap ? h->cap : 4096;
+  while (cap < need) cap *= 2;
+  double *nx, *ny, *nz; int *nw;
+  H3D_CUDA(cudaMalloc(&nx, cap * sizeof(double)));
+  H3D_CUDA(cudaMalloc(&ny, cap * sizeof(double)));
+  H3D_CUDA(cudaMalloc(&nz, cap * sizeof(double)));
+  H3D_CUDA(cudaMalloc(&nw, cap * sizeof(int)));
+  if (h->d.n) {
+    H3D_CUDA(cudaMemcpyAsync(nx, h->px, h->d.n * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    H3D_CUDA(cudaMemcpyAsync(ny, h->py, h->d.n * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    H3D_CUDA(cudaMemcpyAsync(nz, h->pz, h->d.n * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    H3D_CUDA(cudaMemcpyAsync(nw, h->w, h->d.n * sizeof(int), cudaMemcpyDeviceToDevice, h->stream));
+    H3D_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  cudaFree(h->px); cudaFree(h->py); cudaFree(h->pz); cudaFree(h->w);
+  h->px = nx; h->py = ny; h->pz = nz; h->w = nw; h->cap = cap;
+  h->d.px = nx; h->d.py = ny; h->d.pz = nz; h->d.w = nw;
+  return H3D_OK;
+}
+
+static int ensure_stage(h3d_hough *h, size_t n) {
+  if (n <= h->stage_cap) return H3D_OK;
+  cudaFree(h->stage); h->stage = nullptr;
+  cudaFree(h->idx); h->idx = nullptr;
+  size_t cap = h->stage_cap ? h->stage_cap : 4096;
+  while (cap < n) cap *= 2;
+  H3D_CUDA(cudaMalloc(&h->stage, cap * 3 * sizeof(double)));
+  H3D_CUDA(cudaMalloc(&h->idx, cap * sizeof(int)));
+  h->stage_cap = cap; h->idx_cap = cap;
+  return H3D_OK;
+}
+
+// AoS staging -> SoA append, weight +1
+__global__ void append_points_kernel(const double *__restrict__ aos, int n, double *px, double *py, double *pz,
+                                     int *w, int at) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    px[at + i] = aos[3 * i]; py[at + i] = aos[3 * i + 1]; pz[at + i] = aos[3 * i + 2];
+    w[at + i] = 1;
+  }
+}
+
+// Hough::subtract bookkeeping: y_k is matched to the (r+1)-th live point with the
+// same coordinates, r = number of earlier identical y.  idx[k] = matched point or
+// -1.  Brute force: |Y| threads x |X| compares.
+__global__ void match_points_kernel(const double *__restrict__ y, int ny, const double *__restrict__ px,
+                                    const double *__restrict__ py, const double *__restrict__ pz,
+                                    const int *__restrict__ w, int n, int *idx, int *unmatched) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= ny) return;
+  const double x0 = y[3 * k], y0 = y[3 * k + 1], z0 = y[3 * k + 2];
+  int rank = 0;
+  for (int q = 0; q < k; ++q) rank += (y[3 * q] == x0 && y[3 * q + 1] == y0 && y[3 * q + 2] == z0);
+  int found = -1;
+  for (int i = 0; i < n; ++i) {
+    if (w[i] > 0 && px[i] == x0 && py[i] == y0 && pz[i] == z0) {
+      if (rank-- == 0) { found = i; break; }
+    }
+  }
+  idx[k] = found;
+  if (found < 0) atomicAdd(unmatched, 1);
+}
+
+__global__ void kill_points_kernel(const int *__restrict__ idx, int n_idx, int *w) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n_idx && idx[k] >= 0) w[idx[k]] = 0;
+}
+
+// unmatched subtract: append as weight -1 points (unsigned cells wrap like the reference's)
+__global__ void append_negative_kernel(const double *__restrict__ y, const int *__restrict__ idx, int ny,
+                                       double *px, double *py, double *pz, int *w, int at, int *cursor) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= ny || idx[k] >= 0) return;
+  const int slot = at + atomicAdd(cursor, 1);
+  px[slot] = y[3 * k]; py[slot] = y[3 * k + 1]; pz[slot] = y[3 * k + 2];
+  w[slot] = -1;
+}
+
+template <int D, int ABLATE>
+static int launch_vote_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense,
+                         int grid) {
+  const size_t smem = (size_t)D * h->d.plane_stride * sizeof(unsigned);
+  static thread_local size_t configured = 0;
+  if (smem > configured) {
+    H3D_CUDA(cudaFuncSetAttribute(vote_kernel<D, ABLATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)h->dev.smem_optin));
+    configured = h->dev.smem_optin;
+  }
+  vote_kernel<D, ABLATE><<<grid, kVoteThreads, smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
+  H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+
+// D planes per CTA, two CTAs per SM when they fit
+static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const int *count_ptr, int count_imm,
+                       unsigned *dense) {
+  const size_t plane_bytes = (size_t)h->d.plane_stride * sizeof(unsigned);
+  const size_t budget = h->dev.smem_optin - 1024;
+  if (plane_bytes > budget) return fail(H3D_ERR_RANGE, "one (x',y') plane does not fit in shared memory");
+  while (D > 1 && (size_t)D * plane_bytes > budget / 2) D >>= 1;
+  const int per_sm = ((size_t)D * plane_bytes <= budget / 2) ? 2 : 1;
+  const int grid = h->dev.sm_count * per_sm;
+#define H3D_VOTE_CASE(DD)                                                                               \
+  case DD:                                                                                              \
+    if (ablate == 0) return launch_vote_t<DD, 0>(h, list, count_ptr, count_imm, dense, grid);          \
+    if (ablate == 1) return launch_vote_t<DD, 1>(h, list, count_ptr, count_imm, dense, grid);          \
+    return launch_vote_t<DD, 2>(h, list, count_ptr, count_imm, dense, grid);
+  switch (D) {
+    H3D_VOTE_CASE(1)
+    H3D_VOTE_CASE(2)
+    H3D_VOTE_CASE(4)
+    H3D_VOTE_CASE(8)
+  }
+#undef H3D_VOTE_CASE
+  return fail(H3D_ERR_ARG, "bad D");
+}
+
+static int create_impl(const double minP[3], const double maxP[3], double var_dx, size_t dir_begin,
+                       size_t dir_end, bool whole, h3d_hough **out) {
+  if (!minP || !maxP || !out) return fail(H3D_ERR_ARG, "null argument");
+  auto sp = current_space();
+  if (!sp) return fail(H3D_ERR_ARG, "h3d_init_space() has not been called");
+  if (whole) { dir_begin = 0; dir_end = sp->num_b; }
+  if (dir_begin > dir_end || dir_end > sp->num_b) return fail(H3D_ERR_ARG, "bad direction range");
+  h3d_hough *h = new (std::nothrow) h3d_hough();
+  if (!h) return fail(H3D_ERR_NOMEM, "host allocation failed");
+  std::unique_ptr<h3d_hough, void (*)(h3d_hough *)> guard(h, h3d_destroy);
+  h->space = sp;
+  H3D_TRY(device_facts(&h->dev));
+  // lib/hough.cpp:32-38
+  const double nmax = sqrt((maxP[0] * maxP[0]) + (maxP[1] * maxP[1]) + (maxP[2] * maxP[2]));
+  const double nmin = sqrt((minP[0] * minP[0]) + (minP[1] * minP[1]) + (minP[2] * minP[2]));
+  const double max_x = nmax < nmin ? nmin : nmax;
+  const double range_x = 2 * max_x;
+  double dx = var_dx;
+  if (dx == 0.0) dx = range_x / 64.0;
+  const double nxd = round_to_nearest(range_x / dx);
+  if (!(nxd >= 0.0) || nxd > 65535.0) return fail(H3D_ERR_RANGE, "num_x out of range");
+  const size_t num_x = (size_t)nxd;
+  const unsigned long long cells = (unsigned long long)num_x * num_x * sp->num_b;
+  if (cells >= (1ull << 32))
+    return fail(H3D_ERR_RANGE, "accumulator has >= 2^32 cells (the reference's unsigned argmax index wraps)");
+  HoughDev &d = h->d;
+  d.num_x = (int)num_x;
+  d.plane_cells = (unsigned)(num_x * num_x);
+  d.plane_stride = (d.plane_cells + 3u) & ~3u;
+  if (d.plane_stride == 0) d.plane_stride = 4;
+  d.num_b = (int)sp->num_b;
+  d.dir_begin = (int)dir_begin;
+  d.dir_count = (int)(dir_end - dir_begin);
+  d.max_x = max_x; d.dx = dx;
+  d.fast_ok = (num_x >= 1 && num_x <= 4000 && dx > 0.0 && std::isfinite(max_x)) ? 1 : 0;
+  if (d.fast_ok) {
+    const long double inv_s = ldexpl(1.0L / (long double)dx, 20);
+    d.inv_s = (double)inv_s;
+    const long double bias = roundl((long double)max_x * inv_s + 524288.0L);
+    d.kmagic = (double)(6755399441055744.0L + bias);   // 1.5 * 2^52 + bias
+    if (!(bias >= 0.0L && bias < 4294967296.0L)) d.fast_ok = 0;
+  }
+  d.coef = sp->coef_dev;
+  H3D_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  const size_t nd = d.dir_count ? d.dir_count : 1;
+  H3D_CUDA(cudaMalloc(&d.dvotes, nd * sizeof(unsigned)));
+  H3D_CUDA(cudaMalloc(&d.dcell, nd * sizeof(unsigned)));
+  H3D_CUDA(cudaMalloc(&d.dstale, nd));
+  H3D_CUDA(cudaMemsetAsync(d.dvotes, 0, nd * sizeof(unsigned), h->stream));
+  H3D_CUDA(cudaMemsetAsync(d.dcell, 0, nd * sizeof(unsigned), h->stream));
+  H3D_CUDA(cudaMemsetAsync(d.dstale, 0, nd, h->stream));
+  H3D_CUDA(cudaMalloc(&h->keys, 2 * sizeof(unsigned long long)));
+  H3D_CUDA(cudaMalloc(&h->list, nd * sizeof(int)));
+  H3D_CUDA(cudaMalloc(&h->count, 4 * sizeof(int)));
+  H3D_TRY(ensure_points(h, 4096));
+  h->all_dirty = false;   // an empty accumulator: every record is exactly zero
+  *out = guard.release();
+  return H3D_OK;
+}
+
+extern "C" int h3d_create(const double minP[3], const double maxP[3], double dx, h3d_hough **out) {
+  return create_impl(minP, maxP, dx, 0, 0, true, out);
+}
+extern "C" int h3d_create_sharded(const double minP[3], const double maxP[3], double dx, size_t dir_begin,
+                                  size_t dir_end, h3d_hough **out) {
+  return create_impl(minP, maxP, dx, dir_begin, dir_end, false, out);
+}
+
+extern "C" void h3d_destroy(h3d_hough *h) {
+  if (!h) return;
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  cudaFree(h->px); cudaFree(h->py); cudaFree(h->pz); cudaFree(h->w);
+  cudaFree(h->stage); cudaFree(h->idx);
+  cudaFree(h->d.dvotes); cudaFree(h->d.dcell); cudaFree(h->d.dstale);
+  cudaFree(h->keys); cudaFree(h->list); cudaFree(h->count);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+extern "C" int h3d_info(const h3d_hough *h, size_t *num_x, size_t *num_b, double *dx, double *max_x) {
+  if (!h) return fail(H3D_ERR_ARG, "null handle");
+  if (num_x) *num_x = (size_t)h->d.num_x;
+  if (num_b) *num_b = (size_t)h->d.num_b;
+  if (dx) *dx = h->d.dx;
+  if (max_x) *max_x = h->d.max_x;
+  return H3D_OK;
+}
+
+extern "C" int h3d_add(h3d_hough *h, const double *xyz, size_t n) {
+  if (!h || (!xyz && n)) return fail(H3D_ERR_ARG, "null argument");
+  if (n == 0) return H3D_OK;
+  if (h->d.n + n > 0x7FFFFFF0u) return fail(H3D_ERR_RANGE, "too many points");
+  H3D_TRY(ensure_points(h, h->d.n + n));
+  H3D_TRY(ensure_stage(h, n));
+  H3D_CUDA(cudaMemcpyAsync(h->stage, xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  append_points_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->stage, (int)n, h->px, h->py,
+                                                                          h->pz, h->w, h->d.n);
+  H3D_CUDA(cudaGetLastError());
+  H3D_CUDA(cudaStreamSynchronize(h->stream));   // xyz may be pageable and reused by the caller
+  h->d.n += (int)n;
+  h->all_dirty = true;   // new votes can raise any plane: rebuild on the next getLine
+  return H3D_OK;
+}
+
+extern "C" int h3d_subtract(h3d_hough *h, const double *xyz, size_t n) {
+  if (!h || (!xyz && n)) return fail(H3D_ERR_ARG, "null argument");
+  if (n == 0) return H3D_OK;
+  H3D_TRY(ensure_stage(h, n));
+  H3D_TRY(ensure_points(h, h->d.n + n));
+  H3D_CUDA(cudaMemcpyAsync(h->stage, xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  H3D_CUDA(cudaMemsetAsync(h->count, 0, 4 * sizeof(int), h->stream));
+  const unsigned blocks = (unsigned)((n + 127) / 128);
+  match_points_kernel<<<blocks, 128, 0, h->stream>>>(h->stage, (int)n, h->px, h->py, h->pz, h->w, h->d.n,
+                                                     h->idx, h->count + 1);
+  // records stay usable only while they describe the votes still present
+  if (!h->all_dirty) {
+    unvote_kernel<<<h->dev.sm_count * 4, 256, 0, h->stream>>>(h->d, h->idx, (int)n);
+  }
+  kill_points_kernel<<<blocks, 128, 0, h->stream>>>(h->idx, (int)n, h->w);
+  append_negative_kernel<<<blocks, 128, 0, h->stream>>>(h->stage, h->idx, (int)n, h->px, h->py, h->pz, h->w,
+                                                        h->d.n, h->count + 2);
+  H3D_CUDA(cudaGetLastError());
+  int counts[4];
+  H3D_CUDA(cudaMemcpyAsync(counts, h->count, sizeof counts, cudaMemcpyDeviceToHost, h->stream));
+  H3D_CUDA(cudaStreamSynchronize(h->stream));
+  if (counts[1] > 0) {   // subtracting points that were never added: exact, but no bounds any more
+    h->d.n += counts[2];
+    h->has_negative = true;
+    h->all_dirty = true;
+  }
+  return H3D_OK;
+}
+
+// bring every per-direction record needed for the argmax up to date, then reduce
+static int refresh_and_reduce(h3d_hough *h, unsigned long long *key_out) {
+  if (h->d.dir_count == 0) { *key_out = 0; return H3D_OK; }
+  const int blocks = (h->d.dir_count + 255) / 256;
+  H3D_CUDA(cudaMemsetAsync(h->keys, 0, 2 * sizeof(unsigned long long), h->stream));
+  if (h->all_dirty) {
+    H3D_TRY(launch_vote(h, 4, 0, nullptr, nullptr, h->d.dir_count, nullptr));
+    h->votes_cast += (uint64_t)h->d.n * h->d.dir_count;
+    h->all_dirty = h->has_negative;
+  } else {
+    H3D_CUDA(cudaMemsetAsync(h->count, 0, sizeof(int), h->stream));
+    argmax_kernel<<<blocks, 256, 0, h->stream>>>(h->d, 1, h->keys);
+    worklist_kernel<<<blocks, 256, 0, h->stream>>>(h->d, h->keys, h->list, h->count);
+    H3D_CUDA(cudaGetLastError());
+    H3D_TRY(launch_vote(h, 1, 0, h->list, h->count, 0, nullptr));
+  }
+  argmax_kernel<<<blocks, 256, 0, h->stream>>>(h->d, 0, h->keys + 1);
+  H3D_CUDA(cudaGetLastError());
+  H3D_CUDA(cudaMemcpyAsync(key_out, h->keys + 1, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+  H3D_CUDA(cudaStreamSynchronize(h->stream));
+  return H3D_OK;
+}
+
+extern "C" int h3d_line_from_index(const h3d_hough *h, uint64_t flat_index, double a[3], double b[3]) {
+  if (!h || !a || !b) return fail(H3D_ERR_ARG, "null argument");
+  // lib/hough.cpp:114-132, same integer/double conversions
+  const size_t num_x = (size_t)h->d.num_x, num_b = (size_t)h->d.num_b;
+  const double dx = h->d.dx, max_x = h->d.max_x;
+  unsigned int index = (unsigned int)flat_index;
+  if (num_x == 0 || num_b == 0) return fail(H3D_ERR_ARG, "empty accumulator");
+  double x = (int)(index / (num_x * num_b));
+  index -= (int)x * num_x * num_b;
+  x = x * dx - max_x;
+  double y = (int)index / num_b;
+  index -= (int)y * num_b;
+  y = y * dx - max_x;
+  const double *dir = &h->space->dirs[3 * (size_t)index];
+  const double bx = dir[0], by = dir[1], bz = dir[2];
+  b[0] = bx; b[1] = by; b[2] = bz;
+  a[0] = x * (1 - ((bx * bx) / (1 + bz))) - y * ((bx * by) / (1 + bz));
+  a[1] = x * (-((bx * by) / (1 + bz))) + y * (1 - ((by * by) / (1 + bz)));
+  a[2] = -x * bx - y * by;
+  return H3D_OK;
+}
+
+extern "C" int h3d_get_line_key(h3d_hough *h, uint64_t *key) {
+  if (!h || !key) return fail(H3D_ERR_ARG, "null argument");
+  unsigned long long k = 0;
+  H3D_TRY(refresh_and_reduce(h, &k));
+  *key = k;
+  return H3D_OK;
+}
+
+extern "C" int h3d_get_line(h3d_hough *h, double a[3], double b[3], unsigned *votes, uint64_t *flat_index) {
+  if (!h || !a || !b) return fail(H3D_ERR_ARG, "null argument");
+  unsigned long long k = 0;
+  H3D_TRY(refresh_and_reduce(h, &k));
+  const unsigned v = (unsigned)(k >> 32);
+  // an all-zero accumulator (or an empty shard) reports index 0 like the reference
+  const uint64_t flat = (h->d.dir_count && (v || h->d.dir_begin == 0)) ? 0xFFFFFFFFu - (unsigned)k : 0;
+  if (votes) *votes = v;
+  if (flat_index) *flat_index = v ? flat : 0;
+  return h3d_line_from_index(h, v ? flat : 0, a, b);
+}
+
+extern "C" int h3d_download_votes(h3d_hough *h, unsigned *votes, size_t cap) {
+  if (!h || !votes) return fail(H3D_ERR_ARG, "null argument");
+  if (h->d.dir_begin != 0 || h->d.dir_count != h->d.num_b)
+    return fail(H3D_ERR_ARG, "dense download needs an unsharded instance");
+  const size_t cells = (size_t)h->d.plane_cells * h->d.num_b;
+  if (cap < cells) return fail(H3D_ERR_ARG, "vote buffer too small");
+  if (cells == 0) return H3D_OK;
+  unsigned *dense = nullptr;
+  H3D_CUDA(cudaMalloc(&dense, cells * sizeof(unsigned)));
+  int rc = H3D_OK;
+  do {
+    if (cudaMemsetAsync(dense, 0, cells * sizeof(unsigned), h->stream) != cudaSuccess) { rc = H3D_ERR_CUDA; break; }
+    rc = launch_vote(h, 4, 0, nullptr, nullptr, h->d.dir_count, dense);
+    if (rc) break;
+    h->all_dirty = h->has_negative;   // the same pass rebuilt every record
+    if (cudaMemcpyAsync(votes, dense, cells * sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+        cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = H3D_ERR_CUDA; set_error("dense download failed"); }
+  } while (0);
+  cudaFree(dense);
+  return rc;
+}
+
+extern "C" int h3d_bench_vote(h3d_hough *h, int reps, int ablate, float *us_per_launch) {
+  int D = (ablate >> 8) & 0xFF;   // optional: directions per work item in bits 8..15
+  ablate &= 0xFF;
+  if (D == 0) D = 4;
+  if (!h || !us_per_launch || reps < 1 || ablate < 0 || ablate > 2 || (D != 1 && D != 2 && D != 4 && D != 8))
+    return fail(H3D_ERR_ARG, "bad argument");
+  cudaEvent_t e0, e1;
+  H3D_CUDA(cudaEventCreate(&e0));
+  H3D_CUDA(cudaEventCreate(&e1));
+  int rc = launch_vote(h, D, ablate, nullptr, nullptr, h->d.dir_count, nullptr);   // warm-up
+  if (rc == H3D_OK) {
+    cudaEventRecord(e0, h->stream);
+    for (int r = 0; r < reps && rc == H3D_OK; ++r)
+      rc = launch_vote(h, D, ablate, nullptr, nullptr, h->d.dir_count, nullptr);
+    cudaEventRecord(e1, h->stream);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { rc = H3D_ERR_CUDA; set_error("vote bench failed"); }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    *us_per_launch = ms * 1000.0f / reps;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (ablate != 0) h->all_dirty = true;   // ablated launches leave meaningless records
+  return rc;
+}
