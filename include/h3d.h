@@ -174,7 +174,7 @@ int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
 /* runs the vote kernel `reps` times over all directions of h and returns the
  * mean device time per launch in microseconds.  ablate: 0 = full kernel,
  * 1 = projection math only (no shared atomics), 2 = shared atomics only;
- * bits 8..15 of `ablate` optionally give the directions per work item (1,2,4,8). */
+ * bits 8..15 of `ablate` optionally give the directions per work item (1,2,4; 0 = automatic: register-resident points when they fit). */
 int h3d_bench_vote(h3d_hough *h, int reps, int ablate, float *us_per_launch);
 
 #ifdef __cplusplus

@@ -264,21 +264,68 @@ static int launch_vote_t(h3d_hough *h, const int *list, const int *count_ptr, in
   const size_t smem = (size_t)D * h->d.plane_stride * sizeof(unsigned);
   static thread_local size_t configured = 0;
   if (smem > configured) {
+    cudaFuncAttributes fa;
+    H3D_CUDA(cudaFuncGetAttributes(&fa, vote_kernel<D, ABLATE>));
+    const size_t dyn_max = h->dev.smem_optin - fa.sharedSizeBytes;   // opt-in limit covers static + dynamic
     H3D_CUDA(cudaFuncSetAttribute(vote_kernel<D, ABLATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)h->dev.smem_optin));
-    configured = h->dev.smem_optin;
+                                  (int)dyn_max));
+    configured = dyn_max;
   }
   vote_kernel<D, ABLATE><<<grid, kVoteThreads, smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;
 }
 
-// D planes per CTA, two CTAs per SM when they fit
+template <int P, int ABLATE>
+static int launch_resident_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm) {
+  const size_t smem = (size_t)2 * h->d.plane_stride * sizeof(unsigned);
+  static thread_local size_t configured = 0;
+  if (smem > configured) {
+    cudaFuncAttributes fa;
+    H3D_CUDA(cudaFuncGetAttributes(&fa, vote_resident_kernel<P, ABLATE>));
+    const size_t dyn_max = h->dev.smem_optin - fa.sharedSizeBytes;
+    H3D_CUDA(cudaFuncSetAttribute(vote_resident_kernel<P, ABLATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)dyn_max));
+    configured = dyn_max;
+  }
+  vote_resident_kernel<P, ABLATE><<<h->dev.sm_count, kResThreads, smem, h->stream>>>(h->d, list, count_ptr,
+                                                                                    count_imm);
+  H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+
+constexpr int kResidentMaxP = 12;
+static bool resident_ok(const h3d_hough *h) {
+  return !h->has_negative && h->d.n <= kResThreads * kResidentMaxP &&
+         (size_t)2 * h->d.plane_stride * sizeof(unsigned) <= h->dev.smem_optin - 2048;
+}
+
+static int launch_resident(h3d_hough *h, int ablate, const int *list, const int *count_ptr, int count_imm) {
+  const int need = (h->d.n + kResThreads - 1) / kResThreads;
+#define H3D_RES_CASE(PP)                                                                     \
+  if (need <= PP) {                                                                          \
+    if (ablate == 0) return launch_resident_t<PP, 0>(h, list, count_ptr, count_imm);         \
+    if (ablate == 1) return launch_resident_t<PP, 1>(h, list, count_ptr, count_imm);         \
+    return launch_resident_t<PP, 2>(h, list, count_ptr, count_imm);                          \
+  }
+  H3D_RES_CASE(4)
+  H3D_RES_CASE(8)
+  H3D_RES_CASE(12)
+#undef H3D_RES_CASE
+  return fail(H3D_ERR_ARG, "too many points for the resident vote kernel");
+}
+
+// D planes per CTA, two CTAs per SM when they fit.  D == 0: pick the kernel form
+// (register-resident points when they fit, else streaming with D = 2).
 static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const int *count_ptr, int count_imm,
                        unsigned *dense) {
   const size_t plane_bytes = (size_t)h->d.plane_stride * sizeof(unsigned);
-  const size_t budget = h->dev.smem_optin - 1024;
+  const size_t budget = h->dev.smem_optin - 2048;   // static warp_best + per-CTA reserve
   if (plane_bytes > budget) return fail(H3D_ERR_RANGE, "one (x',y') plane does not fit in shared memory");
+  if (D == 0) {
+    if (!dense && resident_ok(h)) return launch_resident(h, ablate, list, count_ptr, count_imm);
+    D = 2;
+  }
   while (D > 1 && (size_t)D * plane_bytes > budget / 2) D >>= 1;
   const int per_sm = ((size_t)D * plane_bytes <= budget / 2) ? 2 : 1;
   const int grid = h->dev.sm_count * per_sm;
@@ -291,7 +338,6 @@ static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const i
     H3D_VOTE_CASE(1)
     H3D_VOTE_CASE(2)
     H3D_VOTE_CASE(4)
-    H3D_VOTE_CASE(8)
   }
 #undef H3D_VOTE_CASE
   return fail(H3D_ERR_ARG, "bad D");
@@ -436,7 +482,7 @@ static int refresh_and_reduce(h3d_hough *h, unsigned long long *key_out) {
   const int blocks = (h->d.dir_count + 255) / 256;
   H3D_CUDA(cudaMemsetAsync(h->keys, 0, 2 * sizeof(unsigned long long), h->stream));
   if (h->all_dirty) {
-    H3D_TRY(launch_vote(h, 4, 0, nullptr, nullptr, h->d.dir_count, nullptr));
+    H3D_TRY(launch_vote(h, 0, 0, nullptr, nullptr, h->d.dir_count, nullptr));
     h->votes_cast += (uint64_t)h->d.n * h->d.dir_count;
     h->all_dirty = h->has_negative;
   } else {
@@ -444,7 +490,7 @@ static int refresh_and_reduce(h3d_hough *h, unsigned long long *key_out) {
     argmax_kernel<<<blocks, 256, 0, h->stream>>>(h->d, 1, h->keys);
     worklist_kernel<<<blocks, 256, 0, h->stream>>>(h->d, h->keys, h->list, h->count);
     H3D_CUDA(cudaGetLastError());
-    H3D_TRY(launch_vote(h, 1, 0, h->list, h->count, 0, nullptr));
+    H3D_TRY(launch_vote(h, 0, 0, h->list, h->count, 0, nullptr));
   }
   argmax_kernel<<<blocks, 256, 0, h->stream>>>(h->d, 0, h->keys + 1);
   H3D_CUDA(cudaGetLastError());
@@ -507,7 +553,7 @@ extern "C" int h3d_download_votes(h3d_hough *h, unsigned *votes, size_t cap) {
   int rc = H3D_OK;
   do {
     if (cudaMemsetAsync(dense, 0, cells * sizeof(unsigned), h->stream) != cudaSuccess) { rc = H3D_ERR_CUDA; break; }
-    rc = launch_vote(h, 4, 0, nullptr, nullptr, h->d.dir_count, dense);
+    rc = launch_vote(h, 2, 0, nullptr, nullptr, h->d.dir_count, dense);
     if (rc) break;
     h->all_dirty = h->has_negative;   // the same pass rebuilt every record
     if (cudaMemcpyAsync(votes, dense, cells * sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
@@ -520,8 +566,7 @@ extern "C" int h3d_download_votes(h3d_hough *h, unsigned *votes, size_t cap) {
 extern "C" int h3d_bench_vote(h3d_hough *h, int reps, int ablate, float *us_per_launch) {
   int D = (ablate >> 8) & 0xFF;   // optional: directions per work item in bits 8..15
   ablate &= 0xFF;
-  if (D == 0) D = 4;
-  if (!h || !us_per_launch || reps < 1 || ablate < 0 || ablate > 2 || (D != 1 && D != 2 && D != 4 && D != 8))
+  if (!h || !us_per_launch || reps < 1 || ablate < 0 || ablate > 2 || (D != 0 && D != 1 && D != 2 && D != 4))
     return fail(H3D_ERR_ARG, "bad argument");
   cudaEvent_t e0, e1;
   H3D_CUDA(cudaEventCreate(&e0));

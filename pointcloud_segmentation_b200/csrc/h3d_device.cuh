@@ -59,40 +59,64 @@ __device__ __forceinline__ double ref_y_new(const DirCoef &c, double px, double 
 // roundToNearest((v + max_x)/dx) of lib/hough.cpp:22-24,86-87 evaluated exactly,
 // as a signed integer.  Values beyond +-2^40 (and NaN) return 2^40: such a vote
 // can never land inside the accumulator.
-__device__ __noinline__ long long ref_cell_slow(double v, double max_x, double dx) {
+__device__ __forceinline__ long long ref_cell_slow(double v, double max_x, double dx) {
   const double q = __ddiv_rn(__dadd_rn(v, max_x), dx);
   const double r = (q > 0.0) ? floor(__dadd_rn(q, 0.5)) : ceil(__dsub_rn(q, 0.5));
   if (!(fabs(r) < 1099511627776.0)) return 1099511627776LL;
   return (long long)r;
 }
 
-// Plane cell x_i*num_x + y_i of one vote, or 0xFFFFFFFF when the reference's
+// Exact plane cell x_i*num_x + y_i of one vote, or 0xFFFFFFFF when the reference's
 // flat-index test `index < VotingSpace.size()` (lib/hough.cpp:92) drops it.
 // Only the FLAT bound is tested, so y_i == num_x aliases into the next row
-// exactly as the reference does.
-__device__ __forceinline__ unsigned vote_cell(const HoughDev &h, const DirCoef &c, double px, double py,
-                                              double pz) {
-  const double xn = ref_x_new(c, px, py, pz);
-  const double yn = ref_y_new(c, px, py, pz);
-  if (h.fast_ok) {
-    // One DFMA per axis.  sx = 1.5*2^52 + n with n = round(t*2^20), t = (x'+max_x)/dx + 0.5,
-    // |error| < 2 units of 2^-20.  If the 20 fraction bits of n are >= 4 units away
-    // from a cell boundary, floor(t) is certain and equals the reference's
-    // floor(fl(fl(x'+max_x)/dx) + 0.5) (its rounding slack is ~1e-12 cells).
-    const double sx = __fma_rn(xn, h.inv_s, h.kmagic);
-    const double sy = __fma_rn(yn, h.inv_s, h.kmagic);
-    const unsigned lx = (unsigned)__double2loint(sx), ly = (unsigned)__double2loint(sy);
-    const bool sure = (__double2hiint(sx) == 0x43380000) & (__double2hiint(sy) == 0x43380000) &
-                      (((lx & 0xFFFFFu) - 4u) < 0xFFFF8u) & (((ly & 0xFFFFFu) - 4u) < 0xFFFF8u);
-    if (sure) {
-      const unsigned cell = (lx >> 20) * (unsigned)h.num_x + (ly >> 20);
-      return cell < h.plane_cells ? cell : 0xFFFFFFFFu;
-    }
-  }
-  const long long xi = ref_cell_slow(xn, h.max_x, h.dx);
-  const long long yi = ref_cell_slow(yn, h.max_x, h.dx);
-  const long long cell = xi * (long long)h.num_x + yi;   // |.| < 2^40 * 2^31: no overflow
-  return (cell >= 0 && cell < (long long)h.plane_cells) ? (unsigned)cell : 0xFFFFFFFFu;
+// exactly as the reference does.  This is the rarely taken exact path.
+// (scalar arguments only: a by-reference HoughDev would force the kernel parameters
+// into local memory at every call site)
+__device__ __noinline__ unsigned vote_cell_exact(const DirCoef *coef_j, double max_x, double dx, int num_x,
+                                                 double px, double py, double pz) {
+  const DirCoef c = *coef_j;
+  const long long xi = ref_cell_slow(ref_x_new(c, px, py, pz), max_x, dx);
+  const long long yi = ref_cell_slow(ref_y_new(c, px, py, pz), max_x, dx);
+  const long long cell = xi * (long long)num_x + yi;   // |.| < 2^40 * 2^31: no overflow
+  return (cell >= 0 && cell < (long long)num_x * num_x) ? (unsigned)cell : 0xFFFFFFFFu;
+}
+
+// Fast path.  Per direction five coefficients pre-scaled by inv_s = 2^20/dx:
+//   sx = fma(c0s,px, fma(c1n,py, fma(bxn,pz, K)))     K = 1.5*2^52 + round(max_x*inv_s + 2^19)
+// so the low mantissa word of sx is n = round(t * 2^20) with t = (x'+max_x)/dx + 0.5 and an
+// error below 2.5 units of 2^-20 cell (three roundings to integer units, the rounding of K,
+// ~1e-6 units from the scaled coefficients; the reference's own rounding slack is ~1e-8
+// units).  When the 20 fraction bits of n are at least 8 units away from a cell boundary,
+// floor(t) is certain and equals the reference's roundToNearest; otherwise (probability
+// ~3e-5 per vote) the exact path decides.  6 DFMA per vote instead of 12 FP64 ops + 2 divisions.
+struct FastCoef {
+  double c0s, c1n, c2s, bxn, byn;
+};
+__device__ __forceinline__ FastCoef make_fast(const DirCoef &c, double inv_s) {
+  FastCoef f;
+  f.c0s = c.c0 * inv_s; f.c1n = -(c.c1 * inv_s); f.c2s = c.c2 * inv_s;
+  f.bxn = -(c.bx * inv_s); f.byn = -(c.by * inv_s);
+  return f;
+}
+
+// branch-free part: candidate cell and whether it is certain
+__device__ __forceinline__ unsigned vote_cell_fast(const FastCoef &f, double kmagic, unsigned num_x, double px,
+                                                   double py, double pz, bool *sure) {
+  const double sx = __fma_rn(f.c0s, px, __fma_rn(f.c1n, py, __fma_rn(f.bxn, pz, kmagic)));
+  const double sy = __fma_rn(f.c1n, px, __fma_rn(f.c2s, py, __fma_rn(f.byn, pz, kmagic)));
+  const unsigned lx = (unsigned)__double2loint(sx), ly = (unsigned)__double2loint(sy);
+  const unsigned hbad = ((unsigned)__double2hiint(sx) ^ 0x43380000u) | ((unsigned)__double2hiint(sy) ^ 0x43380000u);
+  *sure = (hbad == 0) & (((lx << 12) - 0x8000u) < 0xFFFF0000u) & (((ly << 12) - 0x8000u) < 0xFFFF0000u);
+  return (lx >> 20) * num_x + (ly >> 20);
+}
+
+// cell of one vote; the caller tests cell < plane_cells (0xFFFFFFFF from the exact path fails it)
+__device__ __forceinline__ unsigned vote_cell(const HoughDev &h, const FastCoef &f, int j, double px,
+                                              double py, double pz) {
+  bool sure;
+  unsigned cell = vote_cell_fast(f, h.kmagic, (unsigned)h.num_x, px, py, pz, &sure);
+  if (!sure | !h.fast_ok) cell = vote_cell_exact(h.coef + j, h.max_x, h.dx, h.num_x, px, py, pz);
+  return cell;
 }
 
 // packed argmax key: larger votes first, then the LOWEST flat index

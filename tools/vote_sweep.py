@@ -29,7 +29,7 @@ for name, pts, g, dx in cases:
     h = capi.Hough(mn, mx, dx)
     h.add(x)
     votes = len(x) * h.num_b
-    for D in (1, 2, 4, 8):
+    for D in (0, 1, 2, 4):
         for ab in (0, 1, 2):
             try:
                 us = h.bench_vote(reps=5, ablate=ab, D=D)
