@@ -248,6 +248,36 @@ __global__ void kill_points_kernel(const int *__restrict__ idx, int n_idx, int *
   if (k < n_idx && idx[k] >= 0) w[idx[k]] = 0;
 }
 
+// stable in-place compaction of the live points (weight != 0); one CTA walks the array in
+// chunks, so a chunk is entirely in registers before anything at or below it is rewritten
+__global__ void __launch_bounds__(1024, 1)
+compact_points_kernel(double *px, double *py, double *pz, int *w, int n) {
+  __shared__ int warp_sum[32];
+  __shared__ int base_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) base_s = 0;
+  __syncthreads();
+  for (int c0 = 0; c0 < n; c0 += 1024) {
+    const int i = c0 + tid;
+    const int wv = i < n ? w[i] : 0;
+    const bool keep = wv != 0;
+    double x = 0, y = 0, z = 0;
+    if (keep) { x = px[i]; y = py[i]; z = pz[i]; }
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, keep);
+    if (lane == 0) warp_sum[warp] = __popc(bal);
+    __syncthreads();
+    int off = base_s;
+    for (int q = 0; q < warp; ++q) off += warp_sum[q];
+    int total = 0;
+    if (tid == 0) for (int q = 0; q < 32; ++q) total += warp_sum[q];
+    const int pos = off + __popc(bal & ((1u << lane) - 1u));
+    if (keep) { px[pos] = x; py[pos] = y; pz[pos] = z; w[pos] = wv; }
+    __syncthreads();
+    if (tid == 0) base_s += total;
+    __syncthreads();
+  }
+}
+
 // unmatched subtract: append as weight -1 points (unsigned cells wrap like the reference's)
 __global__ void append_negative_kernel(const double *__restrict__ y, const int *__restrict__ idx, int ny,
                                        double *px, double *py, double *pz, int *w, int at, int *cursor) {
@@ -278,7 +308,7 @@ static int launch_vote_t(h3d_hough *h, const int *list, const int *count_ptr, in
 
 template <int P, int ABLATE>
 static int launch_resident_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm) {
-  const size_t smem = (size_t)2 * h->d.plane_stride * sizeof(unsigned);
+  const size_t smem = ((size_t)2 * kResG * h->d.plane_stride + 4) * sizeof(unsigned);
   static thread_local size_t configured = 0;
   if (smem > configured) {
     cudaFuncAttributes fa;
@@ -297,7 +327,7 @@ static int launch_resident_t(h3d_hough *h, const int *list, const int *count_ptr
 constexpr int kResidentMaxP = 12;
 static bool resident_ok(const h3d_hough *h) {
   return !h->has_negative && h->d.n <= kResThreads * kResidentMaxP &&
-         (size_t)2 * h->d.plane_stride * sizeof(unsigned) <= h->dev.smem_optin - 2048;
+         ((size_t)2 * kResG * h->d.plane_stride + 4) * sizeof(unsigned) <= h->dev.smem_optin - 2048;
 }
 
 static int launch_resident(h3d_hough *h, int ablate, const int *list, const int *count_ptr, int count_imm) {
@@ -310,6 +340,7 @@ static int launch_resident(h3d_hough *h, int ablate, const int *list, const int 
   }
   H3D_RES_CASE(4)
   H3D_RES_CASE(8)
+  H3D_RES_CASE(10)
   H3D_RES_CASE(12)
 #undef H3D_RES_CASE
   return fail(H3D_ERR_ARG, "too many points for the resident vote kernel");
@@ -472,6 +503,11 @@ extern "C" int h3d_subtract(h3d_hough *h, const double *xyz, size_t n) {
     h->d.n += counts[2];
     h->has_negative = true;
     h->all_dirty = true;
+  }
+  if (!h->has_negative) {   // keep the live points dense (the resident vote kernel relies on it)
+    compact_points_kernel<<<1, 1024, 0, h->stream>>>(h->px, h->py, h->pz, h->w, h->d.n);
+    H3D_CUDA(cudaGetLastError());
+    h->d.n -= (int)n - counts[1];
   }
   return H3D_OK;
 }

@@ -110,6 +110,47 @@ __device__ __forceinline__ unsigned vote_cell_fast(const FastCoef &f, double kma
   return (lx >> 20) * num_x + (ly >> 20);
 }
 
+// same, for the unrolled hot loops: instead of a per-vote flag the guards are ACCUMULATED
+// (gmin = min over votes of the distance-to-boundary word, hacc = OR of the exponent
+// mismatches) and tested once per batch; the rare unsure batch is then re-examined vote by
+// vote with vote_cell_fast.  4 integer ops of guard per vote instead of ~8.
+__device__ __forceinline__ unsigned vote_cell_acc(const FastCoef &f, double kmagic, unsigned num_x, double px,
+                                                  double py, double pz, unsigned &gmin, unsigned &hacc) {
+  const double sx = __fma_rn(f.c0s, px, __fma_rn(f.c1n, py, __fma_rn(f.bxn, pz, kmagic)));
+  const double sy = __fma_rn(f.c1n, px, __fma_rn(f.c2s, py, __fma_rn(f.byn, pz, kmagic)));
+  const unsigned lx = (unsigned)__double2loint(sx), ly = (unsigned)__double2loint(sy);
+  gmin = min(gmin, min((lx << 12) + 0x8000u, (ly << 12) + 0x8000u));   // < 0x10000: within 8 units
+  hacc |= ((unsigned)__double2hiint(sx) ^ 0x43380000u) | ((unsigned)__double2hiint(sy) ^ 0x43380000u);
+  return (lx >> 20) * num_x + (ly >> 20);
+}
+__device__ __forceinline__ bool batch_unsure(unsigned gmin, unsigned hacc) { return (gmin < 0x10000u) | (hacc != 0u); }
+
+// shared-memory increment by 32-bit shared address, predicated, no return value
+__device__ __forceinline__ void red_shared_inc(unsigned addr) {
+  asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(addr) : "memory");
+}
+__device__ __forceinline__ void red_shared_add(unsigned addr, unsigned val, bool pred) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p red.shared.add.u32 [%0], %1;\n\t}"
+      :: "r"(addr), "r"(val), "r"((unsigned)pred) : "memory");
+}
+__device__ __forceinline__ void cp_async8(unsigned dst_shared, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst_shared), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// Rare path of the unrolled loops, deliberately out of line and self-contained (it shares
+// no intermediate with the fast path, so the fast path keeps nothing alive for it):
+// recompute one vote, return the certain fast cell or the exact one.
+__device__ __noinline__ unsigned vote_cell_checked(const DirCoef *coef_j, double inv_s, double kmagic,
+                                                   double max_x, double dx, int num_x, int fast_ok, double px,
+                                                   double py, double pz) {
+  bool sure;
+  const unsigned cell = vote_cell_fast(make_fast(*coef_j, inv_s), kmagic, (unsigned)num_x, px, py, pz, &sure);
+  if (sure && fast_ok) return cell;
+  return vote_cell_exact(coef_j, max_x, dx, num_x, px, py, pz);
+}
+
 // cell of one vote; the caller tests cell < plane_cells (0xFFFFFFFF from the exact path fails it)
 __device__ __forceinline__ unsigned vote_cell(const HoughDev &h, const FastCoef &f, int j, double px,
                                               double py, double pz) {

@@ -171,75 +171,162 @@ vote_kernel(const HoughDev h, const int *__restrict__ list, const int *__restric
 // ---------------------------------------------------------------------------
 // K1 (resident form, N <= kResThreads * P, weights in {0,1}): one persistent CTA
 // per SM keeps ALL live points in registers (P per thread) for its whole list of
-// directions, so a vote costs 6 DFMA, ~12 integer ops and one shared atomic and
-// no load at all.  Two planes are double-buffered: while the CTA votes direction
-// k into one, it scans (and re-zeroes) the plane of direction k-1 in the other,
-// so there is a single barrier per direction and no scan-only phase.
+// directions, so a vote costs 6 DFMA, ~10 integer ops and one shared-memory RED
+// and no load at all.  Two planes are double-buffered: while the CTA votes
+// direction k into one, it scans (and re-zeroes) the plane of direction k-1 in
+// the other, so there is a single barrier per direction and no scan-only phase.
+// The coefficients of direction k+1 are fetched by cp.async into shared memory
+// during phase k, so no thread waits on global memory inside the loop.
 // ---------------------------------------------------------------------------
 constexpr int kResThreads = 512;
 constexpr int kResWarps = kResThreads / 32;
 
+// (max, first max cell) of a plane, zeroing it; quads whose maximum cannot beat the
+// running best cost 6 instructions
+template <int THREADS>
+__device__ __forceinline__ unsigned long long scan_plane_fast(unsigned *plane, unsigned quads, int t) {
+  uint4 *p4 = reinterpret_cast<uint4 *>(plane);
+  unsigned best = 0, bcell = 0;
+  for (unsigned q = t; q < quads; q += THREADS) {
+    const uint4 v = p4[q];
+    const unsigned m4 = max(max(v.x, v.y), max(v.z, v.w));
+    if (m4 == 0) continue;
+    p4[q] = make_uint4(0, 0, 0, 0);
+    if (m4 > best) {
+      best = m4;
+      bcell = 4 * q + (v.x == m4 ? 0u : v.y == m4 ? 1u : v.z == m4 ? 2u : 3u);
+    }
+  }
+  const unsigned m = __reduce_max_sync(0xFFFFFFFFu, best);
+  const unsigned cm = __reduce_min_sync(0xFFFFFFFFu, best == m ? bcell : 0xFFFFFFFFu);
+  return ((unsigned long long)m << 32) | (0xFFFFFFFFu - cm);
+}
+
+constexpr int kResG = 4;   // directions voted per barrier phase
+
+struct ResShared {
+  unsigned long long warp_best[2][kResG][kResWarps];
+  double coef[2][kResG][6];   // raw DirCoef of the directions voted in phase k (slot k&1)
+  int dir[3][kResG];          // local direction numbers of phase k (slot k%3; -1: none); the
+                              // previous phase's numbers stay readable while the next are staged
+};
+
 template <int P, int ABLATE>
 __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__restrict__ list, int count,
-                                              unsigned *planes, unsigned long long (*warp_best)[32], int cta,
-                                              int n_cta) {
+                                              unsigned *planes, ResShared &sh, int cta, int n_cta) {
+  constexpr int G = kResG;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const unsigned stride = h.plane_stride;
+  const unsigned stride = h.plane_stride, quads = stride / 4;
+  const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
+  const unsigned coef_sa = (unsigned)__cvta_generic_to_shared(&sh.coef[0][0][0]);
+  // points are COMPACT here (every weight +1): slot p of thread t is point t + p*512, so all
+  // slots below n/512 are full for every thread and only one slot is partially filled
   double px[P], py[P], pz[P];
   unsigned live = 0;
 #pragma unroll
   for (int p = 0; p < P; ++p) {
     const int i = tid + p * kResThreads;
-    const bool ok = i < h.n && h.w[i] != 0;
+    const bool ok = i < h.n;
     px[p] = ok ? h.px[i] : 0.0; py[p] = ok ? h.py[i] : 0.0; pz[p] = ok ? h.pz[i] : 0.0;
     live |= ok ? (1u << p) : 0u;
   }
-  unsigned sink = 0;
-  int prev = -1;     // local direction whose plane waits to be scanned
-  int k = 0;
-  for (int e = cta;; e += n_cta, ++k) {
-    const bool have = e < count;
-    unsigned *mine = planes + (k & 1) * stride;
-    unsigned *other = planes + ((k & 1) ^ 1) * stride;
+  const int full_slots = h.n / kResThreads, used_slots = (h.n + kResThreads - 1) / kResThreads;
+  const unsigned dummy_sa = planes_sa + 2u * G * stride * 4u;   // pad word: votes that must not count
+  // thread g < G stages direction g of a group: list entry -> dir[], DirCoef -> coef[] (cp.async)
+  auto stage = [&](int group, int slot, int dslot) {
+    const int e = group * G + tid;
     int l = -1;
-    if (have) {
+    if (e < count) {
       l = list ? list[e] : e;
-      const int j = h.dir_begin + l;
-      const FastCoef f = make_fast(h.coef[j], h.inv_s);
-      const double kmagic = h.kmagic;
-      const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells;
-      unsigned cell[P];
-      unsigned unsure = 0;
+      const double *src = reinterpret_cast<const double *>(h.coef + h.dir_begin + l);
 #pragma unroll
-      for (int p = 0; p < P; ++p) {   // branch-free: P independent chains of 3 DFMA per axis
-        bool sure = true;
-        if (ABLATE == 2) cell[p] = ((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells;
-        else cell[p] = vote_cell_fast(f, kmagic, num_x, px[p], py[p], pz[p], &sure);
-        unsure |= sure ? 0u : (1u << p);
-      }
-      unsure = h.fast_ok ? (unsure & live) : live;
-      if (ABLATE != 2 && unsure) {   // rare: a projection within 8e-6 cell of a boundary
+      for (int c = 0; c < 5; ++c) cp_async8(coef_sa + 48u * (unsigned)(slot * G + tid) + 8u * c, src + c);
+    }
+    sh.dir[dslot][tid] = l;
+  };
+  if (tid < G) { stage(cta, 0, 0); cp_async_wait_all(); }
+  __syncthreads();   // also orders the kernel's zero-fill of the planes
+  const double kmagic = h.kmagic, inv_s = h.inv_s;
+  const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells;
+  unsigned sink = 0;
+  bool prev_any = false;
+  int k = 0;
+  for (int group = cta;; group += n_cta, ++k) {
+    const int slot = k & 1, dslot = k % 3, dprev = (k + 2) % 3;
+    const bool have = group * G < count;
+    if (tid < G) stage(group + n_cta, slot ^ 1, (k + 1) % 3);   // fetched while this group is voted
+    if (have) {
+#pragma unroll 1
+      for (int g = 0; g < G; ++g) {
+        const int l = sh.dir[dslot][g];
+        if (l < 0) break;
+        DirCoef raw;
+        raw.c0 = sh.coef[slot][g][0]; raw.c1 = sh.coef[slot][g][1]; raw.c2 = sh.coef[slot][g][2];
+        raw.bx = sh.coef[slot][g][3]; raw.by = sh.coef[slot][g][4];
+        const FastCoef f = make_fast(raw, inv_s);
+        const unsigned mine_sa = planes_sa + (unsigned)(slot * G + g) * stride * 4u;
+        constexpr int CH = 4;   // votes per batch: 8 independent DFMA chains, 4 cell registers
 #pragma unroll
-        for (int p = 0; p < P; ++p)
-          if (unsure & (1u << p)) cell[p] = vote_cell_exact(h.coef + j, h.max_x, h.dx, h.num_x, px[p], py[p], pz[p]);
-      }
+        for (int p0 = 0; p0 < P; p0 += CH) {
+          if (p0 >= used_slots) break;                    // uniform
+          const bool edge = p0 + CH > full_slots;         // uniform: batch holds the partial slot
+          unsigned cell[CH];
+          unsigned gmin = 0xFFFFFFFFu, hacc = 0;
 #pragma unroll
-      for (int p = 0; p < P; ++p) {
-        if (ABLATE == 1) sink ^= cell[p];
-        else if ((live & (1u << p)) && cell[p] < plane_cells) atomicAdd(&mine[cell[p]], 1u);
+          for (int c = 0; c < CH; ++c) {
+            const int p = p0 + c;
+            if (p >= P) { cell[c] = 0xFFFFFFFFu; continue; }
+            if (ABLATE == 2) cell[c] = ((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells;
+            else cell[c] = vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], gmin, hacc);
+          }
+          if (ABLATE != 2 && (batch_unsure(gmin, hacc) | !h.fast_ok)) {   // rare: within 8e-6 cell of a boundary
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {   // unrolled: register arrays must not be indexed dynamically
+              const int p = p0 + c;
+              if (p < P)
+                cell[c] = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
+                                            h.fast_ok, px[p], py[p], pz[p]);
+            }
+          }
+          // unconditional increments (ATOMS.POPC.INC merges lanes that hit the same cell and needs no
+          // branch this way); a vote the reference drops, or an empty slot, goes to the pad word
+          if (!edge) {
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+              if (p0 + c >= P) continue;
+              if (ABLATE == 1) sink ^= cell[c];
+              else red_shared_inc(cell[c] < plane_cells ? mine_sa + 4u * cell[c] : dummy_sa);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+              const int p = p0 + c;
+              if (p >= P) continue;
+              if (ABLATE == 1) sink ^= cell[c];
+              else red_shared_inc(((cell[c] < plane_cells) & ((live >> p) & 1u)) ? mine_sa + 4u * cell[c] : dummy_sa);
+            }
+          }
+        }
       }
     }
-    if (prev >= 0) {
-      const unsigned long long key = scan_plane<kResThreads>(h, other, tid, h.dir_begin + prev, nullptr);
-      if (lane == 0) warp_best[(k & 1) ^ 1][warp] = key;
+    if (prev_any) {
+#pragma unroll 1
+      for (int g = 0; g < G; ++g) {
+        const unsigned long long key =
+            scan_plane_fast<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, quads, tid);
+        if (lane == 0) sh.warp_best[slot ^ 1][g][warp] = key;
+      }
     }
-    __syncthreads();
-    if (prev >= 0 && warp == 0) {
-      unsigned long long key = lane < kResWarps ? warp_best[(k & 1) ^ 1][lane] : 0ull;
+    if (tid < G) cp_async_wait_all();
+    __syncthreads();   // votes of this group, scan of the previous one, staging of the next: done
+    int prev_l = -1;
+    if (prev_any && warp < G) prev_l = sh.dir[dprev][warp];
+    if (prev_l >= 0) {
+      unsigned long long key = lane < kResWarps ? sh.warp_best[slot ^ 1][warp][lane] : 0ull;
       key = warp_max_u64(key);
-      if (lane == 0) store_record(h, prev, key);
+      if (lane == 0) store_record(h, prev_l, key);
     }
-    prev = l;
+    prev_any = have;
     if (!have) break;
   }
   if (ABLATE == 1 && sink == 0x9E3779B9u) h.dvotes[0] = sink;
@@ -250,12 +337,11 @@ __global__ void __launch_bounds__(kResThreads, 1)
 vote_resident_kernel(const HoughDev h, const int *__restrict__ list, const int *__restrict__ count_ptr,
                      int count_imm) {
   extern __shared__ __align__(16) unsigned planes[];
-  __shared__ unsigned long long warp_best[2][32];
+  __shared__ __align__(16) ResShared sh;
   const int count = count_ptr ? *count_ptr : count_imm;
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
-  for (unsigned q = threadIdx.x; q < 2 * h.plane_stride / 4; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-  __syncthreads();
-  vote_resident<P, ABLATE>(h, list, count, planes, warp_best, blockIdx.x, gridDim.x);
+  for (unsigned q = threadIdx.x; q < 2 * kResG * h.plane_stride / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
+  vote_resident<P, ABLATE>(h, list, count, planes, sh, blockIdx.x, gridDim.x);
 }
 
 // ---------------------------------------------------------------------------
