@@ -151,3 +151,40 @@ class Hough:
             self.close()
         except Exception:
             pass
+
+
+class Trace:
+    """Result of one hough3dlines() call: header fields + per-iteration records with inlier lists."""
+
+    def __init__(self, res, iters, pool):
+        self.rc, self.n_lines, self.n_input = res.rc, res.n_lines, res.n_input
+        self.n_iters = res.n_iters
+        self.shift = np.array(res.shift[:])
+        self.d, self.dx, self.max_x = res.d, res.dx, res.max_x
+        self.num_x, self.num_b = res.num_x, res.num_b
+        self.votes_cast = res.votes_cast
+        self.iters = []
+        for r in iters[: min(res.n_iters, len(iters))]:
+            self.iters.append({
+                "votes": r.votes, "status": r.status, "argmax": r.argmax,
+                "a_raw": np.array(r.a_raw[:]), "b_raw": np.array(r.b_raw[:]),
+                "a1": np.array(r.a1[:]), "b1": np.array(r.b1[:]), "rc1": r.rc1,
+                "a2": np.array(r.a2[:]), "b2": np.array(r.b2[:]), "rc2": r.rc2,
+                "inliers1": pool[r.off1:r.off1 + r.n1].copy(),
+                "inliers2": pool[r.off2:r.off2 + r.n2].copy(),
+            })
+
+
+def hough3dlines(xyz, granularity, dx, minvotes, nlines, mode=0, max_iters=None):
+    """The whole loop on the device (wrap.h:167-350 without the segment post-tests)."""
+    a, p, n = _pts(xyz)
+    if max_iters is None:
+        max_iters = (nlines + 1) if nlines > 0 else 256
+    iters = (Iter * max_iters)()
+    pool_cap = max(1, 2 * max_iters * a.shape[0])
+    pool = np.zeros(pool_cap, dtype=np.uint32)
+    res = Result()
+    check(lib().h3d_hough3dlines(p, n, C.c_int(granularity), C.c_double(dx), C.c_int(minvotes), C.c_int(nlines),
+                                 C.c_int(mode), iters, C.c_size_t(max_iters),
+                                 pool.ctypes.data_as(C.POINTER(C.c_uint32)), C.c_size_t(pool_cap), C.byref(res)))
+    return Trace(res, iters, pool)

@@ -10,7 +10,7 @@
 #include <mutex>
 #include <new>
 
-#include "h3d_kernels.cuh"
+#include "h3d_loop.cuh"
 
 namespace h3d {
 
@@ -374,19 +374,9 @@ static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const i
   return fail(H3D_ERR_ARG, "bad D");
 }
 
-static int create_impl(const double minP[3], const double maxP[3], double var_dx, size_t dir_begin,
-                       size_t dir_end, bool whole, h3d_hough **out) {
-  if (!minP || !maxP || !out) return fail(H3D_ERR_ARG, "null argument");
-  auto sp = current_space();
-  if (!sp) return fail(H3D_ERR_ARG, "h3d_init_space() has not been called");
-  if (whole) { dir_begin = 0; dir_end = sp->num_b; }
-  if (dir_begin > dir_end || dir_end > sp->num_b) return fail(H3D_ERR_ARG, "bad direction range");
-  h3d_hough *h = new (std::nothrow) h3d_hough();
-  if (!h) return fail(H3D_ERR_NOMEM, "host allocation failed");
-  std::unique_ptr<h3d_hough, void (*)(h3d_hough *)> guard(h, h3d_destroy);
-  h->space = sp;
-  H3D_TRY(device_facts(&h->dev));
-  // lib/hough.cpp:32-38
+// Hough::Hough discretisation (lib/hough.cpp:32-40) into the device descriptor
+static int configure_hough(h3d_hough *h, const double minP[3], const double maxP[3], double var_dx) {
+  const Space &sp = *h->space;
   const double nmax = sqrt((maxP[0] * maxP[0]) + (maxP[1] * maxP[1]) + (maxP[2] * maxP[2]));
   const double nmin = sqrt((minP[0] * minP[0]) + (minP[1] * minP[1]) + (minP[2] * minP[2]));
   const double max_x = nmax < nmin ? nmin : nmax;
@@ -396,7 +386,7 @@ static int create_impl(const double minP[3], const double maxP[3], double var_dx
   const double nxd = round_to_nearest(range_x / dx);
   if (!(nxd >= 0.0) || nxd > 65535.0) return fail(H3D_ERR_RANGE, "num_x out of range");
   const size_t num_x = (size_t)nxd;
-  const unsigned long long cells = (unsigned long long)num_x * num_x * sp->num_b;
+  const unsigned long long cells = (unsigned long long)num_x * num_x * sp.num_b;
   if (cells >= (1ull << 32))
     return fail(H3D_ERR_RANGE, "accumulator has >= 2^32 cells (the reference's unsigned argmax index wraps)");
   HoughDev &d = h->d;
@@ -404,10 +394,9 @@ static int create_impl(const double minP[3], const double maxP[3], double var_dx
   d.plane_cells = (unsigned)(num_x * num_x);
   d.plane_stride = (d.plane_cells + 3u) & ~3u;
   if (d.plane_stride == 0) d.plane_stride = 4;
-  d.num_b = (int)sp->num_b;
-  d.dir_begin = (int)dir_begin;
-  d.dir_count = (int)(dir_end - dir_begin);
+  d.num_b = (int)sp.num_b;
   d.max_x = max_x; d.dx = dx;
+  d.inv_s = 0; d.kmagic = 0;
   d.fast_ok = (num_x >= 1 && num_x <= 4000 && dx > 0.0 && std::isfinite(max_x)) ? 1 : 0;
   if (d.fast_ok) {
     const long double inv_s = ldexpl(1.0L / (long double)dx, 20);
@@ -416,7 +405,24 @@ static int create_impl(const double minP[3], const double maxP[3], double var_dx
     d.kmagic = (double)(6755399441055744.0L + bias);   // 1.5 * 2^52 + bias
     if (!(bias >= 0.0L && bias < 4294967296.0L)) d.fast_ok = 0;
   }
-  d.coef = sp->coef_dev;
+  d.coef = sp.coef_dev;
+  return H3D_OK;
+}
+
+// handle + per-direction buffers for directions [dir_begin, dir_end) of the current space
+static int alloc_hough(size_t dir_begin, size_t dir_end, bool whole, h3d_hough **out) {
+  auto sp = current_space();
+  if (!sp) return fail(H3D_ERR_ARG, "h3d_init_space() has not been called");
+  if (whole) { dir_begin = 0; dir_end = sp->num_b; }
+  if (dir_begin > dir_end || dir_end > sp->num_b) return fail(H3D_ERR_ARG, "bad direction range");
+  h3d_hough *h = new (std::nothrow) h3d_hough();
+  if (!h) return fail(H3D_ERR_NOMEM, "host allocation failed");
+  std::unique_ptr<h3d_hough, void (*)(h3d_hough *)> guard(h, h3d_destroy);
+  h->space = sp;
+  H3D_TRY(device_facts(&h->dev));
+  HoughDev &d = h->d;
+  d.dir_begin = (int)dir_begin;
+  d.dir_count = (int)(dir_end - dir_begin);
   H3D_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   const size_t nd = d.dir_count ? d.dir_count : 1;
   H3D_CUDA(cudaMalloc(&d.dvotes, nd * sizeof(unsigned)));
@@ -429,8 +435,19 @@ static int create_impl(const double minP[3], const double maxP[3], double var_dx
   H3D_CUDA(cudaMalloc(&h->list, nd * sizeof(int)));
   H3D_CUDA(cudaMalloc(&h->count, 4 * sizeof(int)));
   H3D_TRY(ensure_points(h, 4096));
-  h->all_dirty = false;   // an empty accumulator: every record is exactly zero
   *out = guard.release();
+  return H3D_OK;
+}
+
+static int create_impl(const double minP[3], const double maxP[3], double var_dx, size_t dir_begin,
+                       size_t dir_end, bool whole, h3d_hough **out) {
+  if (!minP || !maxP || !out) return fail(H3D_ERR_ARG, "null argument");
+  h3d_hough *h = nullptr;
+  H3D_TRY(alloc_hough(dir_begin, dir_end, whole, &h));
+  const int rc = configure_hough(h, minP, maxP, var_dx);
+  if (rc != H3D_OK) { h3d_destroy(h); return rc; }
+  h->all_dirty = false;   // an empty accumulator: every record is exactly zero
+  *out = h;
   return H3D_OK;
 }
 
@@ -621,4 +638,293 @@ extern "C" int h3d_bench_vote(h3d_hough *h, int reps, int ablate, float *us_per_
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   if (ablate != 0) h->all_dirty = true;   // ablated launches leave meaningless records
   return rc;
+}
+
+// =====================================================================================
+// The whole loop on the device: hough3dlines() of wrap.h:167-350 / lib/hough3dlines.cpp:200-317
+// =====================================================================================
+struct PrepOut {
+  int n, pad;
+  double mn[3], mx[3];
+};
+
+// wrap.h:175-189 NaN/Inf strip (ordered) + AoS -> SoA + getMinMax3D (lib/pointcloud.cpp:41-59).
+// One CTA walks the cloud in chunks.  T = double (stride 3) or float (sensor frame, any stride).
+template <typename T>
+__global__ void __launch_bounds__(1024, 1)
+prep_kernel(const T *__restrict__ in, int n, int stride, double *px, double *py, double *pz, unsigned *orig,
+            PrepOut *out) {
+  __shared__ int warp_sum[32];
+  __shared__ double red[6][32];
+  __shared__ int base_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) base_s = 0;
+  __syncthreads();
+  double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int c0 = 0; c0 < n; c0 += 1024) {
+    const int i = c0 + tid;
+    double x = 0, y = 0, z = 0;
+    bool keep = false;
+    if (i < n) {
+      x = (double)in[(size_t)i * stride]; y = (double)in[(size_t)i * stride + 1]; z = (double)in[(size_t)i * stride + 2];
+      keep = isfinite(x) && isfinite(y) && isfinite(z);
+    }
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, keep);
+    if (lane == 0) warp_sum[warp] = __popc(bal);
+    __syncthreads();
+    int off = base_s;
+    for (int q = 0; q < warp; ++q) off += warp_sum[q];
+    if (keep) {
+      const int p = off + __popc(bal & ((1u << lane) - 1u));
+      px[p] = x; py[p] = y; pz[p] = z; orig[p] = (unsigned)i;
+      mn[0] = fmin(mn[0], x); mn[1] = fmin(mn[1], y); mn[2] = fmin(mn[2], z);
+      mx[0] = fmax(mx[0], x); mx[1] = fmax(mx[1], y); mx[2] = fmax(mx[2], z);
+    }
+    __syncthreads();
+    if (tid == 0) { int t = 0; for (int q = 0; q < 32; ++q) t += warp_sum[q]; base_s += t; }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    for (int o = 16; o; o >>= 1) {
+      mn[c] = fmin(mn[c], __shfl_xor_sync(0xFFFFFFFFu, mn[c], o));
+      mx[c] = fmax(mx[c], __shfl_xor_sync(0xFFFFFFFFu, mx[c], o));
+    }
+    if (lane == 0) { red[c][warp] = mn[c]; red[3 + c][warp] = mx[c]; }
+  }
+  __syncthreads();
+  if (warp == 0) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      double a = red[c][lane], b = red[3 + c][lane];
+      for (int o = 16; o; o >>= 1) {
+        a = fmin(a, __shfl_xor_sync(0xFFFFFFFFu, a, o));
+        b = fmax(b, __shfl_xor_sync(0xFFFFFFFFu, b, o));
+      }
+      if (lane == 0) { out->mn[c] = base_s ? a : 0.0; out->mx[c] = base_s ? b : 0.0; }
+    }
+    if (lane == 0) out->n = base_s;
+  }
+}
+
+// PointCloud::shiftToOrigin (lib/pointcloud.cpp:18-26): p = p - newshift, component-wise
+__global__ void shift_points_kernel(double *px, double *py, double *pz, int *w, int n, double sx, double sy,
+                                    double sz) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    px[i] = __dsub_rn(px[i], sx); py[i] = __dsub_rn(py[i], sy); pz[i] = __dsub_rn(pz[i], sz);
+    w[i] = 1;
+  }
+}
+
+namespace {
+
+struct FrameCtx {
+  h3d_hough *hg = nullptr;
+  unsigned granularity = ~0u;
+  size_t cap = 0, iters_cap = 0, pool_cap = 0, in_bytes = 0;
+  void *in_dev = nullptr;
+  unsigned *orig = nullptr;
+  unsigned char *flags = nullptr;
+  int *yidx = nullptr;
+  double *ypx = nullptr, *ypy = nullptr, *ypz = nullptr;
+  h3d_iter *iters_dev = nullptr;
+  unsigned *pool_dev = nullptr;
+  LoopState *st_dev = nullptr;
+  PrepOut *prep_dev = nullptr;
+  LoopState *st_host = nullptr;   // pinned
+  PrepOut *prep_host = nullptr;   // pinned
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  float us[4] = {0, 0, 0, 0};
+
+  ~FrameCtx() { release(); }
+  void release() {
+    if (hg) { h3d_destroy(hg); hg = nullptr; }
+    cudaFree(in_dev); cudaFree(orig); cudaFree(flags); cudaFree(yidx);
+    cudaFree(ypx); cudaFree(ypy); cudaFree(ypz);
+    cudaFree(iters_dev); cudaFree(pool_dev); cudaFree(st_dev); cudaFree(prep_dev);
+    cudaFreeHost(st_host); cudaFreeHost(prep_host);
+    for (auto &e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
+    in_dev = nullptr; orig = nullptr; flags = nullptr; yidx = nullptr; ypx = ypy = ypz = nullptr;
+    iters_dev = nullptr; pool_dev = nullptr; st_dev = nullptr; prep_dev = nullptr;
+    st_host = nullptr; prep_host = nullptr;
+    cap = iters_cap = pool_cap = in_bytes = 0; granularity = ~0u;
+  }
+};
+
+int frame_ensure(FrameCtx &f, unsigned g, size_t n, size_t in_bytes, size_t max_iters, size_t pool_cap) {
+  if (!f.hg || f.granularity != g) {
+    if (f.hg) { h3d_destroy(f.hg); f.hg = nullptr; }
+    H3D_TRY(h3d_init_space(g));
+    H3D_TRY(alloc_hough(0, 0, true, &f.hg));
+    f.granularity = g;
+  }
+  if (!f.st_dev) {
+    H3D_CUDA(cudaMalloc(&f.st_dev, sizeof(LoopState)));
+    H3D_CUDA(cudaMalloc(&f.prep_dev, sizeof(PrepOut)));
+    H3D_CUDA(cudaMallocHost(&f.st_host, sizeof(LoopState)));
+    H3D_CUDA(cudaMallocHost(&f.prep_host, sizeof(PrepOut)));
+    for (auto &e : f.ev) H3D_CUDA(cudaEventCreate(&e));
+  }
+  if (n > f.cap) {
+    size_t cap = f.cap ? f.cap : 8192;
+    while (cap < n) cap *= 2;
+    cudaFree(f.orig); cudaFree(f.flags); cudaFree(f.yidx); cudaFree(f.ypx); cudaFree(f.ypy); cudaFree(f.ypz);
+    f.orig = nullptr; f.flags = nullptr; f.yidx = nullptr; f.ypx = f.ypy = f.ypz = nullptr; f.cap = 0;
+    H3D_CUDA(cudaMalloc(&f.orig, cap * sizeof(unsigned)));
+    H3D_CUDA(cudaMalloc(&f.flags, cap));
+    H3D_CUDA(cudaMalloc(&f.yidx, cap * sizeof(int)));
+    H3D_CUDA(cudaMalloc(&f.ypx, cap * sizeof(double)));
+    H3D_CUDA(cudaMalloc(&f.ypy, cap * sizeof(double)));
+    H3D_CUDA(cudaMalloc(&f.ypz, cap * sizeof(double)));
+    f.cap = cap;
+  }
+  H3D_TRY(ensure_points(f.hg, n ? n : 1));
+  if (in_bytes > f.in_bytes) {
+    cudaFree(f.in_dev); f.in_dev = nullptr; f.in_bytes = 0;
+    H3D_CUDA(cudaMalloc(&f.in_dev, in_bytes));
+    f.in_bytes = in_bytes;
+  }
+  if (max_iters > f.iters_cap) {
+    cudaFree(f.iters_dev); f.iters_dev = nullptr; f.iters_cap = 0;
+    H3D_CUDA(cudaMalloc(&f.iters_dev, max_iters * sizeof(h3d_iter)));
+    f.iters_cap = max_iters;
+  }
+  if (pool_cap > f.pool_cap) {
+    cudaFree(f.pool_dev); f.pool_dev = nullptr; f.pool_cap = 0;
+    H3D_CUDA(cudaMalloc(&f.pool_dev, pool_cap * sizeof(unsigned)));
+    f.pool_cap = pool_cap;
+  }
+  return H3D_OK;
+}
+
+// one iteration of wrap.h:237-342 as a train of kernels on the frame's stream
+int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
+  h3d_hough *h = f.hg;
+  cudaStream_t s = h->stream;
+  const int sm = h->dev.sm_count;
+  const int dblocks = (hd.dir_count + 255) / 256;
+  loop_begin_kernel<<<1, 1, 0, s>>>(lb);
+  loop_unvote_kernel<<<sm * 4, 256, 0, s>>>(hd, lb);                    // hough->subtract(Y)   wrap.h:241
+  loop_argmax_kernel<<<dblocks, 256, 0, s>>>(hd, lb, 1);
+  loop_worklist_kernel<<<dblocks, 256, 0, s>>>(hd, lb);
+  H3D_CUDA(cudaGetLastError());
+  H3D_TRY(launch_vote(h, 0, 0, lb.list, &lb.st->work_count, 0, nullptr));
+  loop_argmax_kernel<<<dblocks, 256, 0, s>>>(hd, lb, 0);                // hough->getLine       wrap.h:243
+  loop_line_kernel<<<1, 32, 0, s>>>(hd, lb);
+  loop_mask_kernel<<<sm * 2, 256, 0, s>>>(hd, lb);                      // pointsCloseToLine    wrap.h:245
+  loop_compact_kernel<<<1, 1024, 0, s>>>(hd, lb, 1);
+  loop_lsq_kernel<<<1, 64, 0, s>>>(hd, lb, 1);                          // orthogonal_LSQ       wrap.h:247
+  loop_mask_kernel<<<sm * 2, 256, 0, s>>>(hd, lb);                      // pointsCloseToLine    wrap.h:250
+  loop_compact_kernel<<<1, 1024, 0, s>>>(hd, lb, 2);
+  loop_lsq_kernel<<<1, 64, 0, s>>>(hd, lb, 2);                          // minvotes, LSQ        wrap.h:251-259
+  loop_remove_kernel<<<1, 1024, 0, s>>>(lb);                            // removePoints, while  wrap.h:339-342
+  H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+
+// everything after the points are on the device (unshifted SoA + orig + PrepOut): bbox checks,
+// Hough ctor, first vote, loop, results.  timing events: ev[1] after prep, ev[2] after the first
+// vote, ev[3] at the end.
+int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int mode, h3d_iter *iters,
+              size_t max_iters, uint32_t *pool, size_t pool_cap, h3d_result *res) {
+  h3d_hough *h = f.hg;
+  cudaStream_t s = h->stream;
+  H3D_CUDA(cudaMemcpyAsync(f.prep_host, f.prep_dev, sizeof(PrepOut), cudaMemcpyDeviceToHost, s));
+  H3D_CUDA(cudaEventRecord(f.ev[1], s));
+  H3D_CUDA(cudaStreamSynchronize(s));
+  const PrepOut P = *f.prep_host;
+  const size_t n = (size_t)P.n;
+  res->n_input = (uint32_t)n;
+  res->num_b = h->space->num_b;
+  if (mode == 1) {                                       // lib/hough3dlines.cpp:170-173, 196-199
+    if (opt_minvotes < 2) opt_minvotes = 2;
+    if (n < 2) { res->rc = 1; return H3D_OK; }
+  }
+  const double ex = P.mx[0] - P.mn[0], ey = P.mx[1] - P.mn[1], ez = P.mx[2] - P.mn[2];
+  const double d = sqrt((ex * ex) + (ey * ey) + (ez * ez));   // (maxP-minP).norm(), wrap.h:201
+  res->d = d;
+  if (d == 0.0) { res->rc = 1; return H3D_OK; }         // wrap.h:202-205
+  double ns[3], minPs[3], maxPs[3];
+  for (int c = 0; c < 3; ++c) {                          // shiftToOrigin + second bbox, wrap.h:206-207
+    ns[c] = (P.mn[c] + P.mx[c]) / 2.0;
+    res->shift[c] = 0.0 + ns[c];
+    minPs[c] = P.mn[c] - ns[c];                          // min(p - s) == min(p) - s: rounding is monotonic
+    maxPs[c] = P.mx[c] - ns[c];
+  }
+  if (mode == 1 && opt_dx == 0.0) opt_dx = d / 64.0;     // lib/hough3dlines.cpp:211-213
+  else if (opt_dx >= d) { res->rc = 1; return H3D_OK; }  // wrap.h:209-212
+  H3D_TRY(configure_hough(h, minPs, maxPs, opt_dx));     // new Hough(...), wrap.h:220
+  HoughDev &hd = h->d;
+  res->dx = hd.dx; res->max_x = hd.max_x; res->num_x = (uint64_t)hd.num_x;
+  hd.n = (int)n;
+  hd.n_dev = nullptr;
+  h->has_negative = false;
+  shift_points_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(h->px, h->py, h->pz, h->w, (int)n, ns[0], ns[1], ns[2]);
+
+  LoopState st;
+  memset(&st, 0, sizeof st);
+  st.opt_dx = opt_dx;
+  for (int c = 0; c < 3; ++c) st.shift[c] = res->shift[c];
+  st.minvotes = opt_minvotes; st.nlines_max = opt_nlines;
+  st.max_iters = (int)(max_iters < f.iters_cap ? max_iters : f.iters_cap);
+  st.pool_cap = (unsigned)(pool_cap < f.pool_cap ? pool_cap : f.pool_cap);
+  st.n_alive = (int)n;
+  *f.st_host = st;
+  H3D_CUDA(cudaMemcpyAsync(f.st_dev, f.st_host, sizeof(LoopState), cudaMemcpyHostToDevice, s));
+
+  // hough->add(X), wrap.h:228: every plane once
+  H3D_TRY(launch_vote(h, 0, 0, nullptr, nullptr, hd.dir_count, nullptr));
+  H3D_CUDA(cudaEventRecord(f.ev[2], s));
+
+  LoopBuffers lb;
+  lb.st = f.st_dev; lb.iters = f.iters_dev; lb.pool = f.pool_dev; lb.orig = f.orig;
+  lb.flags = f.flags; lb.yidx = f.yidx; lb.ypx = f.ypx; lb.ypy = f.ypy; lb.ypz = f.ypz;
+  lb.px = h->px; lb.py = h->py; lb.pz = h->pz; lb.list = h->list; lb.dirs = h->space->dirs_dev;
+  hd.n_dev = &f.st_dev->n_alive;                         // the loop shrinks X on the device
+  int rc = H3D_OK;
+  if (opt_nlines > 0) {
+    for (int it = 0; it < opt_nlines && rc == H3D_OK; ++it) rc = enqueue_iteration(f, hd, lb);
+  } else {                                               // unbounded: look at `done` every few iterations
+    for (;;) {
+      for (int it = 0; it < 8 && rc == H3D_OK; ++it) rc = enqueue_iteration(f, hd, lb);
+      if (rc != H3D_OK) break;
+      if (cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+          cudaStreamSynchronize(s) != cudaSuccess) { rc = fail(H3D_ERR_CUDA, "loop state read-back failed"); break; }
+      if (f.st_host->done) break;
+    }
+  }
+  hd.n_dev = nullptr;
+  if (rc != H3D_OK) return rc;
+  H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
+  H3D_CUDA(cudaEventRecord(f.ev[3], s));
+  H3D_CUDA(cudaStreamSynchronize(s));
+  const LoopState &fin = *f.st_host;
+  res->n_iters = (uint32_t)fin.n_iters; res->n_lines = (uint32_t)fin.n_lines; res->pool_used = fin.pool_used;
+  res->votes_cast = (uint64_t)n * hd.dir_count + fin.votes_cast;
+  const size_t n_rec = (size_t)fin.n_iters < (size_t)st.max_iters ? (size_t)fin.n_iters : (size_t)st.max_iters;
+  if (n_rec && iters) H3D_CUDA(cudaMemcpyAsync(iters, f.iters_dev, n_rec * sizeof(h3d_iter), cudaMemcpyDeviceToHost, s));
+  if (fin.pool_used && pool) H3D_CUDA(cudaMemcpyAsync(pool, f.pool_dev, (size_t)fin.pool_used * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+  H3D_CUDA(cudaStreamSynchronize(s));
+  hd.n = 0;
+  return H3D_OK;
+}
+
+}  // namespace
+
+extern "C" int h3d_hough3dlines(const double *xyz, size_t n, int granularity, double opt_dx, int opt_minvotes,
+                                int opt_nlines, int mode, h3d_iter *iters, size_t max_iters, uint32_t *pool,
+                                size_t pool_cap, h3d_result *res) {
+  if (!res || (!xyz && n) || granularity < 0 || granularity > 8) return fail(H3D_ERR_ARG, "bad argument");
+  if (n > 0x7FFFFFF0u) return fail(H3D_ERR_RANGE, "too many points");
+  memset(res, 0, sizeof *res);
+  static thread_local FrameCtx ctx;
+  FrameCtx &f = ctx;
+  H3D_TRY(frame_ensure(f, (unsigned)granularity, n, n * 3 * sizeof(double), max_iters ? max_iters : 1, pool_cap ? pool_cap : 1));
+  cudaStream_t s = f.hg->stream;
+  H3D_CUDA(cudaEventRecord(f.ev[0], s));
+  if (n) H3D_CUDA(cudaMemcpyAsync(f.in_dev, xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+  prep_kernel<double><<<1, 1024, 0, s>>>(static_cast<const double *>(f.in_dev), (int)n, 3, f.hg->px, f.hg->py,
+                                         f.hg->pz, f.orig, f.prep_dev);
+  H3D_CUDA(cudaGetLastError());
+  return frame_run(f, opt_minvotes, opt_nlines, opt_dx, mode, iters, max_iters, pool, pool_cap, res);
 }

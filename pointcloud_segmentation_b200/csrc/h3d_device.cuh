@@ -40,11 +40,14 @@ struct HoughDev {
   // without a matching added point, 0 removed
   const double *px, *py, *pz;
   const int *w;
-  int n;
+  int n;                  // point count known to the host at launch ...
+  const int *n_dev;       // ... or, when not null, the live count in device memory (loop)
   // per-direction results, indexed by LOCAL direction l = j - dir_begin
   unsigned *dvotes, *dcell;
   unsigned char *dstale;
 };
+
+__device__ __forceinline__ int point_count(const HoughDev &h) { return h.n_dev ? *h.n_dev : h.n; }
 
 // ---- exact reference arithmetic (no FMA anywhere: the reference is built
 // without -march / -ffp-contract, lib/Makefile:19, CMakeLists.txt:5) -----------

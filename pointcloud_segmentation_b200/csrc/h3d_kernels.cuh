@@ -73,6 +73,7 @@ __device__ __forceinline__ void vote_items(const HoughDev &h, const int *__restr
                                            unsigned long long (*warp_best)[kVoteWarps], int cta, int n_cta) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned stride = h.plane_stride;
+  const int n = point_count(h);
   unsigned sink = 0;
 
   for (int item = cta; item * D < count; item += n_cta) {
@@ -89,13 +90,13 @@ __device__ __forceinline__ void vote_items(const HoughDev &h, const int *__restr
     const double kmagic = h.kmagic;
     const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells;
     const bool no_fast = !h.fast_ok;
-    for (int i0 = tid; i0 < h.n; i0 += U * kVoteThreads) {
+    for (int i0 = tid; i0 < n; i0 += U * kVoteThreads) {
       double x[U], y[U], z[U];
       int wi[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int i = i0 + u * kVoteThreads;
-        const bool in = i < h.n;
+        const bool in = i < n;
         wi[u] = in ? h.w[i] : 0;
         x[u] = in ? h.px[i] : 0.0; y[u] = in ? h.py[i] : 0.0; z[u] = in ? h.pz[i] : 0.0;
       }
@@ -221,16 +222,17 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
   const unsigned coef_sa = (unsigned)__cvta_generic_to_shared(&sh.coef[0][0][0]);
   // points are COMPACT here (every weight +1): slot p of thread t is point t + p*512, so all
   // slots below n/512 are full for every thread and only one slot is partially filled
+  const int n = point_count(h);
   double px[P], py[P], pz[P];
   unsigned live = 0;
 #pragma unroll
   for (int p = 0; p < P; ++p) {
     const int i = tid + p * kResThreads;
-    const bool ok = i < h.n;
+    const bool ok = i < n;
     px[p] = ok ? h.px[i] : 0.0; py[p] = ok ? h.py[i] : 0.0; pz[p] = ok ? h.pz[i] : 0.0;
     live |= ok ? (1u << p) : 0u;
   }
-  const int full_slots = h.n / kResThreads, used_slots = (h.n + kResThreads - 1) / kResThreads;
+  const int full_slots = n / kResThreads, used_slots = (n + kResThreads - 1) / kResThreads;
   const unsigned dummy_sa = planes_sa + 2u * G * stride * 4u;   // pad word: votes that must not count
   // thread g < G stages direction g of a group: list entry -> dir[], DirCoef -> coef[] (cp.async)
   auto stage = [&](int group, int slot, int dslot) {

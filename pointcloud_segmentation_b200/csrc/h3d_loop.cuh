@@ -1,0 +1,326 @@
+// h3d_loop.cuh -- the iterative loop on the device (general, multi-kernel form).
+//   hough3dlines()  wrap.h:172-259, 339-347  /  lib/hough3dlines.cpp:200-317
+// One stream, no host round trip inside the loop: every kernel reads the loop state from
+// device memory and returns at once when `done` is set, so the host can enqueue opt_nlines
+// iterations blindly.  Removed points are compacted away in order, like
+// PointCloud::removePoints (lib/pointcloud.cpp:109-128); the live count lives in LoopState.
+#ifndef H3D_LOOP_CUH_
+#define H3D_LOOP_CUH_
+
+#include "../../include/h3d.h"
+#include "h3d_fit.cuh"
+#include "h3d_kernels.cuh"
+
+namespace h3d {
+
+struct LoopState {
+  // configuration
+  double opt_dx;          // inlier radius (wrap.h:245,250)
+  double shift[3];        // X.shift (wrap.h:257)
+  int minvotes, nlines_max, max_iters;
+  unsigned pool_cap;
+  // running state
+  int done;
+  int n_alive;            // |X|
+  int n_lines, n_iters;
+  int ny;                 // |Y| of the current pass
+  int ny_prev;            // |Y| removed by the previous iteration (to un-vote)
+  unsigned pool_used;
+  int work_count;
+  unsigned long long fresh_key, best_key;
+  double a[3], b[3];      // current line
+  unsigned long long votes_cast;
+};
+
+struct LoopBuffers {
+  LoopState *st;
+  h3d_iter *iters;        // max_iters records
+  unsigned *pool;         // pool_cap original indices
+  unsigned *orig;         // original index of live point i (NaN/Inf strip, removals)
+  unsigned char *flags;   // inlier flags of the current pass
+  int *yidx;              // ordered inlier indices of the current pass
+  double *ypx, *ypy, *ypz;  // coordinates removed by the previous iteration (to un-vote)
+  double *px, *py, *pz;   // mutable aliases of the point arrays (compaction)
+  int *list;              // directions to rebuild
+  const double *dirs;     // 3*num_b direction vectors
+};
+
+// ---- start of an iteration: reset the reduction targets -------------------------------
+__global__ void loop_begin_kernel(LoopBuffers lb) {
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  s.fresh_key = 0; s.best_key = 0; s.work_count = 0;
+}
+
+// K4 with the removed set of the previous iteration
+__global__ void loop_unvote_kernel(const HoughDev h, LoopBuffers lb) {
+  const LoopState &s = *lb.st;
+  if (s.done || s.ny_prev == 0) return;
+  const int n_idx = s.ny_prev;
+  const int n_chunks = (n_idx + kUnvoteChunk - 1) / kUnvoteChunk;
+  const long long total = (long long)h.dir_count * n_chunks;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
+       t += (long long)gridDim.x * blockDim.x) {
+    const int l = (int)(t % h.dir_count), chunk = (int)(t / h.dir_count);
+    if (h.dstale[l] || h.dvotes[l] == 0) continue;
+    const unsigned target = h.dcell[l];
+    const FastCoef c = make_fast(h.coef[h.dir_begin + l], h.inv_s);
+    const int e0 = chunk * kUnvoteChunk, e1 = min(e0 + kUnvoteChunk, n_idx);
+    bool hit = false;
+    for (int e = e0; e < e1; ++e) {
+      hit |= vote_cell(h, c, h.dir_begin + l, lb.ypx[e], lb.ypy[e], lb.ypz[e]) == target;
+    }
+    if (hit) h.dstale[l] = 1;
+  }
+}
+
+__global__ void loop_argmax_kernel(const HoughDev h, LoopBuffers lb, int fresh_only) {
+  __shared__ unsigned long long scratch[32];
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  unsigned long long k = 0;
+  for (int l = blockIdx.x * blockDim.x + threadIdx.x; l < h.dir_count; l += gridDim.x * blockDim.x) {
+    if (fresh_only && h.dstale[l]) continue;
+    const unsigned long long kk = line_key(h.dvotes[l], h.dcell[l], h.dir_begin + l, h.num_b);
+    k = kk > k ? kk : k;
+  }
+  k = block_max_u64(k, scratch);
+  if (threadIdx.x == 0) atomicMax(fresh_only ? &s.fresh_key : &s.best_key, k);
+}
+
+__global__ void loop_worklist_kernel(const HoughDev h, LoopBuffers lb) {
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  const unsigned fvotes = (unsigned)(s.fresh_key >> 32);
+  for (int l = blockIdx.x * blockDim.x + threadIdx.x; l < h.dir_count; l += gridDim.x * blockDim.x)
+    if (h.dstale[l] && h.dvotes[l] >= fvotes) lb.list[atomicAdd(&s.work_count, 1)] = l;
+}
+
+// inverse map of Hough::getLine, lib/hough.cpp:114-132 (same conversions, no FMA)
+__device__ inline void line_from_index(const HoughDev &h, const double *dirs, unsigned index, double a[3],
+                                       double b[3]) {
+  const size_t num_x = (size_t)h.num_x, num_b = (size_t)h.num_b;
+  double x = (int)(index / (num_x * num_b));
+  index -= (int)x * num_x * num_b;
+  x = __dsub_rn(__dmul_rn(x, h.dx), h.max_x);
+  double y = (int)index / num_b;
+  index -= (int)y * num_b;
+  y = __dsub_rn(__dmul_rn(y, h.dx), h.max_x);
+  const double bx = dirs[3 * (size_t)index], by = dirs[3 * (size_t)index + 1], bz = dirs[3 * (size_t)index + 2];
+  b[0] = bx; b[1] = by; b[2] = bz;
+  const double opz = __dadd_rn(1.0, bz);
+  const double kxx = __ddiv_rn(__dmul_rn(bx, bx), opz), kxy = __ddiv_rn(__dmul_rn(bx, by), opz);
+  const double kyy = __ddiv_rn(__dmul_rn(by, by), opz);
+  a[0] = __dsub_rn(__dmul_rn(x, __dsub_rn(1.0, kxx)), __dmul_rn(y, kxy));
+  a[1] = __dadd_rn(__dmul_rn(x, -kxy), __dmul_rn(y, __dsub_rn(1.0, kyy)));
+  a[2] = __dsub_rn(__dmul_rn(-x, bx), __dmul_rn(y, by));
+}
+
+// Hough::getLine result of this iteration -> current line + record
+__global__ void loop_line_kernel(const HoughDev h, LoopBuffers lb) {
+  LoopState &s = *lb.st;
+  if (s.done || threadIdx.x != 0) return;
+  const unsigned votes = (unsigned)(s.best_key >> 32);
+  const unsigned flat = votes ? 0xFFFFFFFFu - (unsigned)s.best_key : 0u;
+  line_from_index(h, lb.dirs, flat, s.a, s.b);
+  s.votes_cast += (unsigned long long)s.work_count * (unsigned long long)s.n_alive;
+  if (s.n_iters < s.max_iters) {
+    h3d_iter &r = lb.iters[s.n_iters];
+    r.votes = votes; r.status = 0; r.argmax = flat;
+    for (int c = 0; c < 3; ++c) { r.a_raw[c] = s.a[c]; r.b_raw[c] = s.b[c]; }
+    r.rc1 = 0; r.rc2 = 0; r.n1 = 0; r.n2 = 0; r.off1 = s.pool_used; r.off2 = s.pool_used;
+    for (int c = 0; c < 3; ++c) { r.a1[c] = 0; r.b1[c] = 0; r.a2[c] = 0; r.b2[c] = 0; }
+  }
+}
+
+// K3a: inlier flags of the live points against the current line
+__global__ void loop_mask_kernel(const HoughDev h, LoopBuffers lb) {
+  const LoopState &s = *lb.st;
+  if (s.done) return;
+  const double a[3] = {s.a[0], s.a[1], s.a[2]}, b[3] = {s.b[0], s.b[1], s.b[2]};
+  const double dx = s.opt_dx;
+  const int n = s.n_alive;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    lb.flags[i] = point_near_line(h.px[i], h.py[i], h.pz[i], a, b, dx) ? 1 : 0;
+}
+
+// K3b: ordered compaction of the flags into yidx (one CTA walks the array in chunks), and the
+// inlier list of this pass into the pool (original numbering)
+__global__ void __launch_bounds__(1024, 1) loop_compact_kernel(const HoughDev h, LoopBuffers lb, int pass) {
+  __shared__ int warp_sum[32];
+  __shared__ int base_s;
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) base_s = 0;
+  __syncthreads();
+  const unsigned pool0 = s.pool_used;
+  const int n = s.n_alive;
+  for (int c0 = 0; c0 < n; c0 += 1024) {
+    const int i = c0 + tid;
+    const bool keep = i < n && lb.flags[i];
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, keep);
+    if (lane == 0) warp_sum[warp] = __popc(bal);
+    __syncthreads();
+    int off = base_s;
+    for (int q = 0; q < warp; ++q) off += warp_sum[q];
+    if (keep) {
+      const int pos = off + __popc(bal & ((1u << lane) - 1u));
+      lb.yidx[pos] = i;
+      if (pool0 + (unsigned)pos < s.pool_cap) lb.pool[pool0 + pos] = lb.orig[i];
+    }
+    __syncthreads();
+    if (tid == 0) { int t = 0; for (int q = 0; q < 32; ++q) t += warp_sum[q]; base_s += t; }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int ny = base_s;
+    s.ny = ny;
+    const unsigned used = pool0 + (unsigned)ny;
+    s.pool_used = used < s.pool_cap ? used : s.pool_cap;
+    if (s.n_iters < s.max_iters) {
+      h3d_iter &r = lb.iters[s.n_iters];
+      if (pass == 1) { r.n1 = (unsigned)ny; r.off1 = pool0; r.off2 = s.pool_used; }
+      else { r.n2 = (unsigned)ny; r.off2 = pool0; }
+    }
+  }
+}
+
+// ---- orthogonal_LSQ over an ordered index list (wrap.h:121-150) ------------------------------
+// 2 warps.  Phase A: warp 0 lanes 0..2 carry the sequential DOUBLE sums of the anchor
+// (meanValue, lib/pointcloud.cpp:29-38), warp 1 lanes 0..2 the sequential FLOAT sums of the
+// column means (wrap.h:137).  Phase B: warp 0 lanes 0..5 carry the six sequential float sums of
+// the centred scatter matrix (wrap.h:138).  32 points are staged per step.
+struct LsqOut {
+  double a[3], b[3], rc;
+};
+
+__device__ inline void lsq_block(const double *__restrict__ px, const double *__restrict__ py,
+                                 const double *__restrict__ pz, const int *__restrict__ idx, int n,
+                                 double (*sd)[33], float (*sf)[33], float *mean_s, LsqOut *out) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double acc_d = 0.0;
+  float acc_f = 0.0f;
+  for (int base = 0; base < n; base += 32) {
+    const int cnt = min(32, n - base);
+    if (lane < cnt) {
+      const int i = idx ? idx[base + lane] : base + lane;
+      const double x = px[i], y = py[i], z = pz[i];
+      if (warp == 0) { sd[0][lane] = x; sd[1][lane] = y; sd[2][lane] = z; }
+      else { sf[0][lane] = (float)x; sf[1][lane] = (float)y; sf[2][lane] = (float)z; }
+    }
+    __syncwarp();
+    if (lane < 3) {
+      if (warp == 0) for (int k = 0; k < cnt; ++k) acc_d = __dadd_rn(acc_d, sd[lane][k]);
+      else for (int k = 0; k < cnt; ++k) acc_f = __fadd_rn(acc_f, sf[lane][k]);
+    }
+    __syncwarp();
+  }
+  if (lane < 3) {
+    if (warp == 0) out->a[lane] = n > 0 ? __ddiv_rn(acc_d, (double)n) : acc_d;
+    else mean_s[lane] = __fdiv_rn(acc_f, (float)n);
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const float m0 = mean_s[0], m1 = mean_s[1], m2 = mean_s[2];
+    float acc = 0.0f;
+    for (int base = 0; base < n; base += 32) {
+      const int cnt = min(32, n - base);
+      if (lane < cnt) {
+        const int i = idx ? idx[base + lane] : base + lane;
+        const float cx = __fsub_rn((float)px[i], m0), cy = __fsub_rn((float)py[i], m1), cz = __fsub_rn((float)pz[i], m2);
+        sf[0][lane] = __fmul_rn(cx, cx); sf[1][lane] = __fmul_rn(cx, cy); sf[2][lane] = __fmul_rn(cx, cz);
+        sf[3][lane] = __fmul_rn(cy, cy); sf[4][lane] = __fmul_rn(cy, cz); sf[5][lane] = __fmul_rn(cz, cz);
+      }
+      __syncwarp();
+      if (lane < 6) for (int k = 0; k < cnt; ++k) acc = __fadd_rn(acc, sf[lane][k]);
+      __syncwarp();
+    }
+    if (lane < 6) mean_s[4 + lane] = acc;   // xx xy xz yy yz zz
+    __syncwarp();
+    if (lane == 0) {
+      const float *sc = mean_s + 4;
+      const float m[9] = {sc[0], sc[1], sc[2], sc[1], sc[3], sc[4], sc[2], sc[4], sc[5]};
+      const Eig3f e = eig3f(m);
+      out->b[0] = e.evecs[6]; out->b[1] = e.evecs[7]; out->b[2] = e.evecs[8];   // last column
+      out->rc = (double)e.evals[2];
+    }
+  }
+  __syncthreads();
+}
+
+// pass 1: first LSQ (break on rc == 0); pass 2: minvotes test, second LSQ, accept the line
+__global__ void __launch_bounds__(64, 1) loop_lsq_kernel(const HoughDev h, LoopBuffers lb, int pass) {
+  __shared__ double sd[3][33];
+  __shared__ float sf[6][33];
+  __shared__ float mean_s[12];
+  __shared__ LsqOut out;
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  const bool rec_ok = s.n_iters < s.max_iters;
+  h3d_iter *r = rec_ok ? &lb.iters[s.n_iters] : nullptr;
+  if (pass == 2 && (unsigned)s.ny < (unsigned)s.minvotes) {   // wrap.h:251-252
+    __syncthreads();
+    if (threadIdx.x == 0) { if (r) r->status = 2; s.n_iters++; s.done = 1; }
+    return;
+  }
+  lsq_block(h.px, h.py, h.pz, lb.yidx, s.ny, sd, sf, mean_s, &out);
+  if (threadIdx.x != 0) return;
+  for (int c = 0; c < 3; ++c) { s.a[c] = out.a[c]; s.b[c] = out.b[c]; }
+  if (pass == 1) {
+    if (r) { for (int c = 0; c < 3; ++c) { r->a1[c] = out.a[c]; r->b1[c] = out.b[c]; } r->rc1 = out.rc; }
+    if (out.rc == 0.0) { if (r) r->status = 1; s.n_iters++; s.done = 1; }   // wrap.h:248
+  } else {
+    if (r) { for (int c = 0; c < 3; ++c) { r->a2[c] = out.a[c]; r->b2[c] = out.b[c]; } r->rc2 = out.rc; }
+    if (out.rc == 0.0) { if (r) r->status = 3; s.n_iters++; s.done = 1; return; }   // wrap.h:255
+    if (r) for (int c = 0; c < 3; ++c) r->a2[c] = __dadd_rn(out.a[c], s.shift[c]);   // wrap.h:257
+    s.n_lines++;
+  }
+}
+
+// end of an accepted iteration: X.removePoints(Y) (wrap.h:339) as a stable in-place compaction
+// of the point arrays (the flags of pass 2 mark Y), keeping the removed coordinates for the
+// next iteration's un-vote; then the loop condition (wrap.h:341-342).  One CTA, chunked.
+__global__ void __launch_bounds__(1024, 1) loop_remove_kernel(LoopBuffers lb) {
+  __shared__ int warp_keep[32], warp_drop[32];
+  __shared__ int base_keep, base_drop;
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) { base_keep = 0; base_drop = 0; }
+  __syncthreads();
+  const int n = s.n_alive;
+  for (int c0 = 0; c0 < n; c0 += 1024) {
+    const int i = c0 + tid;
+    const bool in = i < n;
+    const bool drop = in && lb.flags[i];
+    const bool keep = in && !drop;
+    double x = 0, y = 0, z = 0;
+    unsigned o = 0;
+    if (in) { x = lb.px[i]; y = lb.py[i]; z = lb.pz[i]; o = lb.orig[i]; }
+    const unsigned bk = __ballot_sync(0xFFFFFFFFu, keep), bd = __ballot_sync(0xFFFFFFFFu, drop);
+    if (lane == 0) { warp_keep[warp] = __popc(bk); warp_drop[warp] = __popc(bd); }
+    __syncthreads();   // every thread of the chunk holds its point in registers from here on
+    int ok = base_keep, od = base_drop;
+    for (int q = 0; q < warp; ++q) { ok += warp_keep[q]; od += warp_drop[q]; }
+    const unsigned below = (1u << lane) - 1u;
+    if (keep) { const int p = ok + __popc(bk & below); lb.px[p] = x; lb.py[p] = y; lb.pz[p] = z; lb.orig[p] = o; }
+    if (drop) { const int p = od + __popc(bd & below); lb.ypx[p] = x; lb.ypy[p] = y; lb.ypz[p] = z; }
+    __syncthreads();
+    if (tid == 0) {
+      int tk = 0, td = 0;
+      for (int q = 0; q < 32; ++q) { tk += warp_keep[q]; td += warp_drop[q]; }
+      base_keep += tk; base_drop += td;
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    s.n_alive = base_keep;
+    s.ny_prev = base_drop;
+    s.n_iters++;
+    if (!((s.n_alive > 1) && (s.nlines_max == 0 || s.nlines_max > s.n_lines))) s.done = 1;
+  }
+}
+
+}  // namespace h3d
+#endif  // H3D_LOOP_CUH_

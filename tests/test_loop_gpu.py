@@ -1,0 +1,73 @@
+"""GPU parity of the whole iterative loop (h3d_hough3dlines) against the CPU oracle:
+votes, argmax cells and inlier sets bit-exact; fitted lines bit-exact against the oracle's
+canonical float pipeline (and therefore within the 1e-5 relative tolerance of north_star)."""
+import os
+
+import numpy as np
+import pytest
+
+from pointcloud_segmentation_b200 import synth
+
+pytestmark = pytest.mark.gpu
+DATA = os.path.join(os.path.dirname(__file__), "golden")
+REL_TOL = 1e-5   # north_star: anchor/direction within 1e-5 relative
+
+
+def _compare(got, want):
+    assert got.rc == want.rc
+    assert got.n_input == want.n_input
+    if want.rc != 0:
+        return
+    assert (got.num_x, got.num_b) == (want.num_x, want.num_b)
+    assert got.dx == want.dx and got.max_x == want.max_x and got.d == want.d
+    assert np.array_equal(got.shift, want.shift)
+    assert got.n_lines == want.n_lines
+    assert len(got.iters) == len(want.iters)
+    for k, (g, w) in enumerate(zip(got.iters, want.iters)):
+        ctx = f"iteration {k}"
+        assert (g["votes"], g["argmax"], g["status"]) == (w.votes, w.argmax, w.status), ctx
+        assert np.array_equal(g["a_raw"], w.a_raw) and np.array_equal(g["b_raw"], w.b_raw), ctx
+        assert np.array_equal(g["inliers1"], w.inliers1), ctx
+        assert np.array_equal(g["inliers2"], w.inliers2), ctx
+        for key in ("a1", "b1", "a2", "b2"):
+            gv, wv = g[key], getattr(w, key)
+            assert np.allclose(gv, wv, rtol=REL_TOL, atol=REL_TOL * max(1.0, np.abs(wv).max())), (ctx, key)
+            assert np.array_equal(gv, wv), (ctx, key, "not bit-identical to the canonical pipeline")
+        assert g["rc1"] == w.rc1 and g["rc2"] == w.rc2, ctx
+
+
+CASES = [
+    ("tower3k_g4", lambda: synth.steel_tower(3000, seed=1), 4, 0.0, 10, 12, 1),
+    ("tower10k_g4_cfg1", lambda: synth.steel_tower(10000, seed=1), 4, 0.0, 10, 12, 1),
+    ("tower2k_g5_ros", lambda: synth.steel_tower(2000, seed=4), 5, 0.08, 12, 8, 0),
+    ("tower1k_g3_unbounded", lambda: synth.steel_tower(1000, seed=6), 3, 0.0, 40, 0, 1),
+    ("random_g2", lambda: np.random.default_rng(3).standard_normal((400, 3)), 2, 0.0, 5, 6, 1),
+]
+
+
+@pytest.mark.parametrize("name,make,g,dx,minvotes,nlines,mode", CASES, ids=[c[0] for c in CASES])
+def test_loop_matches_oracle(h3d, oracle, name, make, g, dx, minvotes, nlines, mode):
+    pts = make()
+    want = oracle.hough3dlines(pts, g, dx, minvotes, nlines, mode=mode)
+    got = h3d.hough3dlines(pts, g, dx, minvotes, nlines, mode=mode, max_iters=len(want.iters) + 2)
+    _compare(got, want)
+
+
+def test_nan_inf_points_are_stripped(h3d, oracle):
+    pts = synth.steel_tower(1500, seed=8)
+    pts[::97, 0] = np.nan
+    pts[5::131, 2] = np.inf
+    want = oracle.hough3dlines(pts, 4, 0.0, 10, 5, mode=1)
+    got = h3d.hough3dlines(pts, 4, 0.0, 10, 5, mode=1)
+    _compare(got, want)
+
+
+@pytest.mark.parametrize("pts,dx", [
+    (np.zeros((10, 3)), 0.1),                                   # all points identical (wrap.h:202)
+    (np.array([[0.0, 0, 0], [1.0, 1, 1], [2.0, 0, 1]]), 50.0),  # dx too large (wrap.h:209)
+    (np.zeros((0, 3)), 0.1),                                    # empty cloud
+])
+def test_degenerate_inputs(h3d, oracle, pts, dx):
+    want = oracle.hough3dlines(pts, 2, dx, 2, 3, mode=0)
+    got = h3d.hough3dlines(pts, 2, dx, 2, 3, mode=0)
+    assert got.rc == want.rc == 1
