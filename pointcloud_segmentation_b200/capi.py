@@ -188,3 +188,85 @@ def hough3dlines(xyz, granularity, dx, minvotes, nlines, mode=0, max_iters=None)
                                  C.c_int(mode), iters, C.c_size_t(max_iters),
                                  pool.ctypes.data_as(C.POINTER(C.c_uint32)), C.c_size_t(pool_cap), C.byref(res)))
     return Trace(res, iters, pool)
+
+
+def prefilter(xyz_f32, window, leaf):
+    """cloudFiltering of node.cpp:386-421: PassThrough window + VoxelGrid centroids (f32)."""
+    a = np.ascontiguousarray(xyz_f32, dtype=np.float32)
+    a = a.reshape(-1, a.shape[-1] if a.ndim > 1 else 3)
+    n, stride = a.shape
+    out = np.empty((max(n, 1), 3), dtype=np.float32)
+    n_out = C.c_size_t()
+    win = (C.c_float * 6)(*[float(v) for v in window])
+    check(lib().h3d_prefilter(a.ctypes.data_as(C.POINTER(C.c_float)), C.c_size_t(n), C.c_size_t(stride), win,
+                              C.c_float(float(leaf)), out.ctypes.data_as(C.POINTER(C.c_float)),
+                              C.c_size_t(out.shape[0]), C.byref(n_out)))
+    return out[: n_out.value].copy()
+
+
+class Pipeline:
+    """Persistent per-frame pipeline: raw f32 frame -> K0 -> Hough loop (h3d_pipeline_*)."""
+
+    def __init__(self, granularity, window, leaf, opt_dx, minvotes, nlines, max_raw_points, prefilter=True,
+                 max_iters=0):
+        cfg = PipelineConfig()
+        cfg.granularity = granularity
+        cfg.window = (C.c_float * 6)(*[float(v) for v in window])
+        cfg.leaf = float(leaf)
+        cfg.opt_dx = float(opt_dx)
+        cfg.opt_minvotes, cfg.opt_nlines = int(minvotes), int(nlines)
+        cfg.max_raw_points = int(max_raw_points)
+        cfg.max_iters = int(max_iters)
+        cfg.prefilter = 1 if prefilter else 0
+        self._p = C.c_void_p()
+        check(lib().h3d_pipeline_create(C.byref(cfg), C.byref(self._p)))
+        self.max_iters = max_iters or ((nlines + 1) if nlines > 0 else 64)
+        self.iters = (Iter * self.max_iters)()
+        self.pool = np.zeros(2 * self.max_iters * int(max_raw_points), dtype=np.uint32)
+        self.res = Result()
+
+    def _run(self, fn, ptr, n, stride):
+        check(fn(self._p, ptr, C.c_size_t(n), C.c_size_t(stride), self.iters,
+                 self.pool.ctypes.data_as(C.POINTER(C.c_uint32)), C.c_size_t(self.pool.size), C.byref(self.res)))
+        return self.res
+
+    def run(self, raw_f32):
+        """Host frame in, host results out.  Returns the ctypes Result (no unpacking)."""
+        a = raw_f32 if (isinstance(raw_f32, np.ndarray) and raw_f32.dtype == np.float32 and raw_f32.flags.c_contiguous) \
+            else np.ascontiguousarray(raw_f32, dtype=np.float32)
+        n, stride = a.shape
+        return self._run(lib().h3d_pipeline_run, a.ctypes.data_as(C.POINTER(C.c_float)), n, stride)
+
+    def run_ptr(self, host_ptr, n, stride):
+        """Same with a raw host address (e.g. a pinned torch tensor's data_ptr())."""
+        return self._run(lib().h3d_pipeline_run, C.cast(C.c_void_p(host_ptr), C.POINTER(C.c_float)), n, stride)
+
+    def run_dev(self, dev_ptr, n, stride):
+        """Frame already resident in device memory (dev_ptr: integer device address)."""
+        return self._run(lib().h3d_pipeline_run_dev, C.cast(C.c_void_p(dev_ptr), C.POINTER(C.c_float)), n, stride)
+
+    def trace(self):
+        return Trace(self.res, self.iters, self.pool)
+
+    def filtered(self, cap):
+        out = np.empty((cap, 3), dtype=np.float32)
+        n_out = C.c_size_t()
+        check(lib().h3d_pipeline_filtered(self._p, out.ctypes.data_as(C.POINTER(C.c_float)), C.c_size_t(cap),
+                                          C.byref(n_out)))
+        return out[: min(cap, n_out.value)].copy(), n_out.value
+
+    def timing_us(self):
+        us = (C.c_float * 4)()
+        check(lib().h3d_pipeline_timing(self._p, us))
+        return list(us)
+
+    def close(self):
+        if self._p:
+            lib().h3d_pipeline_destroy(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -11,6 +11,7 @@
 #include <new>
 
 #include "h3d_loop.cuh"
+#include "h3d_prefilter.cuh"
 
 namespace h3d {
 
@@ -652,8 +653,9 @@ struct PrepOut {
 // One CTA walks the cloud in chunks.  T = double (stride 3) or float (sensor frame, any stride).
 template <typename T>
 __global__ void __launch_bounds__(1024, 1)
-prep_kernel(const T *__restrict__ in, int n, int stride, double *px, double *py, double *pz, unsigned *orig,
-            PrepOut *out) {
+prep_kernel(const T *__restrict__ in, int n_imm, const int *__restrict__ n_ptr, int stride, double *px, double *py,
+            double *pz, unsigned *orig, PrepOut *out) {
+  const int n = n_ptr ? *n_ptr : n_imm;
   __shared__ int warp_sum[32];
   __shared__ double red[6][32];
   __shared__ int base_s;
@@ -923,8 +925,238 @@ extern "C" int h3d_hough3dlines(const double *xyz, size_t n, int granularity, do
   cudaStream_t s = f.hg->stream;
   H3D_CUDA(cudaEventRecord(f.ev[0], s));
   if (n) H3D_CUDA(cudaMemcpyAsync(f.in_dev, xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
-  prep_kernel<double><<<1, 1024, 0, s>>>(static_cast<const double *>(f.in_dev), (int)n, 3, f.hg->px, f.hg->py,
-                                         f.hg->pz, f.orig, f.prep_dev);
+  prep_kernel<double><<<1, 1024, 0, s>>>(static_cast<const double *>(f.in_dev), (int)n, nullptr, 3, f.hg->px,
+                                         f.hg->py, f.hg->pz, f.orig, f.prep_dev);
   H3D_CUDA(cudaGetLastError());
   return frame_run(f, opt_minvotes, opt_nlines, opt_dx, mode, iters, max_iters, pool, pool_cap, res);
+}
+
+// =====================================================================================
+// K0 host side + the persistent pipeline (pre-filter + loop, buffers kept between frames)
+// =====================================================================================
+namespace {
+
+struct PrefilterCtx {
+  K0State *st = nullptr;
+  K0State *st_host = nullptr;   // pinned
+  int *count = nullptr, *start = nullptr, *slot = nullptr, *cursor = nullptr, *members = nullptr;
+  int2 *block_sums = nullptr;
+  size_t grid_cap = 0, member_cap = 0;
+  ~PrefilterCtx() {
+    cudaFree(st); cudaFreeHost(st_host); cudaFree(count); cudaFree(start); cudaFree(slot); cudaFree(cursor);
+    cudaFree(members); cudaFree(block_sums);
+  }
+};
+
+int prefilter_ensure(PrefilterCtx &p, size_t grid_cells, size_t n_points) {
+  if (!p.st) {
+    H3D_CUDA(cudaMalloc(&p.st, sizeof(K0State)));
+    H3D_CUDA(cudaMallocHost(&p.st_host, sizeof(K0State)));
+  }
+  if (grid_cells > p.grid_cap) {
+    cudaFree(p.count); cudaFree(p.start); cudaFree(p.slot); cudaFree(p.cursor); cudaFree(p.block_sums);
+    p.count = p.start = p.slot = p.cursor = nullptr; p.block_sums = nullptr; p.grid_cap = 0;
+    H3D_CUDA(cudaMalloc(&p.count, grid_cells * sizeof(int)));
+    H3D_CUDA(cudaMalloc(&p.start, grid_cells * sizeof(int)));
+    H3D_CUDA(cudaMalloc(&p.slot, grid_cells * sizeof(int)));
+    H3D_CUDA(cudaMalloc(&p.cursor, grid_cells * sizeof(int)));
+    const size_t nb = (grid_cells + kScanBlock * kScanItems - 1) / (kScanBlock * kScanItems);
+    H3D_CUDA(cudaMalloc(&p.block_sums, (nb + 1) * sizeof(int2)));
+    p.grid_cap = grid_cells;
+  }
+  if (n_points > p.member_cap) {
+    cudaFree(p.members); p.members = nullptr; p.member_cap = 0;
+    H3D_CUDA(cudaMalloc(&p.members, n_points * sizeof(int)));
+    p.member_cap = n_points;
+  }
+  return H3D_OK;
+}
+
+K0Window make_window(const float win[6]) {
+  K0Window w;
+  for (int c = 0; c < 3; ++c) { w.lo[c] = win[2 * c]; w.hi[c] = win[2 * c + 1]; }
+  return w;
+}
+
+// voxel-grid cells a cloud confined to `win` can need
+size_t window_grid_cells(const float win[6], float leaf) {
+  const float inv = 1.0f / leaf;
+  double cells = 1;
+  for (int c = 0; c < 3; ++c) {
+    const double lo = floor((double)(win[2 * c] * inv)), hi = floor((double)(win[2 * c + 1] * inv));
+    cells *= (hi - lo + 2.0);   // +1 cell of slack per axis for float rounding at the limits
+  }
+  if (!(cells >= 1.0) || cells > 268435456.0) return 0;
+  return (size_t)cells;
+}
+
+// phase 1: window + bbox + grid geometry;  phase 2: counting sort + centroids.  All on `s`.
+int prefilter_phase1(PrefilterCtx &p, const float *in_dev, int n, int stride, const K0Window &w, float leaf,
+                     int sm, cudaStream_t s) {
+  k0_init_kernel<<<1, 1, 0, s>>>(p.st);
+  if (n) k0_bbox_kernel<<<sm * 2, 256, 0, s>>>(in_dev, n, stride, w, p.st);
+  k0_setup_kernel<<<1, 1, 0, s>>>(p.st, leaf, (int)(p.grid_cap < 0x7FFFFFFF ? p.grid_cap : 0x7FFFFFFF));
+  H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+int prefilter_phase2(PrefilterCtx &p, const float *in_dev, int n, int stride, const K0Window &w, size_t grid_cells,
+                     float *out_dev, int out_cap, int out_stride, int sm, cudaStream_t s) {
+  if (n == 0 || grid_cells == 0) return H3D_OK;
+  const int nb = (int)((grid_cells + kScanBlock * kScanItems - 1) / (kScanBlock * kScanItems));
+  H3D_CUDA(cudaMemsetAsync(p.count, 0, grid_cells * sizeof(int), s));
+  k0_count_kernel<<<sm * 2, 256, 0, s>>>(in_dev, n, stride, w, p.st, p.count);
+  k0_scan_reduce_kernel<<<nb, kScanBlock, 0, s>>>(p.count, p.st, p.block_sums);
+  k0_scan_spine_kernel<<<1, 1024, 0, s>>>(p.block_sums, p.st);
+  k0_scan_apply_kernel<<<nb, kScanBlock, 0, s>>>(p.count, p.st, p.block_sums, p.start, p.slot, p.cursor);
+  k0_scatter_kernel<<<sm * 2, 256, 0, s>>>(in_dev, n, stride, w, p.st, p.start, p.cursor, p.members);
+  k0_centroid_kernel<<<(unsigned)((grid_cells + 255) / 256), 256, 0, s>>>(in_dev, stride, p.st, p.count, p.start,
+                                                                          p.slot, p.members, out_dev, out_cap,
+                                                                          out_stride);
+  H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+
+}  // namespace
+
+extern "C" int h3d_prefilter(const float *xyz_in, size_t n, size_t stride, const float win[6], float leaf,
+                             float *out_xyz, size_t cap, size_t *n_out) {
+  if ((!xyz_in && n) || !win || !n_out || stride < 3 || !(leaf > 0.0f) || (!out_xyz && cap))
+    return fail(H3D_ERR_ARG, "bad argument");
+  if (n > 0x7FFFFFF0u) return fail(H3D_ERR_RANGE, "too many points");
+  *n_out = 0;
+  if (n == 0) return H3D_OK;
+  DeviceFacts dev;
+  H3D_TRY(device_facts(&dev));
+  static thread_local PrefilterCtx ctx;
+  PrefilterCtx &p = ctx;
+  cudaStream_t s = nullptr;   // legacy default stream: this entry point is synchronous
+  float *in_dev = nullptr, *out_dev = nullptr;
+  H3D_CUDA(cudaMalloc(&in_dev, n * stride * sizeof(float)));
+  int rc = H3D_OK;
+  do {
+    if (cudaMemcpyAsync(in_dev, xyz_in, n * stride * sizeof(float), cudaMemcpyHostToDevice, s) != cudaSuccess) { rc = fail(H3D_ERR_CUDA, "upload failed"); break; }
+    if ((rc = prefilter_ensure(p, 1, n)) != H3D_OK) break;
+    const K0Window w = make_window(win);
+    // the grid is sized from the actual bounding box: geometry first, with an unlimited capacity
+    const size_t saved = p.grid_cap;
+    p.grid_cap = 0x7FFFFFFF;
+    rc = prefilter_phase1(p, in_dev, (int)n, (int)stride, w, leaf, dev.sm_count, s);
+    p.grid_cap = saved;
+    if (rc != H3D_OK) break;
+    if (cudaMemcpyAsync(p.st_host, p.st, sizeof(K0State), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+        cudaStreamSynchronize(s) != cudaSuccess) { rc = fail(H3D_ERR_CUDA, "pre-filter geometry read-back failed"); break; }
+    if (p.st_host->overflow) { rc = fail(H3D_ERR_RANGE, "voxel grid index would overflow int32 (leaf too small)"); break; }
+    const size_t cells = (size_t)p.st_host->n_vox;
+    if (cells == 0) break;   // nothing inside the window
+    if (cells > 268435456u) { rc = fail(H3D_ERR_RANGE, "voxel grid larger than 2^28 cells"); break; }
+    if ((rc = prefilter_ensure(p, cells, n)) != H3D_OK) break;
+    const size_t out_cap = cap < (size_t)p.st_host->n_in_window ? cap : (size_t)p.st_host->n_in_window;
+    if (out_cap && cudaMalloc(&out_dev, out_cap * 3 * sizeof(float)) != cudaSuccess) { rc = fail(H3D_ERR_NOMEM, "output allocation failed"); break; }
+    if ((rc = prefilter_phase2(p, in_dev, (int)n, (int)stride, w, cells, out_dev, (int)out_cap, 3, dev.sm_count, s)) != H3D_OK) break;
+    if (cudaMemcpyAsync(p.st_host, p.st, sizeof(K0State), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+        cudaStreamSynchronize(s) != cudaSuccess) { rc = fail(H3D_ERR_CUDA, "pre-filter failed"); break; }
+    *n_out = (size_t)p.st_host->n_out;
+    const size_t n_copy = *n_out < out_cap ? *n_out : out_cap;
+    if (n_copy && cudaMemcpy(out_xyz, out_dev, n_copy * 3 * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess) rc = fail(H3D_ERR_CUDA, "download failed");
+  } while (0);
+  cudaFree(in_dev); cudaFree(out_dev);
+  return rc;
+}
+
+struct h3d_pipeline {
+  h3d_pipeline_config cfg;
+  FrameCtx f;
+  PrefilterCtx pf;
+  K0Window win;
+  size_t grid_cells = 0;
+  float *raw_dev = nullptr;     // max_raw_points * 4 floats
+  float *filt_dev = nullptr;    // max_raw_points * 3 floats
+  size_t raw_cap_floats = 0;
+};
+
+extern "C" int h3d_pipeline_create(const h3d_pipeline_config *cfg, h3d_pipeline **out) {
+  if (!cfg || !out || cfg->granularity < 0 || cfg->granularity > 8 || cfg->max_raw_points == 0 ||
+      cfg->max_raw_points > 0x7FFFFFF0u)
+    return fail(H3D_ERR_ARG, "bad pipeline configuration");
+  h3d_pipeline *p = new (std::nothrow) h3d_pipeline();
+  if (!p) return fail(H3D_ERR_NOMEM, "host allocation failed");
+  std::unique_ptr<h3d_pipeline, void (*)(h3d_pipeline *)> guard(p, h3d_pipeline_destroy);
+  p->cfg = *cfg;
+  const size_t n = cfg->max_raw_points;
+  const size_t max_iters = cfg->max_iters ? cfg->max_iters : (size_t)(cfg->opt_nlines > 0 ? cfg->opt_nlines + 1 : 64);
+  p->cfg.max_iters = max_iters;
+  H3D_TRY(frame_ensure(p->f, (unsigned)cfg->granularity, n, 0, max_iters, 2 * n * max_iters));
+  if (cfg->prefilter) {
+    if (!(cfg->leaf > 0.0f)) return fail(H3D_ERR_ARG, "leaf must be positive");
+    p->win = make_window(cfg->window);
+    p->grid_cells = window_grid_cells(cfg->window, cfg->leaf);
+    if (p->grid_cells == 0) return fail(H3D_ERR_RANGE, "window / leaf give a voxel grid beyond 2^28 cells");
+    H3D_TRY(prefilter_ensure(p->pf, p->grid_cells, n));
+    H3D_CUDA(cudaMalloc(&p->filt_dev, n * 3 * sizeof(float)));
+  }
+  p->raw_cap_floats = n * 8;
+  H3D_CUDA(cudaMalloc(&p->raw_dev, p->raw_cap_floats * sizeof(float)));
+  *out = guard.release();
+  return H3D_OK;
+}
+
+extern "C" void h3d_pipeline_destroy(h3d_pipeline *p) {
+  if (!p) return;
+  if (p->f.hg) cudaStreamSynchronize(p->f.hg->stream);
+  cudaFree(p->raw_dev); cudaFree(p->filt_dev);
+  delete p;
+}
+
+extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
+                                    uint32_t *pool, size_t pool_cap, h3d_result *res) {
+  if (!p || !res || (!raw_dev && n) || stride < 3) return fail(H3D_ERR_ARG, "bad argument");
+  if (n > p->cfg.max_raw_points) return fail(H3D_ERR_ARG, "frame larger than max_raw_points");
+  memset(res, 0, sizeof *res);
+  FrameCtx &f = p->f;
+  h3d_hough *h = f.hg;
+  cudaStream_t s = h->stream;
+  H3D_CUDA(cudaEventRecord(f.ev[0], s));
+  if (p->cfg.prefilter) {
+    H3D_TRY(prefilter_phase1(p->pf, raw_dev, (int)n, (int)stride, p->win, p->cfg.leaf, h->dev.sm_count, s));
+    H3D_TRY(prefilter_phase2(p->pf, raw_dev, (int)n, (int)stride, p->win, p->grid_cells, p->filt_dev, (int)p->cfg.max_raw_points, 3, h->dev.sm_count, s));
+    // wrap.h:175-189: float -> double widening of the filtered cloud (+ NaN/Inf strip, bbox)
+    prep_kernel<float><<<1, 1024, 0, s>>>(p->filt_dev, 0, &p->pf.st->n_out, 3, h->px, h->py, h->pz, f.orig, f.prep_dev);
+  } else {
+    prep_kernel<float><<<1, 1024, 0, s>>>(raw_dev, (int)n, nullptr, (int)stride, h->px, h->py, h->pz, f.orig, f.prep_dev);
+  }
+  H3D_CUDA(cudaGetLastError());
+  const int rc = frame_run(f, p->cfg.opt_minvotes, p->cfg.opt_nlines, p->cfg.opt_dx, 0, iters, p->cfg.max_iters, pool,
+                           pool_cap, res);
+  if (rc == H3D_OK) {
+    for (int k = 0; k < 3; ++k) cudaEventElapsedTime(&f.us[k], f.ev[k], f.ev[k + 1]);
+    cudaEventElapsedTime(&f.us[3], f.ev[0], f.ev[3]);
+    for (auto &u : f.us) u *= 1000.0f;
+  }
+  return rc;
+}
+
+extern "C" int h3d_pipeline_run(h3d_pipeline *p, const float *raw, size_t n, size_t stride, h3d_iter *iters,
+                                uint32_t *pool, size_t pool_cap, h3d_result *res) {
+  if (!p || (!raw && n) || stride < 3) return fail(H3D_ERR_ARG, "bad argument");
+  if (n * stride > p->raw_cap_floats) return fail(H3D_ERR_ARG, "frame larger than the pipeline's raw buffer");
+  if (n) H3D_CUDA(cudaMemcpyAsync(p->raw_dev, raw, n * stride * sizeof(float), cudaMemcpyHostToDevice, p->f.hg->stream));
+  return h3d_pipeline_run_dev(p, p->raw_dev, n, stride, iters, pool, pool_cap, res);
+}
+
+extern "C" int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n_out) {
+  if (!p || !n_out) return fail(H3D_ERR_ARG, "bad argument");
+  if (!p->cfg.prefilter) return fail(H3D_ERR_ARG, "pipeline has no pre-filter stage");
+  cudaStream_t s = p->f.hg->stream;
+  H3D_CUDA(cudaMemcpyAsync(p->pf.st_host, p->pf.st, sizeof(K0State), cudaMemcpyDeviceToHost, s));
+  H3D_CUDA(cudaStreamSynchronize(s));
+  *n_out = (size_t)p->pf.st_host->n_out;
+  const size_t n_copy = *n_out < cap ? *n_out : cap;
+  if (n_copy && out_xyz) H3D_CUDA(cudaMemcpy(out_xyz, p->filt_dev, n_copy * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+  return H3D_OK;
+}
+
+extern "C" int h3d_pipeline_timing(h3d_pipeline *p, float us[4]) {
+  if (!p || !us) return fail(H3D_ERR_ARG, "bad argument");
+  for (int k = 0; k < 4; ++k) us[k] = p->f.us[k];
+  return H3D_OK;
 }
