@@ -270,3 +270,50 @@ class Pipeline:
             self.close()
         except Exception:
             pass
+
+
+# ---- PointCloud entry points (lib/pointcloud.cpp) on host arrays --------------------------
+def min_max(xyz):
+    a, p, n = _pts(xyz)
+    mn, mx = (C.c_double * 3)(), (C.c_double * 3)()
+    check(lib().h3d_min_max(p, n, mn, mx))
+    return np.array(mn[:]), np.array(mx[:])
+
+
+def shift_to_origin(xyz, shift=None):
+    a = np.array(xyz, dtype=np.float64).reshape(-1, 3)
+    sh = _d3(shift if shift is not None else (0.0, 0.0, 0.0))
+    check(lib().h3d_shift_to_origin(a.ctypes.data_as(C.POINTER(C.c_double)), C.c_size_t(a.shape[0]), sh))
+    return a, np.array(sh[:])
+
+
+def mean_value(xyz):
+    a, p, n = _pts(xyz)
+    m = (C.c_double * 3)()
+    check(lib().h3d_mean_value(p, n, m))
+    return np.array(m[:])
+
+
+def points_close_to_line(xyz, a_, b_, dx):
+    a, p, n = _pts(xyz)
+    idx = np.empty(max(a.shape[0], 1), dtype=np.uint32)
+    n_out = C.c_size_t()
+    check(lib().h3d_points_close_to_line(p, n, _d3(a_), _d3(b_), C.c_double(dx),
+                                         idx.ctypes.data_as(C.POINTER(C.c_uint32)), C.byref(n_out)))
+    return idx[: n_out.value].copy()
+
+
+def remove_points(x, y):
+    xa = np.array(x, dtype=np.float64).reshape(-1, 3)
+    ya, yp, ny = _pts(y)
+    n_out = C.c_size_t()
+    check(lib().h3d_remove_points(xa.ctypes.data_as(C.POINTER(C.c_double)), C.c_size_t(xa.shape[0]), yp, ny,
+                                  C.byref(n_out)))
+    return xa[: n_out.value].copy()
+
+
+def orthogonal_lsq(xyz):
+    a, p, n = _pts(xyz)
+    aa, bb, rc = (C.c_double * 3)(), (C.c_double * 3)(), C.c_double()
+    check(lib().h3d_orthogonal_lsq(p, n, aa, bb, C.byref(rc)))
+    return rc.value, np.array(aa[:]), np.array(bb[:])

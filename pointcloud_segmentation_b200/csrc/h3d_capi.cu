@@ -1160,3 +1160,251 @@ extern "C" int h3d_pipeline_timing(h3d_pipeline *p, float us[4]) {
   for (int k = 0; k < 4; ++k) us[k] = p->f.us[k];
   return H3D_OK;
 }
+
+// =====================================================================================
+// PointCloud entry points on host arrays (lib/pointcloud.cpp:18-128, wrap.h:121-150): each is
+// upload -> kernel -> download; the fused loop above never goes through them.
+// =====================================================================================
+namespace {
+
+// scratch arena of one calling thread
+struct Scratch {
+  void *dev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t bytes[6] = {0, 0, 0, 0, 0, 0};
+  ~Scratch() { for (auto p : dev) cudaFree(p); }
+};
+int scratch_get(Scratch &s, int slot, size_t bytes, void **out) {
+  if (bytes > s.bytes[slot]) {
+    cudaFree(s.dev[slot]); s.dev[slot] = nullptr; s.bytes[slot] = 0;
+    size_t cap = 1 << 16;
+    while (cap < bytes) cap *= 2;
+    H3D_CUDA(cudaMalloc(&s.dev[slot], cap));
+    s.bytes[slot] = cap;
+  }
+  *out = s.dev[slot];
+  return H3D_OK;
+}
+Scratch &scratch() { static thread_local Scratch s; return s; }
+
+}  // namespace
+
+// getMinMax3D on an AoS cloud (one CTA; min/max are order independent)
+__global__ void __launch_bounds__(1024, 1) aos_minmax_kernel(const double *__restrict__ p, int n, double *out6) {
+  __shared__ double red[6][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int i = threadIdx.x; i < n; i += 1024)
+    for (int c = 0; c < 3; ++c) { const double v = p[3 * (size_t)i + c]; mn[c] = fmin(mn[c], v); mx[c] = fmax(mx[c], v); }
+  for (int c = 0; c < 3; ++c) {
+    for (int o = 16; o; o >>= 1) {
+      mn[c] = fmin(mn[c], __shfl_xor_sync(0xFFFFFFFFu, mn[c], o));
+      mx[c] = fmax(mx[c], __shfl_xor_sync(0xFFFFFFFFu, mx[c], o));
+    }
+    if (lane == 0) { red[c][warp] = mn[c]; red[3 + c][warp] = mx[c]; }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    for (int c = 0; c < 3; ++c) {
+      double a = red[c][lane], b = red[3 + c][lane];
+      for (int o = 16; o; o >>= 1) {
+        a = fmin(a, __shfl_xor_sync(0xFFFFFFFFu, a, o));
+        b = fmax(b, __shfl_xor_sync(0xFFFFFFFFu, b, o));
+      }
+      if (lane == 0) { out6[c] = n ? a : 0.0; out6[3 + c] = n ? b : 0.0; }
+    }
+  }
+}
+
+__global__ void aos_shift_kernel(double *p, int n, double sx, double sy, double sz) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    p[3 * (size_t)i] = __dsub_rn(p[3 * (size_t)i], sx);
+    p[3 * (size_t)i + 1] = __dsub_rn(p[3 * (size_t)i + 1], sy);
+    p[3 * (size_t)i + 2] = __dsub_rn(p[3 * (size_t)i + 2], sz);
+  }
+}
+
+__global__ void aos_to_soa_kernel(const double *__restrict__ p, int n, double *px, double *py, double *pz) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    px[i] = p[3 * (size_t)i]; py[i] = p[3 * (size_t)i + 1]; pz[i] = p[3 * (size_t)i + 2];
+  }
+}
+
+__global__ void __launch_bounds__(64, 1) soa_lsq_kernel(const double *px, const double *py, const double *pz, int n,
+                                                        LsqOut *out) {
+  __shared__ double sd[3][33];
+  __shared__ float sf[6][33];
+  __shared__ float mean_s[12];
+  __shared__ LsqOut o;
+  lsq_block(px, py, pz, nullptr, n, sd, sf, mean_s, &o);
+  if (threadIdx.x == 0) *out = o;
+}
+
+__global__ void aos_mask_kernel(const double *__restrict__ p, int n, double a0, double a1, double a2, double b0,
+                                double b1, double b2, double dx, unsigned char *flags) {
+  const double a[3] = {a0, a1, a2}, b[3] = {b0, b1, b2};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    flags[i] = point_near_line(p[3 * (size_t)i], p[3 * (size_t)i + 1], p[3 * (size_t)i + 2], a, b, dx) ? 1 : 0;
+}
+
+// ordered compaction of flagged indices (one CTA, chunked); count -> *n_out
+__global__ void __launch_bounds__(1024, 1) flags_to_index_kernel(const unsigned char *__restrict__ flags, int n,
+                                                                 unsigned *idx, int *n_out) {
+  __shared__ int warp_sum[32];
+  __shared__ int base_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) base_s = 0;
+  __syncthreads();
+  for (int c0 = 0; c0 < n; c0 += 1024) {
+    const int i = c0 + tid;
+    const bool keep = i < n && flags[i];
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, keep);
+    if (lane == 0) warp_sum[warp] = __popc(bal);
+    __syncthreads();
+    int off = base_s;
+    for (int q = 0; q < warp; ++q) off += warp_sum[q];
+    if (keep) idx[off + __popc(bal & ((1u << lane) - 1u))] = (unsigned)i;
+    __syncthreads();
+    if (tid == 0) { int t = 0; for (int q = 0; q < 32; ++q) t += warp_sum[q]; base_s += t; }
+    __syncthreads();
+  }
+  if (tid == 0) *n_out = base_s;
+}
+
+// PointCloud::removePoints (lib/pointcloud.cpp:109-128): greedy ordered matching with exact ==.
+// One warp: for the current y_j it scans X 32 points at a time for the first equal point; every
+// x passed on the way is kept and, since exactly j points were dropped before it, lands at
+// i - j (in place: the target was consumed earlier).
+__global__ void __launch_bounds__(32, 1) remove_points_kernel(double *x, int nx, const double *__restrict__ y, int ny,
+                                                              int *n_out) {
+  const int lane = threadIdx.x;
+  int i = 0, j = 0;
+  while (i < nx && j < ny) {
+    const double y0 = y[3 * (size_t)j], y1 = y[3 * (size_t)j + 1], y2 = y[3 * (size_t)j + 2];
+    const int k = i + lane;
+    double v0 = 0, v1 = 0, v2 = 0;
+    bool eq = false;
+    if (k < nx) {
+      v0 = x[3 * (size_t)k]; v1 = x[3 * (size_t)k + 1]; v2 = x[3 * (size_t)k + 2];
+      eq = (v0 == y0) && (v1 == y1) && (v2 == y2);
+    }
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, eq);
+    const int first = m ? __ffs(m) - 1 : 32;          // lanes below `first` are kept
+    __syncwarp();
+    if (k < nx && lane < first) { const size_t d = (size_t)(k - j); x[3 * d] = v0; x[3 * d + 1] = v1; x[3 * d + 2] = v2; }
+    __syncwarp();
+    if (m) { i += first + 1; ++j; } else { i += 32; }
+  }
+  for (int k = i + lane; k < nx; k += 32) {           // rest after the end of Y, in order
+    const double v0 = x[3 * (size_t)k], v1 = x[3 * (size_t)k + 1], v2 = x[3 * (size_t)k + 2];
+    __syncwarp();
+    const size_t d = (size_t)(k - j);
+    x[3 * d] = v0; x[3 * d + 1] = v1; x[3 * d + 2] = v2;
+    __syncwarp();
+  }
+  if (lane == 0) *n_out = nx - j;
+}
+
+static int upload_aos(const double *xyz, size_t n, int slot, double **dev) {
+  void *p = nullptr;
+  H3D_TRY(scratch_get(scratch(), slot, (n ? n : 1) * 3 * sizeof(double), &p));
+  if (n) H3D_CUDA(cudaMemcpy(p, xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  *dev = static_cast<double *>(p);
+  return H3D_OK;
+}
+
+extern "C" int h3d_min_max(const double *xyz, size_t n, double mn[3], double mx[3]) {
+  if ((!xyz && n) || !mn || !mx || n > 0x7FFFFFF0u) return fail(H3D_ERR_ARG, "bad argument");
+  double *p = nullptr; void *o = nullptr;
+  H3D_TRY(upload_aos(xyz, n, 0, &p));
+  H3D_TRY(scratch_get(scratch(), 5, 64, &o));
+  aos_minmax_kernel<<<1, 1024>>>(p, (int)n, static_cast<double *>(o));
+  double h[6];
+  H3D_CUDA(cudaMemcpy(h, o, sizeof h, cudaMemcpyDeviceToHost));
+  for (int c = 0; c < 3; ++c) { mn[c] = h[c]; mx[c] = h[3 + c]; }
+  return H3D_OK;
+}
+
+extern "C" int h3d_shift_to_origin(double *xyz, size_t n, double shift[3]) {
+  if ((!xyz && n) || !shift || n > 0x7FFFFFF0u) return fail(H3D_ERR_ARG, "bad argument");
+  double *p = nullptr; void *o = nullptr;
+  H3D_TRY(upload_aos(xyz, n, 0, &p));
+  H3D_TRY(scratch_get(scratch(), 5, 64, &o));
+  aos_minmax_kernel<<<1, 1024>>>(p, (int)n, static_cast<double *>(o));
+  double h[6];
+  H3D_CUDA(cudaMemcpy(h, o, sizeof h, cudaMemcpyDeviceToHost));
+  double ns[3];
+  for (int c = 0; c < 3; ++c) ns[c] = (h[c] + h[3 + c]) / 2.0;   // (p1 + p2) / 2.0
+  if (n) {
+    aos_shift_kernel<<<(unsigned)((n + 255) / 256), 256>>>(p, (int)n, ns[0], ns[1], ns[2]);
+    H3D_CUDA(cudaMemcpy(xyz, p, n * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+  for (int c = 0; c < 3; ++c) shift[c] = shift[c] + ns[c];
+  return H3D_OK;
+}
+
+static int lsq_on_host_cloud(const double *xyz, size_t n, LsqOut *res) {
+  double *p = nullptr; void *soa = nullptr, *o = nullptr;
+  H3D_TRY(upload_aos(xyz, n, 0, &p));
+  H3D_TRY(scratch_get(scratch(), 1, (n ? n : 1) * 3 * sizeof(double), &soa));
+  H3D_TRY(scratch_get(scratch(), 5, sizeof(LsqOut), &o));
+  double *px = static_cast<double *>(soa), *py = px + n, *pz = py + n;
+  if (n) aos_to_soa_kernel<<<(unsigned)((n + 255) / 256), 256>>>(p, (int)n, px, py, pz);
+  soa_lsq_kernel<<<1, 64>>>(px, py, pz, (int)n, static_cast<LsqOut *>(o));
+  H3D_CUDA(cudaMemcpy(res, o, sizeof(LsqOut), cudaMemcpyDeviceToHost));
+  return H3D_OK;
+}
+
+extern "C" int h3d_mean_value(const double *xyz, size_t n, double mean[3]) {
+  if ((!xyz && n) || !mean || n > 0x7FFFFFF0u) return fail(H3D_ERR_ARG, "bad argument");
+  LsqOut r;
+  H3D_TRY(lsq_on_host_cloud(xyz, n, &r));
+  for (int c = 0; c < 3; ++c) mean[c] = r.a[c];
+  return H3D_OK;
+}
+
+extern "C" int h3d_orthogonal_lsq(const double *xyz, size_t n, double a[3], double b[3], double *rc) {
+  if ((!xyz && n) || !a || !b || !rc || n > 0x7FFFFFF0u) return fail(H3D_ERR_ARG, "bad argument");
+  LsqOut r;
+  H3D_TRY(lsq_on_host_cloud(xyz, n, &r));
+  for (int c = 0; c < 3; ++c) { a[c] = r.a[c]; b[c] = r.b[c]; }
+  *rc = r.rc;
+  return H3D_OK;
+}
+
+extern "C" int h3d_points_close_to_line(const double *xyz, size_t n, const double a[3], const double b[3], double dx,
+                                        uint32_t *idx_out, size_t *n_out) {
+  if ((!xyz && n) || !a || !b || !n_out || (!idx_out && n) || n > 0x7FFFFFF0u) return fail(H3D_ERR_ARG, "bad argument");
+  *n_out = 0;
+  if (n == 0) return H3D_OK;
+  double *p = nullptr; void *flags = nullptr, *idx = nullptr, *cnt = nullptr;
+  H3D_TRY(upload_aos(xyz, n, 0, &p));
+  H3D_TRY(scratch_get(scratch(), 2, n, &flags));
+  H3D_TRY(scratch_get(scratch(), 3, n * sizeof(unsigned), &idx));
+  H3D_TRY(scratch_get(scratch(), 5, 64, &cnt));
+  aos_mask_kernel<<<(unsigned)((n + 255) / 256), 256>>>(p, (int)n, a[0], a[1], a[2], b[0], b[1], b[2], dx,
+                                                        static_cast<unsigned char *>(flags));
+  flags_to_index_kernel<<<1, 1024>>>(static_cast<unsigned char *>(flags), (int)n, static_cast<unsigned *>(idx),
+                                     static_cast<int *>(cnt));
+  int k = 0;
+  H3D_CUDA(cudaMemcpy(&k, cnt, sizeof k, cudaMemcpyDeviceToHost));
+  if (k) H3D_CUDA(cudaMemcpy(idx_out, idx, (size_t)k * sizeof(unsigned), cudaMemcpyDeviceToHost));
+  *n_out = (size_t)k;
+  return H3D_OK;
+}
+
+extern "C" int h3d_remove_points(double *x_xyz, size_t nx, const double *y_xyz, size_t ny, size_t *n_out) {
+  if ((!x_xyz && nx) || (!y_xyz && ny) || !n_out || nx > 0x7FFFFFF0u || ny > 0x7FFFFFF0u)
+    return fail(H3D_ERR_ARG, "bad argument");
+  *n_out = nx;
+  if (ny == 0 || nx == 0) return H3D_OK;   // lib/pointcloud.cpp:111
+  double *x = nullptr, *y = nullptr; void *cnt = nullptr;
+  H3D_TRY(upload_aos(x_xyz, nx, 0, &x));
+  H3D_TRY(upload_aos(y_xyz, ny, 1, &y));
+  H3D_TRY(scratch_get(scratch(), 5, 64, &cnt));
+  remove_points_kernel<<<1, 32>>>(x, (int)nx, y, (int)ny, static_cast<int *>(cnt));
+  int k = 0;
+  H3D_CUDA(cudaMemcpy(&k, cnt, sizeof k, cudaMemcpyDeviceToHost));
+  if (k) H3D_CUDA(cudaMemcpy(x_xyz, x, (size_t)k * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  *n_out = (size_t)k;
+  return H3D_OK;
+}
