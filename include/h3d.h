@@ -40,6 +40,8 @@ enum {
 };
 
 const char *h3d_last_error(void);
+/* kernels launched by the library so far in this process (bench.py: gpu_launches) */
+unsigned long long h3d_launch_count(void);
 /* library / device facts: sm count, compute capability major*10+minor */
 int h3d_device_info(int *sm_count, int *cc, size_t *smem_per_block_optin);
 
@@ -167,7 +169,9 @@ int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_t n, size_t
 /* filtered cloud of the last frame (f32 xyz), for inspection */
 int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n_out);
 /* per-phase device times of the last frame, microseconds:
- * [0] pre-filter, [1] first vote (Hough::add), [2] loop, [3] total */
+ * [0] pre-filter + widening/bbox, [1] the first vote kernel alone (Hough::add),
+ * [2] loop + result copies, [3] whole frame incl. the host<->device copies of
+ * h3d_pipeline_run.  All zero when the frame ended early (rc != 0). */
 int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
 
 /* ---- measurement hooks (bench.py): raw kernel timings with CUDA events ----- */

@@ -16,6 +16,8 @@
 namespace h3d {
 
 static thread_local std::string g_error;
+static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py: gpu_launches)
+static inline void note_launches(unsigned n) { g_launches += n; }
 void set_error(const std::string &msg) { g_error = msg; }
 
 #define H3D_CUDA(call)                                                                       \
@@ -130,6 +132,7 @@ struct h3d_hough {
 };
 
 extern "C" const char *h3d_last_error(void) { return g_error.c_str(); }
+extern "C" unsigned long long h3d_launch_count(void) { return g_launches; }
 
 extern "C" int h3d_device_info(int *sm_count, int *cc, size_t *smem_optin) {
   DeviceFacts f;
@@ -303,6 +306,7 @@ static int launch_vote_t(h3d_hough *h, const int *list, const int *count_ptr, in
     configured = dyn_max;
   }
   vote_kernel<D, ABLATE><<<grid, kVoteThreads, smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
+  note_launches(1);
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;
 }
@@ -321,6 +325,7 @@ static int launch_resident_t(h3d_hough *h, const int *list, const int *count_ptr
   }
   vote_resident_kernel<P, ABLATE><<<h->dev.sm_count, kResThreads, smem, h->stream>>>(h->d, list, count_ptr,
                                                                                     count_imm);
+  note_launches(1);
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;
 }
@@ -735,8 +740,9 @@ struct FrameCtx {
   PrepOut *prep_dev = nullptr;
   LoopState *st_host = nullptr;   // pinned
   PrepOut *prep_host = nullptr;   // pinned
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // start, prep done, first vote done, end, first vote start
   float us[4] = {0, 0, 0, 0};
+  bool timed = false;   // the last frame ran to the end (all events recorded)
 
   ~FrameCtx() { release(); }
   void release() {
@@ -820,6 +826,7 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
   loop_compact_kernel<<<1, 1024, 0, s>>>(hd, lb, 2);
   loop_lsq_kernel<<<1, 64, 0, s>>>(hd, lb, 2);                          // minvotes, LSQ        wrap.h:251-259
   loop_remove_kernel<<<1, 1024, 0, s>>>(lb);                            // removePoints, while  wrap.h:339-342
+  note_launches(13);   // + the vote kernel counted in launch_vote
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;
 }
@@ -862,6 +869,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   hd.n_dev = nullptr;
   h->has_negative = false;
   shift_points_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(h->px, h->py, h->pz, h->w, (int)n, ns[0], ns[1], ns[2]);
+  note_launches(2);   // + the prep kernel of the caller
 
   LoopState st;
   memset(&st, 0, sizeof st);
@@ -875,6 +883,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   H3D_CUDA(cudaMemcpyAsync(f.st_dev, f.st_host, sizeof(LoopState), cudaMemcpyHostToDevice, s));
 
   // hough->add(X), wrap.h:228: every plane once
+  H3D_CUDA(cudaEventRecord(f.ev[4], s));
   H3D_TRY(launch_vote(h, 0, 0, nullptr, nullptr, hd.dir_count, nullptr));
   H3D_CUDA(cudaEventRecord(f.ev[2], s));
 
@@ -898,7 +907,6 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   hd.n_dev = nullptr;
   if (rc != H3D_OK) return rc;
   H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
-  H3D_CUDA(cudaEventRecord(f.ev[3], s));
   H3D_CUDA(cudaStreamSynchronize(s));
   const LoopState &fin = *f.st_host;
   res->n_iters = (uint32_t)fin.n_iters; res->n_lines = (uint32_t)fin.n_lines; res->pool_used = fin.pool_used;
@@ -906,7 +914,9 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   const size_t n_rec = (size_t)fin.n_iters < (size_t)st.max_iters ? (size_t)fin.n_iters : (size_t)st.max_iters;
   if (n_rec && iters) H3D_CUDA(cudaMemcpyAsync(iters, f.iters_dev, n_rec * sizeof(h3d_iter), cudaMemcpyDeviceToHost, s));
   if (fin.pool_used && pool) H3D_CUDA(cudaMemcpyAsync(pool, f.pool_dev, (size_t)fin.pool_used * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+  H3D_CUDA(cudaEventRecord(f.ev[3], s));
   H3D_CUDA(cudaStreamSynchronize(s));
+  f.timed = true;
   hd.n = 0;
   return H3D_OK;
 }
@@ -925,6 +935,7 @@ extern "C" int h3d_hough3dlines(const double *xyz, size_t n, int granularity, do
   cudaStream_t s = f.hg->stream;
   H3D_CUDA(cudaEventRecord(f.ev[0], s));
   if (n) H3D_CUDA(cudaMemcpyAsync(f.in_dev, xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+  f.timed = false;
   prep_kernel<double><<<1, 1024, 0, s>>>(static_cast<const double *>(f.in_dev), (int)n, nullptr, 3, f.hg->px,
                                          f.hg->py, f.hg->pz, f.orig, f.prep_dev);
   H3D_CUDA(cudaGetLastError());
@@ -996,6 +1007,7 @@ int prefilter_phase1(PrefilterCtx &p, const float *in_dev, int n, int stride, co
   k0_init_kernel<<<1, 1, 0, s>>>(p.st);
   if (n) k0_bbox_kernel<<<sm * 2, 256, 0, s>>>(in_dev, n, stride, w, p.st);
   k0_setup_kernel<<<1, 1, 0, s>>>(p.st, leaf, (int)(p.grid_cap < 0x7FFFFFFF ? p.grid_cap : 0x7FFFFFFF));
+  note_launches(n ? 3 : 2);
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;
 }
@@ -1012,6 +1024,7 @@ int prefilter_phase2(PrefilterCtx &p, const float *in_dev, int n, int stride, co
   k0_centroid_kernel<<<(unsigned)((grid_cells + 255) / 256), 256, 0, s>>>(in_dev, stride, p.st, p.count, p.start,
                                                                           p.slot, p.members, out_dev, out_cap,
                                                                           out_stride);
+  note_launches(6);
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;
 }
@@ -1113,6 +1126,7 @@ extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_
   if (n > p->cfg.max_raw_points) return fail(H3D_ERR_ARG, "frame larger than max_raw_points");
   memset(res, 0, sizeof *res);
   FrameCtx &f = p->f;
+  f.timed = false;
   h3d_hough *h = f.hg;
   cudaStream_t s = h->stream;
   H3D_CUDA(cudaEventRecord(f.ev[0], s));
@@ -1127,9 +1141,12 @@ extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_
   H3D_CUDA(cudaGetLastError());
   const int rc = frame_run(f, p->cfg.opt_minvotes, p->cfg.opt_nlines, p->cfg.opt_dx, 0, iters, p->cfg.max_iters, pool,
                            pool_cap, res);
-  if (rc == H3D_OK) {
-    for (int k = 0; k < 3; ++k) cudaEventElapsedTime(&f.us[k], f.ev[k], f.ev[k + 1]);
-    cudaEventElapsedTime(&f.us[3], f.ev[0], f.ev[3]);
+  for (auto &u : f.us) u = 0.0f;
+  if (rc == H3D_OK && f.timed) {
+    cudaEventElapsedTime(&f.us[0], f.ev[0], f.ev[1]);   // pre-filter + prep
+    cudaEventElapsedTime(&f.us[1], f.ev[4], f.ev[2]);   // the first vote kernel alone (Hough::add)
+    cudaEventElapsedTime(&f.us[2], f.ev[2], f.ev[3]);   // loop + result copies
+    cudaEventElapsedTime(&f.us[3], f.ev[0], f.ev[3]);   // whole frame
     for (auto &u : f.us) u *= 1000.0f;
   }
   return rc;

@@ -1,0 +1,12 @@
+"""A few frames of the bench workload through the pipeline (for ncu launch lists / captures)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from pointcloud_segmentation_b200 import capi, synth
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+frame = synth.tof_frame()
+pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frame.shape[0])
+for _ in range(n):
+    res = pipe.run(frame)
+    print(res.n_input, res.n_lines, [round(u, 1) for u in pipe.timing_us()])
