@@ -174,6 +174,11 @@ int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n
  * h3d_pipeline_run.  All zero when the frame ended early (rc != 0). */
 int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
 
+/* the frame loop runs as one persistent cooperative kernel when the cloud fits the register-
+ * resident form (<= 6144 points); on = 0 forces the general multi-kernel loop.  Returns the
+ * previous setting.  Results are identical either way. */
+int h3d_set_fused(int on);
+
 /* ---- measurement hooks (bench.py): raw kernel timings with CUDA events ----- */
 /* runs the vote kernel `reps` times over all directions of h and returns the
  * mean device time per launch in microseconds.  ablate: 0 = full kernel,

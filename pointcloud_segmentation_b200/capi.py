@@ -317,3 +317,8 @@ def orthogonal_lsq(xyz):
     aa, bb, rc = (C.c_double * 3)(), (C.c_double * 3)(), C.c_double()
     check(lib().h3d_orthogonal_lsq(p, n, aa, bb, C.byref(rc)))
     return rc.value, np.array(aa[:]), np.array(bb[:])
+
+
+def set_fused(on):
+    """Use (True) or bypass (False) the fused persistent loop kernel; returns the previous setting."""
+    return bool(lib().h3d_set_fused(C.c_int(1 if on else 0)))

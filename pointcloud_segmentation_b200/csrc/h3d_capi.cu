@@ -10,7 +10,7 @@
 #include <mutex>
 #include <new>
 
-#include "h3d_loop.cuh"
+#include "h3d_fused.cuh"
 #include "h3d_prefilter.cuh"
 
 namespace h3d {
@@ -738,11 +738,16 @@ struct FrameCtx {
   unsigned *pool_dev = nullptr;
   LoopState *st_dev = nullptr;
   PrepOut *prep_dev = nullptr;
+  unsigned long long *gbest = nullptr;   // fused loop: winner key per iteration
+  size_t gbest_cap = 0;
+  unsigned *sync_dev = nullptr;          // [0] grid barrier, [1] overflow flag
+  unsigned *sync_host = nullptr;         // pinned
   LoopState *st_host = nullptr;   // pinned
   PrepOut *prep_host = nullptr;   // pinned
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // start, prep done, first vote done, end, first vote start
   float us[4] = {0, 0, 0, 0};
   bool timed = false;   // the last frame ran to the end (all events recorded)
+  bool fused = false;   // the last frame ran in the fused persistent kernel
 
   ~FrameCtx() { release(); }
   void release() {
@@ -750,6 +755,8 @@ struct FrameCtx {
     cudaFree(in_dev); cudaFree(orig); cudaFree(flags); cudaFree(yidx);
     cudaFree(ypx); cudaFree(ypy); cudaFree(ypz);
     cudaFree(iters_dev); cudaFree(pool_dev); cudaFree(st_dev); cudaFree(prep_dev);
+    cudaFree(gbest); cudaFree(sync_dev); cudaFreeHost(sync_host);
+    gbest = nullptr; sync_dev = nullptr; sync_host = nullptr; gbest_cap = 0;
     cudaFreeHost(st_host); cudaFreeHost(prep_host);
     for (auto &e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
     in_dev = nullptr; orig = nullptr; flags = nullptr; yidx = nullptr; ypx = ypy = ypz = nullptr;
@@ -771,6 +778,8 @@ int frame_ensure(FrameCtx &f, unsigned g, size_t n, size_t in_bytes, size_t max_
     H3D_CUDA(cudaMalloc(&f.prep_dev, sizeof(PrepOut)));
     H3D_CUDA(cudaMallocHost(&f.st_host, sizeof(LoopState)));
     H3D_CUDA(cudaMallocHost(&f.prep_host, sizeof(PrepOut)));
+    H3D_CUDA(cudaMalloc(&f.sync_dev, 4 * sizeof(unsigned)));
+    H3D_CUDA(cudaMallocHost(&f.sync_host, 4 * sizeof(unsigned)));
     for (auto &e : f.ev) H3D_CUDA(cudaEventCreate(&e));
   }
   if (n > f.cap) {
@@ -831,6 +840,62 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
   return H3D_OK;
 }
 
+static bool g_use_fused = true;
+
+template <int P>
+int launch_fused_t(FrameCtx &f, const FusedArgs &args, size_t smem) {
+  static thread_local size_t configured = 0;
+  if (smem > configured) {
+    H3D_CUDA(cudaFuncSetAttribute(fused_loop_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  void *params[] = {const_cast<FusedArgs *>(&args)};
+  H3D_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(fused_loop_kernel<P>), dim3(f.hg->dev.sm_count),
+                                       dim3(kResThreads), params, smem, f.hg->stream));
+  note_launches(1);
+  return H3D_OK;
+}
+
+// returns H3D_OK with *launched = false when the frame does not qualify for the fused kernel
+int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, bool *launched) {
+  *launched = false;
+  h3d_hough *h = f.hg;
+  const HoughDev &hd = h->d;
+  if (!g_use_fused || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0) return H3D_OK;
+  const int groups = (hd.dir_count + kResG - 1) / kResG;
+  const int n_own = ((groups + h->dev.sm_count - 1) / h->dev.sm_count) * kResG;
+  const size_t plane_bytes = ((size_t)2 * kResG * hd.plane_stride + 4) * sizeof(unsigned);
+  const size_t smem = plane_bytes + (size_t)n_own * (5 * sizeof(double) + 4 * sizeof(unsigned));
+  cudaFuncAttributes fa;
+  H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel<4>));
+  if (smem + fa.sharedSizeBytes > h->dev.smem_optin) return H3D_OK;
+  if ((2 * kResG * (size_t)hd.plane_stride * 4 - 6 * kResThreads * 4) / 24 < 256) return H3D_OK;   // scratch too small
+  const size_t iters = (size_t)(opt_nlines > 0 ? opt_nlines : hd.n) + 2;
+  if (iters > f.gbest_cap) {
+    cudaFree(f.gbest); f.gbest = nullptr; f.gbest_cap = 0;
+    H3D_CUDA(cudaMalloc(&f.gbest, iters * sizeof(unsigned long long)));
+    f.gbest_cap = iters;
+  }
+  cudaStream_t s = h->stream;
+  H3D_CUDA(cudaMemsetAsync(f.gbest, 0, iters * sizeof(unsigned long long), s));
+  H3D_CUDA(cudaMemsetAsync(f.sync_dev, 0, 4 * sizeof(unsigned), s));
+  FusedArgs a;
+  a.h = hd; a.h.n_dev = nullptr;
+  a.st = lb.st; a.iters = lb.iters; a.pool = lb.pool; a.orig = lb.orig; a.dirs = lb.dirs;
+  a.gbest = f.gbest; a.bar = f.sync_dev; a.overflow = reinterpret_cast<int *>(f.sync_dev + 1);
+  a.n_own_max = n_own;
+  const int need = (hd.n + kResThreads - 1) / kResThreads;
+  int rc;
+  if (need <= 4) rc = launch_fused_t<4>(f, a, smem);
+  else if (need <= 8) rc = launch_fused_t<8>(f, a, smem);
+  else if (need <= 10) rc = launch_fused_t<10>(f, a, smem);
+  else rc = launch_fused_t<12>(f, a, smem);
+  if (rc != H3D_OK) return rc;
+  H3D_CUDA(cudaMemcpyAsync(f.sync_host, f.sync_dev, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+  *launched = true;
+  return H3D_OK;
+}
+
 // everything after the points are on the device (unshifted SoA + orig + PrepOut): bbox checks,
 // Hough ctor, first vote, loop, results.  timing events: ev[1] after prep, ev[2] after the first
 // vote, ev[3] at the end.
@@ -882,17 +947,32 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   *f.st_host = st;
   H3D_CUDA(cudaMemcpyAsync(f.st_dev, f.st_host, sizeof(LoopState), cudaMemcpyHostToDevice, s));
 
+  LoopBuffers lb;
+  lb.st = f.st_dev; lb.iters = f.iters_dev; lb.pool = f.pool_dev; lb.orig = f.orig;
+  lb.flags = f.flags; lb.yidx = f.yidx; lb.ypx = f.ypx; lb.ypy = f.ypy; lb.ypz = f.ypz;
+  lb.px = h->px; lb.py = h->py; lb.pz = h->pz; lb.list = h->list; lb.dirs = h->space->dirs_dev;
+  int rc = H3D_OK;
+  // fast path: first vote + the whole loop in one persistent cooperative kernel
+  bool fused = false;
+  H3D_CUDA(cudaEventRecord(f.ev[4], s));
+  H3D_TRY(try_launch_fused(f, lb, opt_nlines, &fused));
+  if (fused) {
+    H3D_CUDA(cudaEventRecord(f.ev[2], s));
+    H3D_CUDA(cudaStreamSynchronize(s));
+    if (f.sync_host[1]) {   // an inlier set larger than the shared-memory scratch: redo with the general loop
+      fused = false;
+      *f.st_host = st;
+      H3D_CUDA(cudaMemcpyAsync(f.st_dev, f.st_host, sizeof(LoopState), cudaMemcpyHostToDevice, s));
+    }
+  }
+  f.fused = fused;
+  if (!fused) {
   // hough->add(X), wrap.h:228: every plane once
   H3D_CUDA(cudaEventRecord(f.ev[4], s));
   H3D_TRY(launch_vote(h, 0, 0, nullptr, nullptr, hd.dir_count, nullptr));
   H3D_CUDA(cudaEventRecord(f.ev[2], s));
 
-  LoopBuffers lb;
-  lb.st = f.st_dev; lb.iters = f.iters_dev; lb.pool = f.pool_dev; lb.orig = f.orig;
-  lb.flags = f.flags; lb.yidx = f.yidx; lb.ypx = f.ypx; lb.ypy = f.ypy; lb.ypz = f.ypz;
-  lb.px = h->px; lb.py = h->py; lb.pz = h->pz; lb.list = h->list; lb.dirs = h->space->dirs_dev;
   hd.n_dev = &f.st_dev->n_alive;                         // the loop shrinks X on the device
-  int rc = H3D_OK;
   if (opt_nlines > 0) {
     for (int it = 0; it < opt_nlines && rc == H3D_OK; ++it) rc = enqueue_iteration(f, hd, lb);
   } else {                                               // unbounded: look at `done` every few iterations
@@ -903,6 +983,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
           cudaStreamSynchronize(s) != cudaSuccess) { rc = fail(H3D_ERR_CUDA, "loop state read-back failed"); break; }
       if (f.st_host->done) break;
     }
+  }
   }
   hd.n_dev = nullptr;
   if (rc != H3D_OK) return rc;
@@ -1424,4 +1505,10 @@ extern "C" int h3d_remove_points(double *x_xyz, size_t nx, const double *y_xyz, 
   if (k) H3D_CUDA(cudaMemcpy(x_xyz, x, (size_t)k * 3 * sizeof(double), cudaMemcpyDeviceToHost));
   *n_out = (size_t)k;
   return H3D_OK;
+}
+
+extern "C" int h3d_set_fused(int on) {
+  const int old = g_use_fused ? 1 : 0;
+  g_use_fused = on != 0;
+  return old;
 }

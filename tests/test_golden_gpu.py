@@ -8,6 +8,14 @@ import golden_util as G
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["fused", "multikernel"])
+def loop_form(request, h3d):
+    """Every test runs with the fused persistent loop kernel and with the general multi-kernel loop."""
+    old = h3d.set_fused(request.param == "fused")
+    yield request.param
+    h3d.set_fused(old)
+
+
 @pytest.fixture(scope="module")
 def gold():
     return G.load()

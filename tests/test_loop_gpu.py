@@ -9,6 +9,14 @@ import pytest
 from pointcloud_segmentation_b200 import synth
 
 pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True, params=["fused", "multikernel"])
+def loop_form(request, h3d):
+    """Every test runs with the fused persistent loop kernel and with the general multi-kernel loop."""
+    old = h3d.set_fused(request.param == "fused")
+    yield request.param
+    h3d.set_fused(old)
 DATA = os.path.join(os.path.dirname(__file__), "golden")
 REL_TOL = 1e-5   # north_star: anchor/direction within 1e-5 relative
 

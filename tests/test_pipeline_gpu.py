@@ -8,6 +8,14 @@ from test_loop_gpu import _compare
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["fused", "multikernel"])
+def loop_form(request, h3d):
+    """Every test runs with the fused persistent loop kernel and with the general multi-kernel loop."""
+    old = h3d.set_fused(request.param == "fused")
+    yield request.param
+    h3d.set_fused(old)
+
+
 def _frames():
     yield "tof_default", synth.tof_frame()
     yield "tof_pose2", synth.tof_frame(pose=(-0.9, 0.4, 1.4, -0.3), seed=9)
