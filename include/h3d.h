@@ -174,6 +174,12 @@ int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n
  * h3d_pipeline_run.  All zero when the frame ended early (rc != 0). */
 int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
 
+/* measurement hook: phase stamps of the fused loop kernel.  out == NULL: enable for `iters`
+ * iterations (0 disables).  out != NULL: copy the stamps of the last frame,
+ * [iteration][cta][n_slots] globaltimer nanoseconds (slot 8: re-voted planes + 1). */
+int h3d_pipeline_profile(h3d_pipeline *p, int iters, unsigned long long *out, size_t cap, int *n_cta,
+                         int *n_slots);
+
 /* the frame loop runs as one persistent cooperative kernel when the cloud fits the register-
  * resident form (<= 6144 points); on = 0 forces the general multi-kernel loop.  Returns the
  * previous setting.  Results are identical either way. */

@@ -385,8 +385,11 @@ size_t h3do_remove_points(double *x, size_t nx, const double *y, size_t ny) {  /
 /* ======================================================================== */
 /* orthogonal_LSQ -- wrap.h:121-150 (== lib/hough3dlines.cpp:49-77)          */
 /* Third party: Eigen3 (un-vendored, version unpinned; Ubuntu 20.04 = 3.3.7).*/
-/* Restated: MatrixXf copy, colwise().mean(), centred^T * centred in float   */
-/* with a k-sequential sum, SelfAdjointEigenSolver<MatrixXf>::compute =      */
+/* Restated: MatrixXf copy, colwise().mean(), centred^T * centred in float,  */
+/* every float sum in the canonical TREE32 order (32 interleaved partial     */
+/* sums, partial l = elements l, l+32, ... in index order, then a halving    */
+/* tree l += l+16, +8, +4, +2, +1 -- the shape of a vectorised reduction such */
+/* as Eigen's), SelfAdjointEigenSolver<MatrixXf>::compute =                  */
 /* scale by max|coeff| -> Householder tridiagonalisation -> implicit         */
 /* symmetric QR with Wilkinson shift -> ascending sort.  PARITY UNPINNED.    */
 /* ======================================================================== */
@@ -516,19 +519,30 @@ int h3do_eig3f(const float m_in[9], float evals[3], float evecs[9]) {
     return ok ? 0 : 1;
 }
 
+/* halving tree over the 32 interleaved partial sums (destroys v) */
+static float tree32_fold(float v[32]) {
+    for (int o = 16; o; o >>= 1) for (int l = 0; l < o; l++) v[l] = v[l] + v[l + o];
+    return v[0];
+}
+
 double h3do_orthogonal_lsq(const double *p, size_t n, double a[3], double b[3]) {
     h3do_mean_value(p, n, a);                         /* wrap.h:126 */
     /* wrap.h:129-134: float copy; wrap.h:137: column means in float */
-    float mean[3] = {0.0f, 0.0f, 0.0f};
-    for (size_t i = 0; i < n; i++) for (int c = 0; c < 3; c++) mean[c] = mean[c] + (float)p[3 * i + c];
-    for (int c = 0; c < 3; c++) mean[c] = mean[c] / (float)n;   /* n==0 -> NaN, unused below */
-    /* wrap.h:138: scatter = centred^T centred, float, sequential in k */
-    float s[6] = {0, 0, 0, 0, 0, 0};                  /* xx xy xz yy yz zz */
+    float part[6][32];
+    float mean[3];
+    memset(part, 0, sizeof part);
+    for (size_t i = 0; i < n; i++) for (int c = 0; c < 3; c++) part[c][i & 31] = part[c][i & 31] + (float)p[3 * i + c];
+    for (int c = 0; c < 3; c++) mean[c] = tree32_fold(part[c]) / (float)n;   /* n==0 -> NaN, unused below */
+    /* wrap.h:138: scatter = centred^T centred, float, TREE32 over k */
+    float s[6];                                       /* xx xy xz yy yz zz */
+    memset(part, 0, sizeof part);
     for (size_t i = 0; i < n; i++) {
         float cx = (float)p[3 * i] - mean[0], cy = (float)p[3 * i + 1] - mean[1], cz = (float)p[3 * i + 2] - mean[2];
-        s[0] = s[0] + cx * cx; s[1] = s[1] + cx * cy; s[2] = s[2] + cx * cz;
-        s[3] = s[3] + cy * cy; s[4] = s[4] + cy * cz; s[5] = s[5] + cz * cz;
+        float *q0 = &part[0][i & 31];
+        q0[0] = q0[0] + cx * cx; q0[32] = q0[32] + cx * cy; q0[64] = q0[64] + cx * cz;
+        q0[96] = q0[96] + cy * cy; q0[128] = q0[128] + cy * cz; q0[160] = q0[160] + cz * cz;
     }
+    for (int c = 0; c < 6; c++) s[c] = tree32_fold(part[c]);
     float m[9] = {s[0], s[1], s[2], s[1], s[3], s[4], s[2], s[4], s[5]};
     float ev[3], evec[9];
     h3do_eig3f(m, ev, evec);                          /* wrap.h:141-142 */

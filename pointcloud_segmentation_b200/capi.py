@@ -260,6 +260,21 @@ class Pipeline:
         check(lib().h3d_pipeline_timing(self._p, us))
         return list(us)
 
+    def profile_enable(self, iters):
+        """Measurement hook: record phase stamps of the fused loop kernel for `iters` iterations."""
+        check(lib().h3d_pipeline_profile(self._p, C.c_int(iters), None, C.c_size_t(0), None, None))
+        self._prof_iters = iters
+
+    def profile_read(self):
+        """[iteration][cta][slot] globaltimer ns of the last frame (slot 8: re-voted planes + 1)."""
+        n_cta, n_slots = C.c_int(), C.c_int()
+        sm = device_info()["sm_count"]
+        buf = np.zeros(self._prof_iters * sm * 16, dtype=np.uint64)
+        check(lib().h3d_pipeline_profile(self._p, C.c_int(0), buf.ctypes.data_as(C.POINTER(C.c_ulonglong)),
+                                         C.c_size_t(buf.size), C.byref(n_cta), C.byref(n_slots)))
+        k = self._prof_iters * n_cta.value * n_slots.value
+        return buf[:k].reshape(self._prof_iters, n_cta.value, n_slots.value)
+
     def close(self):
         if self._p:
             lib().h3d_pipeline_destroy(self._p)

@@ -742,6 +742,8 @@ struct FrameCtx {
   size_t gbest_cap = 0;
   unsigned *sync_dev = nullptr;          // [0] grid barrier, [1] overflow flag
   unsigned *sync_host = nullptr;         // pinned
+  unsigned long long *prof_dev = nullptr;   // measurement hook: fused-loop phase stamps (h3d_pipeline_profile)
+  int prof_iters = 0, prof_ctas = 0;
   LoopState *st_host = nullptr;   // pinned
   PrepOut *prep_host = nullptr;   // pinned
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // start, prep done, first vote done, end, first vote start
@@ -755,7 +757,8 @@ struct FrameCtx {
     cudaFree(in_dev); cudaFree(orig); cudaFree(flags); cudaFree(yidx);
     cudaFree(ypx); cudaFree(ypy); cudaFree(ypz);
     cudaFree(iters_dev); cudaFree(pool_dev); cudaFree(st_dev); cudaFree(prep_dev);
-    cudaFree(gbest); cudaFree(sync_dev); cudaFreeHost(sync_host);
+    cudaFree(gbest); cudaFree(sync_dev); cudaFreeHost(sync_host); cudaFree(prof_dev);
+    prof_dev = nullptr; prof_iters = prof_ctas = 0;
     gbest = nullptr; sync_dev = nullptr; sync_host = nullptr; gbest_cap = 0;
     cudaFreeHost(st_host); cudaFreeHost(prep_host);
     for (auto &e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
@@ -830,10 +833,10 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
   loop_line_kernel<<<1, 32, 0, s>>>(hd, lb);
   loop_mask_kernel<<<sm * 2, 256, 0, s>>>(hd, lb);                      // pointsCloseToLine    wrap.h:245
   loop_compact_kernel<<<1, 1024, 0, s>>>(hd, lb, 1);
-  loop_lsq_kernel<<<1, 64, 0, s>>>(hd, lb, 1);                          // orthogonal_LSQ       wrap.h:247
+  loop_lsq_kernel<<<1, 192, 0, s>>>(hd, lb, 1);                          // orthogonal_LSQ       wrap.h:247
   loop_mask_kernel<<<sm * 2, 256, 0, s>>>(hd, lb);                      // pointsCloseToLine    wrap.h:250
   loop_compact_kernel<<<1, 1024, 0, s>>>(hd, lb, 2);
-  loop_lsq_kernel<<<1, 64, 0, s>>>(hd, lb, 2);                          // minvotes, LSQ        wrap.h:251-259
+  loop_lsq_kernel<<<1, 192, 0, s>>>(hd, lb, 2);                          // minvotes, LSQ        wrap.h:251-259
   loop_remove_kernel<<<1, 1024, 0, s>>>(lb);                            // removePoints, while  wrap.h:339-342
   note_launches(13);   // + the vote kernel counted in launch_vote
   H3D_CUDA(cudaGetLastError());
@@ -884,6 +887,9 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, bool *l
   a.st = lb.st; a.iters = lb.iters; a.pool = lb.pool; a.orig = lb.orig; a.dirs = lb.dirs;
   a.gbest = f.gbest; a.bar = f.sync_dev; a.overflow = reinterpret_cast<int *>(f.sync_dev + 1);
   a.n_own_max = n_own;
+  a.prof = f.prof_dev; a.prof_iters = f.prof_iters;
+  if (f.prof_dev)
+    H3D_CUDA(cudaMemsetAsync(f.prof_dev, 0, (size_t)f.prof_iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long), s));
   const int need = (hd.n + kResThreads - 1) / kResThreads;
   int rc;
   if (need <= 4) rc = launch_fused_t<4>(f, a, smem);
@@ -1253,6 +1259,28 @@ extern "C" int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap
   return H3D_OK;
 }
 
+extern "C" int h3d_pipeline_profile(h3d_pipeline *p, int iters, unsigned long long *out, size_t cap, int *n_cta,
+                                    int *n_slots) {
+  if (!p) return fail(H3D_ERR_ARG, "bad argument");
+  FrameCtx &f = p->f;
+  if (n_slots) *n_slots = kProfSlots;
+  if (out) {
+    if (!f.prof_dev) return fail(H3D_ERR_ARG, "profiling is not enabled");
+    if (n_cta) *n_cta = f.prof_ctas;
+    const size_t words = (size_t)f.prof_iters * f.prof_ctas * kProfSlots;
+    H3D_CUDA(cudaMemcpy(out, f.prof_dev, (words < cap ? words : cap) * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return H3D_OK;
+  }
+  cudaFree(f.prof_dev); f.prof_dev = nullptr; f.prof_iters = 0;
+  if (iters > 0) {
+    f.prof_ctas = f.hg->dev.sm_count;
+    H3D_CUDA(cudaMalloc(&f.prof_dev, (size_t)iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long)));
+    f.prof_iters = iters;
+  }
+  if (n_cta) *n_cta = f.prof_ctas;
+  return H3D_OK;
+}
+
 extern "C" int h3d_pipeline_timing(h3d_pipeline *p, float us[4]) {
   if (!p || !us) return fail(H3D_ERR_ARG, "bad argument");
   for (int k = 0; k < 4; ++k) us[k] = p->f.us[k];
@@ -1327,13 +1355,11 @@ __global__ void aos_to_soa_kernel(const double *__restrict__ p, int n, double *p
   }
 }
 
-__global__ void __launch_bounds__(64, 1) soa_lsq_kernel(const double *px, const double *py, const double *pz, int n,
-                                                        LsqOut *out) {
-  __shared__ double sd[3][33];
-  __shared__ float sf[6][33];
-  __shared__ float mean_s[12];
+__global__ void __launch_bounds__(192, 1) soa_lsq_kernel(const double *px, const double *py, const double *pz, int n,
+                                                         LsqOut *out) {
+  __shared__ LsqShared sh;
   __shared__ LsqOut o;
-  lsq_block(px, py, pz, nullptr, n, sd, sf, mean_s, &o);
+  lsq_cta([&](int k, int c) { return (c == 0 ? px : c == 1 ? py : pz)[k]; }, n, sh, &o);
   if (threadIdx.x == 0) *out = o;
 }
 
@@ -1447,7 +1473,7 @@ static int lsq_on_host_cloud(const double *xyz, size_t n, LsqOut *res) {
   H3D_TRY(scratch_get(scratch(), 5, sizeof(LsqOut), &o));
   double *px = static_cast<double *>(soa), *py = px + n, *pz = py + n;
   if (n) aos_to_soa_kernel<<<(unsigned)((n + 255) / 256), 256>>>(p, (int)n, px, py, pz);
-  soa_lsq_kernel<<<1, 64>>>(px, py, pz, (int)n, static_cast<LsqOut *>(o));
+  soa_lsq_kernel<<<1, 192>>>(px, py, pz, (int)n, static_cast<LsqOut *>(o));
   H3D_CUDA(cudaMemcpy(res, o, sizeof(LsqOut), cudaMemcpyDeviceToHost));
   return H3D_OK;
 }

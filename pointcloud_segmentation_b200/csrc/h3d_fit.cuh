@@ -8,15 +8,19 @@
 // IEEE double without FMA, so the inlier SETS are bit-exact.  The refit feeds the second
 // inlier test, so it must be bit-stable too: the anchor is the reference's sequential double
 // sum in point order; the direction follows the float pipeline of wrap.h:129-147 with the
-// canonical order fixed by the oracle (sequential float sums in point order, Eigen's
-// SelfAdjointEigenSolver<MatrixXf> = scale, Householder tridiagonalisation, implicit
-// symmetric QR with Wilkinson shift, ascending sort).  Eigen is not vendored by the
-// reference: PARITY UNPINNED against Eigen itself, bit-exact against oracle/h3d_oracle.c.
+// canonical order fixed by the oracle: every float sum (column means, scatter products) is
+// TREE32 -- 32 interleaved partial sums (partial l adds elements l, l+32, l+64, ... in index
+// order) combined by a halving tree (l += l+16, l+8, l+4, l+2, l+1), the shape of a vectorised
+// reduction like Eigen's own -- followed by Eigen's SelfAdjointEigenSolver<MatrixXf> = scale,
+// Householder tridiagonalisation, implicit symmetric QR with Wilkinson shift, ascending sort.
+// Eigen is not vendored by the reference: PARITY UNPINNED against Eigen itself, bit-exact
+// against oracle/h3d_oracle.c.
 //
-// Sequential sums are inherently serial; the kernels keep them exact but cheap: a warp
-// stages 32 points at a time (loads, float casts, centring and products run 32-wide), then
-// one lane per accumulator adds the 32 staged values in order, so the serial chain costs one
-// shared-memory read and one add per point.
+// The anchor IS pinned (sequential double sum, lib/pointcloud.cpp:29-38).  It is evaluated in
+// parallel whenever that is provably the same number: if every coordinate is a multiple of
+// 2^lo and n * 2^(hi+1) <= 2^(53+lo) (hi = largest exponent), every partial sum of ANY order is
+// an exactly representable multiple of 2^lo, so the sequential sum equals the exact sum, which
+// an int64 reduction delivers.  Otherwise one lane runs the sequential chain.
 #ifndef H3D_FIT_CUH_
 #define H3D_FIT_CUH_
 
@@ -116,25 +120,46 @@ __host__ __device__ inline Eig3f eig3f(const float m[9]) {
     q[5] = 0.0f - tv;  q[8] = 1.0f - tv * v1;
   }
 
-  // implicit symmetric QR iteration on the tridiagonal matrix
-  const int n = 3;
-  int end = n - 1, start = 0, iter = 0;
+  // implicit symmetric QR iteration on the tridiagonal matrix (Eigen computeFromTridiagonal_impl
+  // + tridiagonal_qr_step), written out for n = 3 on scalars so that everything stays in
+  // registers: the active block [start, end] is [0,2], [1,2] or [0,1]
+  float d0 = diag[0], d1 = diag[1], d2 = diag[2], s0 = sub[0], s1 = sub[1];
+  float q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3], q4 = q[4], q5 = q[5], q6 = q[6], q7 = q[7], q8 = q[8];
+  int end = 2, start = 0, iter = 0;
   const float precision = 2.0f * FLT_EPSILON, consider_zero = FLT_MIN;
   int ok = 1;
+  // one Givens rotation of the QR step on rows/columns (k, k+1); dk, dk1, sk by reference
+#define H3D_EIG_ROT(dk, dk1, sk, qa0, qa1, qa2, qb0, qb1, qb2, PRE, POST)          \
+  {                                                                                \
+    float c, sn;                                                                   \
+    eig_givens(x, z, &c, &sn);                                                     \
+    const float sdk = sn * dk + c * sk;                                            \
+    const float dkp1 = sn * sk + c * dk1;                                          \
+    dk = c * (c * dk - sn * sk) - sn * (c * sk - sn * dk1);                        \
+    dk1 = sn * sdk + c * dkp1;                                                     \
+    sk = c * sdk - sn * dkp1;                                                      \
+    PRE;                                                                           \
+    x = sk;                                                                        \
+    POST;                                                                          \
+    float xi, yi;                                                                  \
+    xi = qa0; yi = qb0; qa0 = c * xi - sn * yi; qb0 = sn * xi + c * yi;            \
+    xi = qa1; yi = qb1; qa1 = c * xi - sn * yi; qb1 = sn * xi + c * yi;            \
+    xi = qa2; yi = qb2; qa2 = c * xi - sn * yi; qb2 = sn * xi + c * yi;            \
+  }
   while (end > 0) {
-    for (int i = start; i < end; i++)
-      if (fabsf(sub[i]) <= (fabsf(diag[i]) + fabsf(diag[i + 1])) * precision || fabsf(sub[i]) <= consider_zero)
-        sub[i] = 0.0f;
-    while (end > 0 && sub[end - 1] == 0.0f) end--;
+    if (start <= 0 && end > 0 && (fabsf(s0) <= (fabsf(d0) + fabsf(d1)) * precision || fabsf(s0) <= consider_zero)) s0 = 0.0f;
+    if (start <= 1 && end > 1 && (fabsf(s1) <= (fabsf(d1) + fabsf(d2)) * precision || fabsf(s1) <= consider_zero)) s1 = 0.0f;
+    if (end == 2 && s1 == 0.0f) end = 1;
+    if (end == 1 && s0 == 0.0f) end = 0;
     if (end <= 0) break;
     iter++;
-    if (iter > 30 * n) { ok = 0; break; }
-    start = end - 1;
-    while (start > 0 && sub[start - 1] != 0.0f) start--;
+    if (iter > 30 * 3) { ok = 0; break; }
+    start = (end == 2 && s0 == 0.0f) ? 1 : 0;
 
-    const float td = (diag[end - 1] - diag[end]) * 0.5f;
-    const float e = sub[end - 1];
-    float mu = diag[end];
+    const float de1 = end == 2 ? d1 : d0, de = end == 2 ? d2 : d1;   // diag[end-1], diag[end]
+    const float td = (de1 - de) * 0.5f;
+    const float e = end == 2 ? s1 : s0;                              // sub[end-1]
+    float mu = de;
     if (td == 0.0f) {
       mu -= fabsf(e);
     } else {
@@ -143,33 +168,36 @@ __host__ __device__ inline Eig3f eig3f(const float m[9]) {
       if (e2 == 0.0f) mu -= (e / (td + (td > 0.0f ? 1.0f : -1.0f))) * (e / hyp);
       else mu -= e2 / (td + (td > 0.0f ? hyp : -hyp));
     }
-    float x = diag[start] - mu;
-    float z = sub[start];
-    for (int k = start; k < end; k++) {
-      float c, s;
-      eig_givens(x, z, &c, &s);
-      const float sdk = s * diag[k] + c * sub[k];
-      const float dkp1 = s * sub[k] + c * diag[k + 1];
-      diag[k] = c * (c * diag[k] - s * sub[k]) - s * (c * sub[k] - s * diag[k + 1]);
-      diag[k + 1] = s * sdk + c * dkp1;
-      sub[k] = c * sdk - s * dkp1;
-      if (k > start) sub[k - 1] = c * sub[k - 1] - s * z;
-      x = sub[k];
-      if (k < end - 1) { z = -s * sub[k + 1]; sub[k + 1] = c * sub[k + 1]; }
-      for (int r = 0; r < 3; r++) {
-        const float xi = q[k * 3 + r], yi = q[(k + 1) * 3 + r];
-        q[k * 3 + r] = c * xi - s * yi;
-        q[(k + 1) * 3 + r] = s * xi + c * yi;
-      }
+    float x = (start == 0 ? d0 : d1) - mu;
+    float z = start == 0 ? s0 : s1;
+    if (start == 0) {
+      if (end == 2) H3D_EIG_ROT(d0, d1, s0, q0, q1, q2, q3, q4, q5, (void)0, (z = -sn * s1, s1 = c * s1))
+      else H3D_EIG_ROT(d0, d1, s0, q0, q1, q2, q3, q4, q5, (void)0, (void)0)
+    }
+    if (end == 2) {
+      if (start == 0) H3D_EIG_ROT(d1, d2, s1, q3, q4, q5, q6, q7, q8, (s0 = c * s0 - sn * z), (void)0)
+      else H3D_EIG_ROT(d1, d2, s1, q3, q4, q5, q6, q7, q8, (void)0, (void)0)
     }
   }
+#undef H3D_EIG_ROT
+  diag[0] = d0; diag[1] = d1; diag[2] = d2;
+  q[0] = q0; q[1] = q1; q[2] = q2; q[3] = q3; q[4] = q4; q[5] = q5; q[6] = q6; q[7] = q7; q[8] = q8;
   if (ok) {   // ascending selection sort, eigenvector columns follow
-    for (int i = 0; i < n - 1; i++) {
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
       int k = i;
-      for (int j = i + 1; j < n; j++) if (diag[j] < diag[k]) k = j;
+      float least = diag[i];
+#pragma unroll
+      for (int j = i + 1; j < 3; j++) if (diag[j] < least) { least = diag[j]; k = j; }
       if (k > i) {
-        const float t = diag[i]; diag[i] = diag[k]; diag[k] = t;
-        for (int r = 0; r < 3; r++) { const float u = q[i * 3 + r]; q[i * 3 + r] = q[k * 3 + r]; q[k * 3 + r] = u; }
+#pragma unroll
+        for (int kk = 1; kk < 3; kk++) {
+          if (kk == k && kk > i) {
+            const float t = diag[i]; diag[i] = diag[kk]; diag[kk] = t;
+#pragma unroll
+            for (int r = 0; r < 3; r++) { const float u = q[i * 3 + r]; q[i * 3 + r] = q[kk * 3 + r]; q[kk * 3 + r] = u; }
+          }
+        }
       }
     }
   }
@@ -177,6 +205,96 @@ __host__ __device__ inline Eig3f eig3f(const float m[9]) {
   for (int i = 0; i < 9; i++) out.evecs[i] = q[i];
   out.ok = ok;
   return out;
+}
+
+// ---- orthogonal_LSQ of an ordered cloud (wrap.h:121-150) by one CTA --------------------------
+struct LsqOut {
+  double a[3], b[3], rc;
+};
+struct LsqShared {
+  float mean[3];
+  float sc[6];   // xx xy xz yy yz zz
+};
+
+__device__ __forceinline__ float tree32_combine(float acc) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) acc = __fadd_rn(acc, __shfl_down_sync(0xFFFFFFFFu, acc, o));
+  return acc;   // lane 0 holds the canonical sum
+}
+
+// meanValue of axis values get(k) (k = 0..n-1 in cloud order) by one warp: the reference's
+// sequential double sum, via the exact int64 route when it is provably identical
+template <class GetAxis>
+__device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
+  int lo = 0x7FFFFFFF, hi = -0x7FFFFFFF;
+  bool bad = false;
+  for (int k = lane; k < n; k += 32) {
+    const long long bits = __double_as_longlong(get(k));
+    const int e = (int)((bits >> 52) & 0x7FF);
+    const long long mant = bits & 0xFFFFFFFFFFFFFLL;
+    if (e == 0x7FF || (e == 0 && mant != 0)) bad = true;          // Inf/NaN/subnormal: sequential path
+    else if (e != 0) {
+      lo = min(lo, e - 1075 + (__ffsll(mant | 0x10000000000000LL) - 1));
+      hi = max(hi, e - 1023);
+    }
+  }
+  lo = __reduce_min_sync(0xFFFFFFFFu, lo);
+  hi = __reduce_max_sync(0xFFFFFFFFu, hi);
+  bad = __any_sync(0xFFFFFFFFu, bad);
+  double sum;
+  if (lo == 0x7FFFFFFF && !bad) {
+    sum = 0.0;                                                     // all zero (or n == 0)
+  } else if (!bad && hi + 1 - lo + (32 - __clz(n)) <= 53 && lo > -900 && hi < 900) {
+    const double scale = __longlong_as_double((long long)(1023 - lo) << 52);   // 2^-lo
+    long long acc = 0;
+    for (int k = lane; k < n; k += 32) acc += __double2ll_rn(__dmul_rn(get(k), scale));
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+    sum = __dmul_rn((double)acc, __longlong_as_double((long long)(1023 + lo) << 52));
+  } else {
+    sum = 0.0;
+    if (lane == 0) for (int k = 0; k < n; ++k) sum = __dadd_rn(sum, get(k));
+    sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+  }
+  return n > 0 ? __ddiv_rn(sum, (double)n) : sum;
+}
+
+// get(k, c): coordinate c of the k-th point of the cloud.  blockDim.x a multiple of 32; all
+// threads of the CTA call it; ends with a barrier (out and s are shared memory).
+template <class Get>
+__device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *out) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+  for (int q = warp; q < 6; q += nwarps) {
+    if (q < 3) {                      // colwise().mean() of the float copy (wrap.h:129-137)
+      float acc = 0.0f;
+      for (int k = lane; k < n; k += 32) acc = __fadd_rn(acc, (float)get(k, q));
+      acc = tree32_combine(acc);
+      if (lane == 0) s.mean[q] = __fdiv_rn(acc, (float)n);
+    } else {                          // meanValue (lib/pointcloud.cpp:29-38)
+      const int c = q - 3;
+      const double m = mean_axis_warp([&](int k) { return get(k, c); }, n, lane);
+      if (lane == 0) out->a[c] = m;
+    }
+  }
+  __syncthreads();
+  for (int q = warp; q < 6; q += nwarps) {   // centred^T * centred (wrap.h:137-138)
+    const int c0 = q < 3 ? 0 : q < 5 ? 1 : 2, c1 = q < 3 ? q : q < 5 ? q - 2 : 2;
+    const float m0 = s.mean[c0], m1 = s.mean[c1];
+    float acc = 0.0f;
+    for (int k = lane; k < n; k += 32)
+      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn((float)get(k, c0), m0), __fsub_rn((float)get(k, c1), m1)));
+    acc = tree32_combine(acc);
+    if (lane == 0) s.sc[q] = acc;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const float *sc = s.sc;
+    const float m[9] = {sc[0], sc[1], sc[2], sc[1], sc[3], sc[4], sc[2], sc[4], sc[5]};
+    const Eig3f e = eig3f(m);
+    out->b[0] = e.evecs[6]; out->b[1] = e.evecs[7]; out->b[2] = e.evecs[8];   // last column, wrap.h:146
+    out->rc = (double)e.evals[2];
+  }
+  __syncthreads();
 }
 
 }  // namespace h3d

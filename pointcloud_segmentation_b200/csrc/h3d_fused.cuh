@@ -34,13 +34,22 @@ struct FusedArgs {
   unsigned *bar;              // zeroed grid-barrier counter
   int *overflow;              // set to 1 when an inlier set does not fit the scratch area
   int n_own_max;              // records per CTA (multiple of kResG)
+  unsigned long long *prof;   // measurement hook (nullable): [it][cta][kProfSlots] globaltimer stamps
+  int prof_iters;
 };
+constexpr int kProfSlots = 10;
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 
 struct FusedShared {
   ResShared res;              // first vote (vote_resident)
   double a[3], b[3];          // current line
   LsqOut lsq;
-  float mean_s[12];
+  LsqShared lsq_s;
   unsigned long long key;
   unsigned long long warp_key[kResWarps];
   int slot_base[16];          // ordered-compaction offsets of the point slots
@@ -64,55 +73,6 @@ __device__ __forceinline__ void grid_sync(unsigned *bar, unsigned &target, unsig
   }
   __syncthreads();
 }
-
-// orthogonal_LSQ over the inlier coordinates staged in shared memory (same order and operations as
-// lsq_block / the oracle).  prod: 6 x 512 floats of scratch.
-__device__ inline void lsq_shared(const double *ypx, const double *ypy, const double *ypz, int n, float *prod,
-                                  float *mean_s, LsqOut *out) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (warp < 2 && lane < 3) {
-    const double *arr = lane == 0 ? ypx : lane == 1 ? ypy : ypz;
-    if (warp == 0) {           // meanValue: sequential double sum (lib/pointcloud.cpp:29-38)
-      double acc = 0.0;
-      for (int k = 0; k < n; ++k) acc = __dadd_rn(acc, arr[k]);
-      out->a[lane] = n > 0 ? __ddiv_rn(acc, (double)n) : acc;
-    } else {                   // colwise().mean() of the float copy (wrap.h:129-137)
-      float acc = 0.0f;
-      for (int k = 0; k < n; ++k) acc = __fadd_rn(acc, (float)arr[k]);
-      mean_s[lane] = __fdiv_rn(acc, (float)n);
-    }
-  }
-  __syncthreads();
-  const float m0 = mean_s[0], m1 = mean_s[1], m2 = mean_s[2];
-  float acc = 0.0f;
-  for (int c0 = 0; c0 < n; c0 += kResThreads) {
-    const int k = c0 + tid;
-    if (k < n) {
-      const float cx = __fsub_rn((float)ypx[k], m0), cy = __fsub_rn((float)ypy[k], m1), cz = __fsub_rn((float)ypz[k], m2);
-      prod[0 * kResThreads + tid] = __fmul_rn(cx, cx); prod[1 * kResThreads + tid] = __fmul_rn(cx, cy);
-      prod[2 * kResThreads + tid] = __fmul_rn(cx, cz); prod[3 * kResThreads + tid] = __fmul_rn(cy, cy);
-      prod[4 * kResThreads + tid] = __fmul_rn(cy, cz); prod[5 * kResThreads + tid] = __fmul_rn(cz, cz);
-    }
-    __syncthreads();
-    if (warp == 0 && lane < 6) {
-      const int cnt = min(kResThreads, n - c0);
-      const float *row = prod + lane * kResThreads;
-      for (int q = 0; q < cnt; ++q) acc = __fadd_rn(acc, row[q]);
-    }
-    __syncthreads();
-  }
-  if (warp == 0 && lane < 6) mean_s[4 + lane] = acc;   // xx xy xz yy yz zz
-  __syncthreads();
-  if (tid == 0) {
-    const float *sc = mean_s + 4;
-    const float m[9] = {sc[0], sc[1], sc[2], sc[1], sc[3], sc[4], sc[2], sc[4], sc[5]};
-    const Eig3f e = eig3f(m);
-    out->b[0] = e.evecs[6]; out->b[1] = e.evecs[7]; out->b[2] = e.evecs[8];
-    out->rc = (double)e.evals[2];
-  }
-  __syncthreads();
-}
-
 
 // votes of all (live) register points for one direction into the plane at shared address plane_sa
 template <int P>
@@ -254,7 +214,12 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   unsigned long long revotes = 0;
   __syncthreads();
 
+  auto stamp = [&](int slot, unsigned long long extra) {
+    if (A.prof && tid == 0 && it < A.prof_iters)
+      A.prof[((size_t)it * n_cta + cta) * kProfSlots + slot] = extra ? extra : globaltimer_ns();
+  };
   for (;;) {
+    stamp(0, 0);
     // ---- publish this CTA's best record, meet the others, read the winner (K2) -----------------------
     {
       unsigned long long k = 0;
@@ -264,7 +229,9 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
       }
       k = block_max_u64(k, sh.warp_key);
       if (tid == 0) atomicMax(&A.gbest[it], k);
+      stamp(1, 0);
       grid_sync(A.bar, bar_target, (unsigned)n_cta);
+      stamp(2, 0);
       if (tid == 0) {
         const unsigned long long key = *reinterpret_cast<volatile unsigned long long *>(&A.gbest[it]);
         const unsigned votes = (unsigned)(key >> 32);
@@ -291,7 +258,9 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     if (rec && tid == 0) { R->n1 = (unsigned)ny1; R->off1 = pool_used; }
     pool_used = min(pool_used + (unsigned)ny1, cfg.pool_cap);
     if (rec && tid == 0) R->off2 = pool_used;
-    lsq_shared(ypx, ypy, ypz, ny1, prod, sh.mean_s, &sh.lsq);
+    stamp(3, 0);
+    lsq_cta([&](int k, int c) { return (c == 0 ? ypx : c == 1 ? ypy : ypz)[k]; }, ny1, sh.lsq_s, &sh.lsq);
+    stamp(4, 0);
     if (tid == 0) for (int c = 0; c < 3; ++c) { sh.a[c] = sh.lsq.a[c]; sh.b[c] = sh.lsq.b[c]; }
     if (rec && tid == 0) { for (int c = 0; c < 3; ++c) { R->a1[c] = sh.lsq.a[c]; R->b1[c] = sh.lsq.b[c]; } R->rc1 = sh.lsq.rc; }
     __syncthreads();
@@ -307,17 +276,19 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
       pool_used = min(pool_used + (unsigned)ny2, cfg.pool_cap);
       if ((unsigned)ny2 < (unsigned)cfg.minvotes) status = 2;                              // wrap.h:251-252
     }
+    stamp(5, 0);
     if (!status) {
-      lsq_shared(ypx, ypy, ypz, ny2, prod, sh.mean_s, &sh.lsq);
+      lsq_cta([&](int k, int c) { return (c == 0 ? ypx : c == 1 ? ypy : ypz)[k]; }, ny2, sh.lsq_s, &sh.lsq);
       if (rec && tid == 0) { for (int c = 0; c < 3; ++c) { R->a2[c] = sh.lsq.a[c]; R->b2[c] = sh.lsq.b[c]; } R->rc2 = sh.lsq.rc; }
       if (sh.lsq.rc == 0.0) status = 3;                                                    // wrap.h:255
     }
+    stamp(6, 0);
     if (status) { if (rec && tid == 0) R->status = (unsigned)status; ++it; break; }
     if (rec && tid == 0) for (int c = 0; c < 3; ++c) R->a2[c] = __dadd_rn(sh.lsq.a[c], cfg.shift[c]);   // wrap.h:257
-    ++n_lines; ++it;
+    ++n_lines;
     live &= ~m2;                                                                           // X.removePoints(Y)
     n_alive -= ny2;
-    if (!((n_alive > 1) && (cfg.nlines_max == 0 || cfg.nlines_max > n_lines))) break;      // wrap.h:341-342
+    if (!((n_alive > 1) && (cfg.nlines_max == 0 || cfg.nlines_max > n_lines))) { ++it; break; }     // wrap.h:341-342
 
     // ---- hough->subtract(Y) for the own directions (K4): Y is still in the scratch area ---------------
     {
@@ -337,6 +308,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
       }
     }
     __syncthreads();
+    stamp(7, 0);
     // give the plane area back: zero what the scratch used
     for (int q = tid; q < max_scratch; q += kResThreads) { ypx[q] = 0.0; ypy[q] = 0.0; ypz[q] = 0.0; }
     for (int q = tid; q < 6 * kResThreads; q += kResThreads) prod[q] = 0.0f;
@@ -356,6 +328,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
       __syncthreads();
     }
     const int nlist = sh.nlist;
+    stamp(8, (unsigned long long)nlist + 1);
     revotes += (unsigned long long)nlist * (unsigned long long)n_alive;
     for (int b0 = 0; b0 < nlist; b0 += 2 * G) {
       const int nb = min(2 * G, nlist - b0);
@@ -384,6 +357,8 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
       }
       __syncthreads();
     }
+    stamp(9, 0);
+    ++it;
   }
   // ---- results --------------------------------------------------------------------------------------
   if (tid == 0) {

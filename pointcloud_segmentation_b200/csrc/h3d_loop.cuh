@@ -186,74 +186,9 @@ __global__ void __launch_bounds__(1024, 1) loop_compact_kernel(const HoughDev h,
   }
 }
 
-// ---- orthogonal_LSQ over an ordered index list (wrap.h:121-150) ------------------------------
-// 2 warps.  Phase A: warp 0 lanes 0..2 carry the sequential DOUBLE sums of the anchor
-// (meanValue, lib/pointcloud.cpp:29-38), warp 1 lanes 0..2 the sequential FLOAT sums of the
-// column means (wrap.h:137).  Phase B: warp 0 lanes 0..5 carry the six sequential float sums of
-// the centred scatter matrix (wrap.h:138).  32 points are staged per step.
-struct LsqOut {
-  double a[3], b[3], rc;
-};
-
-__device__ inline void lsq_block(const double *__restrict__ px, const double *__restrict__ py,
-                                 const double *__restrict__ pz, const int *__restrict__ idx, int n,
-                                 double (*sd)[33], float (*sf)[33], float *mean_s, LsqOut *out) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double acc_d = 0.0;
-  float acc_f = 0.0f;
-  for (int base = 0; base < n; base += 32) {
-    const int cnt = min(32, n - base);
-    if (lane < cnt) {
-      const int i = idx ? idx[base + lane] : base + lane;
-      const double x = px[i], y = py[i], z = pz[i];
-      if (warp == 0) { sd[0][lane] = x; sd[1][lane] = y; sd[2][lane] = z; }
-      else { sf[0][lane] = (float)x; sf[1][lane] = (float)y; sf[2][lane] = (float)z; }
-    }
-    __syncwarp();
-    if (lane < 3) {
-      if (warp == 0) for (int k = 0; k < cnt; ++k) acc_d = __dadd_rn(acc_d, sd[lane][k]);
-      else for (int k = 0; k < cnt; ++k) acc_f = __fadd_rn(acc_f, sf[lane][k]);
-    }
-    __syncwarp();
-  }
-  if (lane < 3) {
-    if (warp == 0) out->a[lane] = n > 0 ? __ddiv_rn(acc_d, (double)n) : acc_d;
-    else mean_s[lane] = __fdiv_rn(acc_f, (float)n);
-  }
-  __syncthreads();
-  if (warp == 0) {
-    const float m0 = mean_s[0], m1 = mean_s[1], m2 = mean_s[2];
-    float acc = 0.0f;
-    for (int base = 0; base < n; base += 32) {
-      const int cnt = min(32, n - base);
-      if (lane < cnt) {
-        const int i = idx ? idx[base + lane] : base + lane;
-        const float cx = __fsub_rn((float)px[i], m0), cy = __fsub_rn((float)py[i], m1), cz = __fsub_rn((float)pz[i], m2);
-        sf[0][lane] = __fmul_rn(cx, cx); sf[1][lane] = __fmul_rn(cx, cy); sf[2][lane] = __fmul_rn(cx, cz);
-        sf[3][lane] = __fmul_rn(cy, cy); sf[4][lane] = __fmul_rn(cy, cz); sf[5][lane] = __fmul_rn(cz, cz);
-      }
-      __syncwarp();
-      if (lane < 6) for (int k = 0; k < cnt; ++k) acc = __fadd_rn(acc, sf[lane][k]);
-      __syncwarp();
-    }
-    if (lane < 6) mean_s[4 + lane] = acc;   // xx xy xz yy yz zz
-    __syncwarp();
-    if (lane == 0) {
-      const float *sc = mean_s + 4;
-      const float m[9] = {sc[0], sc[1], sc[2], sc[1], sc[3], sc[4], sc[2], sc[4], sc[5]};
-      const Eig3f e = eig3f(m);
-      out->b[0] = e.evecs[6]; out->b[1] = e.evecs[7]; out->b[2] = e.evecs[8];   // last column
-      out->rc = (double)e.evals[2];
-    }
-  }
-  __syncthreads();
-}
-
 // pass 1: first LSQ (break on rc == 0); pass 2: minvotes test, second LSQ, accept the line
-__global__ void __launch_bounds__(64, 1) loop_lsq_kernel(const HoughDev h, LoopBuffers lb, int pass) {
-  __shared__ double sd[3][33];
-  __shared__ float sf[6][33];
-  __shared__ float mean_s[12];
+__global__ void __launch_bounds__(192, 1) loop_lsq_kernel(const HoughDev h, LoopBuffers lb, int pass) {
+  __shared__ LsqShared sh;
   __shared__ LsqOut out;
   LoopState &s = *lb.st;
   if (s.done) return;
@@ -264,7 +199,10 @@ __global__ void __launch_bounds__(64, 1) loop_lsq_kernel(const HoughDev h, LoopB
     if (threadIdx.x == 0) { if (r) r->status = 2; s.n_iters++; s.done = 1; }
     return;
   }
-  lsq_block(h.px, h.py, h.pz, lb.yidx, s.ny, sd, sf, mean_s, &out);
+  {
+    const int *idx = lb.yidx;
+    lsq_cta([&](int k, int c) { return (c == 0 ? h.px : c == 1 ? h.py : h.pz)[idx[k]]; }, s.ny, sh, &out);
+  }
   if (threadIdx.x != 0) return;
   for (int c = 0; c < 3; ++c) { s.a[c] = out.a[c]; s.b[c] = out.b[c]; }
   if (pass == 1) {

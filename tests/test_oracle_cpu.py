@@ -130,3 +130,18 @@ def test_product_fails_loudly_without_gpu(h3d):
         h3d.init_space(2)
     with pytest.raises(h3d.H3dError):
         h3d.hough3dlines(np.random.default_rng(0).standard_normal((10, 3)), 2, 0.1, 2, 2)
+
+
+def test_product_eigensolver_matches_oracle_on_host(tmp_path):
+    """eig3f of the product (csrc/h3d_fit.cuh, its __host__ side) vs the oracle's h3do_eig3f."""
+    import shutil
+    import subprocess
+    if not shutil.which("nvcc"):
+        pytest.skip("nvcc not available")
+    exe = str(tmp_path / "eig_check")
+    subprocess.run(["nvcc", "-O2", "-std=c++17", "-fmad=false", "-gencode", "arch=compute_100a,code=sm_100a",
+                    "-Xcompiler", "-ffp-contract=off", "-o", exe, os.path.join(ROOT, "tests", "cpp", "eig_host_check.cu"),
+                    os.path.join(ROOT, "oracle", "h3d_oracle.c"), "-lm", "-lpthread"], check=True,
+                   capture_output=True)
+    r = subprocess.run([exe, "100000"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
