@@ -3,6 +3,7 @@
 // needs a CUDA device and fails with H3D_ERR_CUDA otherwise.
 #include "../../include/h3d.h"
 
+#include <cfloat>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -731,6 +732,7 @@ struct FrameCtx {
   size_t cap = 0, iters_cap = 0, pool_cap = 0, in_bytes = 0;
   void *in_dev = nullptr;
   unsigned *orig = nullptr;
+  unsigned *orig2 = nullptr;             // 2*cap: re-packed numbering of the fused loop
   unsigned char *flags = nullptr;
   int *yidx = nullptr;
   double *ypx = nullptr, *ypy = nullptr, *ypz = nullptr;
@@ -754,7 +756,7 @@ struct FrameCtx {
   ~FrameCtx() { release(); }
   void release() {
     if (hg) { h3d_destroy(hg); hg = nullptr; }
-    cudaFree(in_dev); cudaFree(orig); cudaFree(flags); cudaFree(yidx);
+    cudaFree(in_dev); cudaFree(orig); cudaFree(orig2); cudaFree(flags); cudaFree(yidx);
     cudaFree(ypx); cudaFree(ypy); cudaFree(ypz);
     cudaFree(iters_dev); cudaFree(pool_dev); cudaFree(st_dev); cudaFree(prep_dev);
     cudaFree(gbest); cudaFree(sync_dev); cudaFreeHost(sync_host); cudaFree(prof_dev);
@@ -762,7 +764,7 @@ struct FrameCtx {
     gbest = nullptr; sync_dev = nullptr; sync_host = nullptr; gbest_cap = 0;
     cudaFreeHost(st_host); cudaFreeHost(prep_host);
     for (auto &e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
-    in_dev = nullptr; orig = nullptr; flags = nullptr; yidx = nullptr; ypx = ypy = ypz = nullptr;
+    in_dev = nullptr; orig = nullptr; orig2 = nullptr; flags = nullptr; yidx = nullptr; ypx = ypy = ypz = nullptr;
     iters_dev = nullptr; pool_dev = nullptr; st_dev = nullptr; prep_dev = nullptr;
     st_host = nullptr; prep_host = nullptr;
     cap = iters_cap = pool_cap = in_bytes = 0; granularity = ~0u;
@@ -788,9 +790,10 @@ int frame_ensure(FrameCtx &f, unsigned g, size_t n, size_t in_bytes, size_t max_
   if (n > f.cap) {
     size_t cap = f.cap ? f.cap : 8192;
     while (cap < n) cap *= 2;
-    cudaFree(f.orig); cudaFree(f.flags); cudaFree(f.yidx); cudaFree(f.ypx); cudaFree(f.ypy); cudaFree(f.ypz);
-    f.orig = nullptr; f.flags = nullptr; f.yidx = nullptr; f.ypx = f.ypy = f.ypz = nullptr; f.cap = 0;
+    cudaFree(f.orig); cudaFree(f.orig2); cudaFree(f.flags); cudaFree(f.yidx); cudaFree(f.ypx); cudaFree(f.ypy); cudaFree(f.ypz);
+    f.orig = nullptr; f.orig2 = nullptr; f.flags = nullptr; f.yidx = nullptr; f.ypx = f.ypy = f.ypz = nullptr; f.cap = 0;
     H3D_CUDA(cudaMalloc(&f.orig, cap * sizeof(unsigned)));
+    H3D_CUDA(cudaMalloc(&f.orig2, 2 * cap * sizeof(unsigned)));
     H3D_CUDA(cudaMalloc(&f.flags, cap));
     H3D_CUDA(cudaMalloc(&f.yidx, cap * sizeof(int)));
     H3D_CUDA(cudaMalloc(&f.ypx, cap * sizeof(double)));
@@ -859,8 +862,23 @@ int launch_fused_t(FrameCtx &f, const FusedArgs &args, size_t smem) {
   return H3D_OK;
 }
 
+// largest x with sqrt_rn(x) <= dx: pointsCloseToLine's `sqrt(nn) <= dx` becomes `nn <= x`
+// (sqrt_rn is monotonic, so the two tests accept exactly the same nn)
+static double sqrt_le_threshold(double dx) {
+  if (!(dx >= 0.0)) return -1.0;
+  double c = dx * dx;
+  if (std::isinf(c)) return DBL_MAX;
+  while (c > 0.0 && sqrt(c) > dx) c = nextafter(c, 0.0);
+  for (;;) {
+    const double up = nextafter(c, INFINITY);
+    if (std::isinf(up) || sqrt(up) > dx) break;
+    c = up;
+  }
+  return c;
+}
+
 // returns H3D_OK with *launched = false when the frame does not qualify for the fused kernel
-int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, bool *launched) {
+int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double opt_dx, bool *launched) {
   *launched = false;
   h3d_hough *h = f.hg;
   const HoughDev &hd = h->d;
@@ -868,25 +886,32 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, bool *l
   const int groups = (hd.dir_count + kResG - 1) / kResG;
   const int n_own = ((groups + h->dev.sm_count - 1) / h->dev.sm_count) * kResG;
   const size_t plane_bytes = ((size_t)2 * kResG * hd.plane_stride + 4) * sizeof(unsigned);
-  const size_t smem = plane_bytes + (size_t)n_own * (5 * sizeof(double) + 4 * sizeof(unsigned));
+  const size_t tables = (size_t)n_own * 56;
   cudaFuncAttributes fa;
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel<4>));
-  if (smem + fa.sharedSizeBytes > h->dev.smem_optin) return H3D_OK;
-  if ((2 * kResG * (size_t)hd.plane_stride * 4 - 6 * kResThreads * 4) / 24 < 256) return H3D_OK;   // scratch too small
+  if (h->dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
+  const size_t smem = ((h->dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;   // everything the SM offers
+  if (tables + plane_bytes > smem) return H3D_OK;
+  const size_t scratch = smem - tables;
+  if (scratch / 60 < 256 || scratch < (size_t)hd.n * 8) return H3D_OK;              // scratch too small
   const size_t iters = (size_t)(opt_nlines > 0 ? opt_nlines : hd.n) + 2;
-  if (iters > f.gbest_cap) {
+  if (2 * iters > f.gbest_cap) {
     cudaFree(f.gbest); f.gbest = nullptr; f.gbest_cap = 0;
-    H3D_CUDA(cudaMalloc(&f.gbest, iters * sizeof(unsigned long long)));
-    f.gbest_cap = iters;
+    H3D_CUDA(cudaMalloc(&f.gbest, 2 * iters * sizeof(unsigned long long)));
+    f.gbest_cap = 2 * iters;
   }
   cudaStream_t s = h->stream;
-  H3D_CUDA(cudaMemsetAsync(f.gbest, 0, iters * sizeof(unsigned long long), s));
+  H3D_CUDA(cudaMemsetAsync(f.gbest, 0, 2 * iters * sizeof(unsigned long long), s));
   H3D_CUDA(cudaMemsetAsync(f.sync_dev, 0, 4 * sizeof(unsigned), s));
   FusedArgs a;
   a.h = hd; a.h.n_dev = nullptr;
   a.st = lb.st; a.iters = lb.iters; a.pool = lb.pool; a.orig = lb.orig; a.dirs = lb.dirs;
-  a.gbest = f.gbest; a.bar = f.sync_dev; a.overflow = reinterpret_cast<int *>(f.sync_dev + 1);
+  a.orig_tmp[0] = f.orig2; a.orig_tmp[1] = f.orig2 + f.cap;
+  a.xchg = f.gbest; a.bar = f.sync_dev; a.overflow = reinterpret_cast<int *>(f.sync_dev + 1);
   a.n_own_max = n_own;
+  a.smem_bytes = (unsigned)smem;
+  a.near_t = sqrt_le_threshold(opt_dx);
+  a.cell_off = hd.max_x / hd.dx + 0.5;
   a.prof = f.prof_dev; a.prof_iters = f.prof_iters;
   if (f.prof_dev)
     H3D_CUDA(cudaMemsetAsync(f.prof_dev, 0, (size_t)f.prof_iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long), s));
@@ -961,7 +986,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   // fast path: first vote + the whole loop in one persistent cooperative kernel
   bool fused = false;
   H3D_CUDA(cudaEventRecord(f.ev[4], s));
-  H3D_TRY(try_launch_fused(f, lb, opt_nlines, &fused));
+  H3D_TRY(try_launch_fused(f, lb, opt_nlines, opt_dx, &fused));
   if (fused) {
     H3D_CUDA(cudaEventRecord(f.ev[2], s));
     H3D_CUDA(cudaStreamSynchronize(s));

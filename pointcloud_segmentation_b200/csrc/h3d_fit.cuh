@@ -262,7 +262,10 @@ __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
 // get(k, c): coordinate c of the k-th point of the cloud.  blockDim.x a multiple of 32; all
 // threads of the CTA call it; ends with a barrier (out and s are shared memory).
 template <class Get>
-__device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *out) {
+__device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *out, unsigned long long *dbg = nullptr) {
+  auto dbg_stamp = [&](int k) {
+    if (dbg && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); dbg[k] = t; }
+  };
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   for (int q = warp; q < 6; q += nwarps) {
     if (q < 3) {                      // colwise().mean() of the float copy (wrap.h:129-137)
@@ -277,6 +280,7 @@ __device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *ou
     }
   }
   __syncthreads();
+  dbg_stamp(0);
   for (int q = warp; q < 6; q += nwarps) {   // centred^T * centred (wrap.h:137-138)
     const int c0 = q < 3 ? 0 : q < 5 ? 1 : 2, c1 = q < 3 ? q : q < 5 ? q - 2 : 2;
     const float m0 = s.mean[c0], m1 = s.mean[c1];
@@ -287,6 +291,7 @@ __device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *ou
     if (lane == 0) s.sc[q] = acc;
   }
   __syncthreads();
+  dbg_stamp(1);
   if (tid == 0) {
     const float *sc = s.sc;
     const float m[9] = {sc[0], sc[1], sc[2], sc[1], sc[3], sc[4], sc[2], sc[4], sc[5]};
@@ -294,6 +299,7 @@ __device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *ou
     out->b[0] = e.evecs[6]; out->b[1] = e.evecs[7]; out->b[2] = e.evecs[8];   // last column, wrap.h:146
     out->rc = (double)e.evals[2];
   }
+  dbg_stamp(2);
   __syncthreads();
 }
 
