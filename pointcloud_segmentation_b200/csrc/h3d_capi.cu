@@ -893,7 +893,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   const size_t smem = ((h->dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;   // everything the SM offers
   if (tables + plane_bytes > smem) return H3D_OK;
   const size_t scratch = smem - tables;
-  if (scratch / 60 < 256 || scratch < (size_t)hd.n * 8) return H3D_OK;              // scratch too small
+  if (scratch / 36 < 256 || scratch < ((size_t)hd.n + kResThreads) * 24) return H3D_OK;              // scratch too small
   const size_t iters = (size_t)(opt_nlines > 0 ? opt_nlines : hd.n) + 2;
   if (2 * iters > f.gbest_cap) {
     cudaFree(f.gbest); f.gbest = nullptr; f.gbest_cap = 0;

@@ -132,12 +132,12 @@ __device__ __forceinline__ int for_each_ordered(unsigned m, int (*warp_cnt)[kRes
 }
 
 // Scratch view of the idle plane area (+ whatever dynamic shared memory lies behind it):
-// the current inlier set Y in cloud order, as doubles, as floats, and the six centred products.
+// the current inlier set Y in cloud order, as doubles and as float casts.
 struct FusedScratch {
-  double *yd[3];
-  float *yf[3];
-  float *prod[6];
+  double *base;   // shared memory
   int cap;
+  __device__ __forceinline__ double *yd(int c) const { return base + (size_t)c * cap; }
+  __device__ __forceinline__ float *yf(int c) const { return reinterpret_cast<float *>(base + (size_t)3 * cap) + (size_t)c * cap; }
 };
 
 // frame-level fixed-point facts for the exact parallel anchor (see h3d_fit.cuh): every
@@ -156,9 +156,10 @@ __device__ __forceinline__ void lsq_sums_fused(const FusedScratch &S, int n, con
   if (fast) {             // exact int64 sums, any order (provably the sequential double sum)
     const double scale = __longlong_as_double((long long)(1023 - fx.lo) << 52);   // 2^-lo
     long long acc[3] = {0, 0, 0};
+#pragma unroll 1
     for (int k = tid; k < n; k += kResThreads) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) acc[c] += __double2ll_rn(__dmul_rn(S.yd[c][k], scale));
+      for (int c = 0; c < 3; ++c) acc[c] += __double2ll_rn(__dmul_rn(S.yd(c)[k], scale));
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -168,49 +169,49 @@ __device__ __forceinline__ void lsq_sums_fused(const FusedScratch &S, int n, con
     }
   } else if (warp >= 3 && warp < 6) {
     const int c = warp - 3;
-    const double *src = S.yd[c];
+    const double *src = S.yd(c);
     const double m = mean_axis_warp([&](int k) { return src[k]; }, n, lane);
     if (lane == 0) sh.lsq.a[c] = m;
   }
   if (warp < 3) {          // colwise().mean() of the float copy (wrap.h:129-137), TREE32
-    const float *src = S.yf[warp];
+    const float *src = S.yf(warp);
     float acc = 0.0f;
     int k = lane;
+#pragma unroll 1
     for (; k + 96 < n; k += 128) {
       const float v0 = src[k], v1 = src[k + 32], v2 = src[k + 64], v3 = src[k + 96];
       acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v0), v1), v2), v3);
     }
+#pragma unroll 1
     for (; k < n; k += 32) acc = __fadd_rn(acc, src[k]);
     acc = tree32_combine(acc);
     if (lane == 0) sh.lsq_s.mean[warp] = __fdiv_rn(acc, (float)n);
   }
   __syncthreads();
-  {                        // centred products, 512-wide
-    const float m0 = sh.lsq_s.mean[0], m1 = sh.lsq_s.mean[1], m2 = sh.lsq_s.mean[2];
-    for (int k = tid; k < n; k += kResThreads) {
-      const float cx = __fsub_rn(S.yf[0][k], m0), cy = __fsub_rn(S.yf[1][k], m1), cz = __fsub_rn(S.yf[2][k], m2);
-      S.prod[0][k] = __fmul_rn(cx, cx); S.prod[1][k] = __fmul_rn(cx, cy); S.prod[2][k] = __fmul_rn(cx, cz);
-      S.prod[3][k] = __fmul_rn(cy, cy); S.prod[4][k] = __fmul_rn(cy, cz); S.prod[5][k] = __fmul_rn(cz, cz);
-    }
-    if (fast && tid < 3) {
-      long long s = 0;
-      for (int w = 0; w < kResWarps; ++w) s += sh.ipart[w][tid];
-      const double sum = __dmul_rn((double)s, __longlong_as_double((long long)(1023 + fx.lo) << 52));
-      sh.lsq.a[tid] = n > 0 ? __ddiv_rn(sum, (double)n) : sum;
-    }
-  }
-  __syncthreads();
-  if (warp < 6) {          // centred^T * centred (wrap.h:138), TREE32 per entry
-    const float *src = S.prod[warp];
+  if (warp < 6) {          // centred^T * centred (wrap.h:137-138), TREE32 per entry, products on the fly
+    const int c0 = warp < 3 ? 0 : warp < 5 ? 1 : 2, c1 = warp < 3 ? warp : warp < 5 ? warp - 2 : 2;
+    const float *s0 = S.yf(c0), *s1 = S.yf(c1);
+    const float m0 = sh.lsq_s.mean[c0], m1 = sh.lsq_s.mean[c1];
     float acc = 0.0f;
     int k = lane;
+#pragma unroll 1
     for (; k + 96 < n; k += 128) {
-      const float v0 = src[k], v1 = src[k + 32], v2 = src[k + 64], v3 = src[k + 96];
-      acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v0), v1), v2), v3);
+      const float u0 = s0[k], u1 = s0[k + 32], u2 = s0[k + 64], u3 = s0[k + 96];
+      const float w0 = s1[k], w1 = s1[k + 32], w2 = s1[k + 64], w3 = s1[k + 96];
+      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u0, m0), __fsub_rn(w0, m1)));
+      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u1, m0), __fsub_rn(w1, m1)));
+      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u2, m0), __fsub_rn(w2, m1)));
+      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u3, m0), __fsub_rn(w3, m1)));
     }
-    for (; k < n; k += 32) acc = __fadd_rn(acc, src[k]);
+#pragma unroll 1
+    for (; k < n; k += 32) acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(s0[k], m0), __fsub_rn(s1[k], m1)));
     acc = tree32_combine(acc);
     if (lane == 0) sh.lsq_s.sc[warp] = acc;
+  } else if (warp == 6 && fast && lane < 3) {
+    long long s = 0;
+    for (int w = 0; w < kResWarps; ++w) s += sh.ipart[w][lane];
+    const double sum = __dmul_rn((double)s, __longlong_as_double((long long)(1023 + fx.lo) << 52));
+    sh.lsq.a[lane] = n > 0 ? __ddiv_rn(sum, (double)n) : sum;
   }
   __syncthreads();
 }
@@ -266,23 +267,24 @@ __device__ __forceinline__ void vote_one_direction(const HoughDev &h, const Fast
 // range of t = b*(p - a) over Y into sh.tmin_i / sh.tmax_i.  Ends with a barrier.
 template <int P>
 __device__ __forceinline__ unsigned inlier_pass(const double (&px)[P], const double (&py)[P], const double (&pz)[P],
-                                                unsigned live, const double (&a)[3], const double (&b)[3],
+                                                unsigned live, int used_slots, const double (&a)[3], const double (&b)[3],
                                                 double near_t, FusedShared &sh, const FusedScratch &S, bool track_t,
                                                 bool to_pool, unsigned *pool, unsigned pool_base, unsigned pool_cap,
-                                                const unsigned *orig, int *ny_out) {
+                                                const unsigned *orig, int *ny_out, unsigned long long *dbg) {
   const int tid = threadIdx.x;
   unsigned m = 0;
   float tlo = 3.0e38f, thi = -3.0e38f;
 #pragma unroll
   for (int p = 0; p < P; ++p) {
-    if (__all_sync(0xFFFFFFFFu, (live >> p) == 0)) break;
-    double t;
-    if (point_near_line_t(px[p], py[p], pz[p], a, b, near_t, &t) && ((live >> p) & 1u)) {
-      m |= 1u << p;
-      const float tf = (float)t;
-      tlo = fminf(tlo, tf); thi = fmaxf(thi, tf);
+    if (p < used_slots) {   // uniform
+      double t;
+      if (point_near_line_t(px[p], py[p], pz[p], a, b, near_t, &t) && ((live >> p) & 1u)) {
+        m |= 1u << p;
+        if (track_t) { const float tf = (float)t; tlo = fminf(tlo, tf); thi = fmaxf(thi, tf); }
+      }
     }
   }
+  if (dbg && tid == 0) *dbg = globaltimer_ns();
   if (track_t) {
     const int lo_i = __reduce_min_sync(0xFFFFFFFFu, float_ordered(tlo));
     const int hi_i = __reduce_max_sync(0xFFFFFFFFu, float_ordered(thi));
@@ -291,8 +293,8 @@ __device__ __forceinline__ unsigned inlier_pass(const double (&px)[P], const dou
   const int cap = S.cap;
   const int ny = for_each_ordered<P>(m, sh.warp_cnt, [&](int p, int pos) {
     if (pos < cap) {
-      S.yd[0][pos] = px[p]; S.yd[1][pos] = py[p]; S.yd[2][pos] = pz[p];
-      S.yf[0][pos] = (float)px[p]; S.yf[1][pos] = (float)py[p]; S.yf[2][pos] = (float)pz[p];
+      S.yd(0)[pos] = px[p]; S.yd(1)[pos] = py[p]; S.yd(2)[pos] = pz[p];
+      S.yf(0)[pos] = (float)px[p]; S.yf(1)[pos] = (float)py[p]; S.yf(2)[pos] = (float)pz[p];
     }
     if (to_pool && pool_base + (unsigned)pos < pool_cap) pool[pool_base + pos] = orig[tid + p * kResThreads];
   });
@@ -352,11 +354,8 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
   const unsigned dummy_sa = planes_sa + plane_words * 4u;
   FusedScratch S;
-  S.cap = (int)(((A.smem_bytes - tables_bytes) / 60u) & ~1u);
-  S.yd[0] = reinterpret_cast<double *>(planes); S.yd[1] = S.yd[0] + S.cap; S.yd[2] = S.yd[1] + S.cap;
-  S.yf[0] = reinterpret_cast<float *>(S.yd[2] + S.cap); S.yf[1] = S.yf[0] + S.cap; S.yf[2] = S.yf[1] + S.cap;
-#pragma unroll
-  for (int q = 0; q < 6; ++q) S.prod[q] = S.yf[2] + (size_t)(q + 1) * S.cap;
+  S.cap = (int)(((A.smem_bytes - tables_bytes) / 36u) & ~1u);
+  S.base = reinterpret_cast<double *>(planes);
 
   // ---- hough->add(X): every plane once (K1) ------------------------------------------------------
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
@@ -443,6 +442,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     const unsigned flat = votes ? 0xFFFFFFFFu - (unsigned)key : 0u;
     double a[3], b[3];
     line_from_index(h, A.dirs, flat, a, b);                    // Hough::getLine, lib/hough.cpp:114-132
+    stamp(14, 0);
     const bool rec = cta == 0 && tid == 0 && it < cfg.max_iters;
     h3d_iter *R = rec ? &A.iters[it] : nullptr;
     if (rec) {
@@ -452,44 +452,35 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     }
     int status = 0;
     // ---- X.pointsCloseToLine + orthogonal_LSQ, twice (K3), wrap.h:245-255 ----------------------------
-    int ny1 = 0;
-    (void)inlier_pass<P>(px, py, pz, live, a, b, A.near_t, sh, S, false, cta == 0, A.pool, pool_used, cfg.pool_cap,
-                         cur_orig, &ny1);
-    dirty_n = max(dirty_n, min(ny1, S.cap));
-    if (ny1 > S.cap) { if (tid == 0) *A.overflow = 1; break; }
-    if (rec) { R->n1 = (unsigned)ny1; R->off1 = pool_used; }
-    pool_used = min(pool_used + (unsigned)ny1, cfg.pool_cap);
-    if (rec) R->off2 = pool_used;
-    stamp(3, 0);
-    lsq_sums_fused(S, ny1, fx, sh);
-    if (tid == 0) lsq_eig(sh);
-    __syncthreads();
-    double rc = sh.lsq.rc;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) { a[c] = sh.lsq.a[c]; b[c] = sh.lsq.b[c]; }
-    if (rec) { for (int c = 0; c < 3; ++c) { R->a1[c] = a[c]; R->b1[c] = b[c]; } R->rc1 = rc; }
-    stamp(4, 0);
+    // one copy of the code for both passes (instruction-cache footprint)
     unsigned m2 = 0;
     int ny2 = 0;
     bool last = false;
-    if (rc == 0.0) status = 1;                                                             // wrap.h:248
-    if (!status) {
-      m2 = inlier_pass<P>(px, py, pz, live, a, b, A.near_t, sh, S, true, cta == 0, A.pool, pool_used, cfg.pool_cap,
-                          cur_orig, &ny2);
-      dirty_n = max(dirty_n, min(ny2, S.cap));
-      if (ny2 > S.cap) { if (tid == 0) *A.overflow = 1; break; }
-      if (rec) { R->n2 = (unsigned)ny2; R->off2 = pool_used; }
-      pool_used = min(pool_used + (unsigned)ny2, cfg.pool_cap);
-      if ((unsigned)ny2 < (unsigned)cfg.minvotes) status = 2;                              // wrap.h:251-252
-    }
-    stamp(5, 0);
-    if (!status) {
-      lsq_sums_fused(S, ny2, fx, sh);
-      stamp(6, 0);
-      last = !((n_alive - ny2 > 1) && (cfg.nlines_max == 0 || cfg.nlines_max > n_lines + 1));   // wrap.h:341-342
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+      int ny = 0;
+      const unsigned m = inlier_pass<P>(px, py, pz, live, used_slots, a, b, A.near_t, sh, S, pass == 1, cta == 0, A.pool,
+                                        pool_used, cfg.pool_cap, cur_orig, &ny,
+                                        (A.prof && it < A.prof_iters) ? A.prof + ((size_t)it * n_cta + cta) * kProfSlots + 12 + pass : nullptr);
+      dirty_n = max(dirty_n, min(ny, S.cap));
+      if (ny > S.cap) { status = 9; break; }
+      if (rec) {
+        if (pass == 0) { R->n1 = (unsigned)ny; R->off1 = pool_used; }
+        else { R->n2 = (unsigned)ny; R->off2 = pool_used; }
+      }
+      pool_used = min(pool_used + (unsigned)ny, cfg.pool_cap);
+      if (rec && pass == 0) R->off2 = pool_used;
+      if (pass == 1) {
+        m2 = m; ny2 = ny;
+        if ((unsigned)ny2 < (unsigned)cfg.minvotes) { status = 2; break; }                 // wrap.h:251-252
+        last = !((n_alive - ny2 > 1) && (cfg.nlines_max == 0 || cfg.nlines_max > n_lines + 1));   // wrap.h:341-342
+      }
+      stamp(3 + 2 * pass, 0);
+      lsq_sums_fused(S, ny, fx, sh);
+      stamp(4 + 2 * pass, 0);
       if (warp == 0) {
         if (tid == 0) lsq_eig(sh);
-      } else if (!last) {
+      } else if (pass == 1 && !last) {
         // ---- hough->subtract(Y) for the own directions (K4), overlapped with the eigen-solve ----------
         // Y (pass 2) is in the scratch area; it lies within opt_dx of the line (a, b) of pass 2
         const int ut = tid - 32, un = kResThreads - 32;
@@ -511,14 +502,20 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
           const int s = idx / ny2, e = idx - s * ny2;
           const int r = rlist[s];
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-          if (vote_cell(h, load_fast(own_coef, r), j, S.yd[0][e], S.yd[1][e], S.yd[2][e]) == rcell[r]) rstale[r] = 1;
+          if (vote_cell(h, load_fast(own_coef, r), j, S.yd(0)[e], S.yd(1)[e], S.yd(2)[e]) == rcell[r]) rstale[r] = 1;
         }
       }
       __syncthreads();
-      rc = sh.lsq.rc;
-      if (rec) { for (int c = 0; c < 3; ++c) { R->a2[c] = sh.lsq.a[c]; R->b2[c] = sh.lsq.b[c]; } R->rc2 = rc; }
-      if (rc == 0.0) status = 3;                                                           // wrap.h:255
+      const double rc = sh.lsq.rc;
+      if (rec) {
+        if (pass == 0) { for (int c = 0; c < 3; ++c) { R->a1[c] = sh.lsq.a[c]; R->b1[c] = sh.lsq.b[c]; } R->rc1 = rc; }
+        else { for (int c = 0; c < 3; ++c) { R->a2[c] = sh.lsq.a[c]; R->b2[c] = sh.lsq.b[c]; } R->rc2 = rc; }
+      }
+      if (rc == 0.0) { status = pass == 0 ? 1 : 3; break; }                                // wrap.h:248, 255
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { a[c] = sh.lsq.a[c]; b[c] = sh.lsq.b[c]; }
     }
+    if (status == 9) { if (tid == 0) *A.overflow = 1; break; }
     stamp(7, 0);
     if (status) { if (rec) R->status = (unsigned)status; ++it; break; }
     if (rec) for (int c = 0; c < 3; ++c) R->a2[c] = __dadd_rn(sh.lsq.a[c], cfg.shift[c]);   // wrap.h:257
@@ -529,40 +526,36 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
 
     // ---- give the plane area back: zero what the scratch used ----------------------------------------
     for (int q = tid; q < dirty_n; q += kResThreads) {
-      S.yd[0][q] = 0.0; S.yd[1][q] = 0.0; S.yd[2][q] = 0.0;
-      S.yf[0][q] = 0.0f; S.yf[1][q] = 0.0f; S.yf[2][q] = 0.0f;
-#pragma unroll
-      for (int c = 0; c < 6; ++c) S.prod[c][q] = 0.0f;
+      S.yd(0)[q] = 0.0; S.yd(1)[q] = 0.0; S.yd(2)[q] = 0.0;
+      S.yf(0)[q] = 0.0f; S.yf(1)[q] = 0.0f; S.yf(2)[q] = 0.0f;
     }
     dirty_n = 0;
     // ---- re-pack the live points when a register slot can be freed (order kept) ----------------------
     const int new_slots = (n_alive + kResThreads - 1) / kResThreads;
     if (new_slots < used_slots) {
+      // one ordered pass stages x, y, z (and, on CTA 0, the numbering) by new position
       double *stage = reinterpret_cast<double *>(planes);
+      const int n_old = used_slots * kResThreads;   // >= the old live count: stride of the staging arrays
+      unsigned *odst = A.orig_tmp[orig_flip];
+      const unsigned *osrc = cur_orig;
       __syncthreads();   // zero-fill above is complete before the stage is written
-#define H3D_REPACK_AXIS(ARR)                                                                         \
-      (void)for_each_ordered<P>(live, sh.warp_cnt, [&](int p, int pos) { stage[pos] = ARR[p]; });    \
-      __syncthreads();                                                                               \
-      _Pragma("unroll") for (int p = 0; p < P; ++p) {                                                \
-        const int i = tid + p * kResThreads;                                                         \
-        ARR[p] = i < n_alive ? stage[i] : 0.0;                                                       \
-      }                                                                                              \
+      (void)for_each_ordered<P>(live, sh.warp_cnt, [&](int p, int pos) {
+        stage[pos] = px[p]; stage[n_old + pos] = py[p]; stage[2 * n_old + pos] = pz[p];
+        if (cta == 0) odst[pos] = osrc[tid + p * kResThreads];
+      });
       __syncthreads();
-      H3D_REPACK_AXIS(px)
-      H3D_REPACK_AXIS(py)
-      H3D_REPACK_AXIS(pz)
-#undef H3D_REPACK_AXIS
-      if (cta == 0) {
-        unsigned *dst = A.orig_tmp[orig_flip];
-        const unsigned *src = cur_orig;
-        (void)for_each_ordered<P>(live, sh.warp_cnt, [&](int p, int pos) { dst[pos] = src[tid + p * kResThreads]; });
-        cur_orig = dst;
-        orig_flip ^= 1;
-      }
       live = 0;
 #pragma unroll
-      for (int p = 0; p < P; ++p) live |= (tid + p * kResThreads < n_alive) ? (1u << p) : 0u;
-      for (int q = tid; q < n_alive; q += kResThreads) stage[q] = 0.0;
+      for (int p = 0; p < P; ++p) {
+        const int i = tid + p * kResThreads;
+        const bool ok = i < n_alive;
+        px[p] = ok ? stage[i] : 0.0; py[p] = ok ? stage[n_old + i] : 0.0; pz[p] = ok ? stage[2 * n_old + i] : 0.0;
+        live |= ok ? (1u << p) : 0u;
+      }
+      cur_orig = odst;
+      orig_flip ^= 1;
+      __syncthreads();
+      for (int q = tid; q < n_alive; q += kResThreads) { stage[q] = 0.0; stage[n_old + q] = 0.0; stage[2 * n_old + q] = 0.0; }
       used_slots = new_slots;
     }
     stamp(10, 0);

@@ -13,7 +13,7 @@ print(res.n_input, res.n_lines, [round(u, 1) for u in pipe.timing_us()])
 t = pipe.profile_read().astype(np.int64)
 # slots: 0 start, 1 published, 2 after barrier A, 3 after inliers 1, 4 after lsq 1, 5 after inliers 2,
 #        6 after lsq-2 sums, 7 after eig || un-vote, 10 after zero/re-pack, 11 after barrier B, 8 nlist+1, 9 end
-names = ["publish", "barA", "inl1", "lsq1", "inl2", "sums2", "eig|unvote"]
+names = ["publish", "barA", "inl1", "sums1", "eig1+inl2", "sums2", "eig2|unvote"]
 for it in range(t.shape[0]):
     a = t[it]
     if a[0, 0] == 0:
@@ -21,6 +21,7 @@ for it in range(t.shape[0]):
     c0 = a[0]
     seg = [c0[k + 1] - c0[k] for k in range(7)]
     line = f"it {it:2d} cta0 us: " + " ".join(f"{n}={v/1e3:5.1f}" for n, v in zip(names, seg))
+    line += f" [line {(c0[14]-c0[2])/1e3:.1f} mask1 {(c0[12]-c0[14])/1e3:.1f} eig1+mask2 {(c0[13]-c0[4])/1e3:.1f}]"
     if a[0, 9]:
         nl = a[:, 8] - 1
         rv = (a[:, 9] - a[:, 11]) / 1e3

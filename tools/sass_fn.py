@@ -9,7 +9,7 @@ for b in blocks[1:]:
     if pat in name:
         print("Function :", name)
         for line in b.split("\n"):
-            m = re.match(r"\s+/\*([0-9a-f]{4})\*/\s+(.*?);", line)
+            m = re.match(r"\s+/\*([0-9a-f]{4,6})\*/\s+(.*?);", line)
             if m:
                 print(m.group(1), m.group(2))
         break
