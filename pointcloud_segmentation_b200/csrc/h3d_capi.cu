@@ -885,15 +885,19 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   if (!g_use_fused || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0) return H3D_OK;
   const int groups = (hd.dir_count + kResG - 1) / kResG;
   const int n_own = ((groups + h->dev.sm_count - 1) / h->dev.sm_count) * kResG;
-  const size_t plane_bytes = ((size_t)2 * kResG * hd.plane_stride + 4) * sizeof(unsigned);
+  const size_t plane_bytes = (size_t)hd.plane_stride * sizeof(unsigned);
   const size_t tables = (size_t)n_own * 56;
   cudaFuncAttributes fa;
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel<4>));
   if (h->dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   const size_t smem = ((h->dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;   // everything the SM offers
-  if (tables + plane_bytes > smem) return H3D_OK;
-  const size_t scratch = smem - tables;
-  if (scratch / 36 < 256 || scratch < ((size_t)hd.n + kResThreads) * 24) return H3D_OK;              // scratch too small
+  // first vote: 2*G planes + pad; loop: nb planes + pad + the live points (24 B) + the inlier list (4 B)
+  if (tables + 2 * kResG * plane_bytes + 16 > smem) return H3D_OK;
+  const size_t n_cap = ((size_t)hd.n + 1) & ~(size_t)1;
+  if (tables + 16 + 28 * n_cap + 2 * plane_bytes > smem) return H3D_OK;
+  size_t nb = (smem - tables - 16 - 28 * n_cap) / plane_bytes;
+  if (nb > 2 * kResG) nb = 2 * kResG;
+  nb &= ~(size_t)1;
   const size_t iters = (size_t)(opt_nlines > 0 ? opt_nlines : hd.n) + 2;
   if (2 * iters > f.gbest_cap) {
     cudaFree(f.gbest); f.gbest = nullptr; f.gbest_cap = 0;
@@ -906,10 +910,10 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   FusedArgs a;
   a.h = hd; a.h.n_dev = nullptr;
   a.st = lb.st; a.iters = lb.iters; a.pool = lb.pool; a.orig = lb.orig; a.dirs = lb.dirs;
-  a.orig_tmp[0] = f.orig2; a.orig_tmp[1] = f.orig2 + f.cap;
-  a.xchg = f.gbest; a.bar = f.sync_dev; a.overflow = reinterpret_cast<int *>(f.sync_dev + 1);
+  a.xchg = f.gbest; a.bar = f.sync_dev;
   a.n_own_max = n_own;
-  a.smem_bytes = (unsigned)smem;
+  a.nb_planes = (int)nb;
+  a.n_cap = (int)n_cap;
   a.near_t = sqrt_le_threshold(opt_dx);
   a.cell_off = hd.max_x / hd.dx + 0.5;
   a.prof = f.prof_dev; a.prof_iters = f.prof_iters;

@@ -54,20 +54,34 @@ struct Eig3f {
   int ok;
 };
 
-__host__ __device__ inline void eig_givens(float p, float q, float *c, float *s) {   // JacobiRotation::makeGivens
+// IEEE division / square root out of line on the device: eig3f has ~25 of them and runs on one
+// thread inside persistent kernels whose loop body must stay small (32 KB instruction cache)
+#ifdef __CUDA_ARCH__
+__device__ __noinline__ float eig_div_dev(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __noinline__ float eig_sqrt_dev(float a) { return __fsqrt_rn(a); }
+#define H3D_EIG_DIV(a, b) eig_div_dev((a), (b))
+#define H3D_EIG_SQRT(a) eig_sqrt_dev((a))
+#define H3D_EIG_NOINLINE __noinline__
+#else
+#define H3D_EIG_DIV(a, b) ((a) / (b))
+#define H3D_EIG_SQRT(a) sqrtf((a))
+#define H3D_EIG_NOINLINE
+#endif
+
+__host__ __device__ H3D_EIG_NOINLINE inline void eig_givens(float p, float q, float *c, float *s) {   // JacobiRotation::makeGivens
   if (q == 0.0f) { *c = p < 0.0f ? -1.0f : 1.0f; *s = 0.0f; return; }
   if (p == 0.0f) { *c = 0.0f; *s = q < 0.0f ? 1.0f : -1.0f; return; }
   if (fabsf(p) > fabsf(q)) {
-    const float t = q / p;
-    float u = sqrtf(1.0f + t * t);
+    const float t = H3D_EIG_DIV(q, p);
+    float u = H3D_EIG_SQRT(1.0f + t * t);
     if (p < 0.0f) u = -u;
-    *c = 1.0f / u;
+    *c = H3D_EIG_DIV(1.0f, u);
     *s = -t * *c;
   } else {
-    const float t = p / q;
-    float u = sqrtf(1.0f + t * t);
+    const float t = H3D_EIG_DIV(p, q);
+    float u = H3D_EIG_SQRT(1.0f + t * t);
     if (q < 0.0f) u = -u;
-    *s = -1.0f / u;
+    *s = H3D_EIG_DIV(-1.0f, u);
     *c = -t * *s;
   }
 }
@@ -77,11 +91,11 @@ __host__ __device__ inline float eig_hypot(float x, float y) {   // numext::hypo
   const float big = ax > ay ? ax : ay;
   if (big == 0.0f) return 0.0f;
   const float small = ax > ay ? ay : ax;
-  const float r = small / big;
-  return big * sqrtf(1.0f + r * r);
+  const float r = H3D_EIG_DIV(small, big);
+  return big * H3D_EIG_SQRT(1.0f + r * r);
 }
 
-__host__ __device__ inline Eig3f eig3f(const float m[9]) {
+__host__ __device__ H3D_EIG_NOINLINE inline Eig3f eig3f(const float m[9]) {
   Eig3f out;
   float a00 = m[0], a10 = m[1], a20 = m[2], a11 = m[4], a21 = m[5], a22 = m[8];
   // scale the matrix by its largest coefficient
@@ -92,7 +106,8 @@ __host__ __device__ inline Eig3f eig3f(const float m[9]) {
   if (fabsf(a21) > scale) scale = fabsf(a21);
   if (fabsf(a22) > scale) scale = fabsf(a22);
   if (scale == 0.0f) scale = 1.0f;
-  a00 /= scale; a10 /= scale; a20 /= scale; a11 /= scale; a21 /= scale; a22 /= scale;
+  a00 = H3D_EIG_DIV(a00, scale); a10 = H3D_EIG_DIV(a10, scale); a20 = H3D_EIG_DIV(a20, scale);
+  a11 = H3D_EIG_DIV(a11, scale); a21 = H3D_EIG_DIV(a21, scale); a22 = H3D_EIG_DIV(a22, scale);
 
   // tridiagonalisation: one Householder reflection on column 0
   float diag[3], sub[2];
@@ -101,10 +116,10 @@ __host__ __device__ inline Eig3f eig3f(const float m[9]) {
   if (tail_sq <= FLT_MIN) {
     diag[0] = a00; diag[1] = a11; diag[2] = a22; sub[0] = a10; sub[1] = a21;
   } else {
-    float beta = sqrtf(a10 * a10 + tail_sq);
+    float beta = H3D_EIG_SQRT(a10 * a10 + tail_sq);
     if (a10 >= 0.0f) beta = -beta;
-    const float v1 = a20 / (a10 - beta);
-    const float tau = (beta - a10) / beta;
+    const float v1 = H3D_EIG_DIV(a20, a10 - beta);
+    const float tau = H3D_EIG_DIV(beta - a10, beta);
     const float u0 = tau, u1 = tau * v1;
     const float p0 = a11 * u0 + a21 * u1;
     const float p1 = a21 * u0 + a22 * u1;
@@ -165,19 +180,13 @@ __host__ __device__ inline Eig3f eig3f(const float m[9]) {
     } else {
       const float e2 = e * e;
       const float hyp = eig_hypot(td, e);
-      if (e2 == 0.0f) mu -= (e / (td + (td > 0.0f ? 1.0f : -1.0f))) * (e / hyp);
-      else mu -= e2 / (td + (td > 0.0f ? hyp : -hyp));
+      if (e2 == 0.0f) mu -= H3D_EIG_DIV(e, td + (td > 0.0f ? 1.0f : -1.0f)) * H3D_EIG_DIV(e, hyp);
+      else mu -= H3D_EIG_DIV(e2, td + (td > 0.0f ? hyp : -hyp));
     }
     float x = (start == 0 ? d0 : d1) - mu;
     float z = start == 0 ? s0 : s1;
-    if (start == 0) {
-      if (end == 2) H3D_EIG_ROT(d0, d1, s0, q0, q1, q2, q3, q4, q5, (void)0, (z = -sn * s1, s1 = c * s1))
-      else H3D_EIG_ROT(d0, d1, s0, q0, q1, q2, q3, q4, q5, (void)0, (void)0)
-    }
-    if (end == 2) {
-      if (start == 0) H3D_EIG_ROT(d1, d2, s1, q3, q4, q5, q6, q7, q8, (s0 = c * s0 - sn * z), (void)0)
-      else H3D_EIG_ROT(d1, d2, s1, q3, q4, q5, q6, q7, q8, (void)0, (void)0)
-    }
+    if (start == 0) H3D_EIG_ROT(d0, d1, s0, q0, q1, q2, q3, q4, q5, (void)0, if (end == 2) { z = -sn * s1; s1 = c * s1; })
+    if (end == 2) H3D_EIG_ROT(d1, d2, s1, q3, q4, q5, q6, q7, q8, if (start == 0) s0 = c * s0 - sn * z, (void)0)
   }
 #undef H3D_EIG_ROT
   diag[0] = d0; diag[1] = d1; diag[2] = d2;

@@ -2,13 +2,13 @@
 //   hough->add(X) + do { subtract, getLine, pointsCloseToLine, orthogonal_LSQ x2, removePoints }
 //   wrap.h:228-342 / lib/hough3dlines.cpp:244-317
 //
-// One CTA per SM, every CTA keeps ALL live points in registers.  Division of labour:
+// One CTA per SM.  Division of labour:
 //   * each CTA OWNS a fixed, strided set of directions (the ones it voted in the first pass); their
 //     records (max votes, first max cell, stale flag) and scaled coefficients live in ITS shared
 //     memory.  Un-voting removed points and re-voting stale planes are CTA-local.
 //   * the line fit (inliers -> ordered compaction -> orthogonal_LSQ -> inliers -> LSQ -> remove) is
-//     computed REDUNDANTLY and deterministically by every CTA from its registers, so no CTA waits
-//     for another one's fit.
+//     computed REDUNDANTLY and deterministically by every CTA from its own copy of the points, so no
+//     CTA waits for another one's fit.
 //   * two 8-byte exchanges per iteration, each an atomicMax + grid barrier: (A) the packed winner
 //     key (Hough::getLine), (B) the best EXACT record after the un-vote, which is the bound that
 //     decides which stale planes must be re-voted before the next getLine.
@@ -17,10 +17,15 @@
 // plane of a direction they project into a strip around a segment; a record whose max cell is
 // farther than the strip's half-width from that segment cannot be hit (O(1) test per record),
 // the few others are checked point by point with the exact cell arithmetic.
-// While no plane is being voted the (all-zero) plane area doubles as scratch for the inlier
-// coordinates and the LSQ products; it is re-zeroed before the next vote.  When enough points have
-// been removed to free a register slot the live points are re-packed (order kept), so late
-// iterations vote, test and scan fewer slots.
+//
+// Code size is a first-order concern: the SM's instruction cache holds 32 KB (2048 instructions)
+// and one loop iteration walks through every phase once, so a loop body unrolled over register-
+// resident points (an earlier version: 13 k instructions) is bound by instruction fetch from L2
+// (ncu: icc hit rate 68 %, the first execution of a phase 4x slower than the second).  Hence:
+// the FIRST vote keeps the points in registers (vote_resident, a tight hot loop), but the loop
+// phases read a compact copy of the live points in SHARED memory with rolled loops, removed
+// points are compacted away in place (order kept), Y is an index list, both fit passes share
+// one copy of the code, and the eigen-solver's divisions and square roots are out of line.
 #ifndef H3D_FUSED_CUH_
 #define H3D_FUSED_CUH_
 
@@ -33,20 +38,20 @@ struct FusedArgs {
   LoopState *st;              // configuration in, final state out
   h3d_iter *iters;
   unsigned *pool;
-  const unsigned *orig;       // original index of point i at kernel start
-  unsigned *orig_tmp[2];      // ping-pong buffers for the re-packed numbering (CTA 0 only)
+  unsigned *orig;             // original index of live point i (compacted in place by CTA 0)
   const double *dirs;
   unsigned long long *xchg;   // zeroed: [2*it] winner key, [2*it+1] best exact votes of iteration it
   unsigned *bar;              // zeroed grid-barrier counter
-  int *overflow;              // set to 1 when an inlier set does not fit the scratch area
   int n_own_max;              // records per CTA (multiple of kResG)
-  unsigned smem_bytes;        // dynamic shared memory of the launch
+  int nb_planes;              // planes available to a re-vote round (2..8)
+  int n_cap;                  // capacity of the shared-memory point arrays (>= h.n, even)
   double near_t;              // largest nn with sqrt_rn(nn) <= opt_dx (pointsCloseToLine without the sqrt)
   double cell_off;            // max_x/dx + 0.5: cell coordinate of x' = 0
   unsigned long long *prof;   // measurement hook (nullable): [it][cta][kProfSlots] globaltimer stamps
   int prof_iters;
 };
 constexpr int kProfSlots = 16;
+constexpr int kFusedMaxSlots = 12;
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -55,15 +60,21 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 
 struct FusedShared {
-  ResShared res;              // first vote (vote_resident)
+  ResShared res;              // first vote (vote_resident) and re-vote rounds (warp_best)
   LsqOut lsq;
   LsqShared lsq_s;
   long long ipart[kResWarps][3];
   unsigned long long warp_key[kResWarps];
-  int warp_cnt[12][kResWarps];
+  int warp_cnt[kFusedMaxSlots][kResWarps];
   int red_lo[kResWarps], red_hi[kResWarps];
   int tmin_i, tmax_i;         // ordered-int encodings of float t bounds of Y
   int ns, nlist;
+};
+
+// live points (compact, cloud order) and the current inlier list, all in shared memory
+struct FusedPoints {
+  double *x, *y, *z;
+  int *yidx;
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
@@ -104,62 +115,57 @@ __device__ __forceinline__ bool point_near_line_t(double px, double py, double p
   return nn <= near_t;
 }
 
-// Ordered positions of the set bits of the per-thread slot masks, point order = slot-major,
-// thread-minor (index i = tid + p*512).  Phase 1 publishes the warp counts (one barrier), phase 2
-// lets every warp derive its own offsets with REDUX sums.  body(p, pos) runs for every set bit
-// (p is a compile-time constant after unrolling).  Returns the total.  Ends WITHOUT a barrier.
-template <int P, class Body>
-__device__ __forceinline__ int for_each_ordered(unsigned m, int (*warp_cnt)[kResWarps], Body body) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int p = 0; p < P; ++p) {
-    const unsigned bal = __ballot_sync(0xFFFFFFFFu, (m >> p) & 1u);
-    if (lane == 0) warp_cnt[p][warp] = __popc(bal);
-  }
-  __syncthreads();
-  const unsigned below = (1u << lane) - 1u;
-  int run = 0;
-#pragma unroll
-  for (int p = 0; p < P; ++p) {
-    const int c = lane < kResWarps ? warp_cnt[p][lane] : 0;
-    const int tot = __reduce_add_sync(0xFFFFFFFFu, c);
-    const int pre = __reduce_add_sync(0xFFFFFFFFu, lane < warp ? c : 0);
-    const unsigned bal = __ballot_sync(0xFFFFFFFFu, (m >> p) & 1u);
-    if ((m >> p) & 1u) body(p, run + pre + __popc(bal & below));
-    run += tot;
-  }
-  return run;
-}
-
-// Scratch view of the idle plane area (+ whatever dynamic shared memory lies behind it):
-// the current inlier set Y in cloud order, as doubles and as float casts.
-struct FusedScratch {
-  double *base;   // shared memory
-  int cap;
-  __device__ __forceinline__ double *yd(int c) const { return base + (size_t)c * cap; }
-  __device__ __forceinline__ float *yf(int c) const { return reinterpret_cast<float *>(base + (size_t)3 * cap) + (size_t)c * cap; }
-};
-
 // frame-level fixed-point facts for the exact parallel anchor (see h3d_fit.cuh): every
 // coordinate of the frame is a multiple of 2^lo and below 2^(hi+1); ok = both are sane
 struct FixedPoint {
   int lo, hi, ok;
 };
+__device__ __forceinline__ void fixed_point_scan(double v, int &lo, int &hi) {
+  const long long bits = __double_as_longlong(v);
+  const int e = (int)((bits >> 52) & 0x7FF);
+  const long long mant = bits & 0xFFFFFFFFFFFFFLL;
+  if (e == 0x7FF || (e == 0 && mant != 0)) hi = 100000;           // not finite / subnormal: no fast path
+  else if (e != 0) {
+    lo = min(lo, e - 1075 + (__ffsll(mant | 0x10000000000000LL) - 1));
+    hi = max(hi, e - 1023);
+  }
+}
 
-// orthogonal_LSQ sums over Y (wrap.h:126-138) by the whole CTA: anchor, float column means,
-// centred scatter in the canonical TREE32 order.  Leaves sh.lsq.a and sh.lsq_s.sc ready; the
-// eigen-solve (lsq_eig) is a separate single-thread step so that the caller can overlap it.
-// Ends with a barrier.
-__device__ __forceinline__ void lsq_sums_fused(const FusedScratch &S, int n, const FixedPoint &fx, FusedShared &sh) {
+// TREE32 chain of one warp over v(k), k = lane, lane+32, ... (4 loads in flight)
+template <class F>
+__device__ __forceinline__ float tree32_chain(F v, int n, int lane) {
+  float acc = 0.0f;
+  int k = lane;
+#pragma unroll 1
+  for (; k + 96 < n; k += 128) {
+    const float v0 = v(k), v1 = v(k + 32), v2 = v(k + 64), v3 = v(k + 96);
+    acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v0), v1), v2), v3);
+  }
+#pragma unroll 1
+  for (; k < n; k += 32) acc = __fadd_rn(acc, v(k));
+  return tree32_combine(acc);
+}
+
+// orthogonal_LSQ sums over Y = points[yidx[0..n)] (wrap.h:126-138) by the whole CTA: anchor,
+// float column means, centred scatter in the canonical TREE32 order.  Leaves sh.lsq.a and
+// sh.lsq_s.sc ready; the eigen-solve (lsq_eig) is a separate single-thread step so that the
+// caller can overlap it.  Ends with a barrier.
+__device__ __forceinline__ void lsq_sums_fused(const FusedPoints &Q, int n, const FixedPoint &fx, FusedShared &sh) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool fast = fx.ok && (n == 0 || fx.hi + 1 - fx.lo + (32 - __clz(n)) <= 53);
-  if (fast) {             // exact int64 sums, any order (provably the sequential double sum)
+  if (warp < 3) {          // colwise().mean() of the float copy (wrap.h:129-137), TREE32
+    const double *src = warp == 0 ? Q.x : warp == 1 ? Q.y : Q.z;
+    const float acc = tree32_chain([&](int k) { return (float)src[Q.yidx[k]]; }, n, lane);
+    if (lane == 0) sh.lsq_s.mean[warp] = __fdiv_rn(acc, (float)n);
+  } else if (fast) {       // exact int64 sums, any order (provably the sequential double sum)
     const double scale = __longlong_as_double((long long)(1023 - fx.lo) << 52);   // 2^-lo
     long long acc[3] = {0, 0, 0};
 #pragma unroll 1
-    for (int k = tid; k < n; k += kResThreads) {
-#pragma unroll
-      for (int c = 0; c < 3; ++c) acc[c] += __double2ll_rn(__dmul_rn(S.yd(c)[k], scale));
+    for (int k = tid - 96; k < n; k += kResThreads - 96) {
+      const int i = Q.yidx[k];
+      acc[0] += __double2ll_rn(__dmul_rn(Q.x[i], scale));
+      acc[1] += __double2ll_rn(__dmul_rn(Q.y[i], scale));
+      acc[2] += __double2ll_rn(__dmul_rn(Q.z[i], scale));
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -167,49 +173,24 @@ __device__ __forceinline__ void lsq_sums_fused(const FusedScratch &S, int n, con
       for (int o = 16; o; o >>= 1) acc[c] += __shfl_xor_sync(0xFFFFFFFFu, acc[c], o);
       if (lane == 0) sh.ipart[warp][c] = acc[c];
     }
-  } else if (warp >= 3 && warp < 6) {
-    const int c = warp - 3;
-    const double *src = S.yd(c);
-    const double m = mean_axis_warp([&](int k) { return src[k]; }, n, lane);
-    if (lane == 0) sh.lsq.a[c] = m;
-  }
-  if (warp < 3) {          // colwise().mean() of the float copy (wrap.h:129-137), TREE32
-    const float *src = S.yf(warp);
-    float acc = 0.0f;
-    int k = lane;
-#pragma unroll 1
-    for (; k + 96 < n; k += 128) {
-      const float v0 = src[k], v1 = src[k + 32], v2 = src[k + 64], v3 = src[k + 96];
-      acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v0), v1), v2), v3);
-    }
-#pragma unroll 1
-    for (; k < n; k += 32) acc = __fadd_rn(acc, src[k]);
-    acc = tree32_combine(acc);
-    if (lane == 0) sh.lsq_s.mean[warp] = __fdiv_rn(acc, (float)n);
+  } else if (warp < 6) {   // the reference's sequential double sum (rare)
+    const double *src = warp == 3 ? Q.x : warp == 4 ? Q.y : Q.z;
+    const double m = mean_axis_warp([&](int k) { return src[Q.yidx[k]]; }, n, lane);
+    if (lane == 0) sh.lsq.a[warp - 3] = m;
   }
   __syncthreads();
-  if (warp < 6) {          // centred^T * centred (wrap.h:137-138), TREE32 per entry, products on the fly
+  if (warp < 6) {          // centred^T * centred (wrap.h:137-138), TREE32 per entry
     const int c0 = warp < 3 ? 0 : warp < 5 ? 1 : 2, c1 = warp < 3 ? warp : warp < 5 ? warp - 2 : 2;
-    const float *s0 = S.yf(c0), *s1 = S.yf(c1);
+    const double *s0 = c0 == 0 ? Q.x : c0 == 1 ? Q.y : Q.z, *s1 = c1 == 0 ? Q.x : c1 == 1 ? Q.y : Q.z;
     const float m0 = sh.lsq_s.mean[c0], m1 = sh.lsq_s.mean[c1];
-    float acc = 0.0f;
-    int k = lane;
-#pragma unroll 1
-    for (; k + 96 < n; k += 128) {
-      const float u0 = s0[k], u1 = s0[k + 32], u2 = s0[k + 64], u3 = s0[k + 96];
-      const float w0 = s1[k], w1 = s1[k + 32], w2 = s1[k + 64], w3 = s1[k + 96];
-      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u0, m0), __fsub_rn(w0, m1)));
-      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u1, m0), __fsub_rn(w1, m1)));
-      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u2, m0), __fsub_rn(w2, m1)));
-      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(u3, m0), __fsub_rn(w3, m1)));
-    }
-#pragma unroll 1
-    for (; k < n; k += 32) acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(s0[k], m0), __fsub_rn(s1[k], m1)));
-    acc = tree32_combine(acc);
+    const float acc = tree32_chain([&](int k) {
+      const int i = Q.yidx[k];
+      return __fmul_rn(__fsub_rn((float)s0[i], m0), __fsub_rn((float)s1[i], m1));
+    }, n, lane);
     if (lane == 0) sh.lsq_s.sc[warp] = acc;
   } else if (warp == 6 && fast && lane < 3) {
     long long s = 0;
-    for (int w = 0; w < kResWarps; ++w) s += sh.ipart[w][lane];
+    for (int w = 3; w < kResWarps; ++w) s += sh.ipart[w][lane];
     const double sum = __dmul_rn((double)s, __longlong_as_double((long long)(1023 + fx.lo) << 52));
     sh.lsq.a[lane] = n > 0 ? __ddiv_rn(sum, (double)n) : sum;
   }
@@ -223,84 +204,6 @@ __device__ __forceinline__ void lsq_eig(FusedShared &sh) {
   const Eig3f e = eig3f(m);
   sh.lsq.b[0] = e.evecs[6]; sh.lsq.b[1] = e.evecs[7]; sh.lsq.b[2] = e.evecs[8];   // last column
   sh.lsq.rc = (double)e.evals[2];
-}
-
-// votes of all (live) register points for one direction into the plane at shared address plane_sa
-template <int P>
-__device__ __forceinline__ void vote_one_direction(const HoughDev &h, const FastCoef &f, int j, const double (&px)[P],
-                                                   const double (&py)[P], const double (&pz)[P], unsigned live,
-                                                   unsigned plane_sa, unsigned dummy_sa) {
-  const double kmagic = h.kmagic;
-  const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells;
-  constexpr int CH = 4;
-#pragma unroll
-  for (int p0 = 0; p0 < P; p0 += CH) {
-    if (__all_sync(0xFFFFFFFFu, (live >> p0) == 0)) break;
-    unsigned cell[CH];
-    unsigned gmin = 0xFFFFFFFFu, hacc = 0;
-#pragma unroll
-    for (int c = 0; c < CH; ++c) {
-      const int p = p0 + c;
-      if (p >= P) { cell[c] = 0xFFFFFFFFu; continue; }
-      cell[c] = vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], gmin, hacc);
-    }
-    if (batch_unsure(gmin, hacc) | !h.fast_ok) {
-#pragma unroll
-      for (int c = 0; c < CH; ++c) {
-        const int p = p0 + c;
-        if (p < P)
-          cell[c] = vote_cell_checked(h.coef + j, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, px[p], py[p], pz[p]);
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < CH; ++c) {
-      const int p = p0 + c;
-      if (p >= P) continue;
-      red_shared_inc(((cell[c] < plane_cells) & ((live >> p) & 1u)) ? plane_sa + 4u * cell[c] : dummy_sa);
-    }
-  }
-}
-
-// X.pointsCloseToLine(a, b, dx, &Y) over the register points + ordered compaction of Y into the
-// scratch area (doubles and float casts).  Returns this thread's inlier mask; *ny_out = |Y|
-// (uniform).  CTA 0 also appends the original indices to the pool.  track_t: also reduce the
-// range of t = b*(p - a) over Y into sh.tmin_i / sh.tmax_i.  Ends with a barrier.
-template <int P>
-__device__ __forceinline__ unsigned inlier_pass(const double (&px)[P], const double (&py)[P], const double (&pz)[P],
-                                                unsigned live, int used_slots, const double (&a)[3], const double (&b)[3],
-                                                double near_t, FusedShared &sh, const FusedScratch &S, bool track_t,
-                                                bool to_pool, unsigned *pool, unsigned pool_base, unsigned pool_cap,
-                                                const unsigned *orig, int *ny_out, unsigned long long *dbg) {
-  const int tid = threadIdx.x;
-  unsigned m = 0;
-  float tlo = 3.0e38f, thi = -3.0e38f;
-#pragma unroll
-  for (int p = 0; p < P; ++p) {
-    if (p < used_slots) {   // uniform
-      double t;
-      if (point_near_line_t(px[p], py[p], pz[p], a, b, near_t, &t) && ((live >> p) & 1u)) {
-        m |= 1u << p;
-        if (track_t) { const float tf = (float)t; tlo = fminf(tlo, tf); thi = fmaxf(thi, tf); }
-      }
-    }
-  }
-  if (dbg && tid == 0) *dbg = globaltimer_ns();
-  if (track_t) {
-    const int lo_i = __reduce_min_sync(0xFFFFFFFFu, float_ordered(tlo));
-    const int hi_i = __reduce_max_sync(0xFFFFFFFFu, float_ordered(thi));
-    if ((tid & 31) == 0) { atomicMin(&sh.tmin_i, lo_i); atomicMax(&sh.tmax_i, hi_i); }
-  }
-  const int cap = S.cap;
-  const int ny = for_each_ordered<P>(m, sh.warp_cnt, [&](int p, int pos) {
-    if (pos < cap) {
-      S.yd(0)[pos] = px[p]; S.yd(1)[pos] = py[p]; S.yd(2)[pos] = pz[p];
-      S.yf(0)[pos] = (float)px[p]; S.yf(1)[pos] = (float)py[p]; S.yf(2)[pos] = (float)pz[p];
-    }
-    if (to_pool && pool_base + (unsigned)pos < pool_cap) pool[pool_base + pos] = orig[tid + p * kResThreads];
-  });
-  __syncthreads();
-  *ny_out = ny;
-  return m;
 }
 
 // Can a point of Y vote for cell (cx, cy) of the direction with scaled coefficients f?  Y lies in
@@ -332,6 +235,83 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(threads) : "memory");
 }
 
+// X.pointsCloseToLine(a, b, dx, &Y): inlier mask of this thread's points (bit p = point
+// tid + p*512), Y as an ordered index list in Q.yidx, |Y| in *ny_out (uniform).  CTA 0 also appends
+// the original indices to the pool.  track_t: also reduce the range of t = b*(p - a) over Y into
+// sh.tmin_i / sh.tmax_i.  Leaves the per-(slot, warp) inlier counts in sh.warp_cnt.  Ends with a
+// barrier.
+__device__ __forceinline__ unsigned inlier_pass(const FusedPoints &Q, int n_alive, const double (&a)[3],
+                                                const double (&b)[3], double near_t, FusedShared &sh, bool track_t,
+                                                bool to_pool, unsigned *pool, unsigned pool_base, unsigned pool_cap,
+                                                const unsigned *orig, int *ny_out, unsigned long long *dbg) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int slots = (n_alive + kResThreads - 1) / kResThreads;
+  unsigned m = 0;
+  float tlo = 3.0e38f, thi = -3.0e38f;
+#pragma unroll 1
+  for (int p = 0; p < slots; ++p) {
+    const int i = tid + p * kResThreads;
+    bool in = false;
+    if (i < n_alive) {
+      double t;
+      in = point_near_line_t(Q.x[i], Q.y[i], Q.z[i], a, b, near_t, &t);
+      if (in) { const float tf = (float)t; tlo = fminf(tlo, tf); thi = fmaxf(thi, tf); }
+    }
+    m |= in ? (1u << p) : 0u;
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, in);
+    if (lane == 0) sh.warp_cnt[p][warp] = __popc(bal);
+  }
+  if (dbg && tid == 0) *dbg = globaltimer_ns();
+  if (track_t) {
+    const int lo_i = __reduce_min_sync(0xFFFFFFFFu, float_ordered(tlo));
+    const int hi_i = __reduce_max_sync(0xFFFFFFFFu, float_ordered(thi));
+    if (lane == 0) { atomicMin(&sh.tmin_i, lo_i); atomicMax(&sh.tmax_i, hi_i); }
+  }
+  __syncthreads();
+  const unsigned below = (1u << lane) - 1u;
+  int run = 0;
+#pragma unroll 1
+  for (int p = 0; p < slots; ++p) {
+    const int c = lane < kResWarps ? sh.warp_cnt[p][lane] : 0;
+    const int tot = __reduce_add_sync(0xFFFFFFFFu, c);
+    const int pre = __reduce_add_sync(0xFFFFFFFFu, lane < warp ? c : 0);
+    const bool in = (m >> p) & 1u;
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, in);
+    if (in) {
+      const int pos = run + pre + __popc(bal & below);
+      const int i = tid + p * kResThreads;
+      Q.yidx[pos] = i;
+      if (to_pool && pool_base + (unsigned)pos < pool_cap) pool[pool_base + pos] = orig[i];
+    }
+    run += tot;
+  }
+  __syncthreads();
+  *ny_out = run;
+  return m;
+}
+
+// re-vote of two directions (records r0, r1; r1 < 0: none) over the compact live points
+__device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints &Q, int n_alive, const FastCoef &f0,
+                                            const FastCoef &f1, int j0, int j1, unsigned plane0_sa, unsigned plane1_sa,
+                                            unsigned dummy_sa) {
+  const double kmagic = h.kmagic;
+  const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells;
+  const bool two = j1 >= 0;
+#pragma unroll 2
+  for (int i = threadIdx.x; i < n_alive; i += kResThreads) {
+    const double x = Q.x[i], y = Q.y[i], z = Q.z[i];
+    unsigned gmin = 0xFFFFFFFFu, hacc = 0;
+    unsigned c0 = vote_cell_acc(f0, kmagic, num_x, x, y, z, gmin, hacc);
+    unsigned c1 = vote_cell_acc(f1, kmagic, num_x, x, y, z, gmin, hacc);
+    if (batch_unsure(gmin, hacc) | !h.fast_ok) {   // rare: within 8e-6 cell of a boundary
+      c0 = vote_cell_checked(h.coef + j0, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
+      if (two) c1 = vote_cell_checked(h.coef + j1, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
+    }
+    red_shared_inc(c0 < plane_cells ? plane0_sa + 4u * c0 : dummy_sa);
+    red_shared_inc((two & (c1 < plane_cells)) ? plane1_sa + 4u * c1 : dummy_sa);
+  }
+}
+
 template <int P>
 __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -340,7 +320,8 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   const HoughDev &h = A.h;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int cta = blockIdx.x, n_cta = gridDim.x;
-  // per-CTA record tables first, then the planes (+ pad word), then free scratch
+  // per-CTA record tables first, then the planes (+ pad word); behind the planes of a re-vote
+  // round (the first vote uses 2*G planes over the same area) the live points and the inlier list
   const int n_own = A.n_own_max;
   double *own_coef = reinterpret_cast<double *>(smem_raw);               // 5 scaled coefficients per record
   unsigned *rv = reinterpret_cast<unsigned *>(own_coef + 5 * n_own);     // max votes (bound when stale)
@@ -350,17 +331,20 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   const unsigned tables_bytes = (unsigned)n_own * 56u;                   // n_own % 4 == 0 -> multiple of 16
   unsigned *planes = reinterpret_cast<unsigned *>(smem_raw + tables_bytes);
   const unsigned stride = h.plane_stride, quads = stride / 4;
-  const unsigned plane_words = 2u * G * stride;
   const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
-  const unsigned dummy_sa = planes_sa + plane_words * 4u;
-  FusedScratch S;
-  S.cap = (int)(((A.smem_bytes - tables_bytes) / 36u) & ~1u);
-  S.base = reinterpret_cast<double *>(planes);
+  const int nb = A.nb_planes;
+  const unsigned dummy_sa = planes_sa + (unsigned)nb * stride * 4u;      // pad word of the loop layout
+  FusedPoints Q;
+  Q.x = reinterpret_cast<double *>(planes + (size_t)nb * stride + 4);
+  Q.y = Q.x + A.n_cap; Q.z = Q.y + A.n_cap;
+  Q.yidx = reinterpret_cast<int *>(Q.z + A.n_cap);
 
-  // ---- hough->add(X): every plane once (K1) ------------------------------------------------------
-  uint4 *p4 = reinterpret_cast<uint4 *>(planes);
-  for (unsigned q = tid; q < plane_words / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-  vote_resident<P, 0>(h, nullptr, h.dir_count, planes, sh.res, cta, n_cta);
+  // ---- hough->add(X): every plane once (K1), points in registers ----------------------------------
+  {
+    uint4 *p4 = reinterpret_cast<uint4 *>(planes);
+    for (unsigned q = tid; q < 2u * G * quads + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
+    vote_resident<P, 0>(h, nullptr, h.dir_count, planes, sh.res, cta, n_cta);
+  }
   __syncthreads();
   // own records: entry r = k*G + g is direction (cta + k*n_cta)*G + g
   for (int r = tid; r < n_own; r += kResThreads) {
@@ -373,29 +357,15 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     } else { rv[r] = 0; rcell[r] = 0; }
     rstale[r] = 0;
   }
-  // the points again, for the loop; and the frame's fixed-point facts (exact parallel anchor)
-  double px[P], py[P], pz[P];
-  unsigned live = 0;
+  // the points, for the loop, into shared memory; and the frame's fixed-point facts
   FixedPoint fx;
   {
     int lo = 0x7FFFFFFF, hi = -0x7FFFFFFF;
-#pragma unroll
-    for (int p = 0; p < P; ++p) {
-      const int i = tid + p * kResThreads;
-      const bool ok = i < h.n;
-      px[p] = ok ? h.px[i] : 0.0; py[p] = ok ? h.py[i] : 0.0; pz[p] = ok ? h.pz[i] : 0.0;
-      live |= ok ? (1u << p) : 0u;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const long long bits = __double_as_longlong(c == 0 ? px[p] : c == 1 ? py[p] : pz[p]);
-        const int e = (int)((bits >> 52) & 0x7FF);
-        const long long mant = bits & 0xFFFFFFFFFFFFFLL;
-        if (e == 0x7FF || (e == 0 && mant != 0)) hi = 100000;           // not finite / subnormal: no fast path
-        else if (e != 0) {
-          lo = min(lo, e - 1075 + (__ffsll(mant | 0x10000000000000LL) - 1));
-          hi = max(hi, e - 1023);
-        }
-      }
+#pragma unroll 1
+    for (int i = tid; i < h.n; i += kResThreads) {
+      const double x = h.px[i], y = h.py[i], z = h.pz[i];
+      Q.x[i] = x; Q.y[i] = y; Q.z[i] = z;
+      fixed_point_scan(x, lo, hi); fixed_point_scan(y, lo, hi); fixed_point_scan(z, lo, hi);
     }
     lo = __reduce_min_sync(0xFFFFFFFFu, lo);
     hi = __reduce_max_sync(0xFFFFFFFFu, hi);
@@ -407,13 +377,11 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     fx.ok = (lo != 0x7FFFFFFF && lo > -900 && hi < 900) ? 1 : 0;
   }
   const LoopState cfg = *A.st;
-  int n_alive = h.n, n_lines = 0, it = 0, dirty_n = 0;
-  int used_slots = (h.n + kResThreads - 1) / kResThreads;
+  int n_alive = h.n, n_lines = 0, it = 0;
   unsigned pool_used = 0, bar_target = 0;
   unsigned long long revotes = 0;
-  const unsigned *cur_orig = A.orig;
-  int orig_flip = 0;
   const double reach = 1.4142136 * (0.5 + cfg.opt_dx / h.dx + 0.02), reach2 = reach * reach;
+  const unsigned below = (1u << lane) - 1u;
   __syncthreads();
 
   auto stamp = [&](int slot, unsigned long long extra) {
@@ -442,7 +410,6 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     const unsigned flat = votes ? 0xFFFFFFFFu - (unsigned)key : 0u;
     double a[3], b[3];
     line_from_index(h, A.dirs, flat, a, b);                    // Hough::getLine, lib/hough.cpp:114-132
-    stamp(14, 0);
     const bool rec = cta == 0 && tid == 0 && it < cfg.max_iters;
     h3d_iter *R = rec ? &A.iters[it] : nullptr;
     if (rec) {
@@ -451,19 +418,16 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
       R->rc1 = 0; R->rc2 = 0; R->n1 = 0; R->n2 = 0; R->off1 = pool_used; R->off2 = pool_used;
     }
     int status = 0;
-    // ---- X.pointsCloseToLine + orthogonal_LSQ, twice (K3), wrap.h:245-255 ----------------------------
-    // one copy of the code for both passes (instruction-cache footprint)
+    // ---- X.pointsCloseToLine + orthogonal_LSQ, twice (K3), wrap.h:245-255; one copy of the code -------
     unsigned m2 = 0;
     int ny2 = 0;
     bool last = false;
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
       int ny = 0;
-      const unsigned m = inlier_pass<P>(px, py, pz, live, used_slots, a, b, A.near_t, sh, S, pass == 1, cta == 0, A.pool,
-                                        pool_used, cfg.pool_cap, cur_orig, &ny,
-                                        (A.prof && it < A.prof_iters) ? A.prof + ((size_t)it * n_cta + cta) * kProfSlots + 12 + pass : nullptr);
-      dirty_n = max(dirty_n, min(ny, S.cap));
-      if (ny > S.cap) { status = 9; break; }
+      const unsigned m = inlier_pass(Q, n_alive, a, b, A.near_t, sh, pass == 1, cta == 0, A.pool, pool_used,
+                                     cfg.pool_cap, A.orig, &ny,
+                                     (A.prof && it < A.prof_iters) ? A.prof + ((size_t)it * n_cta + cta) * kProfSlots + 12 + pass : nullptr);
       if (rec) {
         if (pass == 0) { R->n1 = (unsigned)ny; R->off1 = pool_used; }
         else { R->n2 = (unsigned)ny; R->off2 = pool_used; }
@@ -476,13 +440,13 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
         last = !((n_alive - ny2 > 1) && (cfg.nlines_max == 0 || cfg.nlines_max > n_lines + 1));   // wrap.h:341-342
       }
       stamp(3 + 2 * pass, 0);
-      lsq_sums_fused(S, ny, fx, sh);
+      lsq_sums_fused(Q, ny, fx, sh);
       stamp(4 + 2 * pass, 0);
       if (warp == 0) {
         if (tid == 0) lsq_eig(sh);
       } else if (pass == 1 && !last) {
         // ---- hough->subtract(Y) for the own directions (K4), overlapped with the eigen-solve ----------
-        // Y (pass 2) is in the scratch area; it lies within opt_dx of the line (a, b) of pass 2
+        // Y (pass 2) lies within opt_dx of the line (a, b) of pass 2
         const int ut = tid - 32, un = kResThreads - 32;
         const float tl = ordered_float(sh.tmin_i), th = ordered_float(sh.tmax_i);
         const double t0 = (double)tl - (fabs((double)tl) * 1e-6 + 1e-9), t1 = (double)th + (fabs((double)th) * 1e-6 + 1e-9);
@@ -498,11 +462,13 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
         named_bar_sync(1, un);
         const int ns = sh.ns;
         const int total = ns * ny2;
+#pragma unroll 1
         for (int idx = ut; idx < total; idx += un) {
           const int s = idx / ny2, e = idx - s * ny2;
           const int r = rlist[s];
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-          if (vote_cell(h, load_fast(own_coef, r), j, S.yd(0)[e], S.yd(1)[e], S.yd(2)[e]) == rcell[r]) rstale[r] = 1;
+          const int i = Q.yidx[e];
+          if (vote_cell(h, load_fast(own_coef, r), j, Q.x[i], Q.y[i], Q.z[i]) == rcell[r]) rstale[r] = 1;
         }
       }
       __syncthreads();
@@ -515,48 +481,35 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
 #pragma unroll
       for (int c = 0; c < 3; ++c) { a[c] = sh.lsq.a[c]; b[c] = sh.lsq.b[c]; }
     }
-    if (status == 9) { if (tid == 0) *A.overflow = 1; break; }
     stamp(7, 0);
     if (status) { if (rec) R->status = (unsigned)status; ++it; break; }
     if (rec) for (int c = 0; c < 3; ++c) R->a2[c] = __dadd_rn(sh.lsq.a[c], cfg.shift[c]);   // wrap.h:257
     ++n_lines;
-    live &= ~m2;                                                                           // X.removePoints(Y)
-    n_alive -= ny2;
-    if (last) { ++it; break; }
+    if (last) { n_alive -= ny2; ++it; break; }
 
-    // ---- give the plane area back: zero what the scratch used ----------------------------------------
-    for (int q = tid; q < dirty_n; q += kResThreads) {
-      S.yd(0)[q] = 0.0; S.yd(1)[q] = 0.0; S.yd(2)[q] = 0.0;
-      S.yf(0)[q] = 0.0f; S.yf(1)[q] = 0.0f; S.yf(2)[q] = 0.0f;
-    }
-    dirty_n = 0;
-    // ---- re-pack the live points when a register slot can be freed (order kept) ----------------------
-    const int new_slots = (n_alive + kResThreads - 1) / kResThreads;
-    if (new_slots < used_slots) {
-      // one ordered pass stages x, y, z (and, on CTA 0, the numbering) by new position
-      double *stage = reinterpret_cast<double *>(planes);
-      const int n_old = used_slots * kResThreads;   // >= the old live count: stride of the staging arrays
-      unsigned *odst = A.orig_tmp[orig_flip];
-      const unsigned *osrc = cur_orig;
-      __syncthreads();   // zero-fill above is complete before the stage is written
-      (void)for_each_ordered<P>(live, sh.warp_cnt, [&](int p, int pos) {
-        stage[pos] = px[p]; stage[n_old + pos] = py[p]; stage[2 * n_old + pos] = pz[p];
-        if (cta == 0) odst[pos] = osrc[tid + p * kResThreads];
-      });
-      __syncthreads();
-      live = 0;
-#pragma unroll
-      for (int p = 0; p < P; ++p) {
+    // ---- X.removePoints(Y), wrap.h:339: stable in-place compaction, slot by slot ----------------------
+    // (position of a kept point = its index - inliers before it; sh.warp_cnt still holds the per-
+    // (slot, warp) inlier counts of pass 2; a slot is read by everyone before anyone overwrites it)
+    {
+      const int slots = (n_alive + kResThreads - 1) / kResThreads;
+      int run = 0;
+#pragma unroll 1
+      for (int p = 0; p < slots; ++p) {
         const int i = tid + p * kResThreads;
-        const bool ok = i < n_alive;
-        px[p] = ok ? stage[i] : 0.0; py[p] = ok ? stage[n_old + i] : 0.0; pz[p] = ok ? stage[2 * n_old + i] : 0.0;
-        live |= ok ? (1u << p) : 0u;
+        const bool valid = i < n_alive, in = (m2 >> p) & 1u;
+        double x = 0.0, y = 0.0, z = 0.0;
+        unsigned o = 0;
+        if (valid) { x = Q.x[i]; y = Q.y[i]; z = Q.z[i]; if (cta == 0) o = A.orig[i]; }
+        const int c = lane < kResWarps ? sh.warp_cnt[p][lane] : 0;
+        const int tot = __reduce_add_sync(0xFFFFFFFFu, c);
+        const int pre = __reduce_add_sync(0xFFFFFFFFu, lane < warp ? c : 0);
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, in);
+        const int pos = i - (run + pre + __popc(bal & below));
+        __syncthreads();
+        if (valid && !in) { Q.x[pos] = x; Q.y[pos] = y; Q.z[pos] = z; if (cta == 0) A.orig[pos] = o; }
+        run += tot;
       }
-      cur_orig = odst;
-      orig_flip ^= 1;
-      __syncthreads();
-      for (int q = tid; q < n_alive; q += kResThreads) { stage[q] = 0.0; stage[n_old + q] = 0.0; stage[2 * n_old + q] = 0.0; }
-      used_slots = new_slots;
+      n_alive -= ny2;
     }
     stamp(10, 0);
     // ---- (B) best EXACT record of all CTAs: stale records whose bound reaches it must be rebuilt -----
@@ -576,20 +529,25 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     const int nlist = sh.nlist;
     stamp(8, (unsigned long long)nlist + 1);
     revotes += (unsigned long long)nlist * (unsigned long long)n_alive;
-    for (int b0 = 0; b0 < nlist; b0 += 2 * G) {
-      const int nb = min(2 * G, nlist - b0);
-      for (int bi = 0; bi < nb; ++bi) {
-        const int r = rlist[b0 + bi];
-        const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-        vote_one_direction<P>(h, load_fast(own_coef, r), j, px, py, pz, live, planes_sa + (unsigned)bi * stride * 4u, dummy_sa);
+#pragma unroll 1
+    for (int b0 = 0; b0 < nlist; b0 += nb) {
+      const int cnt = min(nb, nlist - b0);
+#pragma unroll 1
+      for (int bi = 0; bi < cnt; bi += 2) {
+        const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
+        const int j0 = h.dir_begin + (cta + (r0 / G) * n_cta) * G + (r0 % G);
+        const int j1 = r1 >= 0 ? h.dir_begin + (cta + (r1 / G) * n_cta) * G + (r1 % G) : -1;
+        revote_pair(h, Q, n_alive, load_fast(own_coef, r0), load_fast(own_coef, r1 >= 0 ? r1 : r0), j0, j1,
+                    planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa);
       }
       __syncthreads();
-      for (int bi = 0; bi < nb; ++bi) {
+#pragma unroll 1
+      for (int bi = 0; bi < cnt; ++bi) {
         const unsigned long long k = scan_plane_fast<kResThreads>(planes + (size_t)bi * stride, quads, tid);
         if (lane == 0) sh.res.warp_best[bi / G][bi % G][warp] = k;
       }
       __syncthreads();
-      if (warp < nb) {
+      if (warp < cnt) {
         unsigned long long k = lane < kResWarps ? sh.res.warp_best[warp / G][warp % G][lane] : 0ull;
         k = warp_max_u64(k);
         if (lane == 0) {

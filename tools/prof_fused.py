@@ -25,7 +25,7 @@ for it in range(t.shape[0]):
     if a[0, 9]:
         nl = a[:, 8] - 1
         rv = (a[:, 9] - a[:, 11]) / 1e3
-        line += (f" repack={(c0[10]-c0[7])/1e3:5.1f} barB={(c0[11]-c0[10])/1e3:5.1f} revote={(c0[9]-c0[11])/1e3:5.1f}"
+        line += (f" remove={(c0[10]-c0[7])/1e3:5.1f} barB={(c0[11]-c0[10])/1e3:5.1f} revote={(c0[9]-c0[11])/1e3:5.1f}"
                  f" | nlist max {nl.max()} mean {nl.mean():.1f} sum {nl.sum()} revote max {rv.max():.1f};"
                  f" span {(a[:,9].max()-a[:,0].min())/1e3:.1f}")
     print(line)
