@@ -8,12 +8,16 @@ granularity 6, opt_nlines 20, opt_minvotes 12, dx = sqrt(3)*leaf.
                                                            (oracle/_ref, else the oracle port)
 
 A step is one pass of the hot path over a batch of FRAMES_PER_STEP distinct synthetic frames
-(poses along the tower trajectory).  `value` is timed with the frames resident in HBM
-(h3d_pipeline_run_dev), `e2e` through h3d_pipeline_run with pinned HOST frames: H2D of the raw
-frame and D2H of the line records and inlier lists are inside the timed region.  Times are CUDA
-event times on the pipeline's stream (the library records them around every frame), summed over
-the frames of the timed steps; for N > 1 every rank replays its own frames (frame-parallel,
-no collective on the data path) and the maximum over ranks is reported.
+(poses along the tower trajectory).  Frames are independent (one Hough per frame) and the loop of
+one frame is latency-bound, so a GPU keeps K frames in flight: K pipelines driven by K host
+threads, each with sm_count/K SMs for its persistent loop kernel (--concurrency, default 4).
+`value` is timed with the frames resident in HBM (h3d_pipeline_run_dev), `e2e` through
+h3d_pipeline_run with pinned HOST frames: H2D of the raw frame and D2H of the line records and
+inlier lists are inside the timed region.  A step is bracketed by device synchronisation and a pair
+of CUDA events (all pipeline streams drained on both sides); for N > 1 every rank replays its own
+frames (frame-parallel, no collective on the data path) and the maximum over ranks is reported.
+A third leg runs one frame at a time on all SMs: `single_frame_latency` (the < 1 ms target of
+BASELINE.json's north_star) and the `roofline` of the frame's one kernel, timed alone.
 Only the cpu_baseline leg and --impl reference execute anything under oracle/.
 """
 from __future__ import annotations
@@ -190,6 +194,7 @@ def cpu_baseline_sample(frames):
 # GPU arm
 # ---------------------------------------------------------------------------------------------
 def run_gpu_arm(args):
+    import ctypes
     import torch
     import torch.distributed as dist
     from pointcloud_segmentation_b200 import capi, synth
@@ -208,29 +213,53 @@ def run_gpu_arm(args):
     pinned = torch.from_numpy(frames).pin_memory()
     on_dev = pinned.cuda()
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
-    pipe = capi.Pipeline(GRANULARITY, synth.WINDOW, synth.LEAF, synth.OPT_DX, MINVOTES, NLINES, max_raw_points=n_pts)
     lib = capi.lib()
-    lib.h3d_launch_count.restype = __import__("ctypes").c_ulonglong
+    lib.h3d_launch_count.restype = ctypes.c_ulonglong
+    sm_count = capi.device_info()["sm_count"]
     frame_bytes = n_pts * stride * 4
+    K = max(1, min(args.concurrency, FRAMES_PER_STEP))
+
+    def new_pipe(share):
+        p = capi.Pipeline(GRANULARITY, synth.WINDOW, synth.LEAF, synth.OPT_DX, MINVOTES, NLINES, max_raw_points=n_pts)
+        p.set_sm_share(share)
+        return p
+
+    # K pipelines, K host threads, sm_count/K SMs each for the persistent loop kernel: frames are
+    # independent (one Hough per frame, wrap.h:220/347) and a frame's loop is latency-bound
+    pipes = [new_pipe(sm_count // K if K > 1 else 0) for _ in range(K)]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def one_step(e2e):
-        """one batch of frames; returns (sum of device times us, [per-phase sums], d2h bytes, lines, votes, n_filtered)"""
+        """one batch of FRAMES_PER_STEP frames over the K pipelines; device time of the whole batch (ms)"""
         flush.fill_(rank + 1)              # L2 flush between timed steps (inputs are far smaller than L2)
+        acc = [dict(d2h=0, lines=0, votes=0, nf=0, iters=0, unvotes=0) for _ in range(K)]
+
+        def work(t):
+            a = acc[t]
+            for k in range(t, FRAMES_PER_STEP, K):
+                if e2e:
+                    res = pipes[t].run_ptr(pinned[k].data_ptr(), n_pts, stride)
+                else:
+                    res = pipes[t].run_dev(on_dev[k].data_ptr(), n_pts, stride)
+                n_rec = min(res.n_iters, pipes[t].max_iters)
+                a["d2h"] += 216 + n_rec * 200 + 4 * res.pool_used      # state + records + inlier lists
+                a["lines"] += res.n_lines; a["votes"] += res.votes_cast; a["nf"] += res.n_input
+                a["iters"] += res.n_iters
+                a["unvotes"] += sum(pipes[t].iters[q].n2 for q in range(n_rec) if pipes[t].iters[q].status == 0)
+
+        th = [threading.Thread(target=work, args=(t,)) for t in range(K)]
         torch.cuda.synchronize()
-        tot, phases, d2h, lines, votes, nf = 0.0, np.zeros(4), 0, 0, 0, 0
-        for k in range(FRAMES_PER_STEP):
-            if e2e:
-                res = pipe.run_ptr(pinned[k].data_ptr(), n_pts, stride)
-            else:
-                res = pipe.run_dev(on_dev[k].data_ptr(), n_pts, stride)
-            us = pipe.timing_us()
-            tot += us[3]
-            phases += np.array(us)
-            d2h += 216 + min(res.n_iters, pipe.max_iters) * 200 + 4 * res.pool_used   # state + records + inlier lists
-            lines += res.n_lines
-            votes += res.votes_cast
-            nf += res.n_input
-        return tot, phases, d2h, lines, votes, nf
+        ev0.record()
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        torch.cuda.synchronize()           # every pipeline stream has drained
+        ev1.record()
+        ev1.synchronize()
+        out = {k: sum(a[k] for a in acc) for k in acc[0]}
+        out["ms"] = ev0.elapsed_time(ev1)
+        return out
 
     def barrier():
         torch.cuda.synchronize()
@@ -243,18 +272,16 @@ def run_gpu_arm(args):
             one_step(e2e)
         barrier()
         launches0 = lib.h3d_launch_count()
-        wall0 = time.perf_counter()
         acc = [one_step(e2e) for _ in range(args.steps)]
         barrier()
-        wall = time.perf_counter() - wall0
         launches = lib.h3d_launch_count() - launches0
-        dev_us = sum(a[0] for a in acc)
-        t = torch.tensor([dev_us], dtype=torch.float64, device="cuda")
+        t = torch.tensor([sum(a["ms"] for a in acc)], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return {"dev_us": float(t.item()), "wall_s": wall, "launches": int(launches),
-                "phases": sum(a[1] for a in acc), "d2h": sum(a[2] for a in acc) / args.steps,
-                "lines": sum(a[3] for a in acc), "votes": sum(a[4] for a in acc), "nf": sum(a[5] for a in acc)}
+        out = {k: sum(a[k] for a in acc) for k in acc[0]}
+        out["ms"] = float(t.item())
+        out["launches"] = int(launches)
+        return out
 
     sampler = ClockSampler(local)
     if rank == 0:
@@ -262,55 +289,101 @@ def run_gpu_arm(args):
     dev = timed(False)
     e2e = timed(True)
     clocks = sampler.stop() if rank == 0 else None
+    for p in pipes:
+        p.close()
+    # ---- single-frame latency + roofline leg: ONE pipeline with all SMs, frames resident in HBM ---------
+    num_b = 20481
+    lat = new_pipe(0)
+    lat_us, phase = [], np.zeros(4)
+    algo_bytes = algo_dense = 0.0
+    votes_add = votes_sub = 0
+    for rep in range(2 + max(1, args.steps // 2)):
+        flush.fill_(7)
+        torch.cuda.synchronize()
+        for k in range(FRAMES_PER_STEP):
+            res = lat.run_dev(on_dev[k].data_ptr(), n_pts, stride)
+            if rep < 2:
+                continue                                         # warm-up
+            us = lat.timing_us()
+            lat_us.append(us[3]); phase += np.array(us)
+            n_alive, cells = res.n_input, res.num_x * res.num_x * num_b
+            b = 8.0 * n_alive * num_b + 24.0 * n_alive + 40.0 * num_b          # K1: Hough::add
+            votes_add += n_alive * num_b
+            dense = 0.0
+            for q in range(min(res.n_iters, lat.max_iters)):
+                r = lat.iters[q]
+                b += 9.0 * num_b + 25.0 * n_alive * (1 if r.status == 1 else 2)   # K2 (records) + K3 passes
+                dense += 4.0 * cells                                              # K2 as the reference scans it
+                if r.status == 0:
+                    b += 8.0 * r.n2 * num_b + 24.0 * r.n2 + 40.0 * num_b          # K4: Hough::subtract
+                    votes_sub += r.n2 * num_b
+                    n_alive -= r.n2
+            algo_bytes += b; algo_dense += b + dense
+    n_lat = len(lat_us)
+    # first-vote phase of the fused kernel from its own globaltimer stamps (measurement hook; a
+    # CUDA event cannot be recorded inside a kernel), one frame
+    k1 = None
+    try:
+        lat.profile_enable(2)
+        res = lat.run_dev(on_dev[0].data_ptr(), n_pts, stride)
+        st = lat.profile_read().astype(np.int64)
+        k1_us = (st[0, :, 0].max() - st[0, :, 15][st[0, :, 15] > 0].min()) / 1e3
+        k1_bytes = 8.0 * res.n_input * num_b + 24.0 * res.n_input + 40.0 * num_b
+        k1 = {"us": float(k1_us), "points": int(res.n_input), "gvotes_per_s": res.n_input * num_b / k1_us / 1e3,
+              "achieved_gbs": k1_bytes / k1_us / 1e3}
+    except Exception as exc:                                     # the hook is optional
+        k1 = {"error": str(exc)}
+    lat.close()
 
     n_frames_rank = FRAMES_PER_STEP * args.steps
     total_frames = n_frames_rank * world
-    value = total_frames / (dev["dev_us"] * 1e-6)
-    e2e_value = total_frames / (e2e["dev_us"] * 1e-6)
-
-    # roofline of the dominant kernel (K1, the first vote = Hough::add), measured live
-    from pointcloud_segmentation_b200.capi import device_info
-    num_b = 20481
-    n_f = dev["nf"] / n_frames_rank
-    vote_us = dev["phases"][1] / n_frames_rank
-    algo_bytes = 8.0 * n_f * num_b + 24.0 * n_f + 40.0 * num_b      # 8 B/vote + 24 B/point + 40 B/direction
+    value = total_frames / (dev["ms"] * 1e-3)
+    e2e_value = total_frames / (e2e["ms"] * 1e-3)
     peak, peak_src = measured_peak()
-    achieved = algo_bytes / (vote_us * 1e-6) / 1e9
+    kernel_us = phase[1] / n_lat
+    achieved = algo_bytes / n_lat / (kernel_us * 1e-6) / 1e9
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "vote_kernel_traffic.json")))["dram_bytes_per_launch"]
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "fused_kernel_traffic.json")))["dram_bytes_per_launch"]
     except Exception:
         pass
 
     if rank == 0:
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dev["dev_us"] / 1e3 / args.steps, "higher_is_better": True,
+            "warmup": args.warmup, "ms_per_step": dev["ms"] / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "configs[1]: single 224x172 ToF frames (38528 px) -> PassThrough+VoxelGrid -> "
                                    "Hough g6 (20481 directions), dx=sqrt(3)*leaf, opt_nlines 20, opt_minvotes 12",
-                       "frames_per_step": FRAMES_PER_STEP, "filtered_points_per_frame": round(n_f, 1),
+                       "frames_per_step": FRAMES_PER_STEP, "filtered_points_per_frame": round(dev["nf"] / n_frames_rank, 1),
                        "lines_per_frame": dev["lines"] / n_frames_rank, "l2": "flushed between steps (256 MiB write)",
-                       "parallelism": f"frame-parallel x{world}" if world > 1 else "single GPU",
-                       "sm_count": device_info()["sm_count"]},
+                       "frames_in_flight_per_gpu": K, "sms_per_frame": sm_count // K if K > 1 else sm_count,
+                       "parallelism": (f"frame-parallel x{world} GPUs, " if world > 1 else "single GPU, ") +
+                                      f"{K} frames in flight per GPU",
+                       "sm_count": sm_count},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": frame_bytes * FRAMES_PER_STEP,
-                    "d2h_bytes_per_step": int(e2e["d2h"]), "ms_per_frame": e2e["dev_us"] / 1e3 / n_frames_rank,
-                    "wall_ms_per_frame": 1e3 * e2e["wall_s"] / n_frames_rank},
+                    "d2h_bytes_per_step": int(e2e["d2h"] / args.steps), "ms_per_step": e2e["ms"] / args.steps},
             "gpu_launches": dev["launches"] + e2e["launches"],
             "clocks": clocks,
-            "roofline": {"kernel": "vote_resident_kernel (K1, Hough::add)", "bound": "hbm", "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes,
-                         "us_per_launch": vote_us, "gvotes_per_s": n_f * num_b / vote_us / 1e3},
-            "votes_per_s": dev["votes"] / (dev["dev_us"] * 1e-6) * world,
-            "phase_us_per_frame": {k: float(v) / n_frames_rank for k, v in
-                                   zip(("prefilter", "first_vote", "loop", "total"), dev["phases"])},
-            "wall_ms_per_frame": 1e3 * dev["wall_s"] / n_frames_rank,
+            "single_frame_latency": {"ms_mean": float(np.mean(lat_us)) / 1e3, "ms_max": float(np.max(lat_us)) / 1e3,
+                                     "frames": n_lat, "note": "one frame at a time on all SMs, frame resident in HBM",
+                                     "phase_us": {k: float(v) / n_lat for k, v in
+                                                  zip(("prefilter", "fused_loop_kernel", "result_copies", "total"), phase)}},
+            "roofline": {"kernel": "fused_loop_kernel (K1 first vote + K2 argmax + K3 fit + K4 un-vote, one launch per frame)",
+                         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": algo_bytes / n_lat, "us_per_launch": kernel_us,
+                         "timed": "CUDA events around the launch, one frame at a time (single_frame_latency leg)",
+                         "note": "SURVEY 8(d) bytes: 8 B/vote (add + subtract) + 24 B/point + 40 B/direction, "
+                                 "25 B/live point per K3 pass, K2 counted on the 9 B/direction records",
+                         "achieved_dense_equivalent": algo_dense / n_lat / (kernel_us * 1e-6) / 1e9,
+                         "k1_first_vote_phase": k1},
+            "votes_per_s": (votes_add + votes_sub) / n_lat / (kernel_us * 1e-6),
+            "votes_evaluated_per_s_throughput": dev["votes"] / (dev["ms"] * 1e-3) * world,
         }
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline_sample(frames)
         print(json.dumps(out), flush=True)
-    pipe.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -321,6 +394,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--concurrency", type=int, default=4,
+                    help="frames in flight per GPU (K pipelines x sm_count/K SMs each); 1 = lowest latency")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10 s CPU sample (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":

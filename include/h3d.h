@@ -174,6 +174,12 @@ int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n
  * h3d_pipeline_run.  All zero when the frame ended early (rc != 0). */
 int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
 
+/* frame-parallel replay on ONE GPU (BASELINE configs[2]): frames are independent (one Hough per
+ * frame, wrap.h:220/347), and the loop of a frame is latency-bound, so K pipelines driven by K
+ * host threads can each take sm_count/K SMs for their persistent loop kernel.  n_ctas = 0: all
+ * SMs (lowest latency for a single frame). */
+int h3d_pipeline_set_sm_share(h3d_pipeline *p, int n_ctas);
+
 /* measurement hook: phase stamps of the fused loop kernel.  out == NULL: enable for `iters`
  * iterations (0 disables).  out != NULL: copy the stamps of the last frame,
  * [iteration][cta][n_slots] globaltimer nanoseconds (slot 8: re-voted planes + 1). */

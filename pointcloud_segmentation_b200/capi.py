@@ -260,6 +260,10 @@ class Pipeline:
         check(lib().h3d_pipeline_timing(self._p, us))
         return list(us)
 
+    def set_sm_share(self, n_ctas):
+        """SMs the persistent loop kernel of this pipeline may use (0 = all)."""
+        check(lib().h3d_pipeline_set_sm_share(self._p, C.c_int(n_ctas)))
+
     def profile_enable(self, iters):
         """Measurement hook: record phase stamps of the fused loop kernel for `iters` iterations."""
         check(lib().h3d_pipeline_profile(self._p, C.c_int(iters), None, C.c_size_t(0), None, None))

@@ -3,6 +3,7 @@
 // needs a CUDA device and fails with H3D_ERR_CUDA otherwise.
 #include "../../include/h3d.h"
 
+#include <atomic>
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
@@ -17,7 +18,7 @@
 namespace h3d {
 
 static thread_local std::string g_error;
-static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py: gpu_launches)
+static std::atomic<unsigned long long> g_launches{0};   // kernels launched by this library (bench.py: gpu_launches)
 static inline void note_launches(unsigned n) { g_launches += n; }
 void set_error(const std::string &msg) { g_error = msg; }
 
@@ -133,7 +134,7 @@ struct h3d_hough {
 };
 
 extern "C" const char *h3d_last_error(void) { return g_error.c_str(); }
-extern "C" unsigned long long h3d_launch_count(void) { return g_launches; }
+extern "C" unsigned long long h3d_launch_count(void) { return g_launches.load(); }
 
 extern "C" int h3d_device_info(int *sm_count, int *cc, size_t *smem_optin) {
   DeviceFacts f;
@@ -752,6 +753,7 @@ struct FrameCtx {
   float us[4] = {0, 0, 0, 0};
   bool timed = false;   // the last frame ran to the end (all events recorded)
   bool fused = false;   // the last frame ran in the fused persistent kernel
+  int fused_ctas = 0;   // CTAs (= SMs) the fused kernel may use; 0 = all (h3d_pipeline_set_sm_share)
 
   ~FrameCtx() { release(); }
   void release() {
@@ -849,14 +851,14 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
 static bool g_use_fused = true;
 
 template <int P>
-int launch_fused_t(FrameCtx &f, const FusedArgs &args, size_t smem) {
+int launch_fused_t(FrameCtx &f, const FusedArgs &args, size_t smem, int grid) {
   static thread_local size_t configured = 0;
   if (smem > configured) {
     H3D_CUDA(cudaFuncSetAttribute(fused_loop_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
   void *params[] = {const_cast<FusedArgs *>(&args)};
-  H3D_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(fused_loop_kernel<P>), dim3(f.hg->dev.sm_count),
+  H3D_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(fused_loop_kernel<P>), dim3(grid),
                                        dim3(kResThreads), params, smem, f.hg->stream));
   note_launches(1);
   return H3D_OK;
@@ -884,7 +886,8 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   const HoughDev &hd = h->d;
   if (!g_use_fused || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0) return H3D_OK;
   const int groups = (hd.dir_count + kResG - 1) / kResG;
-  const int n_own = ((groups + h->dev.sm_count - 1) / h->dev.sm_count) * kResG;
+  const int grid = (f.fused_ctas > 0 && f.fused_ctas < h->dev.sm_count) ? f.fused_ctas : h->dev.sm_count;
+  const int n_own = ((groups + grid - 1) / grid) * kResG;
   const size_t plane_bytes = (size_t)hd.plane_stride * sizeof(unsigned);
   const size_t tables = (size_t)n_own * 56;
   cudaFuncAttributes fa;
@@ -921,10 +924,10 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
     H3D_CUDA(cudaMemsetAsync(f.prof_dev, 0, (size_t)f.prof_iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long), s));
   const int need = (hd.n + kResThreads - 1) / kResThreads;
   int rc;
-  if (need <= 4) rc = launch_fused_t<4>(f, a, smem);
-  else if (need <= 8) rc = launch_fused_t<8>(f, a, smem);
-  else if (need <= 10) rc = launch_fused_t<10>(f, a, smem);
-  else rc = launch_fused_t<12>(f, a, smem);
+  if (need <= 4) rc = launch_fused_t<4>(f, a, smem, grid);
+  else if (need <= 8) rc = launch_fused_t<8>(f, a, smem, grid);
+  else if (need <= 10) rc = launch_fused_t<10>(f, a, smem, grid);
+  else rc = launch_fused_t<12>(f, a, smem, grid);
   if (rc != H3D_OK) return rc;
   H3D_CUDA(cudaMemcpyAsync(f.sync_host, f.sync_dev, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
   *launched = true;
@@ -1307,6 +1310,12 @@ extern "C" int h3d_pipeline_profile(h3d_pipeline *p, int iters, unsigned long lo
     f.prof_iters = iters;
   }
   if (n_cta) *n_cta = f.prof_ctas;
+  return H3D_OK;
+}
+
+extern "C" int h3d_pipeline_set_sm_share(h3d_pipeline *p, int n_ctas) {
+  if (!p || n_ctas < 0) return fail(H3D_ERR_ARG, "bad argument");
+  p->f.fused_ctas = n_ctas;
   return H3D_OK;
 }
 

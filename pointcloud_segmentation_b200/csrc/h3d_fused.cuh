@@ -339,6 +339,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   Q.y = Q.x + A.n_cap; Q.z = Q.y + A.n_cap;
   Q.yidx = reinterpret_cast<int *>(Q.z + A.n_cap);
 
+  if (A.prof && tid == 0 && A.prof_iters > 0) A.prof[(size_t)cta * kProfSlots + 15] = globaltimer_ns();   // kernel start
   // ---- hough->add(X): every plane once (K1), points in registers ----------------------------------
   {
     uint4 *p4 = reinterpret_cast<uint4 *>(planes);
