@@ -17,7 +17,10 @@ keys = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg.per_second", "launch__
         "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio"]
+        "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio",
+        "sm__icc_request_hit_rate.pct", "sm__icc_requests.sum"]
 with open(out, "w") as f:
     f.write(f"# ncu --set full --clock-control none summary of {rep}\n")
     for r in rows[2:]:
