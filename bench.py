@@ -233,9 +233,17 @@ def run_gpu_arm(args):
         """one batch of FRAMES_PER_STEP frames over the K pipelines; device time of the whole batch (ms)"""
         flush.fill_(rank + 1)              # L2 flush between timed steps (inputs are far smaller than L2)
         acc = [dict(d2h=0, lines=0, votes=0, nf=0, iters=0, unvotes=0) for _ in range(K)]
+        errors = []
 
         def work(t):
             a = acc[t]
+            try:
+                run_frames(t, a)
+            except BaseException as exc:   # a failed worker must fail the bench, not shorten the step
+                errors.append(exc)
+
+        def run_frames(t, a):
+            torch.cuda.set_device(local)
             for k in range(t, FRAMES_PER_STEP, K):
                 if e2e:
                     res = pipes[t].run_ptr(pinned[k].data_ptr(), n_pts, stride)
@@ -257,6 +265,8 @@ def run_gpu_arm(args):
         torch.cuda.synchronize()           # every pipeline stream has drained
         ev1.record()
         ev1.synchronize()
+        if errors:
+            raise errors[0]
         out = {k: sum(a[k] for a in acc) for k in acc[0]}
         out["ms"] = ev0.elapsed_time(ev1)
         return out

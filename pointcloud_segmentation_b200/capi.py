@@ -130,6 +130,12 @@ class Hough:
         check(lib().h3d_get_line_key(self._h, C.byref(k)))
         return k.value
 
+    def line_from_index(self, flat):
+        """Inverse map of Hough::getLine (lib/hough.cpp:114-132) for a flat accumulator index."""
+        a, b = (C.c_double * 3)(), (C.c_double * 3)()
+        check(lib().h3d_line_from_index(self._h, C.c_uint64(flat), a, b))
+        return np.array(a[:]), np.array(b[:])
+
     def votes(self):
         cells = self.num_x * self.num_x * self.num_b
         out = np.empty(cells, dtype=np.uint32)

@@ -746,7 +746,7 @@ struct FrameCtx {
   unsigned *sync_dev = nullptr;          // [0] grid barrier, [1] overflow flag
   unsigned *sync_host = nullptr;         // pinned
   unsigned long long *prof_dev = nullptr;   // measurement hook: fused-loop phase stamps (h3d_pipeline_profile)
-  int prof_iters = 0, prof_ctas = 0;
+  int prof_iters = 0, prof_ctas = 0, prof_grid = 0;   // allocated for prof_ctas CTAs; the last launch used prof_grid
   LoopState *st_host = nullptr;   // pinned
   PrepOut *prep_host = nullptr;   // pinned
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // start, prep done, first vote done, end, first vote start
@@ -920,6 +920,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   a.near_t = sqrt_le_threshold(opt_dx);
   a.cell_off = hd.max_x / hd.dx + 0.5;
   a.prof = f.prof_dev; a.prof_iters = f.prof_iters;
+  f.prof_grid = grid;
   if (f.prof_dev)
     H3D_CUDA(cudaMemsetAsync(f.prof_dev, 0, (size_t)f.prof_iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long), s));
   const int need = (hd.n + kResThreads - 1) / kResThreads;
@@ -1201,6 +1202,7 @@ struct h3d_pipeline {
   PrefilterCtx pf;
   K0Window win;
   size_t grid_cells = 0;
+  int device = 0;               // the CUDA device the pipeline was created on
   float *raw_dev = nullptr;     // max_raw_points * 4 floats
   float *filt_dev = nullptr;    // max_raw_points * 3 floats
   size_t raw_cap_floats = 0;
@@ -1214,6 +1216,7 @@ extern "C" int h3d_pipeline_create(const h3d_pipeline_config *cfg, h3d_pipeline 
   if (!p) return fail(H3D_ERR_NOMEM, "host allocation failed");
   std::unique_ptr<h3d_pipeline, void (*)(h3d_pipeline *)> guard(p, h3d_pipeline_destroy);
   p->cfg = *cfg;
+  H3D_CUDA(cudaGetDevice(&p->device));
   const size_t n = cfg->max_raw_points;
   const size_t max_iters = cfg->max_iters ? cfg->max_iters : (size_t)(cfg->opt_nlines > 0 ? cfg->opt_nlines + 1 : 64);
   p->cfg.max_iters = max_iters;
@@ -1243,6 +1246,7 @@ extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_
                                     uint32_t *pool, size_t pool_cap, h3d_result *res) {
   if (!p || !res || (!raw_dev && n) || stride < 3) return fail(H3D_ERR_ARG, "bad argument");
   if (n > p->cfg.max_raw_points) return fail(H3D_ERR_ARG, "frame larger than max_raw_points");
+  H3D_CUDA(cudaSetDevice(p->device));   // the calling thread may be a fresh one (current device 0)
   memset(res, 0, sizeof *res);
   FrameCtx &f = p->f;
   f.timed = false;
@@ -1275,6 +1279,7 @@ extern "C" int h3d_pipeline_run(h3d_pipeline *p, const float *raw, size_t n, siz
                                 uint32_t *pool, size_t pool_cap, h3d_result *res) {
   if (!p || (!raw && n) || stride < 3) return fail(H3D_ERR_ARG, "bad argument");
   if (n * stride > p->raw_cap_floats) return fail(H3D_ERR_ARG, "frame larger than the pipeline's raw buffer");
+  H3D_CUDA(cudaSetDevice(p->device));
   if (n) H3D_CUDA(cudaMemcpyAsync(p->raw_dev, raw, n * stride * sizeof(float), cudaMemcpyHostToDevice, p->f.hg->stream));
   return h3d_pipeline_run_dev(p, p->raw_dev, n, stride, iters, pool, pool_cap, res);
 }
@@ -1298,8 +1303,8 @@ extern "C" int h3d_pipeline_profile(h3d_pipeline *p, int iters, unsigned long lo
   if (n_slots) *n_slots = kProfSlots;
   if (out) {
     if (!f.prof_dev) return fail(H3D_ERR_ARG, "profiling is not enabled");
-    if (n_cta) *n_cta = f.prof_ctas;
-    const size_t words = (size_t)f.prof_iters * f.prof_ctas * kProfSlots;
+    if (n_cta) *n_cta = f.prof_grid;
+    const size_t words = (size_t)f.prof_iters * f.prof_grid * kProfSlots;
     H3D_CUDA(cudaMemcpy(out, f.prof_dev, (words < cap ? words : cap) * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return H3D_OK;
   }

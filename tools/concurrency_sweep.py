@@ -12,8 +12,11 @@ pinned = torch.from_numpy(frames).pin_memory()
 n_pts, stride = frames.shape[1], frames.shape[2]
 sm = capi.device_info()["sm_count"]
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 6
-for K in (1, 2, 3, 4, 6, 8):
-    for share in sorted({sm // K, 0 if K == 1 else sm // K}):
+combos = [(1, 0), (4, 37), (5, 37), (6, 37), (8, 37), (5, 29), (6, 49), (4, 49), (3, 49), (8, 24)]
+if len(sys.argv) > 2:
+    combos = [tuple(int(v) for v in c.split(":")) for c in sys.argv[2].split(",")]
+for K, share in combos:
+    if True:
         pipes = [capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=n_pts) for _ in range(K)]
         for p in pipes:
             p.set_sm_share(share)

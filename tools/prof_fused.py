@@ -6,6 +6,8 @@ from pointcloud_segmentation_b200 import capi, synth
 
 frame = synth.tof_frame()
 pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frame.shape[0])
+share = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+pipe.set_sm_share(share)
 pipe.profile_enable(24)
 for _ in range(3):
     res = pipe.run(frame)
@@ -29,4 +31,6 @@ for it in range(t.shape[0]):
                  f" | nlist max {nl.max()} mean {nl.mean():.1f} sum {nl.sum()} revote max {rv.max():.1f};"
                  f" span {(a[:,9].max()-a[:,0].min())/1e3:.1f}")
     print(line)
+k1 = (t[0, :, 0][t[0, :, 0] > 0].max() - t[0, :, 15][t[0, :, 15] > 0].min()) / 1e3
+print("first vote + prologue us", k1)
 print("loop total us", (t[t > 1e12].max() - t[0, :, 0].min()) / 1e3)

@@ -34,11 +34,13 @@ def topk(Vrows, K):
     part = np.partition(keys, pc - K, axis=1)[:, pc - K:]
     part.sort(axis=1)
     return part[:, ::-1].copy()        # descending keys
-Ks = [1, 2, 3, 4, 8]
+Ks = [1]
+CHUNKS = [0, 148, 592, 2368]   # 0 = all at once (current scheme); else lazily by descending bound, chunk by chunk
 state = {}
-for K in Ks:
-    tk = topk(V, K)
-    state[K] = dict(cells=65535 - (tk & 0xFFFF), B=tk[:, K - 1].copy(), stale=np.zeros(nb, bool), rebuilt=[])
+tk0 = topk(V, 1)
+for K in CHUNKS:
+    state[K] = dict(cells=65535 - (tk0 & 0xFFFF), B=tk0[:, 0].copy(), rebuilt=[])
+Ks = CHUNKS
 alive = np.ones(len(Xc), bool)
 for it, rec in enumerate(tr.iters):
     if rec.status != 0: break
@@ -54,13 +56,25 @@ for it, rec in enumerate(tr.iters):
         exact = M >= s["B"]
         lb = (M[exact] >> 16).max() if exact.any() else 0
         bound = np.where(exact, M, s["B"]) >> 16
-        cand = (~exact) & (bound >= lb)
-        n = int(cand.sum())
-        if n:
-            tk = topk(V[cand], K)
-            s["cells"][cand] = 65535 - (tk & 0xFFFF)
-            s["B"][cand] = tk[:, K - 1]
-        s["rebuilt"].append((n, int((~exact).sum())))
+        cand = np.nonzero((~exact) & (bound >= lb))[0]
+        n = 0
+        rounds = 0
+        if K == 0:
+            n = len(cand); rounds = 1 if n else 0
+            if n:
+                tk = topk(V[cand], 1)
+                s["cells"][cand] = 65535 - (tk & 0xFFFF); s["B"][cand] = tk[:, 0]
+        else:
+            order = cand[np.argsort(-bound[cand].astype(np.int64), kind="stable")]
+            while len(order):
+                order = order[bound[order] >= lb]
+                if not len(order): break
+                chunk, order = order[:K], order[K:]
+                tk = topk(V[chunk], 1)
+                s["cells"][chunk] = 65535 - (tk & 0xFFFF); s["B"][chunk] = tk[:, 0]
+                lb = max(lb, int((tk[:, 0] >> 16).max()))
+                n += len(chunk); rounds += 1
+        s["rebuilt"].append((n, rounds))
     print(f"it {it:2d} |Y| {len(Y):4d} max {gmax:3d} " + "  ".join(f"K{K}: {state[K]['rebuilt'][-1][0]:5d}/{state[K]['rebuilt'][-1][1]:5d}" for K in Ks), flush=True)
 for K in Ks:
     print("K", K, "total rebuilt", sum(r[0] for r in state[K]["rebuilt"]))
