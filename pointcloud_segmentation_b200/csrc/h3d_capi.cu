@@ -400,8 +400,7 @@ static int configure_hough(h3d_hough *h, const double minP[3], const double maxP
   HoughDev &d = h->d;
   d.num_x = (int)num_x;
   d.plane_cells = (unsigned)(num_x * num_x);
-  d.plane_stride = (d.plane_cells + 3u) & ~3u;
-  if (d.plane_stride == 0) d.plane_stride = 4;
+  d.plane_stride = (d.plane_cells + 2u * (unsigned)num_x + 4u + 3u) & ~3u;   // + slack cells (BOUNDED vote form)
   d.num_b = (int)sp.num_b;
   d.max_x = max_x; d.dx = dx;
   d.inv_s = 0; d.kmagic = 0;
@@ -413,6 +412,11 @@ static int configure_hough(h3d_hough *h, const double minP[3], const double maxP
     d.kmagic = (double)(6755399441055744.0L + bias);   // 1.5 * 2^52 + bias
     if (!(bias >= 0.0L && bias < 4294967296.0L)) d.fast_ok = 0;
   }
+  // box symmetric about the origin (PointCloud::shiftToOrigin): with every point inside it,
+  // |x'| <= max_x (1 + 1e-9), so 0 <= x_i, y_i <= num_x + 1 and the fast path needs no range test
+  d.bounded = d.fast_ok && num_x < 2000;
+  for (int c = 0; c < 3; ++c)
+    if (!(fabs(minP[c] + maxP[c]) <= 1e-9 * max_x)) d.bounded = 0;
   d.coef = sp.coef_dev;
   return H3D_OK;
 }
@@ -884,7 +888,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   *launched = false;
   h3d_hough *h = f.hg;
   const HoughDev &hd = h->d;
-  if (!g_use_fused || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0) return H3D_OK;
+  if (!g_use_fused || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0 || !hd.bounded) return H3D_OK;
   const int groups = (hd.dir_count + kResG - 1) / kResG;
   const int grid = (f.fused_ctas > 0 && f.fused_ctas < h->dev.sm_count) ? f.fused_ctas : h->dev.sm_count;
   const int n_own = ((groups + grid - 1) / grid) * kResG;

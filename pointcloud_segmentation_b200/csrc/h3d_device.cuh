@@ -26,7 +26,8 @@ struct HoughDev {
   // discretisation (lib/hough.cpp:32-40)
   int num_x;              // cells per axis
   unsigned plane_cells;   // num_x * num_x
-  unsigned plane_stride;  // plane_cells rounded up to a multiple of 4 (uint4 scan)
+  unsigned plane_stride;  // plane_cells + 2*num_x + 4 slack cells, rounded up to a multiple of 4 (uint4 scan);
+                          // the slack absorbs the out-of-range votes of the BOUNDED vote form
   int num_b;              // directions of the whole space (flat-index multiplier)
   int dir_begin;          // first direction owned by this instance
   int dir_count;          // directions owned
@@ -35,6 +36,8 @@ struct HoughDev {
   // mantissa word of fma(x', inv_s, kmagic)
   double inv_s, kmagic;
   int fast_ok;
+  int bounded;            // box symmetric about the origin (shiftToOrigin) and num_x < 2000: with every point
+                          // inside the box, 0 <= x_i, y_i <= num_x + 1 and the fast path needs no range test
   const DirCoef *coef;    // whole space, indexed by global direction
   // points (SoA, centred frame) and their weights: +1 added, -1 subtracted
   // without a matching added point, 0 removed
@@ -126,6 +129,19 @@ __device__ __forceinline__ unsigned vote_cell_acc(const FastCoef &f, double kmag
   hacc |= ((unsigned)__double2hiint(sx) ^ 0x43380000u) | ((unsigned)__double2hiint(sy) ^ 0x43380000u);
   return (lx >> 20) * num_x + (ly >> 20);
 }
+// BOUNDED form (HoughDev::bounded, all points inside the box): byte offset of the cell inside its
+// plane, 4*(x_i*num_x + y_i) with row4 = 4*num_x.  No exponent test (0 < n < 2^32 is guaranteed) and
+// no range test: x_i, y_i <= num_x + 1, so the offset stays inside the plane's slack cells, which the
+// scan ignores.  14 instructions per vote instead of 19.
+__device__ __forceinline__ unsigned vote_off_bounded(const FastCoef &f, double kmagic, unsigned row4, double px,
+                                                     double py, double pz, unsigned &gmin) {
+  const double sx = __fma_rn(f.c0s, px, __fma_rn(f.c1n, py, __fma_rn(f.bxn, pz, kmagic)));
+  const double sy = __fma_rn(f.c1n, px, __fma_rn(f.c2s, py, __fma_rn(f.byn, pz, kmagic)));
+  const unsigned lx = (unsigned)__double2loint(sx), ly = (unsigned)__double2loint(sy);
+  gmin = min(gmin, min((lx << 12) + 0x8000u, (ly << 12) + 0x8000u));   // < 0x10000: within 8 units
+  return (lx >> 20) * row4 + ((ly >> 20) << 2);
+}
+
 __device__ __forceinline__ bool batch_unsure(unsigned gmin, unsigned hacc) { return (gmin < 0x10000u) | (hacc != 0u); }
 
 // shared-memory increment by 32-bit shared address, predicated, no return value

@@ -290,25 +290,30 @@ __device__ __forceinline__ unsigned inlier_pass(const FusedPoints &Q, int n_aliv
   return m;
 }
 
-// re-vote of two directions (records r0, r1; r1 < 0: none) over the compact live points
+// re-vote of two directions (records r0, r1; r1 < 0: none) over the compact live points; BOUNDED
+// vote form (the host launches this kernel only when HoughDev::bounded holds)
 __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints &Q, int n_alive, const FastCoef &f0,
                                             const FastCoef &f1, int j0, int j1, unsigned plane0_sa, unsigned plane1_sa,
                                             unsigned dummy_sa) {
   const double kmagic = h.kmagic;
-  const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells;
+  const unsigned row4 = 4u * (unsigned)h.num_x, plane_cells = h.plane_cells;
   const bool two = j1 >= 0;
 #pragma unroll 2
   for (int i = threadIdx.x; i < n_alive; i += kResThreads) {
     const double x = Q.x[i], y = Q.y[i], z = Q.z[i];
-    unsigned gmin = 0xFFFFFFFFu, hacc = 0;
-    unsigned c0 = vote_cell_acc(f0, kmagic, num_x, x, y, z, gmin, hacc);
-    unsigned c1 = vote_cell_acc(f1, kmagic, num_x, x, y, z, gmin, hacc);
-    if (batch_unsure(gmin, hacc) | !h.fast_ok) {   // rare: within 8e-6 cell of a boundary
-      c0 = vote_cell_checked(h.coef + j0, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
-      if (two) c1 = vote_cell_checked(h.coef + j1, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
+    unsigned gmin = 0xFFFFFFFFu;
+    unsigned a0 = plane0_sa + vote_off_bounded(f0, kmagic, row4, x, y, z, gmin);
+    unsigned a1 = plane1_sa + vote_off_bounded(f1, kmagic, row4, x, y, z, gmin);
+    if ((gmin < 0x10000u) | !h.fast_ok) {   // rare: within 8e-6 cell of a boundary
+      const unsigned c0 = vote_cell_checked(h.coef + j0, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
+      a0 = c0 < plane_cells ? plane0_sa + 4u * c0 : dummy_sa;
+      if (two) {
+        const unsigned c1 = vote_cell_checked(h.coef + j1, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
+        a1 = c1 < plane_cells ? plane1_sa + 4u * c1 : dummy_sa;
+      }
     }
-    red_shared_inc(c0 < plane_cells ? plane0_sa + 4u * c0 : dummy_sa);
-    red_shared_inc((two & (c1 < plane_cells)) ? plane1_sa + 4u * c1 : dummy_sa);
+    red_shared_inc(a0);
+    red_shared_inc(two ? a1 : dummy_sa);
   }
 }
 
@@ -344,7 +349,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   {
     uint4 *p4 = reinterpret_cast<uint4 *>(planes);
     for (unsigned q = tid; q < 2u * G * quads + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-    vote_resident<P, 0>(h, nullptr, h.dir_count, planes, sh.res, cta, n_cta);
+    vote_resident<P, 0, true>(h, nullptr, h.dir_count, planes, sh.res, cta, n_cta);
   }
   __syncthreads();
   // own records: entry r = k*G + g is direction (cta + k*n_cta)*G + g
@@ -544,7 +549,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
       __syncthreads();
 #pragma unroll 1
       for (int bi = 0; bi < cnt; ++bi) {
-        const unsigned long long k = scan_plane_fast<kResThreads>(planes + (size_t)bi * stride, quads, tid);
+        const unsigned long long k = scan_plane_fast<kResThreads>(planes + (size_t)bi * stride, quads, tid, h.plane_cells);
         if (lane == 0) sh.res.warp_best[bi / G][bi % G][warp] = k;
       }
       __syncthreads();

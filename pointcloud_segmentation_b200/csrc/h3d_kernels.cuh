@@ -184,15 +184,23 @@ constexpr int kResWarps = kResThreads / 32;
 
 // (max, first max cell) of a plane, zeroing it; quads whose maximum cannot beat the
 // running best cost 6 instructions
+// cells >= plane_cells (slack of the BOUNDED vote form) are zeroed but never counted
 template <int THREADS>
-__device__ __forceinline__ unsigned long long scan_plane_fast(unsigned *plane, unsigned quads, int t) {
+__device__ __forceinline__ unsigned long long scan_plane_fast(unsigned *plane, unsigned quads, int t,
+                                                              unsigned plane_cells) {
   uint4 *p4 = reinterpret_cast<uint4 *>(plane);
   unsigned best = 0, bcell = 0;
   for (unsigned q = t; q < quads; q += THREADS) {
-    const uint4 v = p4[q];
-    const unsigned m4 = max(max(v.x, v.y), max(v.z, v.w));
-    if (m4 == 0) continue;
+    uint4 v = p4[q];
+    if ((v.x | v.y | v.z | v.w) == 0) continue;
     p4[q] = make_uint4(0, 0, 0, 0);
+    if (4 * q + 3 >= plane_cells) {
+      if (4 * q >= plane_cells) v.x = 0;
+      if (4 * q + 1 >= plane_cells) v.y = 0;
+      if (4 * q + 2 >= plane_cells) v.z = 0;
+      v.w = 0;
+    }
+    const unsigned m4 = max(max(v.x, v.y), max(v.z, v.w));
     if (m4 > best) {
       best = m4;
       bcell = 4 * q + (v.x == m4 ? 0u : v.y == m4 ? 1u : v.z == m4 ? 2u : 3u);
@@ -212,7 +220,7 @@ struct ResShared {
                               // previous phase's numbers stay readable while the next are staged
 };
 
-template <int P, int ABLATE>
+template <int P, int ABLATE, bool BOUNDED = false>
 __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__restrict__ list, int count,
                                               unsigned *planes, ResShared &sh, int cta, int n_cta) {
   constexpr int G = kResG;
@@ -249,7 +257,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
   if (tid < G) { stage(cta, 0, 0); cp_async_wait_all(); }
   __syncthreads();   // also orders the kernel's zero-fill of the planes
   const double kmagic = h.kmagic, inv_s = h.inv_s;
-  const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells;
+  const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells, row4 = 4u * (unsigned)h.num_x;
   unsigned sink = 0;
   bool prev_any = false;
   int k = 0;
@@ -272,22 +280,27 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
         for (int p0 = 0; p0 < P; p0 += CH) {
           if (p0 >= used_slots) break;                    // uniform
           const bool edge = p0 + CH > full_slots;         // uniform: batch holds the partial slot
-          unsigned cell[CH];
+          // off[c]: byte offset of the vote inside the plane (>= 4*plane_cells when the reference drops it)
+          unsigned off[CH];
           unsigned gmin = 0xFFFFFFFFu, hacc = 0;
+          const unsigned drop_off = dummy_sa - mine_sa;
 #pragma unroll
           for (int c = 0; c < CH; ++c) {
             const int p = p0 + c;
-            if (p >= P) { cell[c] = 0xFFFFFFFFu; continue; }
-            if (ABLATE == 2) cell[c] = ((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells;
-            else cell[c] = vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], gmin, hacc);
+            if (p >= P) { off[c] = drop_off; continue; }
+            if (ABLATE == 2) off[c] = 4u * (((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells);
+            else if (BOUNDED) off[c] = vote_off_bounded(f, kmagic, row4, px[p], py[p], pz[p], gmin);
+            else off[c] = 4u * vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], gmin, hacc);
           }
           if (ABLATE != 2 && (batch_unsure(gmin, hacc) | !h.fast_ok)) {   // rare: within 8e-6 cell of a boundary
 #pragma unroll
             for (int c = 0; c < CH; ++c) {   // unrolled: register arrays must not be indexed dynamically
               const int p = p0 + c;
-              if (p < P)
-                cell[c] = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
-                                            h.fast_ok, px[p], py[p], pz[p]);
+              if (p < P) {
+                const unsigned cell = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
+                                                        h.fast_ok, px[p], py[p], pz[p]);
+                off[c] = cell < plane_cells ? 4u * cell : drop_off;
+              }
             }
           }
           // unconditional increments (ATOMS.POPC.INC merges lanes that hit the same cell and needs no
@@ -296,16 +309,18 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
 #pragma unroll
             for (int c = 0; c < CH; ++c) {
               if (p0 + c >= P) continue;
-              if (ABLATE == 1) sink ^= cell[c];
-              else red_shared_inc(cell[c] < plane_cells ? mine_sa + 4u * cell[c] : dummy_sa);
+              if (ABLATE == 1) sink ^= off[c];
+              else if (BOUNDED) red_shared_inc(mine_sa + off[c]);
+              else red_shared_inc(off[c] < 4u * plane_cells ? mine_sa + off[c] : dummy_sa);
             }
           } else {
 #pragma unroll
             for (int c = 0; c < CH; ++c) {
               const int p = p0 + c;
               if (p >= P) continue;
-              if (ABLATE == 1) sink ^= cell[c];
-              else red_shared_inc(((cell[c] < plane_cells) & ((live >> p) & 1u)) ? mine_sa + 4u * cell[c] : dummy_sa);
+              if (ABLATE == 1) sink ^= off[c];
+              else if (BOUNDED) red_shared_inc(((live >> p) & 1u) ? mine_sa + off[c] : dummy_sa);
+              else red_shared_inc(((off[c] < 4u * plane_cells) & ((live >> p) & 1u)) ? mine_sa + off[c] : dummy_sa);
             }
           }
         }
@@ -315,7 +330,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
 #pragma unroll 1
       for (int g = 0; g < G; ++g) {
         const unsigned long long key =
-            scan_plane_fast<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, quads, tid);
+            scan_plane_fast<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, quads, tid, plane_cells);
         if (lane == 0) sh.warp_best[slot ^ 1][g][warp] = key;
       }
     }
