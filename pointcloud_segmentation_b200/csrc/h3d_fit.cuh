@@ -57,8 +57,8 @@ struct Eig3f {
 // IEEE division / square root out of line on the device: eig3f has ~25 of them and runs on one
 // thread inside persistent kernels whose loop body must stay small (32 KB instruction cache)
 #ifdef __CUDA_ARCH__
-__device__ __noinline__ float eig_div_dev(float a, float b) { return __fdiv_rn(a, b); }
-__device__ __noinline__ float eig_sqrt_dev(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ float eig_div_dev(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float eig_sqrt_dev(float a) { return __fsqrt_rn(a); }
 #define H3D_EIG_DIV(a, b) eig_div_dev((a), (b))
 #define H3D_EIG_SQRT(a) eig_sqrt_dev((a))
 #define H3D_EIG_NOINLINE __noinline__
