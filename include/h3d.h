@@ -180,6 +180,17 @@ int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
  * SMs (lowest latency for a single frame). */
 int h3d_pipeline_set_sm_share(h3d_pipeline *p, int n_ctas);
 
+/* Batched replay of independent frames (BASELINE configs[2]; node.cpp:286-294 hands one frame at a
+ * time to hough3dlines): n_pipes host threads, one per pipeline, pull frames from a shared counter.
+ * Frame i = raw[i] (n_points[i] points, `stride` floats apart; DEVICE pointers when
+ * frames_on_device != 0) -> results[i], iters + i*max_iters, pool + i*pool_cap (iters / pool may be
+ * NULL).  Set CUDA_DEVICE_MAX_CONNECTIONS >= n_pipes + 1 before the first CUDA call, or the
+ * pipelines' streams share hardware queues and serialise. */
+int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw,
+                   const size_t *n_points, size_t stride, size_t n_frames, int frames_on_device,
+                   h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                   h3d_result *results);
+
 /* measurement hook: phase stamps of the fused loop kernel.  out == NULL: enable for `iters`
  * iterations (0 disables).  out != NULL: copy the stamps of the last frame,
  * [iteration][cta][n_slots] globaltimer nanoseconds (slot 8: re-voted planes + 1). */

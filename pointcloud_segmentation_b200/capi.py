@@ -298,6 +298,41 @@ class Pipeline:
 
 
 # ---- PointCloud entry points (lib/pointcloud.cpp) on host arrays --------------------------
+class Replay:
+    """Batched replay of independent frames over K pipelines (h3d_replay_run): K host threads in the
+    library, each pipeline limited to `sm_share` SMs for its persistent loop kernel."""
+
+    def __init__(self, n_pipes, sm_share, granularity, window, leaf, opt_dx, minvotes, nlines, max_raw_points,
+                 max_frames):
+        self.pipes = [Pipeline(granularity, window, leaf, opt_dx, minvotes, nlines, max_raw_points)
+                      for _ in range(n_pipes)]
+        for p in self.pipes:
+            p.set_sm_share(sm_share)
+        self.max_iters = self.pipes[0].max_iters
+        self.pool_cap = 2 * self.max_iters * int(max_raw_points) // 8     # inlier lists of one frame
+        self.max_frames = max_frames
+        self.iters = (Iter * (self.max_iters * max_frames))()
+        self.pool = np.zeros(self.pool_cap * max_frames, dtype=np.uint32)
+        self.results = (Result * max_frames)()
+        self._handles = (C.c_void_p * n_pipes)(*[p._p for p in self.pipes])
+
+    def run(self, ptrs, n_points, stride, on_device):
+        """ptrs: integer addresses of the frames (host or device); returns the ctypes Result array."""
+        n = len(ptrs)
+        assert n <= self.max_frames
+        raw = (C.c_void_p * n)(*ptrs)
+        npts = (C.c_size_t * n)(*n_points)
+        check(lib().h3d_replay_run(self._handles, C.c_size_t(len(self.pipes)), raw, npts, C.c_size_t(stride),
+                                   C.c_size_t(n), C.c_int(1 if on_device else 0), self.iters,
+                                   C.c_size_t(self.max_iters), self.pool.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                   C.c_size_t(self.pool_cap), self.results))
+        return self.results
+
+    def close(self):
+        for p in self.pipes:
+            p.close()
+
+
 def min_max(xyz):
     a, p, n = _pts(xyz)
     mn, mx = (C.c_double * 3)(), (C.c_double * 3)()

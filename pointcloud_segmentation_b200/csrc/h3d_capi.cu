@@ -11,6 +11,7 @@
 #include <map>
 #include <mutex>
 #include <new>
+#include <thread>
 
 #include "h3d_fused.cuh"
 #include "h3d_prefilter.cuh"
@@ -893,7 +894,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   const int grid = (f.fused_ctas > 0 && f.fused_ctas < h->dev.sm_count) ? f.fused_ctas : h->dev.sm_count;
   const int n_own = ((groups + grid - 1) / grid) * kResG;
   const size_t plane_bytes = (size_t)hd.plane_stride * sizeof(unsigned);
-  const size_t tables = (size_t)n_own * 56;
+  const size_t tables = (size_t)n_own * 16;
   cudaFuncAttributes fa;
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel<4>));
   if (h->dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
@@ -1319,6 +1320,48 @@ extern "C" int h3d_pipeline_profile(h3d_pipeline *p, int iters, unsigned long lo
     f.prof_iters = iters;
   }
   if (n_cta) *n_cta = f.prof_ctas;
+  return H3D_OK;
+}
+
+// Batched replay (BASELINE configs[2]): n_pipes host threads, one per pipeline, pull frames from a
+// shared counter.  Frame i: raw[i] (n_points[i] points, `stride` floats apart; device pointers when
+// frames_on_device), results[i], iters + i*max_iters, pool + i*pool_cap.
+extern "C" int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw,
+                              const size_t *n_points, size_t stride, size_t n_frames, int frames_on_device,
+                              h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                              h3d_result *results) {
+  if (!pipes || n_pipes == 0 || (!raw && n_frames) || (!n_points && n_frames) || !results)
+    return fail(H3D_ERR_ARG, "bad argument");
+  for (size_t k = 0; k < n_pipes; ++k) if (!pipes[k]) return fail(H3D_ERR_ARG, "null pipeline");
+  std::atomic<size_t> next{0};
+  std::atomic<int> first_rc{H3D_OK};
+  std::mutex err_mu;
+  std::string err_text;
+  auto worker = [&](size_t t) {
+    for (;;) {
+      const size_t i = next.fetch_add(1);
+      if (i >= n_frames || first_rc.load() != H3D_OK) break;
+      h3d_iter *it = iters ? iters + i * max_iters : nullptr;
+      uint32_t *pl = pool ? pool + i * pool_cap : nullptr;
+      const int rc = frames_on_device
+                         ? h3d_pipeline_run_dev(pipes[t], raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i])
+                         : h3d_pipeline_run(pipes[t], raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i]);
+      if (rc != H3D_OK) {
+        int expected = H3D_OK;
+        if (first_rc.compare_exchange_strong(expected, rc)) {
+          std::lock_guard<std::mutex> lock(err_mu);
+          err_text = h3d_last_error();      // thread-local text of the failing worker
+        }
+        break;
+      }
+    }
+  };
+  std::vector<std::thread> threads;
+  threads.reserve(n_pipes);
+  for (size_t t = 1; t < n_pipes; ++t) threads.emplace_back(worker, t);
+  worker(0);
+  for (auto &th : threads) th.join();
+  if (first_rc.load() != H3D_OK) { set_error(err_text); return first_rc.load(); }
   return H3D_OK;
 }
 

@@ -4,8 +4,8 @@
 //
 // One CTA per SM.  Division of labour:
 //   * each CTA OWNS a fixed, strided set of directions (the ones it voted in the first pass); their
-//     records (max votes, first max cell, stale flag) and scaled coefficients live in ITS shared
-//     memory.  Un-voting removed points and re-voting stale planes are CTA-local.
+//     records (max votes, first max cell, stale flag) live in ITS shared memory (16 B each; the
+//     coefficients are re-read from L2 when a record is tested or re-voted).  Un-voting removed points and re-voting stale planes are CTA-local.
 //   * the line fit (inliers -> ordered compaction -> orthogonal_LSQ -> inliers -> LSQ -> remove) is
 //     computed REDUNDANTLY and deterministically by every CTA from its own copy of the points, so no
 //     CTA waits for another one's fit.
@@ -224,13 +224,6 @@ __device__ __forceinline__ bool strip_may_hit(const FastCoef &f, const double (&
   return ex * ex + ey * ey <= reach2;
 }
 
-__device__ __forceinline__ FastCoef load_fast(const double *own_coef, int r) {
-  FastCoef f;
-  f.c0s = own_coef[5 * r]; f.c1n = own_coef[5 * r + 1]; f.c2s = own_coef[5 * r + 2];
-  f.bxn = own_coef[5 * r + 3]; f.byn = own_coef[5 * r + 4];
-  return f;
-}
-
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(threads) : "memory");
 }
@@ -328,12 +321,11 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   // per-CTA record tables first, then the planes (+ pad word); behind the planes of a re-vote
   // round (the first vote uses 2*G planes over the same area) the live points and the inlier list
   const int n_own = A.n_own_max;
-  double *own_coef = reinterpret_cast<double *>(smem_raw);               // 5 scaled coefficients per record
-  unsigned *rv = reinterpret_cast<unsigned *>(own_coef + 5 * n_own);     // max votes (bound when stale)
+  unsigned *rv = reinterpret_cast<unsigned *>(smem_raw);                 // max votes (bound when stale)
   unsigned *rcell = rv + n_own;                                          // first max cell
   unsigned *rstale = rcell + n_own;
   int *rlist = reinterpret_cast<int *>(rstale + n_own);
-  const unsigned tables_bytes = (unsigned)n_own * 56u;                   // n_own % 4 == 0 -> multiple of 16
+  const unsigned tables_bytes = (unsigned)n_own * 16u;                   // n_own % 4 == 0 -> multiple of 16
   unsigned *planes = reinterpret_cast<unsigned *>(smem_raw + tables_bytes);
   const unsigned stride = h.plane_stride, quads = stride / 4;
   const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
@@ -357,9 +349,6 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     const int l = (cta + (r / G) * n_cta) * G + (r % G);
     if (l < h.dir_count) {
       rv[r] = h.dvotes[l]; rcell[r] = h.dcell[l];
-      const FastCoef f = make_fast(h.coef[h.dir_begin + l], h.inv_s);
-      own_coef[5 * r] = f.c0s; own_coef[5 * r + 1] = f.c1n; own_coef[5 * r + 2] = f.c2s;
-      own_coef[5 * r + 3] = f.bxn; own_coef[5 * r + 4] = f.byn;
     } else { rv[r] = 0; rcell[r] = 0; }
     rstale[r] = 0;
   }
@@ -461,8 +450,9 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
           if (rstale[r] || rv[r] == 0) continue;
           const unsigned cx = rcell[r] / num_x, cy = rcell[r] - cx * num_x;
           // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
+          const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
           if (cy == 0 || cy == num_x - 1 ||
-              strip_may_hit(load_fast(own_coef, r), a, b, t0, t1, A.cell_off, reach2, cx, cy))
+              strip_may_hit(make_fast(h.coef[j], h.inv_s), a, b, t0, t1, A.cell_off, reach2, cx, cy))
             rlist[atomicAdd(&sh.ns, 1)] = r;
         }
         named_bar_sync(1, un);
@@ -474,7 +464,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
           const int r = rlist[s];
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
           const int i = Q.yidx[e];
-          if (vote_cell(h, load_fast(own_coef, r), j, Q.x[i], Q.y[i], Q.z[i]) == rcell[r]) rstale[r] = 1;
+          if (vote_cell(h, make_fast(h.coef[j], h.inv_s), j, Q.x[i], Q.y[i], Q.z[i]) == rcell[r]) rstale[r] = 1;
         }
       }
       __syncthreads();
@@ -543,7 +533,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
         const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
         const int j0 = h.dir_begin + (cta + (r0 / G) * n_cta) * G + (r0 % G);
         const int j1 = r1 >= 0 ? h.dir_begin + (cta + (r1 / G) * n_cta) * G + (r1 % G) : -1;
-        revote_pair(h, Q, n_alive, load_fast(own_coef, r0), load_fast(own_coef, r1 >= 0 ? r1 : r0), j0, j1,
+        revote_pair(h, Q, n_alive, make_fast(h.coef[j0], h.inv_s), make_fast(h.coef[j1 >= 0 ? j1 : j0], h.inv_s), j0, j1,
                     planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa);
       }
       __syncthreads();

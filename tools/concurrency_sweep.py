@@ -16,26 +16,17 @@ combos = [(1, 0), (4, 37), (5, 37), (6, 37), (8, 37), (5, 29), (6, 49), (4, 49),
 if len(sys.argv) > 2:
     combos = [tuple(int(v) for v in c.split(":")) for c in sys.argv[2].split(",")]
 for K, share in combos:
-    if True:
-        pipes = [capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=n_pts) for _ in range(K)]
-        for p in pipes:
-            p.set_sm_share(share)
-        lines = [0] * K
-        def work(t, n_rep):
-            for r in range(n_rep):
-                for k in range(t, 16, K):
-                    res = pipes[t].run_ptr(pinned[k].data_ptr(), n_pts, stride)
-                    lines[t] += res.n_lines
-        def run(n_rep):
-            th = [threading.Thread(target=work, args=(t, n_rep)) for t in range(K)]
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            for t in th: t.start()
-            for t in th: t.join()
-            torch.cuda.synchronize()
-            return time.perf_counter() - t0
-        run(2)
-        dt = run(reps)
-        print(f"K={K} sm_share={share or sm}: {16 * reps / dt:8.1f} frames/s  ({1e3 * dt / (16 * reps):.3f} ms/frame, lines {sum(lines)})", flush=True)
-        for p in pipes:
-            p.close()
+    NF = 64
+    rp = capi.Replay(K, share, 6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, n_pts, NF)
+    ptrs = [pinned[k % 16].data_ptr() for k in range(NF)]
+    def run(n_rep):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(n_rep):
+            res = rp.run(ptrs, [n_pts] * NF, stride, False)
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0, sum(r.n_lines for r in res[:NF])
+    run(2)
+    dt, lines = run(reps)
+    print(f"K={K} sm_share={share or sm}: {NF * reps / dt:8.1f} frames/s  ({1e3 * dt / (NF * reps):.3f} ms/frame, lines {lines})", flush=True)
+    rp.close()
