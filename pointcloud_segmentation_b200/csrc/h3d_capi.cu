@@ -890,6 +890,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   h3d_hough *h = f.hg;
   const HoughDev &hd = h->d;
   if (!g_use_fused || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0 || !hd.bounded) return H3D_OK;
+  if (hd.plane_stride >= 65536u || hd.n >= 65535) return H3D_OK;   // re-vote keys pack (votes, cell) in 16 + 16 bits
   const int groups = (hd.dir_count + kResG - 1) / kResG;
   const int grid = (f.fused_ctas > 0 && f.fused_ctas < h->dev.sm_count) ? f.fused_ctas : h->dev.sm_count;
   const int n_own = ((groups + grid - 1) / grid) * kResG;

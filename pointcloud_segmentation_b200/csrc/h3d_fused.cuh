@@ -69,6 +69,7 @@ struct FusedShared {
   int red_lo[kResWarps], red_hi[kResWarps];
   int tmin_i, tmax_i;         // ordered-int encodings of float t bounds of Y
   int ns, nlist;
+  unsigned rv_best[2 * kResG + 2][kResWarps];   // re-vote rounds: per-warp plane maxima
 };
 
 // live points (compact, cloud order) and the current inlier list, all in shared memory
@@ -283,31 +284,47 @@ __device__ __forceinline__ unsigned inlier_pass(const FusedPoints &Q, int n_aliv
   return m;
 }
 
-// re-vote of two directions (records r0, r1; r1 < 0: none) over the compact live points; BOUNDED
-// vote form (the host launches this kernel only when HoughDev::bounded holds)
+__device__ __forceinline__ unsigned atom_shared_inc_ret(unsigned addr) {
+  unsigned old;
+  asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr) : "memory");
+  return old;
+}
+
+// Re-vote of two directions (j1 < 0: only one) over the compact live points, BOUNDED vote form
+// (the host launches this kernel only when HoughDev::bounded holds).  The planes of late iterations
+// are sparse, so instead of scanning them the increments RETURN the old count: the last voter of a
+// cell sees its final count - 1, hence max over all votes of (old + 1, lowest cell) is the plane's
+// (max votes, first max cell).  key = (old + 1) << 16 | (0xFFFF - cell); the caller zero-fills the
+// planes afterwards.  Votes the reference drops (slack cells, exact path) do not enter the key.
 __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints &Q, int n_alive, const FastCoef &f0,
                                             const FastCoef &f1, int j0, int j1, unsigned plane0_sa, unsigned plane1_sa,
-                                            unsigned dummy_sa) {
+                                            unsigned dummy_sa, unsigned &best0, unsigned &best1) {
   const double kmagic = h.kmagic;
-  const unsigned row4 = 4u * (unsigned)h.num_x, plane_cells = h.plane_cells;
+  const unsigned row4 = 4u * (unsigned)h.num_x, plane_cells = h.plane_cells, lim = 4u * h.plane_cells;
   const bool two = j1 >= 0;
+  unsigned b0 = 0, b1 = 0;
 #pragma unroll 2
   for (int i = threadIdx.x; i < n_alive; i += kResThreads) {
     const double x = Q.x[i], y = Q.y[i], z = Q.z[i];
     unsigned gmin = 0xFFFFFFFFu;
-    unsigned a0 = plane0_sa + vote_off_bounded(f0, kmagic, row4, x, y, z, gmin);
-    unsigned a1 = plane1_sa + vote_off_bounded(f1, kmagic, row4, x, y, z, gmin);
+    unsigned o0 = vote_off_bounded(f0, kmagic, row4, x, y, z, gmin);
+    unsigned o1 = vote_off_bounded(f1, kmagic, row4, x, y, z, gmin);
     if ((gmin < 0x10000u) | !h.fast_ok) {   // rare: within 8e-6 cell of a boundary
       const unsigned c0 = vote_cell_checked(h.coef + j0, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
-      a0 = c0 < plane_cells ? plane0_sa + 4u * c0 : dummy_sa;
+      o0 = c0 < plane_cells ? 4u * c0 : lim;
       if (two) {
         const unsigned c1 = vote_cell_checked(h.coef + j1, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
-        a1 = c1 < plane_cells ? plane1_sa + 4u * c1 : dummy_sa;
+        o1 = c1 < plane_cells ? 4u * c1 : lim;
       }
     }
-    red_shared_inc(a0);
-    red_shared_inc(two ? a1 : dummy_sa);
+    const bool in0 = o0 < lim, in1 = two & (o1 < lim);
+    const unsigned old0 = atom_shared_inc_ret(in0 ? plane0_sa + o0 : dummy_sa);
+    const unsigned old1 = atom_shared_inc_ret(in1 ? plane1_sa + o1 : dummy_sa);
+    const unsigned k0 = ((old0 + 1u) << 16) | (0xFFFFu - (o0 >> 2)), k1 = ((old1 + 1u) << 16) | (0xFFFFu - (o1 >> 2));
+    b0 = max(b0, in0 ? k0 : 0u);
+    b1 = max(b1, in1 ? k1 : 0u);
   }
+  best0 = b0; best1 = b1;
 }
 
 template <int P>
@@ -533,23 +550,25 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
         const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
         const int j0 = h.dir_begin + (cta + (r0 / G) * n_cta) * G + (r0 % G);
         const int j1 = r1 >= 0 ? h.dir_begin + (cta + (r1 / G) * n_cta) * G + (r1 % G) : -1;
+        unsigned k0, k1;
         revote_pair(h, Q, n_alive, make_fast(h.coef[j0], h.inv_s), make_fast(h.coef[j1 >= 0 ? j1 : j0], h.inv_s), j0, j1,
-                    planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa);
+                    planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa, k0, k1);
+        k0 = __reduce_max_sync(0xFFFFFFFFu, k0);
+        k1 = __reduce_max_sync(0xFFFFFFFFu, k1);
+        if (lane == 0) { sh.rv_best[bi][warp] = k0; sh.rv_best[bi + 1][warp] = k1; }
       }
       __syncthreads();
-#pragma unroll 1
-      for (int bi = 0; bi < cnt; ++bi) {
-        const unsigned long long k = scan_plane_fast<kResThreads>(planes + (size_t)bi * stride, quads, tid, h.plane_cells);
-        if (lane == 0) sh.res.warp_best[bi / G][bi % G][warp] = k;
+      {   // the planes of this round back to zero (no scan: the keys already hold the maxima)
+        uint4 *p4 = reinterpret_cast<uint4 *>(planes);
+        for (unsigned q = tid; q < (unsigned)cnt * quads; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
       }
-      __syncthreads();
       if (warp < cnt) {
-        unsigned long long k = lane < kResWarps ? sh.res.warp_best[warp / G][warp % G][lane] : 0ull;
-        k = warp_max_u64(k);
+        unsigned k = lane < kResWarps ? sh.rv_best[warp][lane] : 0u;
+        k = __reduce_max_sync(0xFFFFFFFFu, k);
         if (lane == 0) {
           const int r = rlist[b0 + warp];
-          const unsigned v = (unsigned)(k >> 32);
-          rv[r] = v; rcell[r] = v ? 0xFFFFFFFFu - (unsigned)k : 0u; rstale[r] = 0;
+          const unsigned v = k >> 16;
+          rv[r] = v; rcell[r] = v ? 0xFFFFu - (k & 0xFFFFu) : 0u; rstale[r] = 0;
         }
       }
       __syncthreads();
