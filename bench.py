@@ -176,7 +176,9 @@ def run_cpu_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "configs[1]: single 224x172 ToF frames, g6, opt_nlines 20", "frames_per_step": workers,
+        "config": {"workload": "configs[1]: single 224x172 ToF frames (38528 px) -> PassThrough+VoxelGrid -> "
+                               "Hough g6 (20481 directions), dx=sqrt(3)*leaf, opt_nlines 20, opt_minvotes 12",
+                   "frames_per_step": workers, "parallelism": f"{workers} single-threaded processes, one per host core",
                    "lines_per_frame": lines / max(1, workers * args.steps)},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "reference" if use_ref else "port",
                          "sample": f"{workers} frames per step, one single-threaded process per core"},
