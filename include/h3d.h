@@ -170,7 +170,8 @@ int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_t n, size_t
 int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n_out);
 /* per-phase device times of the last frame, microseconds:
  * [0] pre-filter + widening/bbox, [1] the first vote kernel alone (Hough::add),
- * [2] loop + result copies, [3] whole frame incl. the host<->device copies of
+ * [2] the loop's kernels (one persistent launch on the fused path), [3] whole
+ * frame incl. the result copies and the host<->device copies of
  * h3d_pipeline_run.  All zero when the frame ended early (rc != 0). */
 int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
 

@@ -333,6 +333,25 @@ static int launch_resident_t(h3d_hough *h, const int *list, const int *count_ptr
   return H3D_OK;
 }
 
+// first vote of the fused path: BOUNDED form, `grid` CTAs (the pipeline's SM share)
+template <int P>
+static int launch_first_vote_t(h3d_hough *h, int grid) {
+  const size_t smem = ((size_t)2 * kResG * h->d.plane_stride + 4) * sizeof(unsigned);
+  static thread_local size_t configured = 0;
+  if (smem > configured) {
+    cudaFuncAttributes fa;
+    H3D_CUDA(cudaFuncGetAttributes(&fa, vote_resident_kernel<P, 0, true>));
+    const size_t dyn_max = h->dev.smem_optin - fa.sharedSizeBytes;
+    H3D_CUDA(cudaFuncSetAttribute(vote_resident_kernel<P, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)dyn_max));
+    configured = dyn_max;
+  }
+  vote_resident_kernel<P, 0, true><<<grid, kResThreads, smem, h->stream>>>(h->d, nullptr, nullptr, h->d.dir_count);
+  note_launches(1);
+  H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+
 constexpr int kResidentMaxP = 12;
 static bool resident_ok(const h3d_hough *h) {
   return !h->has_negative && h->d.n <= kResThreads * kResidentMaxP &&
@@ -754,7 +773,7 @@ struct FrameCtx {
   int prof_iters = 0, prof_ctas = 0, prof_grid = 0;   // allocated for prof_ctas CTAs; the last launch used prof_grid
   LoopState *st_host = nullptr;   // pinned
   PrepOut *prep_host = nullptr;   // pinned
-  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // start, prep done, first vote done, end, first vote start
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // start, prep done, first vote done, end, first vote start, loop kernels done
   float us[4] = {0, 0, 0, 0};
   bool timed = false;   // the last frame ran to the end (all events recorded)
   bool fused = false;   // the last frame ran in the fused persistent kernel
@@ -855,15 +874,14 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
 
 static bool g_use_fused = true;
 
-template <int P>
-int launch_fused_t(FrameCtx &f, const FusedArgs &args, size_t smem, int grid) {
+int launch_fused(FrameCtx &f, const FusedArgs &args, size_t smem, int grid) {
   static thread_local size_t configured = 0;
   if (smem > configured) {
-    H3D_CUDA(cudaFuncSetAttribute(fused_loop_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    H3D_CUDA(cudaFuncSetAttribute(fused_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
   void *params[] = {const_cast<FusedArgs *>(&args)};
-  H3D_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(fused_loop_kernel<P>), dim3(grid),
+  H3D_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(fused_loop_kernel), dim3(grid),
                                        dim3(kResThreads), params, smem, f.hg->stream));
   note_launches(1);
   return H3D_OK;
@@ -897,7 +915,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   const size_t plane_bytes = (size_t)hd.plane_stride * sizeof(unsigned);
   const size_t tables = (size_t)n_own * 16;
   cudaFuncAttributes fa;
-  H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel<4>));
+  H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
   if (h->dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   const size_t smem = ((h->dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;   // everything the SM offers
   // first vote: 2*G planes + pad; loop: nb planes + pad + the live points (24 B) + the inlier list (4 B)
@@ -930,13 +948,21 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   if (f.prof_dev)
     H3D_CUDA(cudaMemsetAsync(f.prof_dev, 0, (size_t)f.prof_iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long), s));
   const int need = (hd.n + kResThreads - 1) / kResThreads;
+  // Hough::add: every plane once, points in registers (its own kernel: 128 registers per thread
+  // for the vote alone); then the loop kernel picks the records up from global memory
   int rc;
-  if (need <= 4) rc = launch_fused_t<4>(f, a, smem, grid);
-  else if (need <= 8) rc = launch_fused_t<8>(f, a, smem, grid);
-  else if (need <= 10) rc = launch_fused_t<10>(f, a, smem, grid);
-  else rc = launch_fused_t<12>(f, a, smem, grid);
+  H3D_CUDA(cudaEventRecord(f.ev[4], s));
+  if (need <= 4) rc = launch_first_vote_t<4>(h, grid);
+  else if (need <= 8) rc = launch_first_vote_t<8>(h, grid);
+  else if (need <= 10) rc = launch_first_vote_t<10>(h, grid);
+  else rc = launch_first_vote_t<12>(h, grid);
   if (rc != H3D_OK) return rc;
+  H3D_CUDA(cudaEventRecord(f.ev[2], s));   // "first vote done" (h3d_pipeline_timing [1])
+  rc = launch_fused(f, a, smem, grid);
+  if (rc != H3D_OK) return rc;
+  H3D_CUDA(cudaEventRecord(f.ev[5], s));
   H3D_CUDA(cudaMemcpyAsync(f.sync_host, f.sync_dev, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+  H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
   *launched = true;
   return H3D_OK;
 }
@@ -999,10 +1025,8 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   int rc = H3D_OK;
   // fast path: first vote + the whole loop in one persistent cooperative kernel
   bool fused = false;
-  H3D_CUDA(cudaEventRecord(f.ev[4], s));
   H3D_TRY(try_launch_fused(f, lb, opt_nlines, opt_dx, &fused));
   if (fused) {
-    H3D_CUDA(cudaEventRecord(f.ev[2], s));
     H3D_CUDA(cudaStreamSynchronize(s));
     if (f.sync_host[1]) {   // an inlier set larger than the shared-memory scratch: redo with the general loop
       fused = false;
@@ -1029,11 +1053,14 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
       if (f.st_host->done) break;
     }
   }
+  if (rc == H3D_OK) {
+    H3D_CUDA(cudaEventRecord(f.ev[5], s));
+    H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
+    H3D_CUDA(cudaStreamSynchronize(s));
+  }
   }
   hd.n_dev = nullptr;
   if (rc != H3D_OK) return rc;
-  H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
-  H3D_CUDA(cudaStreamSynchronize(s));
   const LoopState &fin = *f.st_host;
   res->n_iters = (uint32_t)fin.n_iters; res->n_lines = (uint32_t)fin.n_lines; res->pool_used = fin.pool_used;
   res->votes_cast = (uint64_t)n * hd.dir_count + fin.votes_cast;
@@ -1274,7 +1301,7 @@ extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_
   if (rc == H3D_OK && f.timed) {
     cudaEventElapsedTime(&f.us[0], f.ev[0], f.ev[1]);   // pre-filter + prep
     cudaEventElapsedTime(&f.us[1], f.ev[4], f.ev[2]);   // the first vote kernel alone (Hough::add)
-    cudaEventElapsedTime(&f.us[2], f.ev[2], f.ev[3]);   // loop + result copies
+    cudaEventElapsedTime(&f.us[2], f.ev[2], f.ev[5]);   // the loop's kernels
     cudaEventElapsedTime(&f.us[3], f.ev[0], f.ev[3]);   // whole frame
     for (auto &u : f.us) u *= 1000.0f;
   }

@@ -327,7 +327,6 @@ __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints
   best0 = b0; best1 = b1;
 }
 
-template <int P>
 __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(16) FusedShared sh;
@@ -354,13 +353,12 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   Q.yidx = reinterpret_cast<int *>(Q.z + A.n_cap);
 
   if (A.prof && tid == 0 && A.prof_iters > 0) A.prof[(size_t)cta * kProfSlots + 15] = globaltimer_ns();   // kernel start
-  // ---- hough->add(X): every plane once (K1), points in registers ----------------------------------
+  // hough->add(X) ran just before this kernel (vote_resident_kernel, BOUNDED form): the records of
+  // every direction are in global memory.  Planes of the re-vote rounds start at zero.
   {
     uint4 *p4 = reinterpret_cast<uint4 *>(planes);
-    for (unsigned q = tid; q < 2u * G * quads + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-    vote_resident<P, 0, true>(h, nullptr, h.dir_count, planes, sh.res, cta, n_cta);
+    for (unsigned q = tid; q < (unsigned)nb * quads + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
   }
-  __syncthreads();
   // own records: entry r = k*G + g is direction (cta + k*n_cta)*G + g
   for (int r = tid; r < n_own; r += kResThreads) {
     const int l = (cta + (r / G) * n_cta) * G + (r % G);

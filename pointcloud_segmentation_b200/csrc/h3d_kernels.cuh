@@ -349,7 +349,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
   if (ABLATE == 1 && sink == 0x9E3779B9u) h.dvotes[0] = sink;
 }
 
-template <int P, int ABLATE>
+template <int P, int ABLATE, bool BOUNDED = false>
 __global__ void __launch_bounds__(kResThreads, 1)
 vote_resident_kernel(const HoughDev h, const int *__restrict__ list, const int *__restrict__ count_ptr,
                      int count_imm) {
@@ -358,7 +358,7 @@ vote_resident_kernel(const HoughDev h, const int *__restrict__ list, const int *
   const int count = count_ptr ? *count_ptr : count_imm;
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
   for (unsigned q = threadIdx.x; q < 2 * kResG * h.plane_stride / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-  vote_resident<P, ABLATE>(h, list, count, planes, sh, blockIdx.x, gridDim.x);
+  vote_resident<P, ABLATE, BOUNDED>(h, list, count, planes, sh, blockIdx.x, gridDim.x);
 }
 
 // ---------------------------------------------------------------------------
