@@ -952,10 +952,20 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   // for the vote alone); then the loop kernel picks the records up from global memory
   int rc;
   H3D_CUDA(cudaEventRecord(f.ev[4], s));
-  if (need <= 4) rc = launch_first_vote_t<4>(h, grid);
-  else if (need <= 8) rc = launch_first_vote_t<8>(h, grid);
-  else if (need <= 10) rc = launch_first_vote_t<10>(h, grid);
-  else rc = launch_first_vote_t<12>(h, grid);
+  switch (need) {   // one instantiation per slot count: no register or issue slot spent on empty slots
+    case 1: rc = launch_first_vote_t<1>(h, grid); break;
+    case 2: rc = launch_first_vote_t<2>(h, grid); break;
+    case 3: rc = launch_first_vote_t<3>(h, grid); break;
+    case 4: rc = launch_first_vote_t<4>(h, grid); break;
+    case 5: rc = launch_first_vote_t<5>(h, grid); break;
+    case 6: rc = launch_first_vote_t<6>(h, grid); break;
+    case 7: rc = launch_first_vote_t<7>(h, grid); break;
+    case 8: rc = launch_first_vote_t<8>(h, grid); break;
+    case 9: rc = launch_first_vote_t<9>(h, grid); break;
+    case 10: rc = launch_first_vote_t<10>(h, grid); break;
+    case 11: rc = launch_first_vote_t<11>(h, grid); break;
+    default: rc = launch_first_vote_t<12>(h, grid); break;
+  }
   if (rc != H3D_OK) return rc;
   H3D_CUDA(cudaEventRecord(f.ev[2], s));   // "first vote done" (h3d_pipeline_timing [1])
   rc = launch_fused(f, a, smem, grid);

@@ -240,7 +240,11 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
     px[p] = ok ? h.px[i] : 0.0; py[p] = ok ? h.py[i] : 0.0; pz[p] = ok ? h.pz[i] : 0.0;
     live |= ok ? (1u << p) : 0u;
   }
-  const int full_slots = n / kResThreads, used_slots = (n + kResThreads - 1) / kResThreads;
+  // per WARP: slots below full_w hold 32 live lanes, slots in [full_w, used_w) are partly filled,
+  // slots from used_w on are empty for the whole warp and are skipped (warp-uniform branches)
+  const int w0 = warp * 32;
+  const int used_w = n > w0 ? (n - w0 + kResThreads - 1) / kResThreads : 0;
+  const int full_w = n >= w0 + 32 ? (n - w0 - 32) / kResThreads + 1 : 0;
   const unsigned dummy_sa = planes_sa + 2u * G * stride * 4u;   // pad word: votes that must not count
   // thread g < G stages direction g of a group: list entry -> dir[], DirCoef -> coef[] (cp.async)
   auto stage = [&](int group, int slot, int dslot) {
@@ -278,34 +282,33 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
         constexpr int CH = 4;   // votes per batch: 8 independent DFMA chains, 4 cell registers
 #pragma unroll
         for (int p0 = 0; p0 < P; p0 += CH) {
-          if (p0 >= used_slots) break;                    // uniform
-          const bool edge = p0 + CH > full_slots;         // uniform: batch holds the partial slot
-          // off[c]: byte offset of the vote inside the plane (>= 4*plane_cells when the reference drops it)
-          unsigned off[CH];
-          unsigned gmin = 0xFFFFFFFFu, hacc = 0;
+          if (p0 >= used_w) break;                        // warp-uniform
           const unsigned drop_off = dummy_sa - mine_sa;
+          if ((p0 + CH < P ? p0 + CH : P) <= full_w) {    // warp-uniform: every lane of every slot is live
+            // off[c]: byte offset of the vote inside the plane (>= 4*plane_cells when the reference drops it)
+            unsigned off[CH];
+            unsigned gmin = 0xFFFFFFFFu, hacc = 0;
 #pragma unroll
-          for (int c = 0; c < CH; ++c) {
-            const int p = p0 + c;
-            if (p >= P) { off[c] = drop_off; continue; }
-            if (ABLATE == 2) off[c] = 4u * (((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells);
-            else if (BOUNDED) off[c] = vote_off_bounded(f, kmagic, row4, px[p], py[p], pz[p], gmin);
-            else off[c] = 4u * vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], gmin, hacc);
-          }
-          if (ABLATE != 2 && (batch_unsure(gmin, hacc) | !h.fast_ok)) {   // rare: within 8e-6 cell of a boundary
-#pragma unroll
-            for (int c = 0; c < CH; ++c) {   // unrolled: register arrays must not be indexed dynamically
+            for (int c = 0; c < CH; ++c) {
               const int p = p0 + c;
-              if (p < P) {
-                const unsigned cell = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
-                                                        h.fast_ok, px[p], py[p], pz[p]);
-                off[c] = cell < plane_cells ? 4u * cell : drop_off;
+              if (p >= P) { off[c] = drop_off; continue; }
+              if (ABLATE == 2) off[c] = 4u * (((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells);
+              else if (BOUNDED) off[c] = vote_off_bounded(f, kmagic, row4, px[p], py[p], pz[p], gmin);
+              else off[c] = 4u * vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], gmin, hacc);
+            }
+            if (ABLATE != 2 && (batch_unsure(gmin, hacc) | !h.fast_ok)) {   // rare: within 8e-6 cell of a boundary
+#pragma unroll
+              for (int c = 0; c < CH; ++c) {   // unrolled: register arrays must not be indexed dynamically
+                const int p = p0 + c;
+                if (p < P) {
+                  const unsigned cell = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
+                                                          h.fast_ok, px[p], py[p], pz[p]);
+                  off[c] = cell < plane_cells ? 4u * cell : drop_off;
+                }
               }
             }
-          }
-          // unconditional increments (ATOMS.POPC.INC merges lanes that hit the same cell and needs no
-          // branch this way); a vote the reference drops, or an empty slot, goes to the pad word
-          if (!edge) {
+            // unconditional increments (ATOMS.POPC.INC merges lanes that hit the same cell and needs no
+            // branch this way); a vote the reference drops goes to the pad word
 #pragma unroll
             for (int c = 0; c < CH; ++c) {
               if (p0 + c >= P) continue;
@@ -313,14 +316,25 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
               else if (BOUNDED) red_shared_inc(mine_sa + off[c]);
               else red_shared_inc(off[c] < 4u * plane_cells ? mine_sa + off[c] : dummy_sa);
             }
-          } else {
+          } else {                                        // the batch that holds this warp's last slots
 #pragma unroll
             for (int c = 0; c < CH; ++c) {
               const int p = p0 + c;
               if (p >= P) continue;
-              if (ABLATE == 1) sink ^= off[c];
-              else if (BOUNDED) red_shared_inc(((live >> p) & 1u) ? mine_sa + off[c] : dummy_sa);
-              else red_shared_inc(((off[c] < 4u * plane_cells) & ((live >> p) & 1u)) ? mine_sa + off[c] : dummy_sa);
+              if (p >= used_w) continue;                  // warp-uniform: nothing of this warp in the slot
+              unsigned g1 = 0xFFFFFFFFu, h1 = 0, o;
+              if (ABLATE == 2) o = 4u * (((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells);
+              else if (BOUNDED) o = vote_off_bounded(f, kmagic, row4, px[p], py[p], pz[p], g1);
+              else o = 4u * vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], g1, h1);
+              if (ABLATE != 2 && (batch_unsure(g1, h1) | !h.fast_ok)) {
+                const unsigned cell = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
+                                                        h.fast_ok, px[p], py[p], pz[p]);
+                o = cell < plane_cells ? 4u * cell : drop_off;
+              }
+              // an empty lane of a partly filled slot votes into the pad word
+              if (ABLATE == 1) sink ^= o;
+              else if (BOUNDED) red_shared_inc(((live >> p) & 1u) ? mine_sa + o : dummy_sa);
+              else red_shared_inc(((o < 4u * plane_cells) & ((live >> p) & 1u)) ? mine_sa + o : dummy_sa);
             }
           }
         }
