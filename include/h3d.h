@@ -175,6 +175,52 @@ int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n
  * h3d_pipeline_run.  All zero when the frame ended early (rc != 0). */
 int h3d_pipeline_timing(h3d_pipeline *p, float us[4]);
 
+/* ---- segment post-tests: wrap.h:261-337 with find_t (wrap.h:41-68), find_proj
+ *      (wrap.h:78-85), segPCA (wrap.h:94-110) -- SURVEY 8(f) rank 1 ------------
+ * The reference runs them on the host on a copy of Y.points, line by line; here
+ * one launch tests every accepted line of the frame from the inlier index lists
+ * that are still on the device, and only these records come back. */
+#define H3D_MAX_RADIUS_SIZES 8
+typedef struct {
+  double diag_voxel;       /* node.cpp:242: sqrt(3) * leaf_size                  */
+  double min_pca_coeff;    /* node.cpp:200                                       */
+  double rad_2_leaf_ratio; /* node.cpp:210                                       */
+  uint32_t n_radius;       /* entries of radius_sizes in use (1..8), node.cpp:230-239 */
+  uint32_t pad_;
+  double radius_sizes[H3D_MAX_RADIUS_SIZES];
+} h3d_segment_config;
+typedef struct {
+  uint32_t iter;           /* iteration record (h3d_iter) the line came from     */
+  uint32_t status;         /* 0 = pushed to computed_lines (wrap.h:324-335);
+                              1 = failed the radius / gap test (wrap.h:312);
+                              2 = failed the PCA / density test (wrap.h:322);
+                              3 = find_t had no solution, b.x == 0: the reference
+                                  returns 1 from hough3dlines here (wrap.h:276-279) */
+  uint32_t n_points;       /* points_size                                        */
+  int32_t min_nb_points;   /* min_nb_points_seg (wrap.h:320); 0 unless the first test passed */
+  double a[3], b[3];
+  double t_min, t_max;     /* t_values.front() / back()                          */
+  double radius_raw;       /* max(p_radius.front(), p_radius.back()), wrap.h:295 */
+  double radius;           /* closest_radius                                     */
+  double max_dist;         /* largest neighbour gap of p_norm, wrap.h:286-292    */
+  double pca_coeff;        /* 0 unless the first test passed                     */
+  double pca_eigenvalues[3];
+  double length;           /* |p(t_max) - p(t_min)|, wrap.h:317-319              */
+} h3d_segment;
+/* cfg != NULL: every following frame of the pipeline also runs the post-tests
+ * (one extra launch, no extra synchronisation); NULL switches them off. */
+int h3d_pipeline_enable_segments(h3d_pipeline *p, const h3d_segment_config *cfg);
+/* records of the last frame in iteration order, one per line the reference would
+ * have tested.  *rc_ref = what hough3dlines returns: 1 when the LAST record has
+ * status 3 (the reference stops there; later lines are not reported), else the
+ * frame's rc.  *n_segs may exceed cap (then only cap were written). */
+int h3d_pipeline_segments(h3d_pipeline *p, h3d_segment *segs, size_t cap, size_t *n_segs, int *rc_ref);
+/* the same tests on one line from host buffers: y_xyz = the line's final inliers
+ * Y.points (centred frame, n points), shift = X.shift, a = anchor (+ shift), b =
+ * direction.  Returns H3D_OK also when out->status != 0. */
+int h3d_segment_test(const double *y_xyz, size_t n, const double shift[3], const double a[3],
+                     const double b[3], const h3d_segment_config *cfg, h3d_segment *out);
+
 /* frame-parallel replay on ONE GPU (BASELINE configs[2]): frames are independent (one Hough per
  * frame, wrap.h:220/347), and the loop of a frame is latency-bound, so K pipelines driven by K
  * host threads can each take sm_count/K SMs for their persistent loop kernel.  n_ctas = 0: all

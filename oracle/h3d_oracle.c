@@ -415,7 +415,7 @@ static float hypot_f(float x, float y) {                      /* Eigen numext::h
     return p * sqrtf(1.0f + qp * qp);
 }
 
-int h3do_eig3f(const float m_in[9], float evals[3], float evecs[9]) {
+static int eig3f_impl(const float m_in[9], float evals[3], float evecs[9], int fixed3) {
     /* lower triangle of the (column-major, symmetric) input */
     float a00 = m_in[0], a10 = m_in[1], a20 = m_in[2], a11 = m_in[4], a21 = m_in[5], a22 = m_in[8];
     /* scale to [-1,1] */
@@ -431,6 +431,23 @@ int h3do_eig3f(const float m_in[9], float evals[3], float evecs[9]) {
     /* Householder step on column 0 (the second step of a 3x3 is the identity) */
     float diag[3], sub[2];
     float q[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};          /* column-major Q */
+    if (fixed3) {
+        /* Eigen tridiagonalization_inplace_selector<MatrixType,3,false> (fixed-size Matrix3f, as
+         * pcl::PCA uses): closed form, eigenvalues only here (Q stays the identity) */
+        float v1norm2 = a20 * a20;
+        diag[0] = a00;
+        if (v1norm2 <= FLT_MIN) { diag[1] = a11; diag[2] = a22; sub[0] = a10; sub[1] = a21; }
+        else {
+            float beta = sqrtf(a10 * a10 + v1norm2);
+            float inv_beta = 1.0f / beta;
+            float m01 = a10 * inv_beta, m02 = a20 * inv_beta;
+            float qq = 2.0f * m01 * a21 + m02 * (a22 - a11);
+            diag[1] = a11 + m02 * qq;
+            diag[2] = a22 - m02 * qq;
+            sub[0] = beta;
+            sub[1] = a21 - m01 * qq;
+        }
+    } else {
     float tail_sq = a20 * a20;
     if (tail_sq <= FLT_MIN) {
         diag[0] = a00; diag[1] = a11; diag[2] = a22; sub[0] = a10; sub[1] = a21;
@@ -455,6 +472,7 @@ int h3do_eig3f(const float m_in[9], float evals[3], float evecs[9]) {
         float tv = tau * v1;
         q[4] = 1.0f - tau;  q[7] = 0.0f - tau * v1;     /* row 1: (.., 1-tau, -tau*v1) */
         q[5] = 0.0f - tv;   q[8] = 1.0f - tv * v1;      /* row 2 */
+    }
     }
 
     /* implicit symmetric QR on the tridiagonal (Eigen computeFromTridiagonal_impl) */
@@ -519,6 +537,13 @@ int h3do_eig3f(const float m_in[9], float evals[3], float evecs[9]) {
     return ok ? 0 : 1;
 }
 
+int h3do_eig3f(const float m_in[9], float evals[3], float evecs[9]) { return eig3f_impl(m_in, evals, evecs, 0); }
+/* SelfAdjointEigenSolver<Matrix3f>: eigenvalues ascending (eigenvectors not produced) */
+int h3do_eig3f_fixed(const float m_in[9], float evals[3]) {
+    float evecs[9];
+    return eig3f_impl(m_in, evals, evecs, 1);
+}
+
 /* halving tree over the 32 interleaved partial sums (destroys v) */
 static float tree32_fold(float v[32]) {
     for (int o = 16; o; o >>= 1) for (int l = 0; l < o; l++) v[l] = v[l] + v[l + o];
@@ -548,6 +573,122 @@ double h3do_orthogonal_lsq(const double *p, size_t n, double a[3], double b[3]) 
     h3do_eig3f(m, ev, evec);                          /* wrap.h:141-142 */
     b[0] = evec[6]; b[1] = evec[7]; b[2] = evec[8];   /* last column, wrap.h:146 */
     return (double)ev[2];                             /* wrap.h:147 */
+}
+
+/* ======================================================================== */
+/* Segment post-tests on one accepted line -- wrap.h:261-337 with find_t     */
+/* (wrap.h:41-68), find_proj (wrap.h:78-85), segPCA (wrap.h:94-110).          */
+/* Third party: Eigen3 fixed-size Vector3d arithmetic (3-term sums reduce as  */
+/* x0 + (x1 + x2), Eigen's unrolled redux) and pcl::PCA<PointXYZ> (PCL 1.10,  */
+/* un-vendored): float centroid (sequential sum / n), demeaned float cloud,   */
+/* covariance = (1/(n-1)) * sum of products -- restated with the canonical    */
+/* TREE32 order for the sums (PCL leaves the order to Eigen's GEMM) -- and    */
+/* SelfAdjointEigenSolver<Matrix3f>.  PARITY UNPINNED for the PCA part.       */
+/* y: the line's final inliers in the CENTRED frame (Y.points), in Y order;   */
+/* shift = X.shift; a = anchor (already + shift), b = direction.              */
+/* returns 1 when find_t has no solution (b.x == 0): the reference then       */
+/* returns 1 from hough3dlines (wrap.h:276-279); out->status = 3.             */
+/* ======================================================================== */
+
+static double dot3_eigen(const double u[3], const double v[3]) {   /* Eigen redux, 3 terms */
+    return u[0] * v[0] + (u[1] * v[1] + u[2] * v[2]);
+}
+
+int h3do_segment_test(const double *y, size_t n, const double shift[3], const double a[3],
+                      const double b[3], const h3do_segment_config *cfg, h3do_segment *out) {
+    memset(out, 0, sizeof *out);
+    for (int c = 0; c < 3; c++) { out->a[c] = a[c]; out->b[c] = b[c]; }
+    out->n_points = (uint32_t)n;
+    if (n == 0 || cfg->n_radius == 0) { out->status = 1; return 0; }   /* not reachable from the loop */
+    double *t_sorted = (double *)malloc(sizeof(double) * n);
+    double *norm_sorted = (double *)malloc(sizeof(double) * n);
+    float *pf = (float *)malloc(sizeof(float) * 3 * n);
+    size_t m = 0;
+    double r_front = 0.0, r_back = 0.0;
+    double d[3], dd;
+    for (int c = 0; c < 3; c++) d[c] = (a[c] + b[c]) - a[c];           /* p_B - p_A, wrap.h:81-82 */
+    dd = dot3_eigen(d, d);
+    for (size_t i = 0; i < n; i++) {
+        double p[3], pa[3], proj[3], e[3], q[3];
+        for (int c = 0; c < 3; c++) { p[c] = y[3 * i + c] + shift[c]; pa[c] = p[c] - a[c]; }   /* wrap.h:271 */
+        const double num = dot3_eigen(pa, d);
+        for (int c = 0; c < 3; c++) { proj[c] = a[c] + (d[c] * num) / dd; e[c] = proj[c] - p[c]; }
+        const double radius = sqrt(dot3_eigen(e, e));                  /* wrap.h:275 */
+        if (i == 0) r_front = radius;
+        r_back = radius;
+        if (b[0] == 0.0) {                                             /* wrap.h:43-45, 276-279 */
+            out->status = 3;
+            free(t_sorted); free(norm_sorted); free(pf);
+            return 1;
+        }
+        const double t = (proj[0] - a[0]) / b[0];                      /* wrap.h:48 */
+        for (int c = 0; c < 3; c++) q[c] = a[c] + t * b[c];
+        const double nrm = sqrt(dot3_eigen(q, q));
+        /* std::upper_bound: first element greater than t (wrap.h:56) */
+        size_t lo = 0, hi = m;
+        while (lo < hi) { size_t mid = lo + (hi - lo) / 2; if (t < t_sorted[mid]) hi = mid; else lo = mid + 1; }
+        memmove(t_sorted + lo + 1, t_sorted + lo, sizeof(double) * (m - lo));
+        memmove(norm_sorted + lo + 1, norm_sorted + lo, sizeof(double) * (m - lo));
+        t_sorted[lo] = t; norm_sorted[lo] = nrm; m++;
+        for (int c = 0; c < 3; c++) pf[3 * i + c] = (float)p[c];       /* wrap.h:99: pcl::PointXYZ(x, y, z) */
+    }
+    double max_dist = 0.0;                                             /* wrap.h:286-292 */
+    for (size_t i = 0; i + 1 < n; i++) {
+        const double dist = fabs(norm_sorted[i + 1] - norm_sorted[i]);
+        if (dist > max_dist) max_dist = dist;
+    }
+    const double radius = r_front > r_back ? r_front : r_back;         /* std::max(front, back), wrap.h:295 */
+    double closest = cfg->radius_sizes[0];
+    double min_diff = fabs(radius - cfg->radius_sizes[0]);
+    double max_radius = fabs(radius - cfg->radius_sizes[0]);           /* sic, wrap.h:298 */
+    for (uint32_t k = 0; k < cfg->n_radius; k++) {
+        const double r = cfg->radius_sizes[k];
+        const double cur = fabs(radius - r);
+        if (cur < min_diff) { min_diff = cur; closest = r; }
+        if (r > max_radius) max_radius = r;
+    }
+    out->t_min = t_sorted[0]; out->t_max = t_sorted[n - 1];
+    out->radius_raw = radius; out->radius = closest; out->max_dist = max_dist;
+    out->status = 1;
+    if (min_diff < cfg->diag_voxel && max_radius <= closest && max_dist < 2 * cfg->diag_voxel) {   /* wrap.h:312 */
+        /* segPCA: pcl::PCA float */
+        float cen[3] = {0.0f, 0.0f, 0.0f};
+        for (size_t i = 0; i < n; i++) for (int c = 0; c < 3; c++) cen[c] = cen[c] + pf[3 * i + c];
+        for (int c = 0; c < 3; c++) cen[c] = cen[c] / (float)n;
+        float part[6][32];
+        memset(part, 0, sizeof part);
+        for (size_t i = 0; i < n; i++) {
+            const float cx = pf[3 * i] - cen[0], cy = pf[3 * i + 1] - cen[1], cz = pf[3 * i + 2] - cen[2];
+            float *q0 = &part[0][i & 31];
+            q0[0] = q0[0] + cx * cx; q0[32] = q0[32] + cx * cy; q0[64] = q0[64] + cx * cz;
+            q0[96] = q0[96] + cy * cy; q0[128] = q0[128] + cy * cz; q0[160] = q0[160] + cz * cz;
+        }
+        const float inv = 1.0f / ((float)n - 1.0f);
+        float sc[6];
+        for (int c = 0; c < 6; c++) sc[c] = inv * tree32_fold(part[c]);
+        float mat[9] = {sc[0], sc[1], sc[2], sc[1], sc[3], sc[4], sc[2], sc[4], sc[5]};
+        float ev[3] = {NAN, NAN, NAN};
+        int finite = 1;
+        for (int c = 0; c < 6; c++) if (!isfinite(sc[c])) finite = 0;
+        if (finite) h3do_eig3f_fixed(mat, ev);
+        const double e0 = (double)ev[2], e1 = (double)ev[1], e2 = (double)ev[0];   /* descending, wrap.h:107 */
+        out->pca_eigenvalues[0] = e0; out->pca_eigenvalues[1] = e1; out->pca_eigenvalues[2] = e2;
+        out->pca_coeff = e0 / (e0 + e1 + e2);                          /* wrap.h:315 */
+        double p1[3], p2[3], dl[3];
+        for (int c = 0; c < 3; c++) {                                  /* wrap.h:317-319 */
+            p1[c] = t_sorted[0] * b[c] + a[c]; p2[c] = t_sorted[n - 1] * b[c] + a[c]; dl[c] = p2[c] - p1[c];
+        }
+        out->length = sqrt(dot3_eigen(dl, dl));
+        const double want = 2.0 * closest * out->length /
+                            (cfg->rad_2_leaf_ratio * 2 * cfg->diag_voxel * 2 * cfg->diag_voxel);   /* wrap.h:320 */
+        /* static_cast<int>: the x86 conversion (cvttsd2si) gives INT_MIN when out of range or NaN */
+        int min_nb = (want >= 2147483648.0 || want <= -2147483649.0 || want != want) ? INT_MIN : (int)want;
+        out->min_nb_points = min_nb;
+        /* points.size() > min_nb_points_seg compares size_t with int: the int converts to unsigned */
+        out->status = (out->pca_coeff > cfg->min_pca_coeff && (uint64_t)n > (uint64_t)(int64_t)min_nb) ? 0 : 2;
+    }
+    free(t_sorted); free(norm_sorted); free(pf);
+    return 0;
 }
 
 /* ======================================================================== */

@@ -80,6 +80,35 @@ double h3do_orthogonal_lsq(const double *xyz, size_t n, double a[3], double b[3]
 /* the 3x3 float symmetric eigen-solve alone (lower triangle used);
  * evals ascending, evecs column-major 3x3; returns 0 on convergence */
 int    h3do_eig3f(const float m[9], float evals[3], float evecs[9]);
+int    h3do_eig3f_fixed(const float m[9], float evals[3]);   /* SelfAdjointEigenSolver<Matrix3f>, values only */
+
+/* segment post-tests of one accepted line: wrap.h:261-337 (+ find_t :41-68, find_proj :78-85,
+ * segPCA :94-110).  Layout identical to h3d_segment_config / h3d_segment of include/h3d.h. */
+typedef struct {
+  double diag_voxel;          /* node.cpp:242: sqrt(3) * leaf                        */
+  double min_pca_coeff;
+  double rad_2_leaf_ratio;
+  uint32_t n_radius;          /* 1..8 entries used                                   */
+  uint32_t pad_;
+  double radius_sizes[8];
+} h3do_segment_config;
+typedef struct {
+  uint32_t iter;              /* iteration record the line came from                 */
+  uint32_t status;            /* 0 pushed to computed_lines; 1 failed wrap.h:312; 2 failed wrap.h:322;
+                                 3 find_t had no solution (reference returns 1)      */
+  uint32_t n_points;
+  int32_t min_nb_points;
+  double a[3], b[3];
+  double t_min, t_max;
+  double radius_raw;          /* max(p_radius.front(), p_radius.back())              */
+  double radius;              /* closest_radius                                      */
+  double max_dist;
+  double pca_coeff;
+  double pca_eigenvalues[3];
+  double length;
+} h3do_segment;
+int h3do_segment_test(const double *y_xyz, size_t n, const double shift[3], const double a[3],
+                      const double b[3], const h3do_segment_config *cfg, h3do_segment *out);
 
 /* ---- pre-filter (node.cpp:386-421; PCL PassThrough + VoxelGrid) --------- */
 /* xyz_in: n points with `stride` floats per point (x,y,z first).

@@ -43,6 +43,34 @@ class Result(C.Structure):
     ]
 
 
+class SegmentConfig(C.Structure):
+    """wrap.h:167-170 arguments of the post-tests (layout of h3d_segment_config)."""
+    _fields_ = [("diag_voxel", C.c_double), ("min_pca_coeff", C.c_double), ("rad_2_leaf_ratio", C.c_double),
+                ("n_radius", C.c_uint32), ("pad_", C.c_uint32), ("radius_sizes", C.c_double * 8)]
+
+    @classmethod
+    def make(cls, diag_voxel, min_pca_coeff, rad_2_leaf_ratio, radius_sizes):
+        c = cls()
+        c.diag_voxel, c.min_pca_coeff, c.rad_2_leaf_ratio = diag_voxel, min_pca_coeff, rad_2_leaf_ratio
+        c.n_radius = len(radius_sizes)
+        for k, r in enumerate(radius_sizes):
+            c.radius_sizes[k] = r
+        return c
+
+
+class Segment(C.Structure):
+    """One tested line (layout of h3d_segment): status 0 = pushed to computed_lines (wrap.h:324-335)."""
+    _fields_ = [("iter", C.c_uint32), ("status", C.c_uint32), ("n_points", C.c_uint32), ("min_nb_points", C.c_int32),
+                ("a", C.c_double * 3), ("b", C.c_double * 3), ("t_min", C.c_double), ("t_max", C.c_double),
+                ("radius_raw", C.c_double), ("radius", C.c_double), ("max_dist", C.c_double),
+                ("pca_coeff", C.c_double), ("pca_eigenvalues", C.c_double * 3), ("length", C.c_double)]
+
+    def as_tuple(self):
+        return (self.iter, self.status, self.n_points, self.min_nb_points, tuple(self.a), tuple(self.b), self.t_min,
+                self.t_max, self.radius_raw, self.radius, self.max_dist, self.pca_coeff, tuple(self.pca_eigenvalues),
+                self.length)
+
+
 @dataclass
 class Iteration:
     votes: int
@@ -200,6 +228,39 @@ class Oracle(_Base):
         a = np.zeros(3); b = np.zeros(3)
         rc = self.lib.h3do_orthogonal_lsq(_dp(p), C.c_size_t(n), _dp(a), _dp(b))
         return rc, a, b
+
+    def segment_test(self, y_centred, shift, a, b, cfg):
+        """wrap.h:261-337 on one line.  Returns (rc, Segment); rc 1 = find_t had no solution."""
+        p, n = _pts(y_centred)
+        seg = Segment()
+        sh = np.ascontiguousarray(shift, dtype=np.float64)
+        aa = np.ascontiguousarray(a, dtype=np.float64); bb = np.ascontiguousarray(b, dtype=np.float64)
+        rc = self.lib.h3do_segment_test(_dp(p), C.c_size_t(n), _dp(sh), _dp(aa), _dp(bb), C.byref(cfg), C.byref(seg))
+        return rc, seg
+
+    def segments(self, xyz, trace, cfg):
+        """Post-tests of every accepted line of a trace of hough3dlines(xyz, ...): (rc, [Segment]).
+        rc 1 = the reference would return 1 at the last segment of the list (status 3)."""
+        p, _ = _pts(xyz)
+        p = p.reshape(-1, 3)
+        centred = p - trace.shift            # PointCloud::shiftToOrigin, lib/pointcloud.cpp:18-26
+        out = []
+        for k, it in enumerate(trace.iters):
+            if it.status != 0:
+                continue
+            rc, seg = self.segment_test(centred[it.inliers2], trace.shift, it.a2, it.b2, cfg)
+            seg.iter = k
+            out.append(seg)
+            if rc:
+                return 1, out
+        return 0, out
+
+    def eig3f_fixed(self, m):
+        m = np.ascontiguousarray(m, dtype=np.float32).reshape(9)
+        ev = np.zeros(3, np.float32)
+        fp = C.POINTER(C.c_float)
+        rc = self.lib.h3do_eig3f_fixed(m.ctypes.data_as(fp), ev.ctypes.data_as(fp))
+        return rc, ev
 
     def eig3f(self, m):
         m = np.ascontiguousarray(m, dtype=np.float32).reshape(9)

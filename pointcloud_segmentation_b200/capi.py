@@ -50,6 +50,34 @@ class PipelineConfig(C.Structure):
     ]
 
 
+class SegmentConfig(C.Structure):
+    """h3d_segment_config: arguments of the post-tests (wrap.h:167-170)."""
+    _fields_ = [("diag_voxel", C.c_double), ("min_pca_coeff", C.c_double), ("rad_2_leaf_ratio", C.c_double),
+                ("n_radius", C.c_uint32), ("pad_", C.c_uint32), ("radius_sizes", C.c_double * 8)]
+
+    @classmethod
+    def make(cls, diag_voxel, min_pca_coeff, rad_2_leaf_ratio, radius_sizes):
+        c = cls()
+        c.diag_voxel, c.min_pca_coeff, c.rad_2_leaf_ratio = diag_voxel, min_pca_coeff, rad_2_leaf_ratio
+        c.n_radius = len(radius_sizes)
+        for k, r in enumerate(radius_sizes[:8]):
+            c.radius_sizes[k] = r
+        return c
+
+
+class Segment(C.Structure):
+    """h3d_segment: one tested line; status 0 = pushed to computed_lines (wrap.h:324-335)."""
+    _fields_ = [("iter", C.c_uint32), ("status", C.c_uint32), ("n_points", C.c_uint32), ("min_nb_points", C.c_int32),
+                ("a", C.c_double * 3), ("b", C.c_double * 3), ("t_min", C.c_double), ("t_max", C.c_double),
+                ("radius_raw", C.c_double), ("radius", C.c_double), ("max_dist", C.c_double),
+                ("pca_coeff", C.c_double), ("pca_eigenvalues", C.c_double * 3), ("length", C.c_double)]
+
+    def as_tuple(self):
+        return (self.iter, self.status, self.n_points, self.min_nb_points, tuple(self.a), tuple(self.b), self.t_min,
+                self.t_max, self.radius_raw, self.radius, self.max_dist, self.pca_coeff, tuple(self.pca_eigenvalues),
+                self.length)
+
+
 def lib():
     """Load libh3d.so (built in-tree by `make -C pointcloud_segmentation_b200`)."""
     global _lib
@@ -266,6 +294,19 @@ class Pipeline:
         check(lib().h3d_pipeline_timing(self._p, us))
         return list(us)
 
+    def enable_segments(self, cfg):
+        """Run the segment post-tests (wrap.h:261-337) with every following frame; None switches them off."""
+        check(lib().h3d_pipeline_enable_segments(self._p, C.byref(cfg) if cfg is not None else None))
+
+    def segments(self):
+        """(rc of the reference's hough3dlines, [Segment]) of the last frame."""
+        n = C.c_size_t(0)
+        rc_ref = C.c_int(0)
+        cap = int(self.max_iters)
+        segs = (Segment * cap)()
+        check(lib().h3d_pipeline_segments(self._p, segs, C.c_size_t(cap), C.byref(n), C.byref(rc_ref)))
+        return rc_ref.value, [segs[k] for k in range(min(n.value, cap))]
+
     def set_sm_share(self, n_ctas):
         """SMs the persistent loop kernel of this pipeline may use (0 = all)."""
         check(lib().h3d_pipeline_set_sm_share(self._p, C.c_int(n_ctas)))
@@ -377,6 +418,14 @@ def orthogonal_lsq(xyz):
     aa, bb, rc = (C.c_double * 3)(), (C.c_double * 3)(), C.c_double()
     check(lib().h3d_orthogonal_lsq(p, n, aa, bb, C.byref(rc)))
     return rc.value, np.array(aa[:]), np.array(bb[:])
+
+
+def segment_test(y_centred, shift, a_, b_, cfg):
+    """wrap.h:261-337 on one line from host buffers -> Segment."""
+    _, p, n = _pts(y_centred)
+    seg = Segment()
+    check(lib().h3d_segment_test(p, n, _d3(shift), _d3(a_), _d3(b_), C.byref(cfg), C.byref(seg)))
+    return seg
 
 
 def set_fused(on):

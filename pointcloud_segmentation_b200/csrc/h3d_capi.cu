@@ -15,6 +15,7 @@
 
 #include "h3d_fused.cuh"
 #include "h3d_prefilter.cuh"
+#include "h3d_segment.cuh"
 
 namespace h3d {
 
@@ -778,6 +779,15 @@ struct FrameCtx {
   bool timed = false;   // the last frame ran to the end (all events recorded)
   bool fused = false;   // the last frame ran in the fused persistent kernel
   int fused_ctas = 0;   // CTAs (= SMs) the fused kernel may use; 0 = all (h3d_pipeline_set_sm_share)
+  // segment post-tests (h3d_pipeline_enable_segments)
+  bool seg_on = false;
+  h3d_segment_config seg_cfg{};
+  h3d_segment *seg_dev = nullptr, *seg_host = nullptr;   // iters_cap records each; host copy pinned
+  size_t seg_cap = 0, seg_n = 0;
+  double *seg_scr = nullptr;             // 3 * seg_scr_n doubles
+  size_t seg_scr_n = 0;
+  const void *src = nullptr;             // the cloud the pool indexes (set by the caller of frame_run)
+  int src_stride = 3, src_is_float = 0;
 
   ~FrameCtx() { release(); }
   void release() {
@@ -786,6 +796,8 @@ struct FrameCtx {
     cudaFree(ypx); cudaFree(ypy); cudaFree(ypz);
     cudaFree(iters_dev); cudaFree(pool_dev); cudaFree(st_dev); cudaFree(prep_dev);
     cudaFree(gbest); cudaFree(sync_dev); cudaFreeHost(sync_host); cudaFree(prof_dev);
+    cudaFree(seg_dev); cudaFreeHost(seg_host); cudaFree(seg_scr);
+    seg_dev = seg_host = nullptr; seg_scr = nullptr; seg_cap = seg_n = seg_scr_n = 0;
     prof_dev = nullptr; prof_iters = prof_ctas = 0;
     gbest = nullptr; sync_dev = nullptr; sync_host = nullptr; gbest_cap = 0;
     cudaFreeHost(st_host); cudaFreeHost(prep_host);
@@ -977,6 +989,23 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   return H3D_OK;
 }
 
+int segments_ensure(FrameCtx &f, size_t n_rec, size_t n_points) {
+  if (n_rec > f.seg_cap) {
+    cudaFree(f.seg_dev); cudaFreeHost(f.seg_host); f.seg_dev = f.seg_host = nullptr; f.seg_cap = 0;
+    const size_t cap = n_rec > f.iters_cap ? n_rec : f.iters_cap;
+    H3D_CUDA(cudaMalloc(&f.seg_dev, cap * sizeof(h3d_segment)));
+    H3D_CUDA(cudaMallocHost(&f.seg_host, cap * sizeof(h3d_segment)));
+    f.seg_cap = cap;
+  }
+  if (n_points > f.seg_scr_n) {
+    cudaFree(f.seg_scr); f.seg_scr = nullptr; f.seg_scr_n = 0;
+    const size_t cap = n_points > f.cap ? n_points : f.cap;
+    H3D_CUDA(cudaMalloc(&f.seg_scr, 3 * cap * sizeof(double)));
+    f.seg_scr_n = cap;
+  }
+  return H3D_OK;
+}
+
 // everything after the points are on the device (unshifted SoA + orig + PrepOut): bbox checks,
 // Hough ctor, first vote, loop, results.  timing events: ev[1] after prep, ev[2] after the first
 // vote, ev[3] at the end.
@@ -1023,7 +1052,8 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   for (int c = 0; c < 3; ++c) st.shift[c] = res->shift[c];
   st.minvotes = opt_minvotes; st.nlines_max = opt_nlines;
   st.max_iters = (int)(max_iters < f.iters_cap ? max_iters : f.iters_cap);
-  st.pool_cap = (unsigned)(pool_cap < f.pool_cap ? pool_cap : f.pool_cap);
+  // the post-tests read the inlier lists on the device: keep them all even if the host takes fewer
+  st.pool_cap = (unsigned)((pool_cap < f.pool_cap && !f.seg_on) ? pool_cap : f.pool_cap);
   st.n_alive = (int)n;
   *f.st_host = st;
   H3D_CUDA(cudaMemcpyAsync(f.st_dev, f.st_host, sizeof(LoopState), cudaMemcpyHostToDevice, s));
@@ -1076,7 +1106,22 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   res->votes_cast = (uint64_t)n * hd.dir_count + fin.votes_cast;
   const size_t n_rec = (size_t)fin.n_iters < (size_t)st.max_iters ? (size_t)fin.n_iters : (size_t)st.max_iters;
   if (n_rec && iters) H3D_CUDA(cudaMemcpyAsync(iters, f.iters_dev, n_rec * sizeof(h3d_iter), cudaMemcpyDeviceToHost, s));
-  if (fin.pool_used && pool) H3D_CUDA(cudaMemcpyAsync(pool, f.pool_dev, (size_t)fin.pool_used * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+  const size_t n_pool = (size_t)fin.pool_used < pool_cap ? (size_t)fin.pool_used : pool_cap;
+  if (n_pool && pool) H3D_CUDA(cudaMemcpyAsync(pool, f.pool_dev, n_pool * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+  f.seg_n = 0;
+  if (f.seg_on && n_rec) {                                // wrap.h:261-337 on every accepted line
+    H3D_TRY(segments_ensure(f, n_rec, n));
+    SegArgs sa;
+    sa.iters = f.iters_dev; sa.pool = f.pool_dev; sa.pool_cap = st.pool_cap;
+    sa.src = f.src; sa.stride = f.src_stride; sa.src_is_float = f.src_is_float;
+    for (int c = 0; c < 3; ++c) { sa.ns[c] = ns[c]; sa.shift[c] = res->shift[c]; }
+    sa.cfg = f.seg_cfg; sa.scr = f.seg_scr; sa.scr_n = f.seg_scr_n; sa.out = f.seg_dev;
+    segment_tests_kernel<<<(unsigned)n_rec, kSegThreads, 0, s>>>(sa);
+    note_launches(1);
+    H3D_CUDA(cudaGetLastError());
+    H3D_CUDA(cudaMemcpyAsync(f.seg_host, f.seg_dev, n_rec * sizeof(h3d_segment), cudaMemcpyDeviceToHost, s));
+    f.seg_n = n_rec;
+  }
   H3D_CUDA(cudaEventRecord(f.ev[3], s));
   H3D_CUDA(cudaStreamSynchronize(s));
   f.timed = true;
@@ -1099,6 +1144,7 @@ extern "C" int h3d_hough3dlines(const double *xyz, size_t n, int granularity, do
   H3D_CUDA(cudaEventRecord(f.ev[0], s));
   if (n) H3D_CUDA(cudaMemcpyAsync(f.in_dev, xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
   f.timed = false;
+  f.src = f.in_dev; f.src_stride = 3; f.src_is_float = 0;
   prep_kernel<double><<<1, 1024, 0, s>>>(static_cast<const double *>(f.in_dev), (int)n, nullptr, 3, f.hg->px,
                                          f.hg->py, f.hg->pz, f.orig, f.prep_dev);
   H3D_CUDA(cudaGetLastError());
@@ -1301,7 +1347,9 @@ extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_
     H3D_TRY(prefilter_phase2(p->pf, raw_dev, (int)n, (int)stride, p->win, p->grid_cells, p->filt_dev, (int)p->cfg.max_raw_points, 3, h->dev.sm_count, s));
     // wrap.h:175-189: float -> double widening of the filtered cloud (+ NaN/Inf strip, bbox)
     prep_kernel<float><<<1, 1024, 0, s>>>(p->filt_dev, 0, &p->pf.st->n_out, 3, h->px, h->py, h->pz, f.orig, f.prep_dev);
+    f.src = p->filt_dev; f.src_stride = 3; f.src_is_float = 1;
   } else {
+    f.src = raw_dev; f.src_stride = (int)stride; f.src_is_float = 1;
     prep_kernel<float><<<1, 1024, 0, s>>>(raw_dev, (int)n, nullptr, (int)stride, h->px, h->py, h->pz, f.orig, f.prep_dev);
   }
   H3D_CUDA(cudaGetLastError());
@@ -1325,6 +1373,78 @@ extern "C" int h3d_pipeline_run(h3d_pipeline *p, const float *raw, size_t n, siz
   H3D_CUDA(cudaSetDevice(p->device));
   if (n) H3D_CUDA(cudaMemcpyAsync(p->raw_dev, raw, n * stride * sizeof(float), cudaMemcpyHostToDevice, p->f.hg->stream));
   return h3d_pipeline_run_dev(p, p->raw_dev, n, stride, iters, pool, pool_cap, res);
+}
+
+static bool segment_config_ok(const h3d_segment_config *c) {
+  return c && c->n_radius >= 1 && c->n_radius <= H3D_MAX_RADIUS_SIZES;
+}
+
+extern "C" int h3d_pipeline_enable_segments(h3d_pipeline *p, const h3d_segment_config *cfg) {
+  if (!p) return fail(H3D_ERR_ARG, "bad argument");
+  if (!cfg) { p->f.seg_on = false; p->f.seg_n = 0; return H3D_OK; }
+  if (!segment_config_ok(cfg)) return fail(H3D_ERR_ARG, "radius_sizes needs 1..8 entries");
+  p->f.seg_cfg = *cfg;
+  p->f.seg_on = true;
+  return H3D_OK;
+}
+
+// compacts the per-iteration records to the lines the reference tests, up to the first abort
+static size_t collect_segments(const h3d_segment *rec, size_t n_rec, h3d_segment *segs, size_t cap, bool *aborted,
+                               bool *truncated) {
+  size_t m = 0;
+  *aborted = false; *truncated = false;
+  for (size_t k = 0; k < n_rec; ++k) {
+    if (rec[k].status == kSegNone) continue;
+    if (rec[k].status == kSegTruncated) { *truncated = true; break; }
+    if (m < cap && segs) segs[m] = rec[k];
+    ++m;
+    if (rec[k].status == 3) { *aborted = true; break; }
+  }
+  return m;
+}
+
+extern "C" int h3d_pipeline_segments(h3d_pipeline *p, h3d_segment *segs, size_t cap, size_t *n_segs, int *rc_ref) {
+  if (!p || !n_segs) return fail(H3D_ERR_ARG, "bad argument");
+  if (!p->f.seg_on) return fail(H3D_ERR_ARG, "segment post-tests are not enabled on this pipeline");
+  bool aborted, truncated;
+  *n_segs = collect_segments(p->f.seg_host, p->f.seg_n, segs, cap, &aborted, &truncated);
+  if (truncated) return fail(H3D_ERR_RANGE, "an inlier list did not fit the device index pool");
+  if (rc_ref) *rc_ref = aborted ? 1 : 0;
+  return H3D_OK;
+}
+
+extern "C" int h3d_segment_test(const double *y_xyz, size_t n, const double shift[3], const double a[3],
+                                const double b[3], const h3d_segment_config *cfg, h3d_segment *out) {
+  if (!y_xyz || !n || !shift || !a || !b || !out || n > 0x7FFFFFF0u) return fail(H3D_ERR_ARG, "bad argument");
+  if (!segment_config_ok(cfg)) return fail(H3D_ERR_ARG, "radius_sizes needs 1..8 entries");
+  double *pts = nullptr, *scr = nullptr;
+  h3d_iter *rec = nullptr;
+  h3d_segment *seg = nullptr;
+  auto cleanup = [&]() { cudaFree(pts); cudaFree(scr); cudaFree(rec); cudaFree(seg); };
+  h3d_iter r;
+  memset(&r, 0, sizeof r);
+  r.status = 0; r.n2 = (uint32_t)n; r.off2 = 0;
+  for (int c = 0; c < 3; ++c) { r.a2[c] = a[c]; r.b2[c] = b[c]; }
+  cudaError_t e = cudaMalloc(&pts, n * 3 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&scr, n * 3 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&rec, sizeof r);
+  if (e == cudaSuccess) e = cudaMalloc(&seg, sizeof *out);
+  if (e == cudaSuccess) e = cudaMemcpy(pts, y_xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(rec, &r, sizeof r, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    SegArgs sa;
+    sa.iters = rec; sa.pool = nullptr; sa.pool_cap = 0;
+    sa.src = pts; sa.stride = 3; sa.src_is_float = 0;
+    for (int c = 0; c < 3; ++c) { sa.ns[c] = 0.0; sa.shift[c] = shift[c]; }   // y - 0.0 == y
+    sa.cfg = *cfg; sa.scr = scr; sa.scr_n = n; sa.out = seg;
+    segment_tests_kernel<<<1, kSegThreads>>>(sa);
+    note_launches(1);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out, seg, sizeof *out, cudaMemcpyDeviceToHost);
+  cleanup();
+  if (e != cudaSuccess) return fail(H3D_ERR_CUDA, cudaGetErrorString(e));
+  return H3D_OK;
 }
 
 extern "C" int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n_out) {

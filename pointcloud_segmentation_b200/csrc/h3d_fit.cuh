@@ -95,6 +95,10 @@ __host__ __device__ inline float eig_hypot(float x, float y) {   // numext::hypo
   return big * H3D_EIG_SQRT(1.0f + r * r);
 }
 
+// FIXED3: the tridiagonalisation Eigen selects for a fixed-size Matrix3f
+// (tridiagonalization_inplace_selector<MatrixType,3,false>, closed form; pcl::PCA's solver):
+// eigenvalues only, evecs are not meaningful.
+template <bool FIXED3 = false>
 __host__ __device__ H3D_EIG_NOINLINE inline Eig3f eig3f(const float m[9]) {
   Eig3f out;
   float a00 = m[0], a10 = m[1], a20 = m[2], a11 = m[4], a21 = m[5], a22 = m[8];
@@ -113,7 +117,21 @@ __host__ __device__ H3D_EIG_NOINLINE inline Eig3f eig3f(const float m[9]) {
   float diag[3], sub[2];
   float q[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
   const float tail_sq = a20 * a20;
-  if (tail_sq <= FLT_MIN) {
+  if (FIXED3) {
+    diag[0] = a00;
+    if (tail_sq <= FLT_MIN) {
+      diag[1] = a11; diag[2] = a22; sub[0] = a10; sub[1] = a21;
+    } else {
+      const float beta = H3D_EIG_SQRT(a10 * a10 + tail_sq);
+      const float inv_beta = H3D_EIG_DIV(1.0f, beta);
+      const float m01 = a10 * inv_beta, m02 = a20 * inv_beta;
+      const float qq = 2.0f * m01 * a21 + m02 * (a22 - a11);
+      diag[1] = a11 + m02 * qq;
+      diag[2] = a22 - m02 * qq;
+      sub[0] = beta;
+      sub[1] = a21 - m01 * qq;
+    }
+  } else if (tail_sq <= FLT_MIN) {
     diag[0] = a00; diag[1] = a11; diag[2] = a22; sub[0] = a10; sub[1] = a21;
   } else {
     float beta = H3D_EIG_SQRT(a10 * a10 + tail_sq);

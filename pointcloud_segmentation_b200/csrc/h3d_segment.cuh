@@ -1,0 +1,226 @@
+// h3d_segment.cuh -- segment post-tests of every accepted line, on the device.
+//
+// Reference: wrap.h:261-337, the block of hough3dlines() that runs on the
+// final inlier set Y of a line right after the second orthogonal_LSQ: find_proj (wrap.h:78-85),
+// find_t with its sorted insertion (wrap.h:41-68), largest gap between neighbours (wrap.h:286-292),
+// radius match (wrap.h:295-309), segPCA (wrap.h:94-110), density test (wrap.h:320-322).
+// ("wrap.h" = include/pointcloud_segmentation/hough_3d_lines.h of the reference.)
+//
+// The reference copies Y.points into Eigen vectors line by line on the host; here the inlier
+// index lists of the loop are still in device memory (the index pool), so one launch with one
+// CTA per iteration record tests every line of the frame and only the 144-byte records go back.
+//
+// Arithmetic restated (same as oracle/h3d_oracle.c h3do_segment_test):
+//   * Eigen fixed-size Vector3d: sums of three terms reduce as x0 + (x1 + x2); no FMA contraction
+//     (this file is compiled with -fmad=false);
+//   * the sorted insertion of find_t is a stable sort by t: rank(i) = #{j : t_j < t_i or
+//     (t_j == t_i and j < i)} -- computed by counting, no data-dependent order of float sums;
+//   * pcl::PCA<PointXYZ>: float centroid (sequential sum), float demeaned products summed in the
+//     canonical TREE32 order, SelfAdjointEigenSolver<Matrix3f> (eig3f<true>).  PARITY UNPINNED
+//     for this part (PCL and Eigen are not vendored in the reference).
+#ifndef H3D_SEGMENT_CUH_
+#define H3D_SEGMENT_CUH_
+
+#include "../../include/h3d.h"
+#include "h3d_fit.cuh"
+
+namespace h3d {
+
+constexpr int kSegThreads = 256;
+constexpr unsigned kSegNone = 4;        // the iteration did not yield a line
+constexpr unsigned kSegTruncated = 5;   // the inlier list did not fit the index pool
+
+struct SegArgs {
+  const h3d_iter *iters;     // iteration records of the frame (device)
+  const unsigned *pool;      // index pool (device); nullptr: the list is 0..n2-1
+  unsigned pool_cap;
+  const void *src;           // the cloud the pool indexes: f32 or f64, `stride` elements apart
+  int stride, src_is_float;
+  double ns[3];              // what shiftToOrigin subtracted (lib/pointcloud.cpp:18-26)
+  double shift[3];           // X.shift
+  h3d_segment_config cfg;
+  double *scr;               // 3 * scr_n doubles: t, |a + t b|, sorted |a + t b|
+  size_t scr_n;
+  h3d_segment *out;
+};
+
+__device__ __forceinline__ double seg_dot3(double u0, double u1, double u2, double v0, double v1, double v2) {
+  return __dadd_rn(__dmul_rn(u0, v0), __dadd_rn(__dmul_rn(u1, v1), __dmul_rn(u2, v2)));
+}
+
+// point k of the source cloud in the frame of the reported line: (p - ns) + shift, wrap.h:271
+__device__ __forceinline__ void seg_point(const SegArgs &A, unsigned k, double p[3]) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const size_t e = (size_t)k * A.stride + c;
+    const double v = A.src_is_float ? (double)static_cast<const float *>(A.src)[e] : static_cast<const double *>(A.src)[e];
+    p[c] = __dadd_rn(__dsub_rn(v, A.ns[c]), A.shift[c]);
+  }
+}
+
+__device__ __forceinline__ double seg_block_max(double v, double *red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  double m = red[0];
+  for (int w = 1; w < kSegThreads / 32; ++w) m = fmax(m, red[w]);
+  return m;
+}
+
+__global__ void __launch_bounds__(kSegThreads) segment_tests_kernel(const SegArgs A) {
+  __shared__ double red[kSegThreads / 32];
+  __shared__ double sh_t[2], sh_r[2];
+  __shared__ float sh_cen[3], sh_sc[6];
+  const int it = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const h3d_iter &R = A.iters[it];
+  h3d_segment *S = &A.out[it];
+  const unsigned n = R.n2;
+  unsigned status = 1;
+  if (R.status != 0 || n == 0) status = kSegNone;
+  else if (A.pool && (size_t)R.off2 + n > A.pool_cap) status = kSegTruncated;
+  // the final inlier sets of the accepted lines are disjoint (removePoints, wrap.h:339), so
+  // their sizes sum to at most the cloud: scratch base = sizes of the earlier lines
+  size_t base = 0;
+  for (int k = 0; k < it; ++k) if (A.iters[k].status == 0) base += A.iters[k].n2;
+  if (status == 1 && base + n > A.scr_n) status = kSegTruncated;
+  double a[3], b[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { a[c] = R.a2[c]; b[c] = R.b2[c]; }
+  if (status == 1 && b[0] == 0.0) status = 3;                       // find_t: no solution, wrap.h:43-45
+  if (status != 1) {
+    if (tid == 0) {
+      h3d_segment s;
+      memset(&s, 0, sizeof s);
+      s.iter = (uint32_t)it; s.status = status; s.n_points = status == kSegNone ? 0u : n;
+      for (int c = 0; c < 3; ++c) { s.a[c] = a[c]; s.b[c] = b[c]; }
+      *S = s;
+    }
+    return;
+  }
+  const unsigned *list = A.pool ? A.pool + R.off2 : nullptr;
+  double *t_arr = A.scr + base, *n_arr = A.scr + A.scr_n + base, *s_arr = A.scr + 2 * A.scr_n + base;
+  // ---- per point: projection, radius, t, |a + t b| ---------------------------- wrap.h:270-283
+  double d[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) d[c] = __dsub_rn(__dadd_rn(a[c], b[c]), a[c]);      // p_B - p_A
+  const double dd = seg_dot3(d[0], d[1], d[2], d[0], d[1], d[2]);
+  for (unsigned i = tid; i < n; i += kSegThreads) {
+    double p[3], proj[3], e[3], q[3];
+    seg_point(A, list ? list[i] : i, p);
+    const double num = seg_dot3(__dsub_rn(p[0], a[0]), __dsub_rn(p[1], a[1]), __dsub_rn(p[2], a[2]), d[0], d[1], d[2]);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      proj[c] = __dadd_rn(a[c], __ddiv_rn(__dmul_rn(d[c], num), dd));
+      e[c] = __dsub_rn(proj[c], p[c]);
+    }
+    if (i == 0 || i == n - 1) {
+      const double r = __dsqrt_rn(seg_dot3(e[0], e[1], e[2], e[0], e[1], e[2]));
+      if (i == 0) sh_r[0] = r;
+      if (i == n - 1) sh_r[1] = r;
+    }
+    const double t = __ddiv_rn(__dsub_rn(proj[0], a[0]), b[0]);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) q[c] = __dadd_rn(a[c], __dmul_rn(t, b[c]));
+    t_arr[i] = t;
+    n_arr[i] = __dsqrt_rn(seg_dot3(q[0], q[1], q[2], q[0], q[1], q[2]));
+  }
+  __syncthreads();
+  // ---- stable rank of every t (find_t's upper_bound insertion), scatter of the norms ---------
+  for (unsigned i = tid; i < n; i += kSegThreads) {
+    const double ti = t_arr[i];
+    unsigned rank = 0;
+    for (unsigned j = 0; j < n; ++j) {
+      const double tj = t_arr[j];
+      rank += (tj < ti) | ((tj == ti) & (j < i));
+    }
+    s_arr[rank] = n_arr[i];
+    if (rank == 0) sh_t[0] = ti;
+    if (rank == n - 1) sh_t[1] = ti;
+  }
+  __syncthreads();
+  // ---- largest gap between neighbours on the line, wrap.h:286-292 ----------------------------
+  double gap = 0.0;
+  for (unsigned k = tid; k + 1 < n; k += kSegThreads) gap = fmax(gap, fabs(__dsub_rn(s_arr[k + 1], s_arr[k])));
+  const double max_dist = seg_block_max(gap, red);
+  // ---- radius match, wrap.h:295-312 ----------------------------------------------------------
+  const double radius = fmax(sh_r[0], sh_r[1]);
+  double closest = A.cfg.radius_sizes[0];
+  double min_diff = fabs(__dsub_rn(radius, A.cfg.radius_sizes[0]));
+  double max_radius = min_diff;                                                   // sic, wrap.h:298
+  for (unsigned k = 0; k < A.cfg.n_radius; ++k) {
+    const double r = A.cfg.radius_sizes[k];
+    const double cur = fabs(__dsub_rn(radius, r));
+    if (cur < min_diff) { min_diff = cur; closest = r; }
+    if (r > max_radius) max_radius = r;
+  }
+  const bool pass = min_diff < A.cfg.diag_voxel && max_radius <= closest && max_dist < __dmul_rn(2.0, A.cfg.diag_voxel);
+  h3d_segment s;
+  if (tid == 0) {
+    memset(&s, 0, sizeof s);
+    s.iter = (uint32_t)it; s.n_points = n;
+    for (int c = 0; c < 3; ++c) { s.a[c] = a[c]; s.b[c] = b[c]; }
+    s.t_min = sh_t[0]; s.t_max = sh_t[1];
+    s.radius_raw = radius; s.radius = closest; s.max_dist = max_dist;
+    s.status = 1;
+  }
+  if (!pass) {
+    if (tid == 0) *S = s;
+    return;
+  }
+  // ---- segPCA (wrap.h:94-110): pcl::PCA in float ---------------------------------------------
+  if (warp == 0 && lane < 3) {            // compute3DCentroid: sequential float sum per axis
+    float acc = 0.0f;
+    for (unsigned i = 0; i < n; ++i) {
+      double p[3];
+      seg_point(A, list ? list[i] : i, p);
+      acc = __fadd_rn(acc, (float)(lane == 0 ? p[0] : lane == 1 ? p[1] : p[2]));
+    }
+    sh_cen[lane] = __fdiv_rn(acc, (float)n);
+  }
+  __syncthreads();
+  if (warp < 6) {                         // one warp per product: xx xy xz yy yz zz, TREE32
+    const int u = warp < 3 ? 0 : warp < 5 ? 1 : 2;
+    const int v = warp < 3 ? warp : warp < 5 ? warp - 2 : 2;
+    float acc = 0.0f;
+    for (unsigned i = lane; i < n; i += 32) {
+      double p[3];
+      seg_point(A, list ? list[i] : i, p);
+      const float cu = __fsub_rn((float)p[u], sh_cen[u]), cv = __fsub_rn((float)p[v], sh_cen[v]);
+      acc = __fadd_rn(acc, __fmul_rn(cu, cv));
+    }
+    acc = tree32_combine(acc);
+    if (lane == 0) sh_sc[warp] = __fmul_rn(__fdiv_rn(1.0f, __fsub_rn((float)n, 1.0f)), acc);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const float m[9] = {sh_sc[0], sh_sc[1], sh_sc[2], sh_sc[1], sh_sc[3], sh_sc[4], sh_sc[2], sh_sc[4], sh_sc[5]};
+    bool finite = true;
+    for (int c = 0; c < 6; ++c) finite &= isfinite(sh_sc[c]);
+    float ev[3] = {NAN, NAN, NAN};
+    if (finite) {
+      const Eig3f e = eig3f<true>(m);
+      ev[0] = e.evals[0]; ev[1] = e.evals[1]; ev[2] = e.evals[2];
+    }
+    const double e0 = (double)ev[2], e1 = (double)ev[1], e2 = (double)ev[0];      // descending
+    s.pca_eigenvalues[0] = e0; s.pca_eigenvalues[1] = e1; s.pca_eigenvalues[2] = e2;
+    s.pca_coeff = __ddiv_rn(e0, __dadd_rn(__dadd_rn(e0, e1), e2));                // wrap.h:315
+    double dl[3];
+    for (int c = 0; c < 3; ++c)                                                   // wrap.h:317-319
+      dl[c] = __dsub_rn(__dadd_rn(__dmul_rn(s.t_max, b[c]), a[c]), __dadd_rn(__dmul_rn(s.t_min, b[c]), a[c]));
+    s.length = __dsqrt_rn(seg_dot3(dl[0], dl[1], dl[2], dl[0], dl[1], dl[2]));
+    const double den = __dmul_rn(__dmul_rn(__dmul_rn(__dmul_rn(A.cfg.rad_2_leaf_ratio, 2.0), A.cfg.diag_voxel), 2.0), A.cfg.diag_voxel);
+    const double want = __ddiv_rn(__dmul_rn(__dmul_rn(2.0, closest), s.length), den);   // wrap.h:320
+    // static_cast<int> as x86 converts it: out of range or NaN -> INT_MIN
+    const int min_nb = (want >= 2147483648.0 || want <= -2147483649.0 || want != want) ? (int)0x80000000 : __double2int_rz(want);
+    s.min_nb_points = min_nb;
+    // points.size() > min_nb_points_seg: size_t against int, the int converts to unsigned
+    const bool keep = s.pca_coeff > A.cfg.min_pca_coeff && (unsigned long long)n > (unsigned long long)(long long)min_nb;
+    s.status = keep ? 0u : 2u;
+    *S = s;
+  }
+}
+
+}  // namespace h3d
+#endif  // H3D_SEGMENT_CUH_

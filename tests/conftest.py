@@ -21,6 +21,13 @@ def oracle():
 
 
 @pytest.fixture(scope="session")
+def oracle_mod():
+    """The oracle's Python module (its ctypes structures).  Test infrastructure only."""
+    from oracle import oracle as O
+    return O
+
+
+@pytest.fixture(scope="session")
 def h3d():
     """The product: libh3d.so through its C-ABI.  Fails loudly if it is not built."""
     from pointcloud_segmentation_b200 import capi

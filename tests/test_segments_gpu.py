@@ -1,0 +1,106 @@
+"""GPU parity of the segment post-tests (wrap.h:261-337: find_proj, find_t, gap, radius match,
+segPCA, density) against the oracle restatement -- SURVEY 8(f) rank 1.  Every field of every
+record is compared bit for bit (doubles by their bit patterns)."""
+import numpy as np
+import pytest
+
+from pointcloud_segmentation_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(mod, radius_sizes=(0.05,), min_pca=0.995, ratio=1.5, leaf=None):
+    leaf = float(synth.LEAF) if leaf is None else leaf
+    return mod.SegmentConfig.make(np.sqrt(3) * leaf, min_pca, ratio, list(radius_sizes))
+
+
+def _bits(seg):
+    vals = []
+    for v in seg.as_tuple():
+        for x in (v if isinstance(v, tuple) else (v,)):
+            vals.append(np.float64(x).view(np.uint64) if isinstance(x, float) else int(x))
+    return vals
+
+
+def _same(got, want):
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert _bits(g) == _bits(w), (g.as_tuple(), w.as_tuple())
+
+
+@pytest.mark.parametrize("fused", [True, False], ids=["fused", "multikernel"])
+@pytest.mark.parametrize("g,nlines,radii,min_pca", [(6, 20, (0.05,), 0.995), (4, 10, (0.05,), 0.9),
+                                                    (4, 12, (0.03, 0.05), 0.95), (4, 12, (0.03, 0.05, 0.1), 0.95)])
+def test_pipeline_segments_match_oracle(h3d, oracle, oracle_mod, fused, g, nlines, radii, min_pca):
+    old = h3d.set_fused(fused)
+    try:
+        pipe = h3d.Pipeline(g, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, nlines, max_raw_points=224 * 172)
+        pipe.enable_segments(_cfg(h3d, radii, min_pca))
+        seen = set()
+        for pose, seed in (((-1.1, 0.0, 0.8, 0.0), 2), ((-0.9, 0.4, 1.4, -0.3), 9)):
+            frame = synth.tof_frame(pose=pose, seed=seed)
+            filt = oracle.prefilter(frame, synth.WINDOW, float(synth.LEAF)).astype(np.float64)
+            trace = oracle.hough3dlines(filt, g, synth.OPT_DX, 12, nlines, mode=0)
+            rc_want, want = oracle.segments(filt, trace, _cfg(oracle_mod, radii, min_pca))
+            pipe.run(frame)
+            rc_got, got = pipe.segments()
+            assert rc_got == rc_want
+            _same(got, want)
+            seen |= {s.status for s in want}
+        pipe.close()
+        if max(radii) == 0.05:   # a larger size in the list fails every line at wrap.h:312 (max_radius <= closest_radius)
+            assert 1 in seen and (0 in seen or 2 in seen)   # both tests of wrap.h:312 / :322 were exercised
+    finally:
+        h3d.set_fused(old)
+
+
+def test_segments_off_and_host_pool_smaller_than_device_pool(h3d, oracle, oracle_mod):
+    """The post-tests read the device pool even when the caller takes no inlier lists."""
+    frame = synth.tof_frame()
+    filt = oracle.prefilter(frame, synth.WINDOW, float(synth.LEAF)).astype(np.float64)
+    trace = oracle.hough3dlines(filt, 4, synth.OPT_DX, 12, 6, mode=0)
+    _, want = oracle.segments(filt, trace, _cfg(oracle_mod))
+    pipe = h3d.Pipeline(4, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 6, max_raw_points=frame.shape[0])
+    with pytest.raises(h3d.H3dError):
+        pipe.segments()                      # not enabled
+    pipe.enable_segments(_cfg(h3d))
+    import ctypes as C
+    raw = np.ascontiguousarray(frame, dtype=np.float32)
+    res = h3d.Result()
+    h3d.check(h3d.lib().h3d_pipeline_run(pipe._p, raw.ctypes.data_as(C.POINTER(C.c_float)), C.c_size_t(raw.shape[0]),
+                                         C.c_size_t(raw.shape[1]), None, None, C.c_size_t(0), C.byref(res)))
+    rc, got = pipe.segments()
+    assert rc == 0
+    _same(got, want)
+    pipe.close()
+
+
+def test_segment_test_host_form_and_edges(h3d, oracle, oracle_mod):
+    rng = np.random.default_rng(5)
+    shift = np.array([0.7, -0.1, 0.3])
+    b = np.array([0.6, 0.64, 0.48])
+    a = np.array([0.2, 0.1, -0.3]) + shift
+    t = np.sort(rng.uniform(-1.0, 1.0, 300))
+    for label, pts in (
+        ("beam", (a - shift) + t[:, None] * b + rng.normal(0, 0.02, (300, 3))),
+        ("shuffled", ((a - shift) + t[:, None] * b + rng.normal(0, 0.02, (300, 3)))[rng.permutation(300)]),
+        ("gap", (a - shift) + np.concatenate([t[:100] - 3.0, t[100:]])[:, None] * b),
+        ("ties", np.repeat((a - shift) + t[:30, None] * b, 4, axis=0)),            # equal t: stable order
+        ("two", (a - shift) + np.array([[-0.5], [0.5]]) * b),
+        ("one", (a - shift)[None, :] + 0.01),
+        ("blob", rng.normal(0, 0.03, (200, 3))),                                   # low pca_coeff
+    ):
+        for radii in ((0.05,), (0.02, 0.05), (0.1, 0.05)):
+            for min_pca in (0.5, 0.995):
+                rc, want = oracle.segment_test(pts, shift, a, b, _cfg(oracle_mod, radii, min_pca))
+                got = h3d.segment_test(pts, shift, a, b, _cfg(h3d, radii, min_pca))
+                assert rc == 0
+                assert _bits(got)[1:] == _bits(want)[1:], (label, radii, got.as_tuple(), want.as_tuple())
+    # find_t has no solution when b.x == 0: the reference returns 1 (wrap.h:43-45, 276-279)
+    b0 = np.array([0.0, 0.6, 0.8])
+    pts = (a - shift) + t[:50, None] * b0
+    rc, want = oracle.segment_test(pts, shift, a, b0, _cfg(oracle_mod))
+    got = h3d.segment_test(pts, shift, a, b0, _cfg(h3d))
+    assert rc == 1 and want.status == 3 and got.status == 3
+    with pytest.raises(h3d.H3dError):
+        h3d.segment_test(pts, shift, a, b0, h3d.SegmentConfig.make(0.05, 0.9, 1.5, []))
