@@ -328,6 +328,25 @@ def run_gpu_arm(args):
                     n_alive -= r.n2
             algo_bytes += b; algo_dense += b + dense
     n_lat = len(lat_us)
+    # the same frames with the segment post-tests (wrap.h:261-337) switched on
+    seg_leg = None
+    try:
+        lat.enable_segments(capi.SegmentConfig.make(float(np.sqrt(3.0)) * float(synth.LEAF), 0.995, 1.5, [0.05]))
+        seg_us, tested, accepted = [], 0, 0
+        for rep in range(3):
+            for k in range(DISTINCT_FRAMES):
+                lat.run_dev(on_dev[k].data_ptr(), n_pts, stride)
+                if rep == 0:
+                    continue
+                seg_us.append(lat.timing_us()[3])
+                _, segs = lat.segments()
+                tested += len(segs); accepted += sum(1 for s_ in segs if s_.status == 0)
+        lat.enable_segments(None)
+        seg_leg = {"ms_mean": float(np.mean(seg_us)) / 1e3, "extra_us_per_frame": float(np.mean(seg_us) - np.mean(lat_us)),
+                   "lines_tested_per_frame": tested / len(seg_us), "segments_kept_per_frame": accepted / len(seg_us),
+                   "note": "single-frame latency leg with h3d_pipeline_enable_segments: one extra launch per frame"}
+    except Exception as exc:
+        seg_leg = {"error": str(exc)}
     # K1 (Hough::add) is its own launch: CUDA events around it (h3d_pipeline_timing [1])
     k1_us_mean = phase[1] / n_lat
     k1 = {"kernel": "vote_resident_kernel (one launch per frame)", "us_per_launch": float(k1_us_mean),
@@ -380,6 +399,7 @@ def run_gpu_arm(args):
                                  "25 B/live point per K3 pass, K2 counted on the 9 B/direction records",
                          "achieved_dense_equivalent": algo_dense / n_lat / (kernel_us * 1e-6) / 1e9,
                          "k1_first_vote_kernel": k1},
+            "segment_post_tests": seg_leg,
             "votes_per_s": (votes_add + votes_sub) / n_lat / ((kernel_us + k1_us_mean) * 1e-6),
             "votes_evaluated_per_s_throughput": dev["votes"] / (dev["ms"] * 1e-3) * world,
         }

@@ -783,8 +783,10 @@ struct FrameCtx {
   bool seg_on = false;
   h3d_segment_config seg_cfg{};
   h3d_segment *seg_dev = nullptr, *seg_host = nullptr;   // iters_cap records each; host copy pinned
-  size_t seg_cap = 0, seg_n = 0;
-  double *seg_scr = nullptr;             // 3 * seg_scr_n doubles
+  size_t seg_cap = 0, seg_n = 0, seg_grid = 0;
+  double seg_ns[3] = {0, 0, 0};          // what shiftToOrigin subtracted in the current frame
+  unsigned seg_pool_cap = 0;
+  double *seg_scr = nullptr;             // 5 * seg_scr_n doubles
   size_t seg_scr_n = 0;
   const void *src = nullptr;             // the cloud the pool indexes (set by the caller of frame_run)
   int src_stride = 3, src_is_float = 0;
@@ -881,6 +883,41 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
   loop_remove_kernel<<<1, 1024, 0, s>>>(lb);                            // removePoints, while  wrap.h:339-342
   note_launches(13);   // + the vote kernel counted in launch_vote
   H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+
+int segments_ensure(FrameCtx &f, size_t n_rec, size_t n_points) {
+  if (n_rec > f.seg_cap) {
+    cudaFree(f.seg_dev); cudaFreeHost(f.seg_host); f.seg_dev = f.seg_host = nullptr; f.seg_cap = 0;
+    const size_t cap = n_rec > f.iters_cap ? n_rec : f.iters_cap;
+    H3D_CUDA(cudaMalloc(&f.seg_dev, cap * sizeof(h3d_segment)));
+    H3D_CUDA(cudaMallocHost(&f.seg_host, cap * sizeof(h3d_segment)));
+    f.seg_cap = cap;
+  }
+  if (n_points > f.seg_scr_n) {
+    cudaFree(f.seg_scr); f.seg_scr = nullptr; f.seg_scr_n = 0;
+    const size_t cap = n_points > f.cap ? n_points : f.cap;
+    H3D_CUDA(cudaMalloc(&f.seg_scr, 5 * cap * sizeof(double)));
+    f.seg_scr_n = cap;
+  }
+  return H3D_OK;
+}
+
+// wrap.h:261-337 on every accepted line: enqueued right behind the loop's kernels (no host round
+// trip in between), one CTA per iteration record the loop may have written
+int enqueue_segments(FrameCtx &f, size_t grid) {
+  if (!f.seg_on || grid == 0) return H3D_OK;
+  if (grid > f.iters_cap) grid = f.iters_cap;
+  H3D_TRY(segments_ensure(f, grid, (size_t)f.hg->d.n));
+  SegArgs sa;
+  sa.iters = f.iters_dev; sa.n_iters = &f.st_dev->n_iters; sa.pool = f.pool_dev; sa.pool_cap = f.seg_pool_cap;
+  sa.src = f.src; sa.stride = f.src_stride; sa.src_is_float = f.src_is_float;
+  for (int c = 0; c < 3; ++c) { sa.ns[c] = f.seg_ns[c]; sa.shift[c] = f.seg_ns[c]; }   // X.shift = 0 + newshift
+  sa.cfg = f.seg_cfg; sa.scr = f.seg_scr; sa.scr_n = f.seg_scr_n; sa.out = f.seg_dev;
+  segment_tests_kernel<<<(unsigned)grid, kSegThreads, 0, f.hg->stream>>>(sa);
+  note_launches(1);
+  H3D_CUDA(cudaGetLastError());
+  f.seg_grid = grid;
   return H3D_OK;
 }
 
@@ -983,26 +1020,10 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   rc = launch_fused(f, a, smem, grid);
   if (rc != H3D_OK) return rc;
   H3D_CUDA(cudaEventRecord(f.ev[5], s));
+  H3D_TRY(enqueue_segments(f, opt_nlines > 0 ? (size_t)opt_nlines : f.iters_cap));
   H3D_CUDA(cudaMemcpyAsync(f.sync_host, f.sync_dev, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
   H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
   *launched = true;
-  return H3D_OK;
-}
-
-int segments_ensure(FrameCtx &f, size_t n_rec, size_t n_points) {
-  if (n_rec > f.seg_cap) {
-    cudaFree(f.seg_dev); cudaFreeHost(f.seg_host); f.seg_dev = f.seg_host = nullptr; f.seg_cap = 0;
-    const size_t cap = n_rec > f.iters_cap ? n_rec : f.iters_cap;
-    H3D_CUDA(cudaMalloc(&f.seg_dev, cap * sizeof(h3d_segment)));
-    H3D_CUDA(cudaMallocHost(&f.seg_host, cap * sizeof(h3d_segment)));
-    f.seg_cap = cap;
-  }
-  if (n_points > f.seg_scr_n) {
-    cudaFree(f.seg_scr); f.seg_scr = nullptr; f.seg_scr_n = 0;
-    const size_t cap = n_points > f.cap ? n_points : f.cap;
-    H3D_CUDA(cudaMalloc(&f.seg_scr, 3 * cap * sizeof(double)));
-    f.seg_scr_n = cap;
-  }
   return H3D_OK;
 }
 
@@ -1055,6 +1076,8 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   // the post-tests read the inlier lists on the device: keep them all even if the host takes fewer
   st.pool_cap = (unsigned)((pool_cap < f.pool_cap && !f.seg_on) ? pool_cap : f.pool_cap);
   st.n_alive = (int)n;
+  for (int c = 0; c < 3; ++c) f.seg_ns[c] = ns[c];
+  f.seg_pool_cap = st.pool_cap; f.seg_grid = 0;
   *f.st_host = st;
   H3D_CUDA(cudaMemcpyAsync(f.st_dev, f.st_host, sizeof(LoopState), cudaMemcpyHostToDevice, s));
 
@@ -1095,6 +1118,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   }
   if (rc == H3D_OK) {
     H3D_CUDA(cudaEventRecord(f.ev[5], s));
+    H3D_TRY(enqueue_segments(f, opt_nlines > 0 ? (size_t)opt_nlines : f.iters_cap));
     H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
     H3D_CUDA(cudaStreamSynchronize(s));
   }
@@ -1109,18 +1133,10 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   const size_t n_pool = (size_t)fin.pool_used < pool_cap ? (size_t)fin.pool_used : pool_cap;
   if (n_pool && pool) H3D_CUDA(cudaMemcpyAsync(pool, f.pool_dev, n_pool * sizeof(unsigned), cudaMemcpyDeviceToHost, s));
   f.seg_n = 0;
-  if (f.seg_on && n_rec) {                                // wrap.h:261-337 on every accepted line
-    H3D_TRY(segments_ensure(f, n_rec, n));
-    SegArgs sa;
-    sa.iters = f.iters_dev; sa.pool = f.pool_dev; sa.pool_cap = st.pool_cap;
-    sa.src = f.src; sa.stride = f.src_stride; sa.src_is_float = f.src_is_float;
-    for (int c = 0; c < 3; ++c) { sa.ns[c] = ns[c]; sa.shift[c] = res->shift[c]; }
-    sa.cfg = f.seg_cfg; sa.scr = f.seg_scr; sa.scr_n = f.seg_scr_n; sa.out = f.seg_dev;
-    segment_tests_kernel<<<(unsigned)n_rec, kSegThreads, 0, s>>>(sa);
-    note_launches(1);
-    H3D_CUDA(cudaGetLastError());
-    H3D_CUDA(cudaMemcpyAsync(f.seg_host, f.seg_dev, n_rec * sizeof(h3d_segment), cudaMemcpyDeviceToHost, s));
-    f.seg_n = n_rec;
+  if (f.seg_on && n_rec) {                                // records of enqueue_segments()
+    const size_t m = n_rec < f.seg_grid ? n_rec : f.seg_grid;
+    H3D_CUDA(cudaMemcpyAsync(f.seg_host, f.seg_dev, m * sizeof(h3d_segment), cudaMemcpyDeviceToHost, s));
+    f.seg_n = m;
   }
   H3D_CUDA(cudaEventRecord(f.ev[3], s));
   H3D_CUDA(cudaStreamSynchronize(s));
@@ -1426,14 +1442,14 @@ extern "C" int h3d_segment_test(const double *y_xyz, size_t n, const double shif
   r.status = 0; r.n2 = (uint32_t)n; r.off2 = 0;
   for (int c = 0; c < 3; ++c) { r.a2[c] = a[c]; r.b2[c] = b[c]; }
   cudaError_t e = cudaMalloc(&pts, n * 3 * sizeof(double));
-  if (e == cudaSuccess) e = cudaMalloc(&scr, n * 3 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&scr, n * 5 * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&rec, sizeof r);
   if (e == cudaSuccess) e = cudaMalloc(&seg, sizeof *out);
   if (e == cudaSuccess) e = cudaMemcpy(pts, y_xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(rec, &r, sizeof r, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) {
     SegArgs sa;
-    sa.iters = rec; sa.pool = nullptr; sa.pool_cap = 0;
+    sa.iters = rec; sa.n_iters = nullptr; sa.pool = nullptr; sa.pool_cap = 0;
     sa.src = pts; sa.stride = 3; sa.src_is_float = 0;
     for (int c = 0; c < 3; ++c) { sa.ns[c] = 0.0; sa.shift[c] = shift[c]; }   // y - 0.0 == y
     sa.cfg = *cfg; sa.scr = scr; sa.scr_n = n; sa.out = seg;

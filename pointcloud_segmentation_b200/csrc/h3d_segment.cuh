@@ -13,8 +13,10 @@
 // Arithmetic restated (same as oracle/h3d_oracle.c h3do_segment_test):
 //   * Eigen fixed-size Vector3d: sums of three terms reduce as x0 + (x1 + x2); no FMA contraction
 //     (this file is compiled with -fmad=false);
-//   * the sorted insertion of find_t is a stable sort by t: rank(i) = #{j : t_j < t_i or
-//     (t_j == t_i and j < i)} -- computed by counting, no data-dependent order of float sums;
+//   * the sorted insertion of find_t is a stable sort by t (equal t keep Y order): a bitonic sort of
+//     (order-preserving 64-bit key of t, index) pairs in shared memory for up to 2048 inliers, else
+//     rank(i) = #{j : t_j < t_i or (t_j == t_i and j < i)} by counting; only max/min-type results
+//     depend on the order, no float sum does (NaN t -- a non-finite anchor -- is not reproduced);
 //   * pcl::PCA<PointXYZ>: float centroid (sequential sum), float demeaned products summed in the
 //     canonical TREE32 order, SelfAdjointEigenSolver<Matrix3f> (eig3f<true>).  PARITY UNPINNED
 //     for this part (PCL and Eigen are not vendored in the reference).
@@ -29,9 +31,11 @@ namespace h3d {
 constexpr int kSegThreads = 256;
 constexpr unsigned kSegNone = 4;        // the iteration did not yield a line
 constexpr unsigned kSegTruncated = 5;   // the inlier list did not fit the index pool
+constexpr unsigned kSegSortCap = 2048;  // inliers per line sorted in shared memory
 
 struct SegArgs {
   const h3d_iter *iters;     // iteration records of the frame (device)
+  const int *n_iters;        // records written by the loop (device; nullptr: every CTA has one)
   const unsigned *pool;      // index pool (device); nullptr: the list is 0..n2-1
   unsigned pool_cap;
   const void *src;           // the cloud the pool indexes: f32 or f64, `stride` elements apart
@@ -39,7 +43,7 @@ struct SegArgs {
   double ns[3];              // what shiftToOrigin subtracted (lib/pointcloud.cpp:18-26)
   double shift[3];           // X.shift
   h3d_segment_config cfg;
-  double *scr;               // 3 * scr_n doubles: t, |a + t b|, sorted |a + t b|
+  double *scr;               // 5 * scr_n doubles: t, |a + t b|, sorted |a + t b|, then 3 * scr_n floats (points)
   size_t scr_n;
   h3d_segment *out;
 };
@@ -73,17 +77,20 @@ __global__ void __launch_bounds__(kSegThreads) segment_tests_kernel(const SegArg
   __shared__ double red[kSegThreads / 32];
   __shared__ double sh_t[2], sh_r[2];
   __shared__ float sh_cen[3], sh_sc[6];
+  __shared__ unsigned long long sh_key[kSegSortCap];
+  __shared__ unsigned sh_idx[kSegSortCap];
   const int it = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const h3d_iter &R = A.iters[it];
   h3d_segment *S = &A.out[it];
   const unsigned n = R.n2;
   unsigned status = 1;
-  if (R.status != 0 || n == 0) status = kSegNone;
+  if ((A.n_iters && it >= *A.n_iters) || R.status != 0 || n == 0) status = kSegNone;
   else if (A.pool && (size_t)R.off2 + n > A.pool_cap) status = kSegTruncated;
   // the final inlier sets of the accepted lines are disjoint (removePoints, wrap.h:339), so
   // their sizes sum to at most the cloud: scratch base = sizes of the earlier lines
   size_t base = 0;
-  for (int k = 0; k < it; ++k) if (A.iters[k].status == 0) base += A.iters[k].n2;
+  if (status == 1)
+    for (int k = 0; k < it; ++k) if (A.iters[k].status == 0) base += A.iters[k].n2;
   if (status == 1 && base + n > A.scr_n) status = kSegTruncated;
   double a[3], b[3];
 #pragma unroll
@@ -101,6 +108,10 @@ __global__ void __launch_bounds__(kSegThreads) segment_tests_kernel(const SegArg
   }
   const unsigned *list = A.pool ? A.pool + R.off2 : nullptr;
   double *t_arr = A.scr + base, *n_arr = A.scr + A.scr_n + base, *s_arr = A.scr + 2 * A.scr_n + base;
+  float *pf = reinterpret_cast<float *>(A.scr + 3 * A.scr_n) + 3 * base;          // pcl::PointXYZ(x, y, z), wrap.h:99
+  unsigned np2 = 1;
+  while (np2 < n) np2 <<= 1;
+  const bool in_smem = np2 <= kSegSortCap;
   // ---- per point: projection, radius, t, |a + t b| ---------------------------- wrap.h:270-283
   double d[3];
 #pragma unroll
@@ -125,19 +136,45 @@ __global__ void __launch_bounds__(kSegThreads) segment_tests_kernel(const SegArg
     for (int c = 0; c < 3; ++c) q[c] = __dadd_rn(a[c], __dmul_rn(t, b[c]));
     t_arr[i] = t;
     n_arr[i] = __dsqrt_rn(seg_dot3(q[0], q[1], q[2], q[0], q[1], q[2]));
-  }
-  __syncthreads();
-  // ---- stable rank of every t (find_t's upper_bound insertion), scatter of the norms ---------
-  for (unsigned i = tid; i < n; i += kSegThreads) {
-    const double ti = t_arr[i];
-    unsigned rank = 0;
-    for (unsigned j = 0; j < n; ++j) {
-      const double tj = t_arr[j];
-      rank += (tj < ti) | ((tj == ti) & (j < i));
+    pf[3 * i] = (float)p[0]; pf[3 * i + 1] = (float)p[1]; pf[3 * i + 2] = (float)p[2];
+    if (in_smem) {
+      const long long bits = __double_as_longlong(__dadd_rn(t, 0.0));             // -0.0 == +0.0 for upper_bound
+      sh_key[i] = (unsigned long long)(bits < 0 ? ~bits : (bits | (long long)0x8000000000000000ull));
+      sh_idx[i] = i;
     }
-    s_arr[rank] = n_arr[i];
-    if (rank == 0) sh_t[0] = ti;
-    if (rank == n - 1) sh_t[1] = ti;
+  }
+  if (in_smem)
+    for (unsigned i = n + tid; i < np2; i += kSegThreads) { sh_key[i] = ~0ull; sh_idx[i] = 0xFFFFFFFFu; }
+  __syncthreads();
+  // ---- find_t's upper_bound insertion = stable sort by t; norms follow ------------------------
+  if (in_smem) {
+    for (unsigned k = 2; k <= np2; k <<= 1)
+      for (unsigned j = k >> 1; j > 0; j >>= 1) {
+        for (unsigned i = tid; i < np2; i += kSegThreads) {
+          const unsigned l = i ^ j;
+          if (l > i) {
+            const unsigned long long ka = sh_key[i], kb = sh_key[l];
+            const unsigned ia = sh_idx[i], ib = sh_idx[l];
+            const bool gt = (ka > kb) | ((ka == kb) & (ia > ib));
+            if (gt == ((i & k) == 0)) { sh_key[i] = kb; sh_key[l] = ka; sh_idx[i] = ib; sh_idx[l] = ia; }
+          }
+        }
+        __syncthreads();
+      }
+    for (unsigned k = tid; k < n; k += kSegThreads) s_arr[k] = n_arr[sh_idx[k]];
+    if (tid == 0) { sh_t[0] = t_arr[sh_idx[0]]; sh_t[1] = t_arr[sh_idx[n - 1]]; }
+  } else {
+    for (unsigned i = tid; i < n; i += kSegThreads) {
+      const double ti = t_arr[i];
+      unsigned rank = 0;
+      for (unsigned j = 0; j < n; ++j) {
+        const double tj = t_arr[j];
+        rank += (tj < ti) | ((tj == ti) & (j < i));
+      }
+      s_arr[rank] = n_arr[i];
+      if (rank == 0) sh_t[0] = ti;
+      if (rank == n - 1) sh_t[1] = ti;
+    }
   }
   __syncthreads();
   // ---- largest gap between neighbours on the line, wrap.h:286-292 ----------------------------
@@ -172,11 +209,15 @@ __global__ void __launch_bounds__(kSegThreads) segment_tests_kernel(const SegArg
   // ---- segPCA (wrap.h:94-110): pcl::PCA in float ---------------------------------------------
   if (warp == 0 && lane < 3) {            // compute3DCentroid: sequential float sum per axis
     float acc = 0.0f;
-    for (unsigned i = 0; i < n; ++i) {
-      double p[3];
-      seg_point(A, list ? list[i] : i, p);
-      acc = __fadd_rn(acc, (float)(lane == 0 ? p[0] : lane == 1 ? p[1] : p[2]));
+    unsigned i = 0;
+    for (; i + 8 <= n; i += 8) {            // loads up front, the adds stay in cloud order
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = pf[3 * (i + u) + lane];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc = __fadd_rn(acc, v[u]);
     }
+    for (; i < n; ++i) acc = __fadd_rn(acc, pf[3 * i + lane]);
     sh_cen[lane] = __fdiv_rn(acc, (float)n);
   }
   __syncthreads();
@@ -185,9 +226,7 @@ __global__ void __launch_bounds__(kSegThreads) segment_tests_kernel(const SegArg
     const int v = warp < 3 ? warp : warp < 5 ? warp - 2 : 2;
     float acc = 0.0f;
     for (unsigned i = lane; i < n; i += 32) {
-      double p[3];
-      seg_point(A, list ? list[i] : i, p);
-      const float cu = __fsub_rn((float)p[u], sh_cen[u]), cv = __fsub_rn((float)p[v], sh_cen[v]);
+      const float cu = __fsub_rn(pf[3 * i + u], sh_cen[u]), cv = __fsub_rn(pf[3 * i + v], sh_cen[v]);
       acc = __fadd_rn(acc, __fmul_rn(cu, cv));
     }
     acc = tree32_combine(acc);

@@ -89,6 +89,8 @@ def test_segment_test_host_form_and_edges(h3d, oracle, oracle_mod):
         ("two", (a - shift) + np.array([[-0.5], [0.5]]) * b),
         ("one", (a - shift)[None, :] + 0.01),
         ("blob", rng.normal(0, 0.03, (200, 3))),                                   # low pca_coeff
+        ("big", (a - shift) + rng.uniform(-1, 1, 3000)[:, None] * b + rng.normal(0, 0.01, (3000, 3))),   # > 2048: counting path
+        ("pow2", (a - shift) + rng.uniform(-1, 1, 2048)[:, None] * b + rng.normal(0, 0.01, (2048, 3))),
     ):
         for radii in ((0.05,), (0.02, 0.05), (0.1, 0.05)):
             for min_pca in (0.5, 0.995):
