@@ -166,6 +166,22 @@ int h3d_pipeline_run(h3d_pipeline *p, const float *raw, size_t n, size_t stride,
 /* same with the raw frame already resident in device memory */
 int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride,
                          h3d_iter *iters, uint32_t *pool, size_t pool_cap, h3d_result *res);
+/* sensor_msgs/PointCloud2 adapter (node.cpp:286-289 pcl_conversions::toPCL +
+ * cloudFiltering, node.cpp:415 fromPCLPointCloud2): the message's byte buffer goes to the device
+ * as it is and the frame runs from there -- no host pass over the points.  x, y, z must be
+ * FLOAT32 fields (datatype 7) of a little-endian message.  Point i = row i / width, column
+ * i % width, at data[row * row_step + col * point_step + off_*].  When x,y,z are adjacent and the
+ * rows carry no padding the kernels read the message bytes in place; otherwise one gather kernel
+ * packs them first. */
+typedef struct {
+  uint32_t width, height;       /* sensor_msgs/PointCloud2.width / .height      */
+  uint32_t point_step, row_step;
+  uint32_t off_x, off_y, off_z; /* fields[].offset of "x", "y", "z"             */
+  uint32_t is_bigendian;        /* must be 0                                    */
+} h3d_cloud2_layout;
+int h3d_pipeline_run_cloud2(h3d_pipeline *p, const uint8_t *data, size_t data_bytes,
+                            const h3d_cloud2_layout *layout, h3d_iter *iters, uint32_t *pool,
+                            size_t pool_cap, h3d_result *res);
 /* filtered cloud of the last frame (f32 xyz), for inspection */
 int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n_out);
 /* per-phase device times of the last frame, microseconds:

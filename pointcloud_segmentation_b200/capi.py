@@ -50,6 +50,12 @@ class PipelineConfig(C.Structure):
     ]
 
 
+class Cloud2Layout(C.Structure):
+    """h3d_cloud2_layout: sensor_msgs/PointCloud2 geometry (width, height, steps, x/y/z byte offsets)."""
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("point_step", C.c_uint32), ("row_step", C.c_uint32),
+                ("off_x", C.c_uint32), ("off_y", C.c_uint32), ("off_z", C.c_uint32), ("is_bigendian", C.c_uint32)]
+
+
 class SegmentConfig(C.Structure):
     """h3d_segment_config: arguments of the post-tests (wrap.h:167-170)."""
     _fields_ = [("diag_voxel", C.c_double), ("min_pca_coeff", C.c_double), ("rad_2_leaf_ratio", C.c_double),
@@ -270,6 +276,15 @@ class Pipeline:
             else np.ascontiguousarray(raw_f32, dtype=np.float32)
         n, stride = a.shape
         return self._run(lib().h3d_pipeline_run, a.ctypes.data_as(C.POINTER(C.c_float)), n, stride)
+
+    def run_cloud2(self, data, width, height, point_step, row_step, off_x, off_y, off_z, is_bigendian=0):
+        """A sensor_msgs/PointCloud2 byte buffer (bytes / uint8 array) as it comes off the wire."""
+        buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+        lay = Cloud2Layout(width, height, point_step, row_step, off_x, off_y, off_z, is_bigendian)
+        check(lib().h3d_pipeline_run_cloud2(self._p, buf.ctypes.data_as(C.POINTER(C.c_uint8)), C.c_size_t(buf.size),
+                                            C.byref(lay), self.iters, self.pool.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                            C.c_size_t(self.pool.size), C.byref(self.res)))
+        return self.res
 
     def run_ptr(self, host_ptr, n, stride):
         """Same with a raw host address (e.g. a pinned torch tensor's data_ptr())."""

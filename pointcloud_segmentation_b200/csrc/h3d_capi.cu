@@ -1311,7 +1311,19 @@ struct h3d_pipeline {
   float *raw_dev = nullptr;     // max_raw_points * 4 floats
   float *filt_dev = nullptr;    // max_raw_points * 3 floats
   size_t raw_cap_floats = 0;
+  unsigned char *msg_dev = nullptr;   // PointCloud2 byte buffer of the current frame (h3d_pipeline_run_cloud2)
+  size_t msg_cap = 0;
 };
+
+// packs x,y,z of a PointCloud2 byte buffer into (x,y,z,0) float quadruples, message order
+__global__ void cloud2_gather_kernel(const unsigned char *__restrict__ data, h3d_cloud2_layout L, float4 *out) {
+  const size_t n = (size_t)L.width * L.height;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const unsigned char *pt = data + (i / L.width) * L.row_step + (i % L.width) * L.point_step;
+    out[i] = make_float4(*reinterpret_cast<const float *>(pt + L.off_x), *reinterpret_cast<const float *>(pt + L.off_y),
+                         *reinterpret_cast<const float *>(pt + L.off_z), 0.0f);
+  }
+}
 
 extern "C" int h3d_pipeline_create(const h3d_pipeline_config *cfg, h3d_pipeline **out) {
   if (!cfg || !out || cfg->granularity < 0 || cfg->granularity > 8 || cfg->max_raw_points == 0 ||
@@ -1343,7 +1355,7 @@ extern "C" int h3d_pipeline_create(const h3d_pipeline_config *cfg, h3d_pipeline 
 extern "C" void h3d_pipeline_destroy(h3d_pipeline *p) {
   if (!p) return;
   if (p->f.hg) cudaStreamSynchronize(p->f.hg->stream);
-  cudaFree(p->raw_dev); cudaFree(p->filt_dev);
+  cudaFree(p->raw_dev); cudaFree(p->filt_dev); cudaFree(p->msg_dev);
   delete p;
 }
 
@@ -1461,6 +1473,42 @@ extern "C" int h3d_segment_test(const double *y_xyz, size_t n, const double shif
   cleanup();
   if (e != cudaSuccess) return fail(H3D_ERR_CUDA, cudaGetErrorString(e));
   return H3D_OK;
+}
+
+extern "C" int h3d_pipeline_run_cloud2(h3d_pipeline *p, const uint8_t *data, size_t data_bytes,
+                                       const h3d_cloud2_layout *L, h3d_iter *iters, uint32_t *pool, size_t pool_cap,
+                                       h3d_result *res) {
+  if (!p || !L || !res) return fail(H3D_ERR_ARG, "bad argument");
+  if (L->is_bigendian) return fail(H3D_ERR_ARG, "big-endian PointCloud2 is not supported");
+  const size_t n = (size_t)L->width * L->height;
+  if (n > p->cfg.max_raw_points) return fail(H3D_ERR_ARG, "frame larger than max_raw_points");
+  const uint32_t off[3] = {L->off_x, L->off_y, L->off_z};
+  for (uint32_t o : off)
+    if ((o & 3u) || (size_t)o + 4 > L->point_step) return fail(H3D_ERR_ARG, "x/y/z must be 4-byte aligned FLOAT32 fields inside point_step");
+  if ((L->point_step & 3u) || (L->row_step & 3u) || (size_t)L->width * L->point_step > L->row_step)
+    return fail(H3D_ERR_ARG, "bad point_step / row_step");
+  if (n && (!data || (size_t)L->height * L->row_step > data_bytes)) return fail(H3D_ERR_ARG, "data shorter than height * row_step");
+  H3D_CUDA(cudaSetDevice(p->device));
+  cudaStream_t s = p->f.hg->stream;
+  const size_t bytes = (size_t)L->height * L->row_step;
+  if (bytes > p->msg_cap) {
+    H3D_CUDA(cudaStreamSynchronize(s));
+    cudaFree(p->msg_dev); p->msg_dev = nullptr; p->msg_cap = 0;
+    H3D_CUDA(cudaMalloc(&p->msg_dev, bytes + 16));
+    p->msg_cap = bytes;
+  }
+  if (bytes) H3D_CUDA(cudaMemcpyAsync(p->msg_dev, data, bytes, cudaMemcpyHostToDevice, s));
+  const bool in_place = L->off_y == L->off_x + 4 && L->off_z == L->off_x + 8 &&
+                        (L->height <= 1 || L->row_step == L->width * L->point_step);
+  if (in_place)   // point i starts at msg_dev + off_x + i * point_step: the kernels' (pointer, stride) form
+    return h3d_pipeline_run_dev(p, reinterpret_cast<const float *>(p->msg_dev + L->off_x), n, L->point_step / 4, iters, pool,
+                                pool_cap, res);
+  if (n) {
+    cloud2_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p->msg_dev, *L, reinterpret_cast<float4 *>(p->raw_dev));
+    note_launches(1);
+    H3D_CUDA(cudaGetLastError());
+  }
+  return h3d_pipeline_run_dev(p, p->raw_dev, n, 4, iters, pool, pool_cap, res);
 }
 
 extern "C" int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap, size_t *n_out) {

@@ -45,7 +45,7 @@ __device__ __forceinline__ int float_to_ordered(float f) {
 __device__ __forceinline__ float ordered_to_float(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
 
 __device__ __forceinline__ float3 load_xyz(const float *__restrict__ in, int i, int stride) {
-  if (stride == 4) {
+  if (stride == 4 && (reinterpret_cast<size_t>(in) & 15) == 0) {   // 16-byte aligned quadruples
     const float4 v = reinterpret_cast<const float4 *>(in)[i];
     return make_float3(v.x, v.y, v.z);
   }
