@@ -222,7 +222,22 @@ typedef struct {
   double pca_coeff;        /* 0 unless the first test passed                     */
   double pca_eigenvalues[3];
   double length;           /* |p(t_max) - p(t_min)|, wrap.h:317-319              */
+  /* drone -> world transform + height cut-off (node.cpp:429-470), filled for status 0
+   * when a pose is set (h3d_pipeline_set_pose), else zero: */
+  double a_world[3], b_world[3];   /* R*a + position, R*b (node.cpp:437-438)     */
+  uint32_t world_status;   /* 0 = no pose / not a kept segment; 1 = above the floor
+                              (kept by heighSegmentCutoff, node.cpp:461); 2 = trimmed */
+  uint32_t pad_;
 } h3d_segment;
+/* pose of the sensor for the following frames: orientation quaternion
+ * (w, x, y, z) as Eigen::Quaterniond::toRotationMatrix reads it, position, and
+ * floor_trim_height (config_pc_seg: 0.3).  NULL: no transform. */
+typedef struct {
+  double q[4];
+  double position[3];
+  double floor_trim_height;
+} h3d_pose;
+int h3d_pipeline_set_pose(h3d_pipeline *p, const h3d_pose *pose);
 /* cfg != NULL: every following frame of the pipeline also runs the post-tests
  * (one extra launch, no extra synchronisation); NULL switches them off. */
 int h3d_pipeline_enable_segments(h3d_pipeline *p, const h3d_segment_config *cfg);
@@ -236,6 +251,10 @@ int h3d_pipeline_segments(h3d_pipeline *p, h3d_segment *segs, size_t cap, size_t
  * direction.  Returns H3D_OK also when out->status != 0. */
 int h3d_segment_test(const double *y_xyz, size_t n, const double shift[3], const double a[3],
                      const double b[3], const h3d_segment_config *cfg, h3d_segment *out);
+/* same with the drone -> world step (pose may be NULL) */
+int h3d_segment_test_pose(const double *y_xyz, size_t n, const double shift[3], const double a[3],
+                          const double b[3], const h3d_segment_config *cfg, const h3d_pose *pose,
+                          h3d_segment *out);
 
 /* frame-parallel replay on ONE GPU (BASELINE configs[2]): frames are independent (one Hough per
  * frame, wrap.h:220/347), and the loop of a frame is latency-bound, so K pipelines driven by K

@@ -691,6 +691,28 @@ int h3do_segment_test(const double *y, size_t n, const double shift[3], const do
     return 0;
 }
 
+/* drone2WorldSeg (node.cpp:429-447) + heighSegmentCutoff (node.cpp:455-470).  Third party: Eigen3
+ * Quaterniond::toRotationMatrix and the fixed-size 3x3 * 3x1 product (each row reduces as
+ * x0 + (x1 + x2)).  No reference test pins it: PARITY UNPINNED. */
+void h3do_segment_to_world(const h3do_pose *P, h3do_segment *s) {
+    const double w = P->q[0], x = P->q[1], y = P->q[2], z = P->q[3];
+    const double tx = 2.0 * x, ty = 2.0 * y, tz = 2.0 * z;
+    const double twx = tx * w, twy = ty * w, twz = tz * w;
+    const double txx = tx * x, txy = ty * x, txz = tz * x;
+    const double tyy = ty * y, tyz = tz * y, tzz = tz * z;
+    const double R[3][3] = {{1.0 - (tyy + tzz), txy - twz, txz + twy},
+                            {txy + twz, 1.0 - (txx + tzz), tyz - twx},
+                            {txz - twy, tyz + twx, 1.0 - (txx + tyy)}};
+    if (s->status != 0) return;
+    for (int i = 0; i < 3; i++) {
+        s->a_world[i] = dot3_eigen(R[i], s->a) + P->position[i];
+        s->b_world[i] = dot3_eigen(R[i], s->b);
+    }
+    const double z1 = s->t_min * s->b_world[2] + s->a_world[2];
+    const double z2 = s->t_max * s->b_world[2] + s->a_world[2];
+    s->world_status = (z1 > P->floor_trim_height || z2 > P->floor_trim_height) ? 1u : 2u;
+}
+
 /* ======================================================================== */
 /* Pre-filter -- node.cpp:386-421.  Third party: PCL 1.10 (un-vendored):     */
 /* PassThrough<PCLPointCloud2> x,y,z (inclusive, drops non-finite field) then */

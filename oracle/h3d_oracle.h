@@ -106,7 +106,17 @@ typedef struct {
   double pca_coeff;
   double pca_eigenvalues[3];
   double length;
+  double a_world[3], b_world[3];   /* node.cpp:437-438 */
+  uint32_t world_status;           /* 0 none, 1 kept by heighSegmentCutoff (node.cpp:461), 2 trimmed */
+  uint32_t pad_;
 } h3do_segment;
+typedef struct {
+  double q[4];                /* w, x, y, z */
+  double position[3];
+  double floor_trim_height;
+} h3do_pose;
+/* drone2WorldSeg + heighSegmentCutoff (node.cpp:429-470) on a kept segment (status 0) */
+void h3do_segment_to_world(const h3do_pose *pose, h3do_segment *s);
 int h3do_segment_test(const double *y_xyz, size_t n, const double shift[3], const double a[3],
                       const double b[3], const h3do_segment_config *cfg, h3do_segment *out);
 

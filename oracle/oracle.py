@@ -63,12 +63,29 @@ class Segment(C.Structure):
     _fields_ = [("iter", C.c_uint32), ("status", C.c_uint32), ("n_points", C.c_uint32), ("min_nb_points", C.c_int32),
                 ("a", C.c_double * 3), ("b", C.c_double * 3), ("t_min", C.c_double), ("t_max", C.c_double),
                 ("radius_raw", C.c_double), ("radius", C.c_double), ("max_dist", C.c_double),
-                ("pca_coeff", C.c_double), ("pca_eigenvalues", C.c_double * 3), ("length", C.c_double)]
+                ("pca_coeff", C.c_double), ("pca_eigenvalues", C.c_double * 3), ("length", C.c_double),
+                ("a_world", C.c_double * 3), ("b_world", C.c_double * 3), ("world_status", C.c_uint32),
+                ("pad_", C.c_uint32)]
 
     def as_tuple(self):
         return (self.iter, self.status, self.n_points, self.min_nb_points, tuple(self.a), tuple(self.b), self.t_min,
                 self.t_max, self.radius_raw, self.radius, self.max_dist, self.pca_coeff, tuple(self.pca_eigenvalues),
-                self.length)
+                self.length, tuple(self.a_world), tuple(self.b_world), self.world_status)
+
+
+class Pose(C.Structure):
+    """Sensor pose for drone2WorldSeg / heighSegmentCutoff (node.cpp:429-470): q = (w, x, y, z)."""
+    _fields_ = [("q", C.c_double * 4), ("position", C.c_double * 3), ("floor_trim_height", C.c_double)]
+
+    @classmethod
+    def make(cls, q_wxyz, position, floor_trim_height):
+        p = cls()
+        for k in range(4):
+            p.q[k] = float(q_wxyz[k])
+        for k in range(3):
+            p.position[k] = float(position[k])
+        p.floor_trim_height = float(floor_trim_height)
+        return p
 
 
 @dataclass
@@ -238,9 +255,10 @@ class Oracle(_Base):
         rc = self.lib.h3do_segment_test(_dp(p), C.c_size_t(n), _dp(sh), _dp(aa), _dp(bb), C.byref(cfg), C.byref(seg))
         return rc, seg
 
-    def segments(self, xyz, trace, cfg):
+    def segments(self, xyz, trace, cfg, pose=None):
         """Post-tests of every accepted line of a trace of hough3dlines(xyz, ...): (rc, [Segment]).
-        rc 1 = the reference would return 1 at the last segment of the list (status 3)."""
+        rc 1 = the reference would return 1 at the last segment of the list (status 3).
+        pose: also drone2WorldSeg + heighSegmentCutoff (node.cpp:429-470) on the kept segments."""
         p, _ = _pts(xyz)
         p = p.reshape(-1, 3)
         centred = p - trace.shift            # PointCloud::shiftToOrigin, lib/pointcloud.cpp:18-26
@@ -250,6 +268,8 @@ class Oracle(_Base):
                 continue
             rc, seg = self.segment_test(centred[it.inliers2], trace.shift, it.a2, it.b2, cfg)
             seg.iter = k
+            if pose is not None:
+                self.lib.h3do_segment_to_world(C.byref(pose), C.byref(seg))
             out.append(seg)
             if rc:
                 return 1, out

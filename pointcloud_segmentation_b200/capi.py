@@ -76,12 +76,29 @@ class Segment(C.Structure):
     _fields_ = [("iter", C.c_uint32), ("status", C.c_uint32), ("n_points", C.c_uint32), ("min_nb_points", C.c_int32),
                 ("a", C.c_double * 3), ("b", C.c_double * 3), ("t_min", C.c_double), ("t_max", C.c_double),
                 ("radius_raw", C.c_double), ("radius", C.c_double), ("max_dist", C.c_double),
-                ("pca_coeff", C.c_double), ("pca_eigenvalues", C.c_double * 3), ("length", C.c_double)]
+                ("pca_coeff", C.c_double), ("pca_eigenvalues", C.c_double * 3), ("length", C.c_double),
+                ("a_world", C.c_double * 3), ("b_world", C.c_double * 3), ("world_status", C.c_uint32),
+                ("pad_", C.c_uint32)]
 
     def as_tuple(self):
         return (self.iter, self.status, self.n_points, self.min_nb_points, tuple(self.a), tuple(self.b), self.t_min,
                 self.t_max, self.radius_raw, self.radius, self.max_dist, self.pca_coeff, tuple(self.pca_eigenvalues),
-                self.length)
+                self.length, tuple(self.a_world), tuple(self.b_world), self.world_status)
+
+
+class Pose(C.Structure):
+    """Sensor pose for drone2WorldSeg / heighSegmentCutoff (node.cpp:429-470): q = (w, x, y, z)."""
+    _fields_ = [("q", C.c_double * 4), ("position", C.c_double * 3), ("floor_trim_height", C.c_double)]
+
+    @classmethod
+    def make(cls, q_wxyz, position, floor_trim_height):
+        p = cls()
+        for k in range(4):
+            p.q[k] = float(q_wxyz[k])
+        for k in range(3):
+            p.position[k] = float(position[k])
+        p.floor_trim_height = float(floor_trim_height)
+        return p
 
 
 def lib():
@@ -313,6 +330,10 @@ class Pipeline:
         """Run the segment post-tests (wrap.h:261-337) with every following frame; None switches them off."""
         check(lib().h3d_pipeline_enable_segments(self._p, C.byref(cfg) if cfg is not None else None))
 
+    def set_pose(self, pose):
+        """Sensor pose for the drone -> world step of the post-tests (node.cpp:429-470); None: off."""
+        check(lib().h3d_pipeline_set_pose(self._p, C.byref(pose) if pose is not None else None))
+
     def segments(self):
         """(rc of the reference's hough3dlines, [Segment]) of the last frame."""
         n = C.c_size_t(0)
@@ -435,11 +456,12 @@ def orthogonal_lsq(xyz):
     return rc.value, np.array(aa[:]), np.array(bb[:])
 
 
-def segment_test(y_centred, shift, a_, b_, cfg):
-    """wrap.h:261-337 on one line from host buffers -> Segment."""
+def segment_test(y_centred, shift, a_, b_, cfg, pose=None):
+    """wrap.h:261-337 on one line from host buffers (+ node.cpp:429-470 with a pose) -> Segment."""
     _, p, n = _pts(y_centred)
     seg = Segment()
-    check(lib().h3d_segment_test(p, n, _d3(shift), _d3(a_), _d3(b_), C.byref(cfg), C.byref(seg)))
+    check(lib().h3d_segment_test_pose(p, n, _d3(shift), _d3(a_), _d3(b_), C.byref(cfg),
+                                      C.byref(pose) if pose is not None else None, C.byref(seg)))
     return seg
 
 

@@ -782,6 +782,8 @@ struct FrameCtx {
   // segment post-tests (h3d_pipeline_enable_segments)
   bool seg_on = false;
   h3d_segment_config seg_cfg{};
+  h3d_pose seg_pose{};
+  bool seg_pose_on = false;
   h3d_segment *seg_dev = nullptr, *seg_host = nullptr;   // iters_cap records each; host copy pinned
   size_t seg_cap = 0, seg_n = 0, seg_grid = 0;
   double seg_ns[3] = {0, 0, 0};          // what shiftToOrigin subtracted in the current frame
@@ -914,6 +916,7 @@ int enqueue_segments(FrameCtx &f, size_t grid) {
   sa.src = f.src; sa.stride = f.src_stride; sa.src_is_float = f.src_is_float;
   for (int c = 0; c < 3; ++c) { sa.ns[c] = f.seg_ns[c]; sa.shift[c] = f.seg_ns[c]; }   // X.shift = 0 + newshift
   sa.cfg = f.seg_cfg; sa.scr = f.seg_scr; sa.scr_n = f.seg_scr_n; sa.out = f.seg_dev;
+  sa.pose = f.seg_pose; sa.pose_on = f.seg_pose_on ? 1 : 0;
   segment_tests_kernel<<<(unsigned)grid, kSegThreads, 0, f.hg->stream>>>(sa);
   note_launches(1);
   H3D_CUDA(cudaGetLastError());
@@ -1441,8 +1444,21 @@ extern "C" int h3d_pipeline_segments(h3d_pipeline *p, h3d_segment *segs, size_t 
   return H3D_OK;
 }
 
+extern "C" int h3d_pipeline_set_pose(h3d_pipeline *p, const h3d_pose *pose) {
+  if (!p) return fail(H3D_ERR_ARG, "bad argument");
+  p->f.seg_pose_on = pose != nullptr;
+  if (pose) p->f.seg_pose = *pose;
+  return H3D_OK;
+}
+
 extern "C" int h3d_segment_test(const double *y_xyz, size_t n, const double shift[3], const double a[3],
                                 const double b[3], const h3d_segment_config *cfg, h3d_segment *out) {
+  return h3d_segment_test_pose(y_xyz, n, shift, a, b, cfg, nullptr, out);
+}
+
+extern "C" int h3d_segment_test_pose(const double *y_xyz, size_t n, const double shift[3], const double a[3],
+                                     const double b[3], const h3d_segment_config *cfg, const h3d_pose *pose,
+                                     h3d_segment *out) {
   if (!y_xyz || !n || !shift || !a || !b || !out || n > 0x7FFFFFF0u) return fail(H3D_ERR_ARG, "bad argument");
   if (!segment_config_ok(cfg)) return fail(H3D_ERR_ARG, "radius_sizes needs 1..8 entries");
   double *pts = nullptr, *scr = nullptr;
@@ -1465,6 +1481,8 @@ extern "C" int h3d_segment_test(const double *y_xyz, size_t n, const double shif
     sa.src = pts; sa.stride = 3; sa.src_is_float = 0;
     for (int c = 0; c < 3; ++c) { sa.ns[c] = 0.0; sa.shift[c] = shift[c]; }   // y - 0.0 == y
     sa.cfg = *cfg; sa.scr = scr; sa.scr_n = n; sa.out = seg;
+    sa.pose_on = pose ? 1 : 0;
+    if (pose) sa.pose = *pose; else memset(&sa.pose, 0, sizeof sa.pose);
     segment_tests_kernel<<<1, kSegThreads>>>(sa);
     note_launches(1);
     e = cudaGetLastError();

@@ -8,7 +8,7 @@
 //
 // The reference copies Y.points into Eigen vectors line by line on the host; here the inlier
 // index lists of the loop are still in device memory (the index pool), so one launch with one
-// CTA per iteration record tests every line of the frame and only the 144-byte records go back.
+// CTA per iteration record tests every line of the frame and only the 200-byte records go back.
 //
 // Arithmetic restated (same as oracle/h3d_oracle.c h3do_segment_test):
 //   * Eigen fixed-size Vector3d: sums of three terms reduce as x0 + (x1 + x2); no FMA contraction
@@ -43,6 +43,8 @@ struct SegArgs {
   double ns[3];              // what shiftToOrigin subtracted (lib/pointcloud.cpp:18-26)
   double shift[3];           // X.shift
   h3d_segment_config cfg;
+  h3d_pose pose;             // drone -> world (node.cpp:429-470)
+  int pose_on;
   double *scr;               // 5 * scr_n doubles: t, |a + t b|, sorted |a + t b|, then 3 * scr_n floats (points)
   size_t scr_n;
   h3d_segment *out;
@@ -60,6 +62,27 @@ __device__ __forceinline__ void seg_point(const SegArgs &A, unsigned k, double p
     const double v = A.src_is_float ? (double)static_cast<const float *>(A.src)[e] : static_cast<const double *>(A.src)[e];
     p[c] = __dadd_rn(__dsub_rn(v, A.ns[c]), A.shift[c]);
   }
+}
+
+// drone2WorldSeg + heighSegmentCutoff (node.cpp:429-470) on one kept segment.
+// R = Eigen::Quaterniond::toRotationMatrix(); R*v per row as x0 + (x1 + x2), then + position.
+__device__ __forceinline__ void seg_to_world(const h3d_pose &P, h3d_segment &s) {
+  const double w = P.q[0], x = P.q[1], y = P.q[2], z = P.q[3];
+  const double tx = __dmul_rn(2.0, x), ty = __dmul_rn(2.0, y), tz = __dmul_rn(2.0, z);
+  const double twx = __dmul_rn(tx, w), twy = __dmul_rn(ty, w), twz = __dmul_rn(tz, w);
+  const double txx = __dmul_rn(tx, x), txy = __dmul_rn(ty, x), txz = __dmul_rn(tz, x);
+  const double tyy = __dmul_rn(ty, y), tyz = __dmul_rn(tz, y), tzz = __dmul_rn(tz, z);
+  const double R[3][3] = {{__dsub_rn(1.0, __dadd_rn(tyy, tzz)), __dsub_rn(txy, twz), __dadd_rn(txz, twy)},
+                          {__dadd_rn(txy, twz), __dsub_rn(1.0, __dadd_rn(txx, tzz)), __dsub_rn(tyz, twx)},
+                          {__dsub_rn(txz, twy), __dadd_rn(tyz, twx), __dsub_rn(1.0, __dadd_rn(txx, tyy))}};
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    s.a_world[i] = __dadd_rn(seg_dot3(R[i][0], R[i][1], R[i][2], s.a[0], s.a[1], s.a[2]), P.position[i]);
+    s.b_world[i] = seg_dot3(R[i][0], R[i][1], R[i][2], s.b[0], s.b[1], s.b[2]);
+  }
+  const double z1 = __dadd_rn(__dmul_rn(s.t_min, s.b_world[2]), s.a_world[2]);
+  const double z2 = __dadd_rn(__dmul_rn(s.t_max, s.b_world[2]), s.a_world[2]);
+  s.world_status = (z1 > P.floor_trim_height || z2 > P.floor_trim_height) ? 1u : 2u;
 }
 
 __device__ __forceinline__ double seg_block_max(double v, double *red) {
@@ -257,6 +280,7 @@ __global__ void __launch_bounds__(kSegThreads) segment_tests_kernel(const SegArg
     // points.size() > min_nb_points_seg: size_t against int, the int converts to unsigned
     const bool keep = s.pca_coeff > A.cfg.min_pca_coeff && (unsigned long long)n > (unsigned long long)(long long)min_nb;
     s.status = keep ? 0u : 2u;
+    if (keep && A.pose_on) seg_to_world(A.pose, s);
     *S = s;
   }
 }

@@ -12,7 +12,7 @@ def _cfg(mod, radii=(0.05,), min_pca=0.995):
 
 
 def test_layouts_agree(oracle_mod):
-    assert C.sizeof(capi.Segment) == C.sizeof(oracle_mod.Segment) == 144
+    assert C.sizeof(capi.Segment) == C.sizeof(oracle_mod.Segment) == 200
     assert C.sizeof(capi.SegmentConfig) == C.sizeof(oracle_mod.SegmentConfig) == 96
     for a, b in zip(capi.Segment._fields_, oracle_mod.Segment._fields_):
         assert a[0] == b[0] and getattr(capi.Segment, a[0]).offset == getattr(oracle_mod.Segment, b[0]).offset
@@ -63,6 +63,35 @@ def test_oracle_segment_quirks(oracle, oracle_mod):
     assert rc == 1 and s3.status == 3
 
 
+def test_oracle_world_transform_against_scipy(oracle, oracle_mod):
+    """drone2WorldSeg + heighSegmentCutoff (node.cpp:429-470)."""
+    from scipy.spatial.transform import Rotation
+    rng = np.random.default_rng(2)
+    shift = np.zeros(3)
+    a = np.array([0.2, -0.1, 0.4]); b = np.array([0.6, 0.0, 0.8])
+    y = a + np.linspace(-1, 1, 80)[:, None] * b + rng.normal(0, 0.01, (80, 3))
+    kept = trimmed = 0
+    for k in range(40):
+        q = rng.normal(size=4); q /= np.linalg.norm(q)
+        pos = rng.uniform(-2, 2, 3)
+        floor = rng.uniform(-1.5, 1.5)
+        rc, s = oracle.segment_test(y, shift, a, b, _cfg(oracle_mod, (0.05,), 0.5))
+        assert rc == 0 and s.status == 0
+        pose = oracle_mod.Pose.make(q, pos, floor)
+        oracle.lib.h3do_segment_to_world(C.byref(pose), C.byref(s))
+        R = Rotation.from_quat([q[1], q[2], q[3], q[0]]).as_matrix()          # scipy: x, y, z, w
+        assert np.allclose(list(s.a_world), R @ a + pos, atol=1e-12)
+        assert np.allclose(list(s.b_world), R @ b, atol=1e-12)
+        z1 = s.t_min * s.b_world[2] + s.a_world[2]; z2 = s.t_max * s.b_world[2] + s.a_world[2]
+        assert s.world_status == (1 if (z1 > floor or z2 > floor) else 2)
+        kept += s.world_status == 1; trimmed += s.world_status == 2
+    assert kept and trimmed
+    # a rejected line is not transformed
+    rc, s = oracle.segment_test(y, shift, a, b, _cfg(oracle_mod, (0.05,), 0.99999))
+    oracle.lib.h3do_segment_to_world(C.byref(oracle_mod.Pose.make([1, 0, 0, 0], [0, 0, 0], 0.0)), C.byref(s))
+    assert s.status == 2 and s.world_status == 0 and list(s.a_world) == [0.0, 0.0, 0.0]
+
+
 def test_oracle_fixed_eigensolver(oracle):
     rng = np.random.default_rng(3)
     for _ in range(200):
@@ -78,5 +107,6 @@ def test_oracle_fixed_eigensolver(oracle):
 
 def test_library_exports_segment_entry_points():
     lib = C.CDLL(capi.LIB_PATH)
-    for name in ("h3d_pipeline_enable_segments", "h3d_pipeline_segments", "h3d_segment_test"):
+    for name in ("h3d_pipeline_enable_segments", "h3d_pipeline_segments", "h3d_segment_test", "h3d_segment_test_pose",
+                 "h3d_pipeline_set_pose", "h3d_pipeline_run_cloud2"):
         assert hasattr(lib, name)

@@ -106,3 +106,38 @@ def test_segment_test_host_form_and_edges(h3d, oracle, oracle_mod):
     assert rc == 1 and want.status == 3 and got.status == 3
     with pytest.raises(h3d.H3dError):
         h3d.segment_test(pts, shift, a, b0, h3d.SegmentConfig.make(0.05, 0.9, 1.5, []))
+
+
+def test_world_transform_and_height_cutoff(h3d, oracle, oracle_mod):
+    """node.cpp:429-470 on the kept segments: pipeline form and host form, several poses."""
+    rng = np.random.default_rng(8)
+    frame = synth.tof_frame(pose=(-1.1, 0.0, 0.8, 0.0), seed=2)
+    filt = oracle.prefilter(frame, synth.WINDOW, float(synth.LEAF)).astype(np.float64)
+    trace = oracle.hough3dlines(filt, 6, synth.OPT_DX, 12, 20, mode=0)
+    pipe = h3d.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frame.shape[0])
+    pipe.enable_segments(_cfg(h3d, (0.05,), 0.99))
+    seen = set()
+    for k in range(4):
+        q = rng.normal(size=4); q /= np.linalg.norm(q)
+        if k == 0:
+            q = np.array([0.9238795325112867, 0.0, 0.0, 0.3826834323650898])     # yaw 45 deg
+        pos, floor = rng.uniform(-1, 1, 3), [0.3, -0.2, 0.8, 0.0][k]
+        pipe.set_pose(h3d.Pose.make(q, pos, floor))
+        pipe.run(frame)
+        rc_got, got = pipe.segments()
+        rc_want, want = oracle.segments(filt, trace, _cfg(oracle_mod, (0.05,), 0.99), oracle_mod.Pose.make(q, pos, floor))
+        assert rc_got == rc_want
+        _same(got, want)
+        seen |= {s.world_status for s in want}
+        # host form on the first kept line
+        s0 = next(s for s in want if s.status == 0)
+        it = trace.iters[s0.iter]
+        one = h3d.segment_test((filt - trace.shift)[it.inliers2], trace.shift, it.a2, it.b2, _cfg(h3d, (0.05,), 0.99),
+                               h3d.Pose.make(q, pos, floor))
+        assert _bits(one)[1:] == _bits(s0)[1:]
+    assert {0, 1, 2} <= seen
+    pipe.set_pose(None)
+    pipe.run(frame)
+    _, got = pipe.segments()
+    assert all(s.world_status == 0 for s in got)
+    pipe.close()
