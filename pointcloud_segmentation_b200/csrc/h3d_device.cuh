@@ -170,6 +170,14 @@ __device__ __noinline__ unsigned vote_cell_checked(const DirCoef *coef_j, double
   return vote_cell_exact(coef_j, max_x, dx, num_x, px, py, pz);
 }
 
+// same, reading everything it needs from the kernel's __grid_constant__ HoughDev: the call site
+// passes one pointer and three coordinates, so the hot loop keeps no register or constant load
+// alive for the rare path
+__device__ __noinline__ unsigned vote_cell_checked_h(const HoughDev *h, int l, double px, double py, double pz) {
+  return vote_cell_checked(h->coef + h->dir_begin + l, h->inv_s, h->kmagic, h->max_x, h->dx, h->num_x, h->fast_ok,
+                           px, py, pz);
+}
+
 // cell of one vote; the caller tests cell < plane_cells (0xFFFFFFFF from the exact path fails it)
 __device__ __forceinline__ unsigned vote_cell(const HoughDev &h, const FastCoef &f, int j, double px,
                                               double py, double pz) {

@@ -301,8 +301,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
               for (int c = 0; c < CH; ++c) {   // unrolled: register arrays must not be indexed dynamically
                 const int p = p0 + c;
                 if (p < P) {
-                  const unsigned cell = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
-                                                          h.fast_ok, px[p], py[p], pz[p]);
+                  const unsigned cell = vote_cell_checked_h(&h, l, px[p], py[p], pz[p]);
                   off[c] = cell < plane_cells ? 4u * cell : drop_off;
                 }
               }
@@ -327,8 +326,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
               else if (BOUNDED) o = vote_off_bounded(f, kmagic, row4, px[p], py[p], pz[p], g1);
               else o = 4u * vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], g1, h1);
               if (ABLATE != 2 && (batch_unsure(g1, h1) | !h.fast_ok)) {
-                const unsigned cell = vote_cell_checked(h.coef + h.dir_begin + l, inv_s, kmagic, h.max_x, h.dx, h.num_x,
-                                                        h.fast_ok, px[p], py[p], pz[p]);
+                const unsigned cell = vote_cell_checked_h(&h, l, px[p], py[p], pz[p]);
                 o = cell < plane_cells ? 4u * cell : drop_off;
               }
               // an empty lane of a partly filled slot votes into the pad word
@@ -365,8 +363,8 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
 
 template <int P, int ABLATE, bool BOUNDED = false>
 __global__ void __launch_bounds__(kResThreads, 1)
-vote_resident_kernel(const HoughDev h, const int *__restrict__ list, const int *__restrict__ count_ptr,
-                     int count_imm) {
+vote_resident_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ list,
+                     const int *__restrict__ count_ptr, int count_imm) {
   extern __shared__ __align__(16) unsigned planes[];
   __shared__ __align__(16) ResShared sh;
   const int count = count_ptr ? *count_ptr : count_imm;
