@@ -182,33 +182,42 @@ vote_kernel(const HoughDev h, const int *__restrict__ list, const int *__restric
 constexpr int kResThreads = 512;
 constexpr int kResWarps = kResThreads / 32;
 
-// (max, first max cell) of a plane, zeroing it; quads whose maximum cannot beat the
-// running best cost 6 instructions
-// cells >= plane_cells (slack of the BOUNDED vote form) are zeroed but never counted
+// (max, first max cell) of this thread's quads of a plane, zeroing them.  Three quads are loaded
+// before any is examined (independent LDS.128 in flight instead of a load -> test -> branch chain
+// per quad).  Cells >= plane_cells (slack of the BOUNDED vote form) are zeroed but never counted.
+// Quads are visited in ascending order and the update is strict, so bcell is the thread's first
+// maximum; the warp / CTA reductions of the caller keep the lowest cell among equal maxima.
 template <int THREADS>
-__device__ __forceinline__ unsigned long long scan_plane_fast(unsigned *plane, unsigned quads, int t,
-                                                              unsigned plane_cells) {
+__device__ __forceinline__ void scan_plane_local(unsigned *plane, unsigned quads, int t, unsigned plane_cells,
+                                                 unsigned &best, unsigned &bcell) {
   uint4 *p4 = reinterpret_cast<uint4 *>(plane);
-  unsigned best = 0, bcell = 0;
-  for (unsigned q = t; q < quads; q += THREADS) {
-    uint4 v = p4[q];
-    if ((v.x | v.y | v.z | v.w) == 0) continue;
-    p4[q] = make_uint4(0, 0, 0, 0);
-    if (4 * q + 3 >= plane_cells) {
-      if (4 * q >= plane_cells) v.x = 0;
-      if (4 * q + 1 >= plane_cells) v.y = 0;
-      if (4 * q + 2 >= plane_cells) v.z = 0;
-      v.w = 0;
+  best = 0; bcell = 0;
+  for (unsigned q0 = t; q0 < quads; q0 += 3 * THREADS) {
+    uint4 v[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const unsigned q = q0 + u * THREADS;
+      v[u] = q < quads ? p4[q] : make_uint4(0, 0, 0, 0);
     }
-    const unsigned m4 = max(max(v.x, v.y), max(v.z, v.w));
-    if (m4 > best) {
-      best = m4;
-      bcell = 4 * q + (v.x == m4 ? 0u : v.y == m4 ? 1u : v.z == m4 ? 2u : 3u);
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const unsigned q = q0 + u * THREADS;
+      uint4 w = v[u];
+      if ((w.x | w.y | w.z | w.w) == 0) continue;
+      p4[q] = make_uint4(0, 0, 0, 0);
+      if (4 * q + 3 >= plane_cells) {
+        if (4 * q >= plane_cells) w.x = 0;
+        if (4 * q + 1 >= plane_cells) w.y = 0;
+        if (4 * q + 2 >= plane_cells) w.z = 0;
+        w.w = 0;
+      }
+      const unsigned m4 = max(max(w.x, w.y), max(w.z, w.w));
+      if (m4 > best) {
+        best = m4;
+        bcell = 4 * q + (w.x == m4 ? 0u : w.y == m4 ? 1u : w.z == m4 ? 2u : 3u);
+      }
     }
   }
-  const unsigned m = __reduce_max_sync(0xFFFFFFFFu, best);
-  const unsigned cm = __reduce_min_sync(0xFFFFFFFFu, best == m ? bcell : 0xFFFFFFFFu);
-  return ((unsigned long long)m << 32) | (0xFFFFFFFFu - cm);
 }
 
 constexpr int kResG = 4;   // directions voted per barrier phase
@@ -338,12 +347,20 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
         }
       }
     }
-    if (prev_any) {
-#pragma unroll 1
-      for (int g = 0; g < G; ++g) {
-        const unsigned long long key =
-            scan_plane_fast<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, quads, tid, plane_cells);
-        if (lane == 0) sh.warp_best[slot ^ 1][g][warp] = key;
+    if (prev_any) {   // scan the previous group's planes: local maxima first, then 2*G independent reductions
+      unsigned best[G], bcell[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g)
+        scan_plane_local<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, quads, tid, plane_cells, best[g], bcell[g]);
+      unsigned m[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g) m[g] = __reduce_max_sync(0xFFFFFFFFu, best[g]);
+#pragma unroll
+      for (int g = 0; g < G; ++g) bcell[g] = __reduce_min_sync(0xFFFFFFFFu, best[g] == m[g] ? bcell[g] : 0xFFFFFFFFu);
+      if (lane == 0) {
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+          sh.warp_best[slot ^ 1][g][warp] = ((unsigned long long)m[g] << 32) | (0xFFFFFFFFu - bcell[g]);
       }
     }
     if (tid < G) cp_async_wait_all();
