@@ -273,6 +273,21 @@ int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const float *cons
                    h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
                    h3d_result *results);
 
+/* how the host thread of a frame waits for the device: 0 (default) = cudaStreamSynchronize, which
+ * spins -- lowest latency; 1 = a blocking event, the thread sleeps -- use it when more pipelines
+ * are in flight than the host has cores (several GPUs x frames in flight).  Process-wide; returns
+ * the previous setting. */
+int h3d_set_wait_mode(int blocking);
+
+/* same, also collecting the segment records of every frame (the pipelines must have
+ * h3d_pipeline_enable_segments on): segments + i*max_segments, n_segments[i] (may exceed
+ * max_segments), rc_ref[i] = what the reference's hough3dlines returns for frame i (may be NULL). */
+int h3d_replay_run_segments(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw,
+                            const size_t *n_points, size_t stride, size_t n_frames, int frames_on_device,
+                            h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                            h3d_result *results, h3d_segment *segments, size_t max_segments,
+                            uint32_t *n_segments, int *rc_ref);
+
 /* measurement hook: phase stamps of the fused loop kernel.  out == NULL: enable for `iters`
  * iterations (0 disables).  out != NULL: copy the stamps of the last frame,
  * [iteration][cta][n_slots] globaltimer nanoseconds (slot 8: re-voted planes + 1). */

@@ -392,6 +392,23 @@ class Replay:
         self.pool = np.zeros(self.pool_cap * max_frames, dtype=np.uint32)
         self.results = (Result * max_frames)()
         self._handles = (C.c_void_p * n_pipes)(*[p._p for p in self.pipes])
+        self.segments = None
+
+    def enable_segments(self, cfg, pose=None):
+        """Segment post-tests (+ world transform with a pose) on every pipeline; run() then fills
+        self.segments / self.n_segments / self.rc_ref per frame."""
+        for p in self.pipes:
+            p.enable_segments(cfg)
+            p.set_pose(pose)
+        if cfg is None:
+            self.segments = None
+        else:
+            self.segments = (Segment * (self.max_iters * self.max_frames))()
+            self.n_segments = (C.c_uint32 * self.max_frames)()
+            self.rc_ref = (C.c_int * self.max_frames)()
+
+    def frame_segments(self, i):
+        return [self.segments[i * self.max_iters + k] for k in range(min(self.n_segments[i], self.max_iters))]
 
     def run(self, ptrs, n_points, stride, on_device):
         """ptrs: integer addresses of the frames (host or device); returns the ctypes Result array."""
@@ -399,6 +416,13 @@ class Replay:
         assert n <= self.max_frames
         raw = (C.c_void_p * n)(*ptrs)
         npts = (C.c_size_t * n)(*n_points)
+        if self.segments is not None:
+            check(lib().h3d_replay_run_segments(self._handles, C.c_size_t(len(self.pipes)), raw, npts, C.c_size_t(stride),
+                                                C.c_size_t(n), C.c_int(1 if on_device else 0), self.iters,
+                                                C.c_size_t(self.max_iters), self.pool.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                                C.c_size_t(self.pool_cap), self.results, self.segments,
+                                                C.c_size_t(self.max_iters), self.n_segments, self.rc_ref))
+            return self.results
         check(lib().h3d_replay_run(self._handles, C.c_size_t(len(self.pipes)), raw, npts, C.c_size_t(stride),
                                    C.c_size_t(n), C.c_int(1 if on_device else 0), self.iters,
                                    C.c_size_t(self.max_iters), self.pool.ctypes.data_as(C.POINTER(C.c_uint32)),
@@ -463,6 +487,11 @@ def segment_test(y_centred, shift, a_, b_, cfg, pose=None):
     check(lib().h3d_segment_test_pose(p, n, _d3(shift), _d3(a_), _d3(b_), C.byref(cfg),
                                       C.byref(pose) if pose is not None else None, C.byref(seg)))
     return seg
+
+
+def set_wait_mode(blocking):
+    """0: host threads spin on their stream (lowest latency); 1: they sleep on a blocking event."""
+    return lib().h3d_set_wait_mode(C.c_int(1 if blocking else 0))
 
 
 def set_fused(on):

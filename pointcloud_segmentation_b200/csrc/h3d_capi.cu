@@ -775,6 +775,7 @@ struct FrameCtx {
   LoopState *st_host = nullptr;   // pinned
   PrepOut *prep_host = nullptr;   // pinned
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // start, prep done, first vote done, end, first vote start, loop kernels done
+  cudaEvent_t ev_block = nullptr;   // blocking-sync event of frame_wait()
   float us[4] = {0, 0, 0, 0};
   bool timed = false;   // the last frame ran to the end (all events recorded)
   bool fused = false;   // the last frame ran in the fused persistent kernel
@@ -806,12 +807,28 @@ struct FrameCtx {
     gbest = nullptr; sync_dev = nullptr; sync_host = nullptr; gbest_cap = 0;
     cudaFreeHost(st_host); cudaFreeHost(prep_host);
     for (auto &e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
+    if (ev_block) { cudaEventDestroy(ev_block); ev_block = nullptr; }
     in_dev = nullptr; orig = nullptr; orig2 = nullptr; flags = nullptr; yidx = nullptr; ypx = ypy = ypz = nullptr;
     iters_dev = nullptr; pool_dev = nullptr; st_dev = nullptr; prep_dev = nullptr;
     st_host = nullptr; prep_host = nullptr;
     cap = iters_cap = pool_cap = in_bytes = 0; granularity = ~0u;
   }
 };
+
+// how a host thread waits for its frame's stream: 0 = cudaStreamSynchronize (spins: lowest
+// latency), 1 = a blocking event (the thread sleeps: for more pipelines than host cores)
+std::atomic<int> g_wait_mode{0};
+
+cudaError_t frame_wait(FrameCtx &f) {
+  cudaStream_t s = f.hg->stream;
+  if (g_wait_mode.load(std::memory_order_relaxed) == 0) return cudaStreamSynchronize(s);
+  if (!f.ev_block) {
+    const cudaError_t e = cudaEventCreateWithFlags(&f.ev_block, cudaEventBlockingSync | cudaEventDisableTiming);
+    if (e != cudaSuccess) return e;
+  }
+  const cudaError_t e = cudaEventRecord(f.ev_block, s);
+  return e != cudaSuccess ? e : cudaEventSynchronize(f.ev_block);
+}
 
 int frame_ensure(FrameCtx &f, unsigned g, size_t n, size_t in_bytes, size_t max_iters, size_t pool_cap) {
   if (!f.hg || f.granularity != g) {
@@ -1039,7 +1056,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   cudaStream_t s = h->stream;
   H3D_CUDA(cudaMemcpyAsync(f.prep_host, f.prep_dev, sizeof(PrepOut), cudaMemcpyDeviceToHost, s));
   H3D_CUDA(cudaEventRecord(f.ev[1], s));
-  H3D_CUDA(cudaStreamSynchronize(s));
+  H3D_CUDA(frame_wait(f));
   const PrepOut P = *f.prep_host;
   const size_t n = (size_t)P.n;
   res->n_input = (uint32_t)n;
@@ -1093,7 +1110,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   bool fused = false;
   H3D_TRY(try_launch_fused(f, lb, opt_nlines, opt_dx, &fused));
   if (fused) {
-    H3D_CUDA(cudaStreamSynchronize(s));
+    H3D_CUDA(frame_wait(f));
     if (f.sync_host[1]) {   // an inlier set larger than the shared-memory scratch: redo with the general loop
       fused = false;
       *f.st_host = st;
@@ -1115,7 +1132,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
       for (int it = 0; it < 8 && rc == H3D_OK; ++it) rc = enqueue_iteration(f, hd, lb);
       if (rc != H3D_OK) break;
       if (cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
-          cudaStreamSynchronize(s) != cudaSuccess) { rc = fail(H3D_ERR_CUDA, "loop state read-back failed"); break; }
+          frame_wait(f) != cudaSuccess) { rc = fail(H3D_ERR_CUDA, "loop state read-back failed"); break; }
       if (f.st_host->done) break;
     }
   }
@@ -1123,7 +1140,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
     H3D_CUDA(cudaEventRecord(f.ev[5], s));
     H3D_TRY(enqueue_segments(f, opt_nlines > 0 ? (size_t)opt_nlines : f.iters_cap));
     H3D_CUDA(cudaMemcpyAsync(f.st_host, f.st_dev, sizeof(LoopState), cudaMemcpyDeviceToHost, s));
-    H3D_CUDA(cudaStreamSynchronize(s));
+    H3D_CUDA(frame_wait(f));
   }
   }
   hd.n_dev = nullptr;
@@ -1142,7 +1159,7 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
     f.seg_n = m;
   }
   H3D_CUDA(cudaEventRecord(f.ev[3], s));
-  H3D_CUDA(cudaStreamSynchronize(s));
+  H3D_CUDA(frame_wait(f));
   f.timed = true;
   hd.n = 0;
   return H3D_OK;
@@ -1570,8 +1587,18 @@ extern "C" int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const 
                               const size_t *n_points, size_t stride, size_t n_frames, int frames_on_device,
                               h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
                               h3d_result *results) {
+  return h3d_replay_run_segments(pipes, n_pipes, raw, n_points, stride, n_frames, frames_on_device, iters, max_iters,
+                                 pool, pool_cap, results, nullptr, 0, nullptr, nullptr);
+}
+
+extern "C" int h3d_replay_run_segments(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw,
+                                       const size_t *n_points, size_t stride, size_t n_frames, int frames_on_device,
+                                       h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                                       h3d_result *results, h3d_segment *segments, size_t max_segments,
+                                       uint32_t *n_segments, int *rc_ref) {
   if (!pipes || n_pipes == 0 || (!raw && n_frames) || (!n_points && n_frames) || !results)
     return fail(H3D_ERR_ARG, "bad argument");
+  if (segments && !n_segments) return fail(H3D_ERR_ARG, "segments needs n_segments");
   for (size_t k = 0; k < n_pipes; ++k) if (!pipes[k]) return fail(H3D_ERR_ARG, "null pipeline");
   std::atomic<size_t> next{0};
   std::atomic<int> first_rc{H3D_OK};
@@ -1583,9 +1610,16 @@ extern "C" int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const 
       if (i >= n_frames || first_rc.load() != H3D_OK) break;
       h3d_iter *it = iters ? iters + i * max_iters : nullptr;
       uint32_t *pl = pool ? pool + i * pool_cap : nullptr;
-      const int rc = frames_on_device
+      int rc = frames_on_device
                          ? h3d_pipeline_run_dev(pipes[t], raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i])
                          : h3d_pipeline_run(pipes[t], raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i]);
+      if (rc == H3D_OK && segments) {
+        size_t m = 0;
+        int ref = 0;
+        rc = h3d_pipeline_segments(pipes[t], segments + i * max_segments, max_segments, &m, &ref);
+        n_segments[i] = (uint32_t)m;
+        if (rc_ref) rc_ref[i] = ref;
+      }
       if (rc != H3D_OK) {
         int expected = H3D_OK;
         if (first_rc.compare_exchange_strong(expected, rc)) {
@@ -1603,6 +1637,10 @@ extern "C" int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const 
   for (auto &th : threads) th.join();
   if (first_rc.load() != H3D_OK) { set_error(err_text); return first_rc.load(); }
   return H3D_OK;
+}
+
+extern "C" int h3d_set_wait_mode(int blocking) {
+  return g_wait_mode.exchange(blocking ? 1 : 0);
 }
 
 extern "C" int h3d_pipeline_set_sm_share(h3d_pipeline *p, int n_ctas) {

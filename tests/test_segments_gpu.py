@@ -141,3 +141,20 @@ def test_world_transform_and_height_cutoff(h3d, oracle, oracle_mod):
     _, got = pipe.segments()
     assert all(s.world_status == 0 for s in got)
     pipe.close()
+
+
+def test_replay_collects_segments_of_every_frame(h3d, oracle, oracle_mod):
+    """Frames in flight (h3d_replay_run_segments): the records of each frame, not only the last."""
+    frames = [synth.tof_frame(pose=(-1.1, 0.1 * k, 0.8, 0.05 * k), seed=20 + k).astype(np.float32) for k in range(5)]
+    rep = h3d.Replay(3, 40, 4, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 8, max_raw_points=frames[0].shape[0],
+                     max_frames=len(frames))
+    pose_args = ([0.9238795325112867, 0.0, 0.0, 0.3826834323650898], [0.5, -0.2, 1.0], 0.3)
+    rep.enable_segments(_cfg(h3d, (0.05,), 0.99), h3d.Pose.make(*pose_args))
+    rep.run([f.ctypes.data for f in frames], [f.shape[0] for f in frames], frames[0].shape[1], on_device=False)
+    for i, f in enumerate(frames):
+        filt = oracle.prefilter(f, synth.WINDOW, float(synth.LEAF)).astype(np.float64)
+        trace = oracle.hough3dlines(filt, 4, synth.OPT_DX, 12, 8, mode=0)
+        rc_want, want = oracle.segments(filt, trace, _cfg(oracle_mod, (0.05,), 0.99), oracle_mod.Pose.make(*pose_args))
+        assert rep.rc_ref[i] == rc_want
+        _same(rep.frame_segments(i), want)
+    rep.close()
