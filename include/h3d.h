@@ -275,9 +275,9 @@ int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const float *cons
 
 /* how the host thread of a frame waits for the device: 0 (default) = cudaStreamSynchronize, which
  * spins -- lowest latency; 1 = a blocking event, the thread sleeps -- use it when more pipelines
- * are in flight than the host has cores (several GPUs x frames in flight).  Process-wide; returns
- * the previous setting. */
-int h3d_set_wait_mode(int blocking);
+ * are in flight than the host has cores (several GPUs x frames in flight); 2 = poll an event and
+ * yield the core between polls.  Process-wide; returns the previous setting. */
+int h3d_set_wait_mode(int mode);
 
 /* same, also collecting the segment records of every frame (the pipelines must have
  * h3d_pipeline_enable_segments on): segments + i*max_segments, n_segments[i] (may exceed

@@ -489,9 +489,10 @@ def segment_test(y_centred, shift, a_, b_, cfg, pose=None):
     return seg
 
 
-def set_wait_mode(blocking):
-    """0: host threads spin on their stream (lowest latency); 1: they sleep on a blocking event."""
-    return lib().h3d_set_wait_mode(C.c_int(1 if blocking else 0))
+def set_wait_mode(mode):
+    """0: host threads spin on their stream (lowest latency); 1: they sleep on a blocking event;
+    2: they poll an event and yield the core between polls."""
+    return lib().h3d_set_wait_mode(C.c_int(int(mode)))
 
 
 def set_fused(on):

@@ -816,7 +816,8 @@ struct FrameCtx {
 };
 
 // how a host thread waits for its frame's stream: 0 = cudaStreamSynchronize (spins: lowest
-// latency), 1 = a blocking event (the thread sleeps: for more pipelines than host cores)
+// latency), 1 = a blocking event (the thread sleeps: for more pipelines than host cores),
+// 2 = event polling with sched_yield between polls
 std::atomic<int> g_wait_mode{0};
 
 cudaError_t frame_wait(FrameCtx &f) {
@@ -826,8 +827,13 @@ cudaError_t frame_wait(FrameCtx &f) {
     const cudaError_t e = cudaEventCreateWithFlags(&f.ev_block, cudaEventBlockingSync | cudaEventDisableTiming);
     if (e != cudaSuccess) return e;
   }
-  const cudaError_t e = cudaEventRecord(f.ev_block, s);
-  return e != cudaSuccess ? e : cudaEventSynchronize(f.ev_block);
+  cudaError_t e = cudaEventRecord(f.ev_block, s);
+  if (e != cudaSuccess) return e;
+  if (g_wait_mode.load(std::memory_order_relaxed) == 1) return cudaEventSynchronize(f.ev_block);
+  // mode 2: poll and give the core away between polls -- as quick as spinning while cores are
+  // free, and the other pipelines' threads get to run when they are not
+  while ((e = cudaEventQuery(f.ev_block)) == cudaErrorNotReady) std::this_thread::yield();
+  return e;
 }
 
 int frame_ensure(FrameCtx &f, unsigned g, size_t n, size_t in_bytes, size_t max_iters, size_t pool_cap) {
@@ -1639,8 +1645,8 @@ extern "C" int h3d_replay_run_segments(h3d_pipeline *const *pipes, size_t n_pipe
   return H3D_OK;
 }
 
-extern "C" int h3d_set_wait_mode(int blocking) {
-  return g_wait_mode.exchange(blocking ? 1 : 0);
+extern "C" int h3d_set_wait_mode(int mode) {
+  return g_wait_mode.exchange(mode == 1 ? 1 : mode == 2 ? 2 : 0);
 }
 
 extern "C" int h3d_pipeline_set_sm_share(h3d_pipeline *p, int n_ctas) {
