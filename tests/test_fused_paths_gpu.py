@@ -93,9 +93,15 @@ def test_replay_matches_one_frame_at_a_time(h3d):
         want.append(_trace_tuple(single.trace()))
     single.close()
     rp = h3d.Replay(3, 40, 5, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 6, n_max, len(frames))
-    res = rp.run([f.ctypes.data for f in frames], [f.shape[0] for f in frames], frames[0].shape[1], on_device=False)
-    for k in range(len(frames)):
-        its = rp.iters[k * rp.max_iters:(k + 1) * rp.max_iters]
-        pool = rp.pool[k * rp.pool_cap:(k + 1) * rp.pool_cap]
-        assert _trace_tuple(h3d.Trace(res[k], its, pool)) == want[k], f"frame {k}"
+    try:
+        for mode in (0, 1, 2):    # spin, blocking event, poll + yield (h3d_set_wait_mode): same results
+            h3d.set_wait_mode(mode)
+            res = rp.run([f.ctypes.data for f in frames], [f.shape[0] for f in frames], frames[0].shape[1],
+                         on_device=False)
+            for k in range(len(frames)):
+                its = rp.iters[k * rp.max_iters:(k + 1) * rp.max_iters]
+                pool = rp.pool[k * rp.pool_cap:(k + 1) * rp.pool_cap]
+                assert _trace_tuple(h3d.Trace(res[k], its, pool)) == want[k], f"frame {k}, wait mode {mode}"
+    finally:
+        assert h3d.set_wait_mode(0) in (0, 1, 2)
     rp.close()
