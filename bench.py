@@ -235,8 +235,9 @@ def run_gpu_arm(args):
         host_cores = len(os.sched_getaffinity(0))
     except AttributeError:
         host_cores = os.cpu_count() or 1
-    crowded = (K + 1) * world > host_cores
-    wait_mode = {"spin": 0, "block": 1, "yield": 2}.get(args.wait, 2 if crowded else 0)
+    # auto = poll + yield whenever frames are in flight: equal to spinning while cores are free
+    # (3.31 k vs 3.31 k frames/s at 1 GPU / 16 cores), far ahead of it when they are not
+    wait_mode = {"spin": 0, "block": 1, "yield": 2}.get(args.wait, 2 if K > 1 else 0)
     capi.set_wait_mode(wait_mode)
     share = 0 if K == 1 else (args.sm_share if args.sm_share > 0 else max(1, sm_count // K))
 
@@ -431,7 +432,7 @@ def main():
     ap.add_argument("--concurrency", type=int, default=FRAMES_IN_FLIGHT,
                     help="frames in flight per GPU (K pipelines, K host threads); 1 = lowest latency")
     ap.add_argument("--wait", choices=("auto", "spin", "block", "yield"), default="auto",
-                    help="how the K host threads wait for the device (auto: poll + yield when ranks x threads exceed the cores)")
+                    help="how the K host threads wait for the device (auto: poll + yield when frames are in flight)")
     ap.add_argument("--sm-share", type=int, default=SM_SHARE, help="SMs per frame in flight (0: sm_count / concurrency)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10 s CPU sample (profiling runs)")
     args = ap.parse_args()
