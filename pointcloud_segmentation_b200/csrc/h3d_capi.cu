@@ -758,7 +758,6 @@ struct FrameCtx {
   size_t cap = 0, iters_cap = 0, pool_cap = 0, in_bytes = 0;
   void *in_dev = nullptr;
   unsigned *orig = nullptr;
-  unsigned *orig2 = nullptr;             // 2*cap: re-packed numbering of the fused loop
   unsigned char *flags = nullptr;
   int *yidx = nullptr;
   double *ypx = nullptr, *ypy = nullptr, *ypz = nullptr;
@@ -797,7 +796,7 @@ struct FrameCtx {
   ~FrameCtx() { release(); }
   void release() {
     if (hg) { h3d_destroy(hg); hg = nullptr; }
-    cudaFree(in_dev); cudaFree(orig); cudaFree(orig2); cudaFree(flags); cudaFree(yidx);
+    cudaFree(in_dev); cudaFree(orig); cudaFree(flags); cudaFree(yidx);
     cudaFree(ypx); cudaFree(ypy); cudaFree(ypz);
     cudaFree(iters_dev); cudaFree(pool_dev); cudaFree(st_dev); cudaFree(prep_dev);
     cudaFree(gbest); cudaFree(sync_dev); cudaFreeHost(sync_host); cudaFree(prof_dev);
@@ -808,7 +807,7 @@ struct FrameCtx {
     cudaFreeHost(st_host); cudaFreeHost(prep_host);
     for (auto &e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
     if (ev_block) { cudaEventDestroy(ev_block); ev_block = nullptr; }
-    in_dev = nullptr; orig = nullptr; orig2 = nullptr; flags = nullptr; yidx = nullptr; ypx = ypy = ypz = nullptr;
+    in_dev = nullptr; orig = nullptr; flags = nullptr; yidx = nullptr; ypx = ypy = ypz = nullptr;
     iters_dev = nullptr; pool_dev = nullptr; st_dev = nullptr; prep_dev = nullptr;
     st_host = nullptr; prep_host = nullptr;
     cap = iters_cap = pool_cap = in_bytes = 0; granularity = ~0u;
@@ -855,10 +854,9 @@ int frame_ensure(FrameCtx &f, unsigned g, size_t n, size_t in_bytes, size_t max_
   if (n > f.cap) {
     size_t cap = f.cap ? f.cap : 8192;
     while (cap < n) cap *= 2;
-    cudaFree(f.orig); cudaFree(f.orig2); cudaFree(f.flags); cudaFree(f.yidx); cudaFree(f.ypx); cudaFree(f.ypy); cudaFree(f.ypz);
-    f.orig = nullptr; f.orig2 = nullptr; f.flags = nullptr; f.yidx = nullptr; f.ypx = f.ypy = f.ypz = nullptr; f.cap = 0;
+    cudaFree(f.orig); cudaFree(f.flags); cudaFree(f.yidx); cudaFree(f.ypx); cudaFree(f.ypy); cudaFree(f.ypz);
+    f.orig = nullptr; f.flags = nullptr; f.yidx = nullptr; f.ypx = f.ypy = f.ypz = nullptr; f.cap = 0;
     H3D_CUDA(cudaMalloc(&f.orig, cap * sizeof(unsigned)));
-    H3D_CUDA(cudaMalloc(&f.orig2, 2 * cap * sizeof(unsigned)));
     H3D_CUDA(cudaMalloc(&f.flags, cap));
     H3D_CUDA(cudaMalloc(&f.yidx, cap * sizeof(int)));
     H3D_CUDA(cudaMalloc(&f.ypx, cap * sizeof(double)));

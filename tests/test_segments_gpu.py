@@ -158,3 +158,46 @@ def test_replay_collects_segments_of_every_frame(h3d, oracle, oracle_mod):
         assert rep.rc_ref[i] == rc_want
         _same(rep.frame_segments(i), want)
     rep.close()
+
+
+@pytest.mark.parametrize("fused", [True, False], ids=["fused", "multikernel"])
+def test_segments_with_unbounded_line_count(h3d, oracle, oracle_mod, fused):
+    """opt_nlines == 0 (wrap.h:342): the loop ends on its own break rules; one CTA per possible record."""
+    old = h3d.set_fused(fused)
+    try:
+        frame = synth.tof_frame(pose=(-1.1, 0.0, 0.8, 0.0), seed=3)
+        filt = oracle.prefilter(frame, synth.WINDOW, float(synth.LEAF)).astype(np.float64)
+        trace = oracle.hough3dlines(filt, 4, synth.OPT_DX, 40, 0, mode=0, max_iters=64)
+        assert 2 <= len(trace.iters) < 64
+        rc_want, want = oracle.segments(filt, trace, _cfg(oracle_mod, (0.05,), 0.9))
+        pipe = h3d.Pipeline(4, synth.WINDOW, synth.LEAF, synth.OPT_DX, 40, 0, max_raw_points=frame.shape[0])
+        pipe.enable_segments(_cfg(h3d, (0.05,), 0.9))
+        pipe.run(frame)
+        rc_got, got = pipe.segments()
+        assert rc_got == rc_want
+        _same(got, want)
+        pipe.close()
+    finally:
+        h3d.set_fused(old)
+
+
+def test_segments_on_a_cloud2_message_without_prefilter(h3d, oracle, oracle_mod):
+    """The post-tests read the points through the (pointer, stride) form of the message buffer."""
+    from test_cloud2_gpu import _message
+    frame = synth.tof_frame(pose=(-1.1, 0.0, 0.8, 0.0), seed=4).astype(np.float32)[::9][:4000]
+    width, height = frame.shape[0] // 8, 8
+    frame = np.ascontiguousarray(frame[: width * height])
+    keep = np.isfinite(frame[:, :3]).all(axis=1)
+    cloud = frame[keep, :3].astype(np.float64)                      # wrap.h:175-189: strip + widen
+    trace = oracle.hough3dlines(cloud, 4, 0.06, 12, 8, mode=0)
+    # pool indices of the device run refer to the message (pre-strip numbering): compare through points
+    rc_want, want = oracle.segments(cloud, trace, _cfg(oracle_mod, (0.05,), 0.9))
+    pipe = h3d.Pipeline(4, synth.WINDOW, synth.LEAF, 0.06, 12, 8, max_raw_points=frame.shape[0], prefilter=False)
+    pipe.enable_segments(_cfg(h3d, (0.05,), 0.9))
+    for point_step, offs, pad in ((32, (4, 8, 12), 0), (24, (0, 8, 20), 16)):   # in place / gathered
+        buf, row_step = _message(frame, point_step, offs, width, height, pad)
+        pipe.run_cloud2(buf, width, height, point_step, row_step, *offs)
+        rc_got, got = pipe.segments()
+        assert rc_got == rc_want and len(want) > 0
+        _same(got, want)
+    pipe.close()
