@@ -288,6 +288,75 @@ int h3d_replay_run_segments(h3d_pipeline *const *pipes, size_t n_pipes, const fl
                             h3d_result *results, h3d_segment *segments, size_t max_segments,
                             uint32_t *n_segments, int *rc_ref);
 
+/* ---- world model across frames: segFiltering, checkSimilarity, checkConnections
+ *      (node.cpp:479-667), saveSegmentsToFile / saveIntersectionsToFile
+ *      (node.cpp:850-897) -- SURVEY 8(f) rank 4 --------------------------------
+ * State kept ACROSS frames on tens of segments, O(s^2) scalar work: host C++ in
+ * the reference and here (no kernel); it consumes the 200-byte records the device
+ * post-tests return, so a replay reproduces segments.csv / intersections.csv
+ * without ROS.  Vector arithmetic follows Eigen's fixed-size evaluation order
+ * (3-term sums reduce as x0 + (x1 + x2)), no FMA. */
+typedef struct h3d_world h3d_world;
+typedef struct {
+  double diag_voxel;       /* node.cpp:242 */
+  double min_weight;       /* node.cpp:205 (config_pc_seg: /min_weight)          */
+} h3d_world_config;
+typedef struct {           /* `segment` of wrap.h:21-29 without the point copies */
+  double a[3], b[3];
+  double t_min, t_max;
+  double radius;
+  int32_t points_size;
+  int32_t pad_;
+  double pca_coeff;
+  double pca_eigenvalues[3];
+} h3d_world_segment;
+int h3d_world_create(const h3d_world_config *cfg, h3d_world **out);
+void h3d_world_destroy(h3d_world *w);
+/* segFiltering(drone_segments) (node.cpp:479-542): drone = the frame's segments
+ * in the world frame, in order.  Quirks kept: similarity is tested against the
+ * segments as they were BEFORE the frame; a later drone segment similar to the
+ * same world segment overwrites the earlier fusion; a new segment is recorded
+ * under the index `size after push + i` (node.cpp:508), so its connections are
+ * looked for only when that index happens to exist; entries of the intersection
+ * matrix are never reset.  Defined here where the reference reads indeterminate
+ * values: `segment target_seg;` (node.cpp:494) is uninitialised when
+ * checkSimilarity adds to its points_size / pca_coeff / pca_eigenvalues
+ * (node.cpp:651-654) -- this build starts them from the WORLD segment (the
+ * "[in,out]" the doc comment announces); and points_size 0 + 0 (integer division
+ * by zero, node.cpp:617) gives weight 0. */
+int h3d_world_update(h3d_world *w, const h3d_world_segment *drone, size_t n);
+/* same from the device records of one frame (h3d_pipeline_segments): takes those
+ * with status 0 and world_status 1 (drone2WorldSeg + heighSegmentCutoff kept
+ * them), a/b = a_world/b_world.  *n_used (may be NULL) = how many were taken. */
+int h3d_world_update_frame(h3d_world *w, const h3d_segment *segs, size_t n, size_t *n_used);
+int h3d_world_segments(const h3d_world *w, h3d_world_segment *out, size_t cap, size_t *n);
+/* intersection_matrix (node.cpp:138): t_pairs[(i*n + j)*2 + {0,1}] for all i, j < n
+ * ((-1, -1) = none; only j < i is ever set); cap_pairs = pairs t_pairs can hold. */
+int h3d_world_intersections(const h3d_world *w, double *t_pairs, size_t cap_pairs, size_t *n);
+/* checkSimilarity (node.cpp:594-667): *similar = 1 and *target = the fused segment,
+ * else *target = *drone.  target_init = the value `target_seg` holds on entry. */
+int h3d_check_similarity(const h3d_world_segment *drone, const h3d_world_segment *world,
+                         const h3d_world_config *cfg, const h3d_world_segment *target_init,
+                         h3d_world_segment *target, int *similar);
+/* checkConnections (node.cpp:556-590): sol = colPivHouseholderQr solution
+ * (t along s1 from t_min, t along s2 from t_min, distance); *connected as the
+ * reference returns it.  sol is written also when not connected (zero if parallel). */
+int h3d_check_connections(const h3d_world_segment *s1, const h3d_world_segment *s2,
+                          const h3d_world_config *cfg, double sol[3], int *connected);
+/* saveSegmentsToFile / saveIntersectionsToFile (node.cpp:850-897): same columns,
+ * default ostream formatting (%g, 6 significant digits).  Either path may be NULL. */
+int h3d_world_save_csv(const h3d_world *w, const char *segments_path, const char *intersections_path);
+
+/* ROS-free replay of node.cpp:286-306 for n_frames frames: hough3dlines with the post-tests,
+ * drone2WorldSeg + heighSegmentCutoff with poses[i] (the pipelines must have
+ * h3d_pipeline_enable_segments on), then segFiltering into `world` in frame order.  Frames run in
+ * flight on the pipelines; the world update is sequential and runs on the collected records.
+ * segments / n_segments / rc_ref as in h3d_replay_run_segments; max_segments must hold every frame. */
+int h3d_replay_run_world(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw,
+                         const size_t *n_points, size_t stride, size_t n_frames, int frames_on_device,
+                         const h3d_pose *poses, h3d_result *results, h3d_segment *segments,
+                         size_t max_segments, uint32_t *n_segments, int *rc_ref, h3d_world *world);
+
 /* measurement hook: phase stamps of the fused loop kernel.  out == NULL: enable for `iters`
  * iterations (0 disables).  out != NULL: copy the stamps of the last frame,
  * [iteration][cta][n_slots] globaltimer nanoseconds (slot 8: re-voted planes + 1). */

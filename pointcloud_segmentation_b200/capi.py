@@ -429,6 +429,19 @@ class Replay:
                                    C.c_size_t(self.pool_cap), self.results))
         return self.results
 
+    def run_world(self, ptrs, n_points, stride, on_device, poses, world):
+        """node.cpp:286-306 without ROS (h3d_replay_run_world): frame i with sensor pose poses[i] (Pose), the
+        kept world-frame segments of every frame fused into `world` (World) in frame order."""
+        n = len(ptrs)
+        assert n <= self.max_frames and len(poses) == n and self.segments is not None
+        raw = (C.c_void_p * n)(*ptrs)
+        npts = (C.c_size_t * n)(*n_points)
+        check(lib().h3d_replay_run_world(self._handles, C.c_size_t(len(self.pipes)), raw, npts, C.c_size_t(stride),
+                                         C.c_size_t(n), C.c_int(1 if on_device else 0), (Pose * n)(*poses),
+                                         self.results, self.segments, C.c_size_t(self.max_iters), self.n_segments,
+                                         self.rc_ref, world._w))
+        return self.results
+
     def close(self):
         for p in self.pipes:
             p.close()
@@ -487,6 +500,97 @@ def segment_test(y_centred, shift, a_, b_, cfg, pose=None):
     check(lib().h3d_segment_test_pose(p, n, _d3(shift), _d3(a_), _d3(b_), C.byref(cfg),
                                       C.byref(pose) if pose is not None else None, C.byref(seg)))
     return seg
+
+
+class WorldConfig(C.Structure):
+    """h3d_world_config: diag_voxel (node.cpp:242), min_weight (node.cpp:205)."""
+    _fields_ = [("diag_voxel", C.c_double), ("min_weight", C.c_double)]
+
+
+class WorldSegment(C.Structure):
+    """h3d_world_segment: `segment` of wrap.h:21-29 without the point copies."""
+    _fields_ = [("a", C.c_double * 3), ("b", C.c_double * 3), ("t_min", C.c_double), ("t_max", C.c_double),
+                ("radius", C.c_double), ("points_size", C.c_int32), ("pad_", C.c_int32), ("pca_coeff", C.c_double),
+                ("pca_eigenvalues", C.c_double * 3)]
+
+    @classmethod
+    def make(cls, a_, b_, t_min, t_max, radius, points_size, pca_coeff, pca_eigenvalues):
+        s = cls()
+        for k in range(3):
+            s.a[k], s.b[k], s.pca_eigenvalues[k] = float(a_[k]), float(b_[k]), float(pca_eigenvalues[k])
+        s.t_min, s.t_max, s.radius, s.pca_coeff = float(t_min), float(t_max), float(radius), float(pca_coeff)
+        s.points_size = int(points_size)
+        return s
+
+    def key(self):
+        return (tuple(self.a), tuple(self.b), self.t_min, self.t_max, self.radius, self.points_size, self.pca_coeff,
+                tuple(self.pca_eigenvalues))
+
+
+def check_similarity(drone, world, cfg, target_init=None):
+    """checkSimilarity (node.cpp:594-667) -> (similar, target segment)."""
+    out, sim = WorldSegment(), C.c_int(0)
+    check(lib().h3d_check_similarity(C.byref(drone), C.byref(world), C.byref(cfg),
+                                     C.byref(target_init) if target_init is not None else None, C.byref(out),
+                                     C.byref(sim)))
+    return bool(sim.value), out
+
+
+def check_connections(s1, s2, cfg):
+    """checkConnections (node.cpp:556-590) -> (connected, (t1, t2, distance))."""
+    sol, con = (C.c_double * 3)(), C.c_int(0)
+    check(lib().h3d_check_connections(C.byref(s1), C.byref(s2), C.byref(cfg), sol, C.byref(con)))
+    return bool(con.value), tuple(sol)
+
+
+class World:
+    """world_segments + intersection_matrix kept across frames (node.cpp:136-138, segFiltering node.cpp:479-542)."""
+
+    def __init__(self, diag_voxel, min_weight):
+        self.cfg = WorldConfig(diag_voxel, min_weight)
+        self._w = C.c_void_p()
+        check(lib().h3d_world_create(C.byref(self.cfg), C.byref(self._w)))
+
+    def close(self):
+        if self._w:
+            lib().h3d_world_destroy(self._w)
+            self._w = C.c_void_p()
+
+    __del__ = close
+
+    def update(self, drone):
+        """drone: sequence of WorldSegment already in the world frame."""
+        arr = (WorldSegment * max(len(drone), 1))(*drone)
+        check(lib().h3d_world_update(self._w, arr, C.c_size_t(len(drone))))
+
+    def update_frame(self, segs):
+        """segs: the Segment records of one frame (Pipeline.segments / Replay.frame_segments); returns how many were taken."""
+        arr = (Segment * max(len(segs), 1))(*segs)
+        used = C.c_size_t(0)
+        check(lib().h3d_world_update_frame(self._w, arr, C.c_size_t(len(segs)), C.byref(used)))
+        return used.value
+
+    def segments(self):
+        n = C.c_size_t(0)
+        check(lib().h3d_world_segments(self._w, None, C.c_size_t(0), C.byref(n)))
+        out = (WorldSegment * max(n.value, 1))()
+        check(lib().h3d_world_segments(self._w, out, C.c_size_t(n.value), C.byref(n)))
+        return [out[k] for k in range(n.value)]
+
+    def intersections(self):
+        """n x n x 2 array of (t1, t2); (-1, -1) = none."""
+        n = C.c_size_t(0)
+        check(lib().h3d_world_intersections(self._w, None, C.c_size_t(0), C.byref(n)))
+        m = n.value
+        buf = np.full((m, m, 2), -1.0)
+        if m:
+            check(lib().h3d_world_intersections(self._w, buf.ctypes.data_as(C.POINTER(C.c_double)), C.c_size_t(m * m),
+                                                C.byref(n)))
+        return buf
+
+    def save_csv(self, segments_path=None, intersections_path=None):
+        enc = lambda p: p.encode() if p is not None else None
+        check(lib().h3d_world_save_csv(self._w, enc(segments_path), enc(intersections_path)))
 
 
 def set_wait_mode(mode):

@@ -1584,6 +1584,11 @@ extern "C" int h3d_pipeline_profile(h3d_pipeline *p, int iters, unsigned long lo
   return H3D_OK;
 }
 
+static int replay_impl(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw, const size_t *n_points,
+                       size_t stride, size_t n_frames, int frames_on_device, h3d_iter *iters, size_t max_iters,
+                       uint32_t *pool, size_t pool_cap, h3d_result *results, h3d_segment *segments,
+                       size_t max_segments, uint32_t *n_segments, int *rc_ref, const h3d_pose *poses);
+
 // Batched replay (BASELINE configs[2]): n_pipes host threads, one per pipeline, pull frames from a
 // shared counter.  Frame i: raw[i] (n_points[i] points, `stride` floats apart; device pointers when
 // frames_on_device), results[i], iters + i*max_iters, pool + i*pool_cap.
@@ -1600,6 +1605,33 @@ extern "C" int h3d_replay_run_segments(h3d_pipeline *const *pipes, size_t n_pipe
                                        h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
                                        h3d_result *results, h3d_segment *segments, size_t max_segments,
                                        uint32_t *n_segments, int *rc_ref) {
+  return replay_impl(pipes, n_pipes, raw, n_points, stride, n_frames, frames_on_device, iters, max_iters, pool,
+                     pool_cap, results, segments, max_segments, n_segments, rc_ref, nullptr);
+}
+
+// Replay with one sensor pose per frame and the world model fed in frame order (node.cpp:286-306:
+// hough3dlines -> drone2WorldSeg -> heighSegmentCutoff -> segFiltering).  Frames run in flight on the
+// pipelines; segFiltering is sequential across frames, so it runs on the collected records afterwards.
+extern "C" int h3d_replay_run_world(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw,
+                                    const size_t *n_points, size_t stride, size_t n_frames, int frames_on_device,
+                                    const h3d_pose *poses, h3d_result *results, h3d_segment *segments,
+                                    size_t max_segments, uint32_t *n_segments, int *rc_ref, h3d_world *world) {
+  if (!poses || !segments || !n_segments || !world) return fail(H3D_ERR_ARG, "bad argument");
+  int rc = replay_impl(pipes, n_pipes, raw, n_points, stride, n_frames, frames_on_device, nullptr, 0, nullptr, 0,
+                       results, segments, max_segments, n_segments, rc_ref, poses);
+  if (rc != H3D_OK) return rc;
+  for (size_t i = 0; i < n_frames; ++i) {
+    if (n_segments[i] > max_segments) return fail(H3D_ERR_RANGE, "max_segments too small for a frame");
+    rc = h3d_world_update_frame(world, segments + i * max_segments, n_segments[i], nullptr);
+    if (rc != H3D_OK) return rc;
+  }
+  return H3D_OK;
+}
+
+static int replay_impl(h3d_pipeline *const *pipes, size_t n_pipes, const float *const *raw, const size_t *n_points,
+                       size_t stride, size_t n_frames, int frames_on_device, h3d_iter *iters, size_t max_iters,
+                       uint32_t *pool, size_t pool_cap, h3d_result *results, h3d_segment *segments,
+                       size_t max_segments, uint32_t *n_segments, int *rc_ref, const h3d_pose *poses) {
   if (!pipes || n_pipes == 0 || (!raw && n_frames) || (!n_points && n_frames) || !results)
     return fail(H3D_ERR_ARG, "bad argument");
   if (segments && !n_segments) return fail(H3D_ERR_ARG, "segments needs n_segments");
@@ -1614,6 +1646,7 @@ extern "C" int h3d_replay_run_segments(h3d_pipeline *const *pipes, size_t n_pipe
       if (i >= n_frames || first_rc.load() != H3D_OK) break;
       h3d_iter *it = iters ? iters + i * max_iters : nullptr;
       uint32_t *pl = pool ? pool + i * pool_cap : nullptr;
+      if (poses) h3d_pipeline_set_pose(pipes[t], &poses[i]);
       int rc = frames_on_device
                          ? h3d_pipeline_run_dev(pipes[t], raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i])
                          : h3d_pipeline_run(pipes[t], raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i]);
