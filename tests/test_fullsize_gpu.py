@@ -1,0 +1,96 @@
+"""BASELINE.json configs[3] at FULL size on one GPU: 1 M-point infrastructure cloud, granularity 6 (20 481
+directions, 2.05e10 votes per add), dx = d/64, opt_nlines 50.  The oracle's voting would take minutes here,
+so votes and argmax are checked through size-independent properties (conservation, the dense accumulator
+against the per-direction records, linearity of add / subtract, shards against the whole) and everything
+downstream of getLine -- inlier sets, anchors, directions, removal -- against the oracle itself, which is
+O(N) per iteration.  Bit-exact throughout."""
+import numpy as np
+import pytest
+
+from pointcloud_segmentation_b200 import synth
+
+pytestmark = pytest.mark.gpu
+G, MINVOTES, NLINES = 6, 10, 50
+
+
+@pytest.fixture(scope="module")
+def cloud():
+    return synth.infrastructure()
+
+
+@pytest.fixture(scope="module")
+def trace(h3d, cloud):
+    return h3d.hough3dlines(cloud, G, 0.0, MINVOTES, NLINES, mode=1)
+
+
+def test_c4_loop_downstream_of_getline_matches_oracle(h3d, oracle, cloud, trace):
+    n = cloud.shape[0]
+    assert trace.rc == 0 and trace.n_input == n and (trace.num_x, trace.num_b) == (64, 20481)
+    assert trace.n_lines == NLINES and len(trace.iters) == NLINES
+    x, shift = oracle.shift_to_origin(cloud)
+    assert np.array_equal(shift, trace.shift)
+    alive = np.ones(n, dtype=bool)
+    prev_votes = None
+    for k, it in enumerate(trace.iters):
+        ctx = f"iteration {k}"
+        assert it["status"] == 0, ctx
+        assert prev_votes is None or it["votes"] <= prev_votes, ctx     # removing points only lowers the maximum
+        prev_votes = it["votes"]
+        live = np.flatnonzero(alive)
+        xl = x[live]
+        y1 = live[oracle.points_close_to_line(xl, it["a_raw"], it["b_raw"], trace.dx)]
+        assert np.array_equal(y1, it["inliers1"]), ctx
+        rc1, a1, b1 = oracle.orthogonal_lsq(x[y1])
+        assert np.array_equal(a1, it["a1"]) and np.array_equal(b1, it["b1"]), ctx
+        y2 = live[oracle.points_close_to_line(xl, a1, b1, trace.dx)]
+        assert np.array_equal(y2, it["inliers2"]), ctx
+        assert len(y2) >= MINVOTES, ctx
+        rc2, a2, b2 = oracle.orthogonal_lsq(x[y2])
+        assert np.array_equal(a2 + shift, it["a2"]) and np.array_equal(b2, it["b2"]), ctx
+        alive[y2] = False
+
+
+def test_c4_votes_conservation_records_linearity_and_shards(h3d, oracle, cloud, trace):
+    n = cloud.shape[0]
+    x, _ = oracle.shift_to_origin(cloud)
+    mn, mx = oracle.min_max(x)
+    h3d.init_space(G)
+    hg = h3d.Hough(mn, mx, trace.dx)
+    assert (hg.num_x, hg.num_b) == (trace.num_x, trace.num_b)
+    hg.add(x)
+    v0, a0, b0, flat0 = hg.get_line()                                   # from the per-direction records
+    it0 = trace.iters[0]
+    assert (v0, flat0) == (it0["votes"], it0["argmax"])
+    assert np.array_equal(a0, it0["a_raw"]) and np.array_equal(b0, it0["b_raw"])
+    dense = hg.votes()                                                  # the reference's VotingSpace, 84 M cells
+    assert int(dense.sum(dtype=np.uint64)) == n * hg.num_b              # every vote of a centred cloud lands
+    assert int(np.argmax(dense)) == flat0 and int(dense[flat0]) == v0   # first maximum in flat order
+    # direction shards against the whole: keys combine to the global winner, slices tile the accumulator
+    nb = hg.num_b
+    keys = []
+    for r in range(3):
+        j0, j1 = nb * r // 3, nb * (r + 1) // 3
+        sh = h3d.Hough(mn, mx, trace.dx, shard=(j0, j1))
+        sh.add(x)
+        keys.append(sh.get_line_key())
+        sh.close()
+    key = max(keys)
+    assert (key >> 32, 0xFFFFFFFF - (key & 0xFFFFFFFF)) == (v0, flat0)
+    # linearity: subtracting the first line's inliers = the accumulator of the remaining points
+    y = x[it0["inliers2"]]
+    hg.subtract(y)
+    v1, _, _, flat1 = hg.get_line()
+    it1 = trace.iters[1]
+    assert (v1, flat1) == (it1["votes"], it1["argmax"])
+    after = hg.votes()
+    hy = h3d.Hough(mn, mx, trace.dx)
+    hy.add(y)
+    assert np.array_equal(dense - hy.votes(), after)
+    hy.close()
+    # add -> subtract of everything left gives the empty accumulator back
+    alive = np.ones(n, dtype=bool)
+    alive[it0["inliers2"]] = False
+    hg.subtract(x[alive])
+    assert not hg.votes().any()
+    assert hg.get_line()[0] == 0
+    hg.close()
