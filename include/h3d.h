@@ -142,6 +142,30 @@ int h3d_hough3dlines(const double *xyz, size_t n, int granularity, double opt_dx
                      h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
                      h3d_result *res);
 
+/* ---- the same loop with the accumulator sharded by DIRECTION over the ranks of one box
+ *      (BASELINE configs[3]) ---------------------------------------
+ * A vote for direction j touches only plane j (lib/hough.cpp:90): rank r of `world` owns directions
+ * [num_b*r/world, num_b*(r+1)/world), every rank holds all points, and Hough::getLine is the MAX over
+ * ranks of the packed key votes << 32 | (0xFFFFFFFF - global flat index) -- one 8-byte ncclAllReduce per
+ * iteration, enqueued on the loop's stream between the shard's argmax and the line fit, so the loop stays
+ * device-resident.  Inliers, LSQ and removal are computed redundantly and deterministically by every rank:
+ * every rank returns the same iteration records as h3d_hough3dlines on one GPU (votes_cast counts the
+ * rank's own votes).  One process (or thread) per GPU; NCCL is opened with dlopen("libnccl.so.2") on first
+ * use, libh3d.so does not link it. */
+typedef struct h3d_comm h3d_comm;
+#define H3D_COMM_ID_BYTES 128
+/* rank 0 makes the id (ncclGetUniqueId) and hands it to the other ranks by the host's own means */
+int h3d_comm_unique_id(unsigned char id[H3D_COMM_ID_BYTES]);
+/* collective over all ranks; binds to the calling thread's current CUDA device */
+int h3d_comm_create(const unsigned char id[H3D_COMM_ID_BYTES], int rank, int world, h3d_comm **out);
+void h3d_comm_destroy(h3d_comm *c);
+/* comm == NULL: all directions on this GPU (== h3d_hough3dlines).  Collective: every rank calls it with
+ * the same points and options. */
+int h3d_hough3dlines_sharded(const double *xyz, size_t n, int granularity, double opt_dx,
+                             int opt_minvotes, int opt_nlines, int mode, h3d_comm *comm,
+                             h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                             h3d_result *res);
+
 /* ---- persistent pipeline: pre-filter + loop, buffers kept between frames --- */
 typedef struct h3d_pipeline h3d_pipeline;
 typedef struct {

@@ -232,8 +232,31 @@ class Trace:
             })
 
 
-def hough3dlines(xyz, granularity, dx, minvotes, nlines, mode=0, max_iters=None):
-    """The whole loop on the device (wrap.h:167-350 without the segment post-tests)."""
+class Comm:
+    """h3d_comm: NCCL communicator of the direction-sharded loop (one rank per GPU).  Rank 0 calls
+    Comm.unique_id() and hands the 128 bytes to the other ranks; Comm(id, rank, world) is collective."""
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_ubyte * 128)()
+        check(lib().h3d_comm_unique_id(buf))
+        return bytes(buf)
+
+    def __init__(self, uid, rank, world):
+        self.rank, self.world = rank, world
+        self._c = C.c_void_p()
+        check(lib().h3d_comm_create((C.c_ubyte * 128)(*uid), C.c_int(rank), C.c_int(world), C.byref(self._c)))
+
+    def close(self):
+        if self._c:
+            lib().h3d_comm_destroy(self._c)
+            self._c = C.c_void_p()
+
+
+def hough3dlines(xyz, granularity, dx, minvotes, nlines, mode=0, max_iters=None, comm=None):
+    """The whole loop on the device (wrap.h:167-350 without the segment post-tests).  comm: a Comm to
+    shard the accumulator by direction over its ranks (h3d_hough3dlines_sharded; every rank gets the
+    same Trace)."""
     a, p, n = _pts(xyz)
     if max_iters is None:
         max_iters = (nlines + 1) if nlines > 0 else 256
@@ -241,9 +264,10 @@ def hough3dlines(xyz, granularity, dx, minvotes, nlines, mode=0, max_iters=None)
     pool_cap = max(1, 2 * max_iters * a.shape[0])
     pool = np.zeros(pool_cap, dtype=np.uint32)
     res = Result()
-    check(lib().h3d_hough3dlines(p, n, C.c_int(granularity), C.c_double(dx), C.c_int(minvotes), C.c_int(nlines),
-                                 C.c_int(mode), iters, C.c_size_t(max_iters),
-                                 pool.ctypes.data_as(C.POINTER(C.c_uint32)), C.c_size_t(pool_cap), C.byref(res)))
+    check(lib().h3d_hough3dlines_sharded(p, n, C.c_int(granularity), C.c_double(dx), C.c_int(minvotes),
+                                         C.c_int(nlines), C.c_int(mode), comm._c if comm is not None else None,
+                                         iters, C.c_size_t(max_iters), pool.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                         C.c_size_t(pool_cap), C.byref(res)))
     return Trace(res, iters, pool)
 
 

@@ -3,6 +3,9 @@
 // needs a CUDA device and fails with H3D_ERR_CUDA otherwise.
 #include "../../include/h3d.h"
 
+#include <dlfcn.h>
+#include <nccl.h>   // types and enums only: NCCL is bound with dlopen, no symbol of it is linked
+
 #include <atomic>
 #include <cfloat>
 #include <cmath>
@@ -752,6 +755,49 @@ __global__ void shift_points_kernel(double *px, double *py, double *pz, int *w, 
 
 namespace {
 
+// ---- NCCL, bound at run time -------------------------------------------------------------------
+// The direction-sharded loop needs one 8-byte MAX all-reduce per iteration, in stream order.  NCCL is
+// opened with dlopen when a communicator is asked for (a process that already loaded a libnccl.so.2,
+// e.g. through torch, gets that one), so libh3d.so itself does not depend on it.
+}  // namespace
+struct h3d_comm {
+  ncclComm_t comm = nullptr;
+  int rank = 0, world = 1;
+};
+namespace {
+struct NcclApi {
+  void *lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi *nccl_api() {
+  static std::mutex mu;
+  static NcclApi api;
+  std::lock_guard<std::mutex> lock(mu);
+  if (api.lib) return &api;
+  void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) return nullptr;
+  api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(dlsym(lib, "ncclGetUniqueId"));
+  api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(dlsym(lib, "ncclCommInitRank"));
+  api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
+  api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(dlsym(lib, "ncclAllReduce"));
+  api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
+  if (!api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.AllReduce || !api.GetErrorString) {
+    dlclose(lib);
+    return nullptr;
+  }
+  api.lib = lib;
+  return &api;
+}
+int nccl_fail(NcclApi *api, ncclResult_t r, const char *what) {
+  set_error(std::string(what) + ": " + (api ? api->GetErrorString(r) : "NCCL not available"));
+  return H3D_ERR_NCCL;
+}
+
 struct FrameCtx {
   h3d_hough *hg = nullptr;
   unsigned granularity = ~0u;
@@ -791,6 +837,7 @@ struct FrameCtx {
   double *seg_scr = nullptr;             // 5 * seg_scr_n doubles
   size_t seg_scr_n = 0;
   const void *src = nullptr;             // the cloud the pool indexes (set by the caller of frame_run)
+  h3d_comm *comm = nullptr;              // direction-sharded loop (h3d_hough3dlines_sharded): this frame only
   int src_stride = 3, src_is_float = 0;
 
   ~FrameCtx() { release(); }
@@ -896,6 +943,11 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
   H3D_CUDA(cudaGetLastError());
   H3D_TRY(launch_vote(h, 0, 0, lb.list, &lb.st->work_count, 0, nullptr));
   loop_argmax_kernel<<<dblocks, 256, 0, s>>>(hd, lb, 0);                // hough->getLine       wrap.h:243
+  if (f.comm) {   // direction shards: the global winner is the MAX of the packed keys (global flat indices)
+    NcclApi *api = nccl_api();
+    const ncclResult_t r = api->AllReduce(&lb.st->best_key, &lb.st->best_key, 1, ncclUint64, ncclMax, f.comm->comm, s);
+    if (r != ncclSuccess) return nccl_fail(api, r, "ncclAllReduce");
+  }
   loop_line_kernel<<<1, 32, 0, s>>>(hd, lb);
   loop_mask_kernel<<<sm * 2, 256, 0, s>>>(hd, lb);                      // pointsCloseToLine    wrap.h:245
   loop_compact_kernel<<<1, 1024, 0, s>>>(hd, lb, 1);
@@ -980,7 +1032,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   *launched = false;
   h3d_hough *h = f.hg;
   const HoughDev &hd = h->d;
-  if (!g_use_fused || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0 || !hd.bounded) return H3D_OK;
+  if (!g_use_fused || f.comm || !resident_ok(h) || hd.n < 1 || hd.dir_begin != 0 || !hd.bounded) return H3D_OK;
   if (hd.plane_stride >= 65536u || hd.n >= 65535) return H3D_OK;   // re-vote keys pack (votes, cell) in 16 + 16 bits
   const int groups = (hd.dir_count + kResG - 1) / kResG;
   const int grid = (f.fused_ctas > 0 && f.fused_ctas < h->dev.sm_count) ? f.fused_ctas : h->dev.sm_count;
@@ -1085,6 +1137,12 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   H3D_TRY(configure_hough(h, minPs, maxPs, opt_dx));     // new Hough(...), wrap.h:220
   HoughDev &hd = h->d;
   res->dx = hd.dx; res->max_x = hd.max_x; res->num_x = (uint64_t)hd.num_x;
+  hd.dir_begin = 0; hd.dir_count = hd.num_b;
+  if (f.comm) {   // this rank's slice of the direction sphere (every rank holds all points)
+    const size_t nb = (size_t)hd.num_b, r = (size_t)f.comm->rank, w = (size_t)f.comm->world;
+    hd.dir_begin = (int)(nb * r / w);
+    hd.dir_count = (int)(nb * (r + 1) / w) - hd.dir_begin;
+  }
   hd.n = (int)n;
   hd.n_dev = nullptr;
   h->has_negative = false;
@@ -1174,6 +1232,50 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
 extern "C" int h3d_hough3dlines(const double *xyz, size_t n, int granularity, double opt_dx, int opt_minvotes,
                                 int opt_nlines, int mode, h3d_iter *iters, size_t max_iters, uint32_t *pool,
                                 size_t pool_cap, h3d_result *res) {
+  return h3d_hough3dlines_sharded(xyz, n, granularity, opt_dx, opt_minvotes, opt_nlines, mode, nullptr, iters,
+                                  max_iters, pool, pool_cap, res);
+}
+
+extern "C" int h3d_comm_unique_id(unsigned char id[H3D_COMM_ID_BYTES]) {
+  if (!id) return fail(H3D_ERR_ARG, "bad argument");
+  NcclApi *api = nccl_api();
+  if (!api) return nccl_fail(nullptr, ncclSystemError, "dlopen(libnccl.so.2)");
+  ncclUniqueId u;
+  const ncclResult_t r = api->GetUniqueId(&u);
+  if (r != ncclSuccess) return nccl_fail(api, r, "ncclGetUniqueId");
+  static_assert(sizeof u == H3D_COMM_ID_BYTES, "ncclUniqueId size");
+  memcpy(id, &u, sizeof u);
+  return H3D_OK;
+}
+
+extern "C" int h3d_comm_create(const unsigned char id[H3D_COMM_ID_BYTES], int rank, int world, h3d_comm **out) {
+  if (!id || !out || world < 1 || rank < 0 || rank >= world) return fail(H3D_ERR_ARG, "bad argument");
+  NcclApi *api = nccl_api();
+  if (!api) return nccl_fail(nullptr, ncclSystemError, "dlopen(libnccl.so.2)");
+  int dev_count = 0;
+  if (cudaGetDeviceCount(&dev_count) != cudaSuccess || dev_count == 0) { cudaGetLastError(); return fail(H3D_ERR_CUDA, "no CUDA device"); }
+  ncclUniqueId u;
+  memcpy(&u, id, sizeof u);
+  h3d_comm *c = new (std::nothrow) h3d_comm();
+  if (!c) return fail(H3D_ERR_NOMEM, "host allocation failed");
+  c->rank = rank; c->world = world;
+  const ncclResult_t r = api->CommInitRank(&c->comm, world, u, rank);
+  if (r != ncclSuccess) { delete c; return nccl_fail(api, r, "ncclCommInitRank"); }
+  *out = c;
+  return H3D_OK;
+}
+
+extern "C" void h3d_comm_destroy(h3d_comm *c) {
+  if (!c) return;
+  NcclApi *api = nccl_api();
+  if (api && c->comm) api->CommDestroy(c->comm);
+  delete c;
+}
+
+extern "C" int h3d_hough3dlines_sharded(const double *xyz, size_t n, int granularity, double opt_dx,
+                                        int opt_minvotes, int opt_nlines, int mode, h3d_comm *comm,
+                                        h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
+                                        h3d_result *res) {
   if (!res || (!xyz && n) || granularity < 0 || granularity > 8) return fail(H3D_ERR_ARG, "bad argument");
   if (n > 0x7FFFFFF0u) return fail(H3D_ERR_RANGE, "too many points");
   memset(res, 0, sizeof *res);
@@ -1188,7 +1290,10 @@ extern "C" int h3d_hough3dlines(const double *xyz, size_t n, int granularity, do
   prep_kernel<double><<<1, 1024, 0, s>>>(static_cast<const double *>(f.in_dev), (int)n, nullptr, 3, f.hg->px,
                                          f.hg->py, f.hg->pz, f.orig, f.prep_dev);
   H3D_CUDA(cudaGetLastError());
-  return frame_run(f, opt_minvotes, opt_nlines, opt_dx, mode, iters, max_iters, pool, pool_cap, res);
+  f.comm = comm;
+  const int rc = frame_run(f, opt_minvotes, opt_nlines, opt_dx, mode, iters, max_iters, pool, pool_cap, res);
+  f.comm = nullptr;
+  return rc;
 }
 
 // =====================================================================================
