@@ -392,6 +392,11 @@ int h3d_pipeline_profile(h3d_pipeline *p, int iters, unsigned long long *out, si
  * previous setting.  Results are identical either way. */
 int h3d_set_fused(int on);
 
+/* clouds of 32 768 points and more run K3 and removePoints with chunked multi-CTA kernels (every
+ * 1024-point chunk is one CTA's work item) instead of the one-CTA kernels of the frame loop; on = 0
+ * forces the one-CTA kernels.  Returns the previous setting.  Results are identical either way. */
+int h3d_set_big_kernels(int on);
+
 /* ---- measurement hooks (bench.py): raw kernel timings with CUDA events ----- */
 /* runs the vote kernel `reps` times over all directions of h and returns the
  * mean device time per launch in microseconds.  ablate: 0 = full kernel,

@@ -838,11 +838,20 @@ struct FrameCtx {
   size_t seg_scr_n = 0;
   const void *src = nullptr;             // the cloud the pool indexes (set by the caller of frame_run)
   h3d_comm *comm = nullptr;              // direction-sharded loop (h3d_hough3dlines_sharded): this frame only
+  // large clouds (>= kBigCloud points): chunked multi-CTA compaction / removal (h3d_loop.cuh)
+  bool big = false;
+  size_t big_n = 0;                      // points of the frame when the loop started
+  int *ccount = nullptr, *coff = nullptr;   // cap / kChunk + 2 entries each
+  double *sx = nullptr, *sy = nullptr, *sz = nullptr;
+  unsigned *so = nullptr;
+  size_t scr_cap = 0;
   int src_stride = 3, src_is_float = 0;
 
   ~FrameCtx() { release(); }
   void release() {
     if (hg) { h3d_destroy(hg); hg = nullptr; }
+    cudaFree(ccount); cudaFree(coff); cudaFree(sx); cudaFree(sy); cudaFree(sz); cudaFree(so);
+    ccount = coff = nullptr; sx = sy = sz = nullptr; so = nullptr; scr_cap = 0;
     cudaFree(in_dev); cudaFree(orig); cudaFree(flags); cudaFree(yidx);
     cudaFree(ypx); cudaFree(ypy); cudaFree(ypz);
     cudaFree(iters_dev); cudaFree(pool_dev); cudaFree(st_dev); cudaFree(prep_dev);
@@ -909,7 +918,19 @@ int frame_ensure(FrameCtx &f, unsigned g, size_t n, size_t in_bytes, size_t max_
     H3D_CUDA(cudaMalloc(&f.ypx, cap * sizeof(double)));
     H3D_CUDA(cudaMalloc(&f.ypy, cap * sizeof(double)));
     H3D_CUDA(cudaMalloc(&f.ypz, cap * sizeof(double)));
+    cudaFree(f.ccount); cudaFree(f.coff); f.ccount = f.coff = nullptr;
+    H3D_CUDA(cudaMalloc(&f.ccount, (cap / kChunk + 2) * sizeof(int)));
+    H3D_CUDA(cudaMalloc(&f.coff, (cap / kChunk + 2) * sizeof(int)));
     f.cap = cap;
+  }
+  if (n >= (size_t)kBigCloud && f.scr_cap < f.cap) {
+    cudaFree(f.sx); cudaFree(f.sy); cudaFree(f.sz); cudaFree(f.so);
+    f.sx = f.sy = f.sz = nullptr; f.so = nullptr; f.scr_cap = 0;
+    H3D_CUDA(cudaMalloc(&f.sx, f.cap * sizeof(double)));
+    H3D_CUDA(cudaMalloc(&f.sy, f.cap * sizeof(double)));
+    H3D_CUDA(cudaMalloc(&f.sz, f.cap * sizeof(double)));
+    H3D_CUDA(cudaMalloc(&f.so, f.cap * sizeof(unsigned)));
+    f.scr_cap = f.cap;
   }
   H3D_TRY(ensure_points(f.hg, n ? n : 1));
   if (in_bytes > f.in_bytes) {
@@ -949,6 +970,24 @@ int enqueue_iteration(FrameCtx &f, const HoughDev &hd, const LoopBuffers &lb) {
     if (r != ncclSuccess) return nccl_fail(api, r, "ncclAllReduce");
   }
   loop_line_kernel<<<1, 32, 0, s>>>(hd, lb);
+  if (f.big) {   // large cloud: every 1024-point chunk is a CTA's work item (same order, same results)
+    const int nchunks = (int)((f.big_n + kChunk - 1) / kChunk);
+    const int cgrid = nchunks < sm * 2 ? nchunks : sm * 2;
+    big_mask_kernel<<<cgrid, kChunk, 0, s>>>(hd, lb);                   // pointsCloseToLine    wrap.h:245
+    big_scan_kernel<<<1, 1024, 0, s>>>(lb, 1);
+    big_scatter_kernel<<<cgrid, kChunk, 0, s>>>(lb);
+    loop_lsq_kernel<<<1, 192, 0, s>>>(hd, lb, 1);                        // orthogonal_LSQ       wrap.h:247
+    big_mask_kernel<<<cgrid, kChunk, 0, s>>>(hd, lb);                   // pointsCloseToLine    wrap.h:250
+    big_scan_kernel<<<1, 1024, 0, s>>>(lb, 2);
+    big_scatter_kernel<<<cgrid, kChunk, 0, s>>>(lb);
+    loop_lsq_kernel<<<1, 192, 0, s>>>(hd, lb, 2);                        // minvotes, LSQ        wrap.h:251-259
+    big_remove_kernel<<<cgrid, kChunk, 0, s>>>(lb);                     // removePoints         wrap.h:339
+    big_copyback_kernel<<<sm * 4, 256, 0, s>>>(lb);
+    big_finish_kernel<<<1, 1, 0, s>>>(lb);                              // while (...)          wrap.h:341-342
+    note_launches(17);
+    H3D_CUDA(cudaGetLastError());
+    return H3D_OK;
+  }
   loop_mask_kernel<<<sm * 2, 256, 0, s>>>(hd, lb);                      // pointsCloseToLine    wrap.h:245
   loop_compact_kernel<<<1, 1024, 0, s>>>(hd, lb, 1);
   loop_lsq_kernel<<<1, 192, 0, s>>>(hd, lb, 1);                          // orthogonal_LSQ       wrap.h:247
@@ -998,6 +1037,7 @@ int enqueue_segments(FrameCtx &f, size_t grid) {
 }
 
 static bool g_use_fused = true;
+static bool g_big_kernels = true;   // h3d_set_big_kernels: chunked K3 / removal kernels for large clouds
 
 int launch_fused(FrameCtx &f, const FusedArgs &args, size_t smem, int grid) {
   static thread_local size_t configured = 0;
@@ -1167,6 +1207,9 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   lb.st = f.st_dev; lb.iters = f.iters_dev; lb.pool = f.pool_dev; lb.orig = f.orig;
   lb.flags = f.flags; lb.yidx = f.yidx; lb.ypx = f.ypx; lb.ypy = f.ypy; lb.ypz = f.ypz;
   lb.px = h->px; lb.py = h->py; lb.pz = h->pz; lb.list = h->list; lb.dirs = h->space->dirs_dev;
+  lb.ccount = f.ccount; lb.coff = f.coff; lb.sx = f.sx; lb.sy = f.sy; lb.sz = f.sz; lb.so = f.so;
+  f.big = n >= (size_t)kBigCloud && f.scr_cap >= n && g_big_kernels;
+  f.big_n = n;
   int rc = H3D_OK;
   // fast path: first vote + the whole loop in one persistent cooperative kernel
   bool fused = false;
@@ -2046,5 +2089,11 @@ extern "C" int h3d_remove_points(double *x_xyz, size_t nx, const double *y_xyz, 
 extern "C" int h3d_set_fused(int on) {
   const int old = g_use_fused ? 1 : 0;
   g_use_fused = on != 0;
+  return old;
+}
+
+extern "C" int h3d_set_big_kernels(int on) {
+  const int old = g_big_kernels ? 1 : 0;
+  g_big_kernels = on != 0;
   return old;
 }

@@ -20,7 +20,7 @@
 // parallel whenever that is provably the same number: if every coordinate is a multiple of
 // 2^lo and n * 2^(hi+1) <= 2^(53+lo) (hi = largest exponent), every partial sum of ANY order is
 // an exactly representable multiple of 2^lo, so the sequential sum equals the exact sum, which
-// an int64 reduction delivers.  Otherwise one lane runs the sequential chain.
+// an int64 reduction delivers.  Otherwise the warp runs the sequential chain (loads batched, adds in order).
 #ifndef H3D_FIT_CUH_
 #define H3D_FIT_CUH_
 
@@ -279,9 +279,20 @@ __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
     sum = __dmul_rn((double)acc, __longlong_as_double((long long)(1023 + lo) << 52));
   } else {
+    // the sequential chain itself, with the loads taken off it: the warp fetches 32 values at a time
+    // (the next batch is in flight while this one is added) and every lane adds them in order from
+    // the shuffles, so only the 32 dependent DADDs remain per batch (a lone lane reading get(k)
+    // paid two dependent L2 round trips per element: 2 ms for the 11 k inliers of a configs[3] line)
     sum = 0.0;
-    if (lane == 0) for (int k = 0; k < n; ++k) sum = __dadd_rn(sum, get(k));
-    sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+    double cur = lane < n ? get(lane) : 0.0;
+    for (int k0 = 0; k0 < n; k0 += 32) {
+      const int kn = k0 + 32 + lane;
+      const double nxt = kn < n ? get(kn) : 0.0;
+      const int m = n - k0 < 32 ? n - k0 : 32;
+#pragma unroll 4
+      for (int j = 0; j < m; ++j) sum = __dadd_rn(sum, __shfl_sync(0xFFFFFFFFu, cur, j));
+      cur = nxt;
+    }
   }
   return n > 0 ? __ddiv_rn(sum, (double)n) : sum;
 }

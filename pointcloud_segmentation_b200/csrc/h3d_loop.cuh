@@ -43,7 +43,14 @@ struct LoopBuffers {
   double *px, *py, *pz;   // mutable aliases of the point arrays (compaction)
   int *list;              // directions to rebuild
   const double *dirs;     // 3*num_b direction vectors
+  // large clouds (kBigCloud points and more): chunked multi-CTA compaction / removal
+  int *ccount, *coff;     // inliers per 1024-point chunk of the current pass, their exclusive prefix
+  double *sx, *sy, *sz;   // scratch copy of the kept points (removal goes out of place and back)
+  unsigned *so;
 };
+
+constexpr int kBigCloud = 32768;   // from here on the loop uses the chunked kernels below
+constexpr int kChunk = 1024;
 
 // ---- start of an iteration: reset the reduction targets -------------------------------
 __global__ void loop_begin_kernel(LoopBuffers lb) {
@@ -258,6 +265,144 @@ __global__ void __launch_bounds__(1024, 1) loop_remove_kernel(LoopBuffers lb) {
     s.n_iters++;
     if (!((s.n_alive > 1) && (s.nlines_max == 0 || s.nlines_max > s.n_lines))) s.done = 1;
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The same K3 / removal steps for LARGE clouds (configs[3]: 1 M points): the single-CTA kernels above
+// walk the cloud chunk by chunk, which is fine for the few thousand points of a ToF frame and far too
+// serial for a million.  Here every 1024-point chunk is one CTA's work item: flags + per-chunk counts,
+// a one-CTA scan of the (n/1024) counts, an ordered scatter.  Same order, same results.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kChunk) big_mask_kernel(const HoughDev h, LoopBuffers lb) {
+  const LoopState &s = *lb.st;
+  if (s.done) return;
+  const double a[3] = {s.a[0], s.a[1], s.a[2]}, b[3] = {s.b[0], s.b[1], s.b[2]};
+  const double dx = s.opt_dx;
+  const int n = s.n_alive, nchunks = (n + kChunk - 1) / kChunk;
+  for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const int i = c * kChunk + threadIdx.x;
+    const bool keep = i < n && point_near_line(h.px[i], h.py[i], h.pz[i], a, b, dx);
+    if (i < n) lb.flags[i] = keep ? 1 : 0;
+    const int cnt = __syncthreads_count(keep);
+    if (threadIdx.x == 0) lb.ccount[c] = cnt;
+  }
+}
+
+// exclusive prefix of the chunk counts + the bookkeeping of loop_compact_kernel's tail
+__global__ void __launch_bounds__(1024, 1) big_scan_kernel(LoopBuffers lb, int pass) {
+  __shared__ int warp_sum[32];
+  __shared__ int base_s;
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) base_s = 0;
+  __syncthreads();
+  const int n = s.n_alive, nchunks = (n + kChunk - 1) / kChunk;
+  for (int c0 = 0; c0 < nchunks; c0 += 1024) {
+    const int c = c0 + tid;
+    const int v = c < nchunks ? lb.ccount[c] : 0;
+    int incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+    if (lane == 31) warp_sum[warp] = incl;
+    __syncthreads();
+    int off = base_s;
+    for (int q = 0; q < warp; ++q) off += warp_sum[q];
+    if (c < nchunks) lb.coff[c] = off + incl - v;
+    __syncthreads();
+    if (tid == 0) { int t = 0; for (int q = 0; q < 32; ++q) t += warp_sum[q]; base_s += t; }
+    __syncthreads();
+  }
+  if (tid == 0 && pass != 0) {
+    const unsigned pool0 = s.pool_used;
+    const int ny = base_s;
+    s.ny = ny;
+    lb.coff[nchunks] = (int)pool0;   // where this pass's list starts in the pool (read by the scatter)
+    const unsigned used = pool0 + (unsigned)ny;
+    s.pool_used = used < s.pool_cap ? used : s.pool_cap;
+    if (s.n_iters < s.max_iters) {
+      h3d_iter &r = lb.iters[s.n_iters];
+      if (pass == 1) { r.n1 = (unsigned)ny; r.off1 = pool0; r.off2 = s.pool_used; }
+      else { r.n2 = (unsigned)ny; r.off2 = pool0; }
+    }
+  }
+}
+
+// position of a flagged thread among the flagged threads of its 1024-thread chunk, in thread order
+__device__ __forceinline__ int chunk_rank(bool flag, int *warp_sum) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned bal = __ballot_sync(0xFFFFFFFFu, flag);
+  __syncthreads();   // warp_sum of the previous use has been read
+  if (lane == 0) warp_sum[warp] = __popc(bal);
+  __syncthreads();
+  int off = 0;
+  for (int q = 0; q < warp; ++q) off += warp_sum[q];
+  return off + __popc(bal & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(kChunk) big_scatter_kernel(LoopBuffers lb) {
+  __shared__ int warp_sum[32];
+  const LoopState &s = *lb.st;
+  if (s.done) return;
+  const int n = s.n_alive, nchunks = (n + kChunk - 1) / kChunk;
+  const unsigned pool0 = (unsigned)lb.coff[nchunks];
+  for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    if (lb.ccount[c] == 0) continue;   // uniform
+    const int i = c * kChunk + threadIdx.x;
+    const bool keep = i < n && lb.flags[i];
+    const int r = chunk_rank(keep, warp_sum);
+    if (keep) {
+      const int pos = lb.coff[c] + r;
+      lb.yidx[pos] = i;
+      if (pool0 + (unsigned)pos < s.pool_cap) lb.pool[pool0 + pos] = lb.orig[i];
+    }
+  }
+}
+
+// X.removePoints(Y): kept points to the scratch arrays (ordered), removed coordinates to ypx/ypy/ypz;
+// ccount / coff still describe the flags of pass 2
+__global__ void __launch_bounds__(kChunk) big_remove_kernel(LoopBuffers lb) {
+  __shared__ int warp_sum[32];
+  const LoopState &s = *lb.st;
+  if (s.done) return;
+  const int n = s.n_alive, nchunks = (n + kChunk - 1) / kChunk;
+  for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const int i = c * kChunk + threadIdx.x;
+    const bool in = i < n;
+    const bool drop = in && lb.flags[i];
+    const bool keep = in && !drop;
+    const int doff = lb.coff[c], koff = c * kChunk - doff;
+    double x = 0, y = 0, z = 0;
+    unsigned o = 0;
+    if (in) { x = lb.px[i]; y = lb.py[i]; z = lb.pz[i]; o = lb.orig[i]; }
+    if (lb.ccount[c] == 0) {           // uniform: nothing of this chunk is removed
+      if (in) { const int p = koff + threadIdx.x; lb.sx[p] = x; lb.sy[p] = y; lb.sz[p] = z; lb.so[p] = o; }
+      continue;
+    }
+    const int rk = chunk_rank(keep, warp_sum);
+    const int rd = chunk_rank(drop, warp_sum);
+    if (keep) { const int p = koff + rk; lb.sx[p] = x; lb.sy[p] = y; lb.sz[p] = z; lb.so[p] = o; }
+    if (drop) { const int p = doff + rd; lb.ypx[p] = x; lb.ypy[p] = y; lb.ypz[p] = z; }
+  }
+}
+
+__global__ void big_copyback_kernel(LoopBuffers lb) {
+  const LoopState &s = *lb.st;
+  if (s.done) return;
+  const int nk = s.n_alive - s.ny;   // ny = |Y| of pass 2
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nk; i += gridDim.x * blockDim.x) {
+    lb.px[i] = lb.sx[i]; lb.py[i] = lb.sy[i]; lb.pz[i] = lb.sz[i]; lb.orig[i] = lb.so[i];
+  }
+}
+
+// the loop condition (wrap.h:341-342), after the copy-back has read n_alive
+__global__ void big_finish_kernel(LoopBuffers lb) {
+  LoopState &s = *lb.st;
+  if (s.done) return;
+  s.ny_prev = s.ny;
+  s.n_alive = s.n_alive - s.ny;
+  s.n_iters++;
+  if (!((s.n_alive > 1) && (s.nlines_max == 0 || s.nlines_max > s.n_lines))) s.done = 1;
 }
 
 }  // namespace h3d

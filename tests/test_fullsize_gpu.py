@@ -94,3 +94,22 @@ def test_c4_votes_conservation_records_linearity_and_shards(h3d, oracle, cloud, 
     assert not hg.votes().any()
     assert hg.get_line()[0] == 0
     hg.close()
+
+
+def test_big_cloud_kernels_match_one_cta_kernels_and_oracle(h3d, oracle):
+    """Clouds >= 32 768 points take the chunked multi-CTA compaction / removal kernels: same records as the
+    one-CTA kernels of the frame loop, and both equal to the oracle (40 k-point tower, g4; a ragged last chunk)."""
+    pts = synth.steel_tower(40000 + 77, seed=8)
+    want = oracle.hough3dlines(pts, 4, 0.0, 10, 14, mode=1)
+    runs = []
+    for on in (1, 0):
+        old = h3d.set_big_kernels(on)
+        runs.append(h3d.hough3dlines(pts, 4, 0.0, 10, 14, mode=1))
+        h3d.set_big_kernels(old)
+    for got in runs:
+        assert (got.rc, got.n_lines, len(got.iters)) == (want.rc, want.n_lines, len(want.iters))
+        for g, w in zip(got.iters, want.iters):
+            assert (g["votes"], g["argmax"], g["status"]) == (w.votes, w.argmax, w.status)
+            assert np.array_equal(g["inliers1"], w.inliers1) and np.array_equal(g["inliers2"], w.inliers2)
+            for key in ("a_raw", "b_raw", "a1", "b1", "a2", "b2"):
+                assert np.array_equal(g[key], getattr(w, key)), key
