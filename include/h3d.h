@@ -397,6 +397,12 @@ int h3d_set_fused(int on);
  * forces the one-CTA kernels.  Returns the previous setting.  Results are identical either way. */
 int h3d_set_big_kernels(int on);
 
+/* a full vote (Hough::add) over no more directions than the GPU has SMs and 65 536 points or more
+ * (granularity 0-2 on large clouds, or a narrow direction shard) slices the points of a direction over
+ * CTAs and merges the partial planes in global memory; on = 0 forces one work item per direction.
+ * Returns the previous setting.  Results are identical either way. */
+int h3d_set_sliced_vote(int on);
+
 /* ---- measurement hooks (bench.py): raw kernel timings with CUDA events ----- */
 /* runs the vote kernel `reps` times over all directions of h and returns the
  * mean device time per launch in microseconds.  ablate: 0 = full kernel,

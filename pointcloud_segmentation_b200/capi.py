@@ -623,6 +623,11 @@ def set_wait_mode(mode):
     return lib().h3d_set_wait_mode(C.c_int(int(mode)))
 
 
+def set_sliced_vote(on):
+    """Point-sliced full vote for few directions x many points (default on); returns the previous setting."""
+    return int(lib().h3d_set_sliced_vote(C.c_int(1 if on else 0)))
+
+
 def set_big_kernels(on):
     """Chunked multi-CTA K3 / removal kernels for clouds >= 32 768 points (default on); returns the previous setting."""
     return int(lib().h3d_set_big_kernels(C.c_int(1 if on else 0)))

@@ -135,6 +135,8 @@ struct h3d_hough {
   int *idx = nullptr;             // scratch: indices of removed points
   size_t idx_cap = 0;
   int vote_d = 1;                 // directions per work item of the full vote
+  unsigned *gplanes = nullptr;    // sliced vote form: dir_count global planes (few directions, many points)
+  size_t gplanes_cells = 0;
   uint64_t votes_cast = 0;
 };
 
@@ -380,6 +382,7 @@ static int launch_resident(h3d_hough *h, int ablate, const int *list, const int 
 
 // D planes per CTA, two CTAs per SM when they fit.  D == 0: pick the kernel form
 // (register-resident points when they fit, else streaming with D = 2).
+static bool g_sliced_vote = true;   // h3d_set_sliced_vote
 static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const int *count_ptr, int count_imm,
                        unsigned *dense) {
   const size_t plane_bytes = (size_t)h->d.plane_stride * sizeof(unsigned);
@@ -387,6 +390,37 @@ static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const i
   if (plane_bytes > budget) return fail(H3D_ERR_RANGE, "one (x',y') plane does not fit in shared memory");
   if (D == 0) {
     if (!dense && resident_ok(h)) return launch_resident(h, ablate, list, count_ptr, count_imm);
+    // few directions, many points: slice the points of a direction over CTAs (full votes only)
+    if (g_sliced_vote && !dense && !list && !count_ptr && ablate == 0 && count_imm == h->d.dir_count &&
+        h->d.dir_count > 0 && h->d.dir_count <= h->dev.sm_count && h->d.n >= 65536 &&   // g0-g2, narrow shards (at 321 directions it lost at 4 M points)
+        (size_t)h->d.dir_count * h->d.plane_cells <= ((size_t)64 << 20) / sizeof(unsigned)) {
+      const size_t cells = (size_t)h->d.dir_count * h->d.plane_cells;
+      if (cells > h->gplanes_cells) {
+        cudaFree(h->gplanes); h->gplanes = nullptr; h->gplanes_cells = 0;
+        H3D_CUDA(cudaMalloc(&h->gplanes, cells * sizeof(unsigned)));
+        H3D_CUDA(cudaMemsetAsync(h->gplanes, 0, cells * sizeof(unsigned), h->stream));
+        h->gplanes_cells = cells;
+      }
+      const int grid = h->dev.sm_count * 2;
+      int slices = (4 * grid + h->d.dir_count - 1) / h->d.dir_count;   // ~4 items per CTA: balanced tail
+      const int max_slices = h->d.n / 8192;                 // a slice is worth a CTA from 8 k points on
+      if (slices > max_slices) slices = max_slices;
+      const int min_slices = (h->d.n + 262143) / 262144;    // <= 256 k points (7 MB) per slice: measured, 4 M points
+      if (slices < min_slices) slices = min_slices;
+      if (slices < 1) slices = 1;
+      const size_t smem = (size_t)h->d.plane_stride * sizeof(unsigned);
+      static thread_local size_t configured = 0;
+      if (smem > configured) {
+        H3D_CUDA(cudaFuncSetAttribute(vote_sliced_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)(h->dev.smem_optin - 2048)));
+        configured = h->dev.smem_optin - 2048;
+      }
+      vote_sliced_kernel<<<grid, kVoteThreads, smem, h->stream>>>(h->d, slices, h->gplanes);
+      sliced_scan_kernel<<<h->d.dir_count, 256, 0, h->stream>>>(h->d, h->gplanes);
+      note_launches(2);
+      H3D_CUDA(cudaGetLastError());
+      return H3D_OK;
+    }
     D = 2;
   }
   while (D > 1 && (size_t)D * plane_bytes > budget / 2) D >>= 1;
@@ -501,7 +535,7 @@ extern "C" void h3d_destroy(h3d_hough *h) {
   cudaFree(h->px); cudaFree(h->py); cudaFree(h->pz); cudaFree(h->w);
   cudaFree(h->stage); cudaFree(h->idx);
   cudaFree(h->d.dvotes); cudaFree(h->d.dcell); cudaFree(h->d.dstale);
-  cudaFree(h->keys); cudaFree(h->list); cudaFree(h->count);
+  cudaFree(h->keys); cudaFree(h->list); cudaFree(h->count); cudaFree(h->gplanes);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -2089,6 +2123,12 @@ extern "C" int h3d_remove_points(double *x_xyz, size_t nx, const double *y_xyz, 
 extern "C" int h3d_set_fused(int on) {
   const int old = g_use_fused ? 1 : 0;
   g_use_fused = on != 0;
+  return old;
+}
+
+extern "C" int h3d_set_sliced_vote(int on) {
+  const int old = g_sliced_vote ? 1 : 0;
+  g_sliced_vote = on != 0;
   return old;
 }
 

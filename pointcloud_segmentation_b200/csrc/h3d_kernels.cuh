@@ -170,6 +170,88 @@ vote_kernel(const HoughDev h, const int *__restrict__ list, const int *__restric
 }
 
 // ---------------------------------------------------------------------------
+// K1 (sliced form): FEW directions, MANY points (granularity 0-3 on 100 k+ points, configs[4]).  A
+// direction is one work item in the forms above, so fewer directions than CTAs leave SMs idle.
+// Here a work item is (direction l, slice s of S): the CTA votes points [s*n/S, (s+1)*n/S) into a
+// shared-memory plane exactly as above, then adds the non-zero cells to the direction's plane in
+// global memory (num_x^2 u32 per direction: the accumulator of these granularities is a few MB);
+// sliced_scan_kernel then reduces each global plane to its record and zeroes it again.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(kVoteThreads, 2)
+vote_sliced_kernel(const HoughDev h, int slices, unsigned *__restrict__ gplanes) {
+  extern __shared__ __align__(16) unsigned planes[];
+  const int tid = threadIdx.x;
+  const unsigned plane_cells = h.plane_cells;
+  for (unsigned q = tid; q < plane_cells; q += kVoteThreads) planes[q] = 0;
+  __syncthreads();
+  const int n = point_count(h);
+  const double kmagic = h.kmagic;
+  const unsigned num_x = (unsigned)h.num_x;
+  const bool no_fast = !h.fast_ok;
+  const int items = h.dir_count * slices;
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    // slice-major: CTAs running side by side vote the SAME points for different directions, so a slice
+    // comes from DRAM once and from L2 afterwards (4 M points do not fit L2 with their 28 B each)
+    const int sl = item / h.dir_count, l = item - sl * h.dir_count;
+    const int i_begin = (int)((long long)n * sl / slices), i_end = (int)((long long)n * (sl + 1) / slices);
+    const FastCoef f = make_fast(h.coef[h.dir_begin + l], h.inv_s);
+    constexpr int U = 4;   // independent vote chains per thread
+    for (int i0 = i_begin + tid; i0 < i_end; i0 += U * kVoteThreads) {
+      unsigned cell[U];
+      int wi[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int i = i0 + u * kVoteThreads;
+        const bool in = i < i_end;
+        wi[u] = in ? h.w[i] : 0;
+        const double x = in ? h.px[i] : 0.0, y = in ? h.py[i] : 0.0, z = in ? h.pz[i] : 0.0;
+        bool sure = true;
+        cell[u] = vote_cell_fast(f, kmagic, num_x, x, y, z, &sure);
+        if (wi[u] != 0 && (!sure | no_fast))
+          cell[u] = vote_cell_exact(h.coef + h.dir_begin + l, h.max_x, h.dx, h.num_x, x, y, z);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (wi[u] != 0 && cell[u] < plane_cells) atomicAdd(&planes[cell[u]], (unsigned)wi[u]);
+    }
+    __syncthreads();
+    unsigned *g = gplanes + (size_t)l * plane_cells;
+    for (unsigned q = tid; q < plane_cells; q += kVoteThreads) {
+      const unsigned v = planes[q];
+      if (v) { atomicAdd(&g[q], v); planes[q] = 0; }
+    }
+    __syncthreads();
+  }
+}
+
+// one CTA per direction: (max, first max cell) of its global plane -> record; the plane is zeroed
+__global__ void __launch_bounds__(256) sliced_scan_kernel(const HoughDev h, unsigned *__restrict__ gplanes) {
+  __shared__ unsigned long long scratch[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int l = blockIdx.x; l < h.dir_count; l += gridDim.x) {
+    unsigned *g = gplanes + (size_t)l * h.plane_cells;
+    unsigned long long k = 0;
+    for (unsigned q = threadIdx.x; q < h.plane_cells; q += blockDim.x) {
+      const unsigned v = g[q];
+      if (v) {
+        g[q] = 0;
+        const unsigned long long kk = ((unsigned long long)v << 32) | (0xFFFFFFFFu - q);
+        k = kk > k ? kk : k;
+      }
+    }
+    k = warp_max_u64(k);
+    if (lane == 0) scratch[warp] = k;
+    __syncthreads();
+    if (warp == 0) {
+      k = lane < (int)(blockDim.x >> 5) ? scratch[lane] : 0ull;
+      k = warp_max_u64(k);
+      if (lane == 0) store_record(h, l, k);
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------
 // K1 (resident form, N <= kResThreads * P, weights in {0,1}): one persistent CTA
 // per SM keeps ALL live points in registers (P per thread) for its whole list of
 // directions, so a vote costs 6 DFMA, ~10 integer ops and one shared-memory RED

@@ -113,3 +113,36 @@ def test_big_cloud_kernels_match_one_cta_kernels_and_oracle(h3d, oracle):
             assert np.array_equal(g["inliers1"], w.inliers1) and np.array_equal(g["inliers2"], w.inliers2)
             for key in ("a_raw", "b_raw", "a1", "b1", "a2", "b2"):
                 assert np.array_equal(g[key], getattr(w, key)), key
+
+
+@pytest.mark.parametrize("g", [0, 1, 2, 3])
+def test_sliced_vote_few_directions_many_points(h3d, oracle, g):
+    """Granularity 0-3 on a 100 k-point cloud: the full vote slices the points of a direction over CTAs and merges
+    partial planes in global memory.  Same records as one work item per direction, the loop equal to the oracle, and
+    the records equal to the dense accumulator (built by the streaming form)."""
+    pts = synth.beam_cloud(synth.tower_beams(), 100_003, seed=5)
+    want = oracle.hough3dlines(pts, g, 0.0, 10, 6, mode=1)
+    for on in (1, 0):
+        old = h3d.set_sliced_vote(on)
+        got = h3d.hough3dlines(pts, g, 0.0, 10, 6, mode=1)
+        h3d.set_sliced_vote(old)
+        assert (got.rc, got.n_lines, len(got.iters)) == (want.rc, want.n_lines, len(want.iters))
+        for a, w in zip(got.iters, want.iters):
+            assert (a["votes"], a["argmax"], a["status"]) == (w.votes, w.argmax, w.status)
+            assert np.array_equal(a["inliers1"], w.inliers1) and np.array_equal(a["inliers2"], w.inliers2)
+            for key in ("a_raw", "b_raw", "a1", "b1", "a2", "b2"):
+                assert np.array_equal(a[key], getattr(w, key)), key
+    x, _ = oracle.shift_to_origin(pts)
+    mn, mx = oracle.min_max(x)
+    h3d.init_space(g)
+    hg = h3d.Hough(mn, mx, 0.0)
+    hg.add(x)                                   # sliced form
+    v, _, _, flat = hg.get_line()
+    dense = hg.votes()                          # streaming form, materialised
+    assert int(dense.sum(dtype=np.uint64)) == len(x) * hg.num_b
+    assert (int(np.argmax(dense)), int(dense.max())) == (flat, v)
+    hg.add(x[:70000])                           # a second add on top: 170 003 points, all re-voted
+    v2, _, _, flat2 = hg.get_line()
+    dense2 = hg.votes()
+    assert (int(np.argmax(dense2)), int(dense2.max())) == (flat2, v2)
+    hg.close()
