@@ -25,6 +25,7 @@ Only the cpu_baseline leg and --impl reference execute anything under oracle/.
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -111,6 +112,119 @@ class ClockSampler:
         busy = [s for s in sm if s > 0.5 * max(mx or [1])] or sm
         return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def check_against_golden(frames, lines):
+    """rank 0's frames are the ones tests/golden/reference_golden_g56.npz holds reference traces of (recorded
+    from oracle/_ref by tests/golden/make_golden_g56.py): compare the per-frame line counts when the raw frames
+    regenerated here are bit-identical to the recorded ones."""
+    path = os.path.join(ROOT, "tests", "golden", "reference_golden_g56.npz")
+    try:
+        gold = np.load(path)
+        same = all(hashlib.sha256(np.ascontiguousarray(frames[k]).tobytes()).hexdigest() == str(gold[f"tof{k}_raw_sha256"])
+                   for k in range(len(lines)))
+        if not same:
+            return {"frames_identical_to_golden": False}
+        bad = sum(int(gold[f"tof{k}_n_lines"]) != lines[k] for k in range(len(lines)))
+        return {"frames_identical_to_golden": True, "frames": len(lines), "line_count_mismatches": bad,
+                "reference_lines_total": int(gold["tof_total_lines"]), "lines_total": int(sum(lines))}
+    except Exception as exc:   # the golden file is test infrastructure: its absence must not stop a bench
+        return {"error": str(exc)}
+
+
+C4_POINTS, C4_NLINES = 1_000_000, 50
+C4_DIGEST_N1 = "2a671c5540398251"   # the 50 lines of configs[3] on ONE GPU (profiles/r01_c4_direction_sharded.json n1)
+
+
+def direction_sharded_leg(rank, world, dev, reps=2):
+    """BASELINE.json configs[3]: the 1 M-point infrastructure cloud (200 beams), granularity 6, dx = d/64, 50 lines,
+    the accumulator sharded by DIRECTION over the ranks (h3d_hough3dlines_sharded: every rank holds all points
+    and directions [j0, j1); Hough::getLine is one in-stream 8-byte ncclAllReduce(MAX) per iteration over the
+    torch-initialised NCCL world).  STRONG scaling: the work is fixed, N = 1 runs the same cloud on one GPU.
+    Device times (CUDA events on the loop's stream), max over ranks; the digest of the detected lines is
+    compared on every rank with the committed one-GPU digest."""
+    import torch
+    import torch.distributed as dist
+    from pointcloud_segmentation_b200 import capi, sharding, synth
+
+    def max_over_ranks(v):
+        if world == 1:
+            return float(v)
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    pts = synth.infrastructure(C4_POINTS)
+    num_b = 20481
+    capi.init_space(GRANULARITY)
+    # Hough::add of the rank's shard alone (the vote kernel), CUDA events inside the library
+    x, _ = capi.shift_to_origin(pts)
+    mn, mx = capi.min_max(x)
+    dx = float(np.sqrt(((mx - mn) ** 2).sum())) / 64.0
+    j0, j1 = sharding.direction_shards(num_b, world)[rank]
+    hg = capi.Hough(mn, mx, dx, shard=(j0, j1))
+    hg.add(x)
+    add_us = max_over_ranks(hg.bench_vote(reps=3))
+    hg.close()
+    del x
+    ar_us, comm = 0.0, None
+    if world > 1:
+        t = torch.zeros(1, dtype=torch.int64, device=dev)
+        for _ in range(20):
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(200):
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e1.record()
+        torch.cuda.synchronize()
+        ar_us = max_over_ranks(e0.elapsed_time(e1) * 1e3 / 200)
+        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid = torch.tensor(list(capi.Comm.unique_id()), dtype=torch.uint8, device=dev)
+        dist.broadcast(uid, 0)
+        comm = capi.Comm(bytes(uid.cpu().tolist()), rank, world)
+    loop_ms, phases, wall_ms = [], None, []
+    for rep in range(reps + 1):                      # the first run warms NCCL and the allocations up
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        tr = capi.hough3dlines(pts, GRANULARITY, 0.0, 10, C4_NLINES, mode=1, comm=comm)
+        wall = (time.perf_counter() - t0) * 1e3
+        us = capi.hough3dlines_timing()
+        if rep:
+            loop_ms.append(max_over_ranks(us[3] / 1e3)); wall_ms.append(max_over_ranks(wall))
+            phases = [max_over_ranks(u / 1e3) for u in us]
+    if comm is not None:
+        comm.close()
+    dig = hashlib.sha256()
+    n_lines = 0
+    for it in tr.iters:
+        if it["status"] == 0:
+            n_lines += 1
+            dig.update(np.array([it["votes"], it["argmax"], len(it["inliers2"])], dtype=np.uint64).tobytes() +
+                       np.asarray(it["a2"]).tobytes() + np.asarray(it["b2"]).tobytes())
+    digest = dig.hexdigest()[:16]
+    ok = torch.tensor([1.0 if digest == C4_DIGEST_N1 else 0.0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    votes = C4_POINTS * num_b
+    return {
+        "workload": "configs[3]: 1M-point infrastructure cloud (200 beams), g6, dx=d/64, opt_nlines 50, accumulator "
+                    "sharded by direction over the ranks, all points on every rank",
+        "scaling": "strong", "n_gpus": world, "directions_per_rank": j1 - j0,
+        "add_ms": add_us / 1e3, "add_gvotes_per_s": votes / add_us / 1e3,
+        "add_roofline_frac": (8.0 * votes + 24.0 * C4_POINTS + 40.0 * num_b) / (add_us * 1e-6) / 1e9 / (measured_peak()[0] * world),
+        "allreduce_us": ar_us, "loop_ms": float(np.min(loop_ms)), "loop_ms_runs": loop_ms,
+        "loop_wall_ms": float(np.min(wall_ms)),
+        "loop_phase_ms": dict(zip(("upload_prep", "first_vote", "loop_kernels", "total"), phases)),
+        "lines": n_lines, "lines_digest": digest, "digest_n1_golden": C4_DIGEST_N1,
+        "digest_matches_n1": bool(ok.item() == 1.0),
+        "timed": "CUDA events on the loop's stream around the whole h3d_hough3dlines_sharded call (host points in, "
+                 "records out), max over ranks, best of %d runs after one warm-up" % reps,
+    }
 
 
 def measured_peak():
@@ -256,6 +370,28 @@ def run_gpu_arm(args):
     counts = [n_pts] * FRAMES_PER_STEP
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
+    iter_bytes = ctypes.sizeof(capi.Iter)
+
+    def frame_digest(res, iters_base, pool_arr, pool_base, max_iters):
+        """sha256 over everything a frame returns: header counts, every iteration record (votes, argmax,
+        status, fitted lines, inlier counts/offsets) and both inlier index lists of every iteration"""
+        n_rec = min(res.n_iters, max_iters)
+        h = hashlib.sha256()
+        h.update(np.array([res.rc, res.n_iters, res.n_lines, res.n_input, res.num_x, res.pool_used], dtype=np.int64).tobytes())
+        h.update(ctypes.string_at(iters_base, n_rec * iter_bytes))
+        h.update(pool_arr[pool_base:pool_base + int(res.pool_used)].tobytes())
+        return h.digest()
+
+    # what every frame must return: each distinct frame once through ONE pipeline on all SMs, before any timing
+    want_digest, want_lines = [], []
+    ref_pipe = new_pipe(0)
+    for k in range(DISTINCT_FRAMES):
+        r = ref_pipe.run_dev(on_dev[k].data_ptr(), n_pts, stride)
+        want_digest.append(frame_digest(r, ctypes.addressof(ref_pipe.iters), ref_pipe.pool, 0, ref_pipe.max_iters))
+        want_lines.append(int(r.n_lines))
+    ref_pipe.close()
+    golden = check_against_golden(frames, want_lines) if rank == 0 else None
+
     def one_step(e2e):
         """one batch of FRAMES_PER_STEP frames over the K pipelines; device time of the whole batch (ms)"""
         flush.fill_(rank + 1)              # L2 flush between timed steps (inputs are far smaller than L2)
@@ -265,12 +401,17 @@ def run_gpu_arm(args):
         torch.cuda.synchronize()           # every pipeline stream has drained
         ev1.record()
         ev1.synchronize()
-        out = dict(d2h=0, lines=0, votes=0, nf=0, iters=0)
+        out = dict(d2h=0, lines=0, votes=0, nf=0, iters=0, mismatches=0, checked=0)
+        base = ctypes.addressof(replay.iters)
         for k in range(FRAMES_PER_STEP):
             r = res[k]
             n_rec = min(r.n_iters, replay.max_iters)
             out["d2h"] += 216 + n_rec * 200 + 4 * r.pool_used          # state + records + inlier lists
             out["lines"] += r.n_lines; out["votes"] += r.votes_cast; out["nf"] += r.n_input; out["iters"] += r.n_iters
+            # parity inside the timed legs: the frame's complete result against the one-pipeline run of the same frame
+            got = frame_digest(r, base + k * replay.max_iters * iter_bytes, replay.pool, k * replay.pool_cap, replay.max_iters)
+            out["checked"] += 1
+            out["mismatches"] += got != want_digest[k % DISTINCT_FRAMES]
         out["ms"] = ev0.elapsed_time(ev1)
         return out
 
@@ -368,8 +509,20 @@ def run_gpu_arm(args):
     k1["frac"] = k1["achieved"] / measured_peak()[0]
     lat.close()
 
+    # ---- configs[3]: the direction-sharded loop over the same NCCL world (every N, N = 1 included) ---------
+    sharded = None
+    if not args.no_direction_sharded:
+        try:
+            sharded = direction_sharded_leg(rank, world, torch.device("cuda", local))
+        except Exception as exc:   # reported, and fatal below: a missing leg must not pass silently
+            sharded = {"error": f"{type(exc).__name__}: {exc}"}
     n_frames_rank = FRAMES_PER_STEP * args.steps
     total_frames = n_frames_rank * world
+    parity = torch.tensor([dev["checked"] + e2e["checked"], dev["mismatches"] + e2e["mismatches"]],
+                          dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(parity, op=dist.ReduceOp.SUM)
+    parity = parity.tolist()
     value = total_frames / (dev["ms"] * 1e-3)
     e2e_value = total_frames / (e2e["ms"] * 1e-3)
     peak, peak_src = measured_peak()
@@ -396,7 +549,13 @@ def run_gpu_arm(args):
                        "sm_count": sm_count, "host_cores": host_cores,
                        "host_wait": ("spin", "blocking events", "poll + yield")[wait_mode]},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": frame_bytes * FRAMES_PER_STEP,
-                    "d2h_bytes_per_step": int(e2e["d2h"] / args.steps), "ms_per_step": e2e["ms"] / args.steps},
+                    "d2h_bytes_per_step": int(e2e["d2h"] / args.steps), "ms_per_step": e2e["ms"] / args.steps,
+                    "lines_per_frame": e2e["lines"] / n_frames_rank},
+            "parity_in_timed_region": {
+                "frames": int(parity[0]), "mismatches": int(parity[1]),
+                "checked": "sha256 of every frame's complete result (iteration records + both inlier lists) in BOTH "
+                           "timed legs, all ranks, against the same frame run alone through one pipeline",
+                "expected_lines_per_frame": sum(want_lines) / DISTINCT_FRAMES, "golden": golden},
             "gpu_launches": dev["launches"] + e2e["launches"],
             "clocks": clocks,
             "single_frame_latency": {"ms_mean": float(np.mean(lat_us)) / 1e3, "ms_max": float(np.max(lat_us)) / 1e3,
@@ -412,6 +571,7 @@ def run_gpu_arm(args):
                                  "25 B/live point per K3 pass, K2 counted on the 9 B/direction records",
                          "achieved_dense_equivalent": algo_dense / n_lat / (kernel_us * 1e-6) / 1e9,
                          "k1_first_vote_kernel": k1},
+            "direction_sharded": sharded,
             "segment_post_tests": seg_leg,
             "votes_per_s": (votes_add + votes_sub) / n_lat / ((kernel_us + k1_us_mean) * 1e-6),
             "votes_evaluated_per_s_throughput": dev["votes"] / (dev["ms"] * 1e-3) * world,
@@ -421,6 +581,11 @@ def run_gpu_arm(args):
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if sharded is not None and (sharded.get("error") or not sharded.get("digest_matches_n1")):
+        raise SystemExit(f"bench.py: direction-sharded leg failed on rank {rank}: {sharded}")
+    if parity[1] > 0:
+        raise SystemExit(f"bench.py: {int(parity[1])} of {int(parity[0])} frames in the timed legs differ from the "
+                         "one-pipeline result of the same frame")
 
 
 def main():
@@ -435,6 +600,8 @@ def main():
                     help="how the K host threads wait for the device (auto: poll + yield when frames are in flight)")
     ap.add_argument("--sm-share", type=int, default=SM_SHARE, help="SMs per frame in flight (0: sm_count / concurrency)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10 s CPU sample (profiling runs)")
+    ap.add_argument("--no-direction-sharded", action="store_true",
+                    help="skip the configs[3] leg (1 M points, accumulator sharded by direction over the ranks)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_cpu_arm(args)

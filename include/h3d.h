@@ -165,6 +165,11 @@ int h3d_hough3dlines_sharded(const double *xyz, size_t n, int granularity, doubl
                              int opt_minvotes, int opt_nlines, int mode, h3d_comm *comm,
                              h3d_iter *iters, size_t max_iters, uint32_t *pool, size_t pool_cap,
                              h3d_result *res);
+/* device times (CUDA events on the loop's stream, microseconds) of the calling thread's last
+ * h3d_hough3dlines / h3d_hough3dlines_sharded call: [0] upload + NaN strip + bbox, [1] Hough::add (the
+ * first vote), [2] the loop's kernels including the in-stream all-reduces, [3] the whole call with its
+ * result copies.  All zero when the call returned early (rc != 0). */
+int h3d_hough3dlines_timing(float us[4]);
 
 /* ---- persistent pipeline: pre-filter + loop, buffers kept between frames --- */
 typedef struct h3d_pipeline h3d_pipeline;
@@ -402,6 +407,12 @@ int h3d_set_big_kernels(int on);
  * CTAs and merges the partial planes in global memory; on = 0 forces one work item per direction.
  * Returns the previous setting.  Results are identical either way. */
 int h3d_set_sliced_vote(int on);
+
+/* debug aid: on != 0 makes every frame start from per-direction records of 0xFFFFFFFF votes, so a
+ * record the first vote fails to write wins every argmax instead of silently keeping the previous
+ * frame's value (the parity tests of the frames-in-flight replay run with it).  Returns the previous
+ * setting.  Results are identical either way when the kernels are correct. */
+int h3d_set_debug_poison(int on);
 
 /* ---- measurement hooks (bench.py): raw kernel timings with CUDA events ----- */
 /* runs the vote kernel `reps` times over all directions of h and returns the

@@ -271,6 +271,14 @@ def hough3dlines(xyz, granularity, dx, minvotes, nlines, mode=0, max_iters=None,
     return Trace(res, iters, pool)
 
 
+def hough3dlines_timing():
+    """[upload+prep, first vote, loop kernels, whole call] in microseconds on the device (CUDA events) for this
+    thread's last hough3dlines() call."""
+    us = (C.c_float * 4)()
+    check(lib().h3d_hough3dlines_timing(us))
+    return list(us)
+
+
 def prefilter(xyz_f32, window, leaf):
     """cloudFiltering of node.cpp:386-421: PassThrough window + VoxelGrid centroids (f32)."""
     a = np.ascontiguousarray(xyz_f32, dtype=np.float32)
@@ -636,3 +644,9 @@ def set_big_kernels(on):
 def set_fused(on):
     """Use (True) or bypass (False) the fused persistent loop kernel; returns the previous setting."""
     return bool(lib().h3d_set_fused(C.c_int(1 if on else 0)))
+
+
+def set_debug_poison(on):
+    """Start every frame from per-direction records of 0xFFFFFFFF votes (a record the first vote skips then
+    wins every argmax); returns the previous setting."""
+    return int(lib().h3d_set_debug_poison(C.c_int(1 if on else 0)))

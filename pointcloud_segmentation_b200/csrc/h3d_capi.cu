@@ -73,6 +73,27 @@ static int device_facts(DeviceFacts *out) {
   return H3D_OK;
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of (device, kernel), not of the calling
+// thread: one host thread may drive pipelines on several GPUs (h3d_pipeline_run sets the device), and
+// many threads share one device.  The opt-in is cached per (device ordinal, kernel address).
+static int ensure_dyn_smem(const void *kernel, size_t want, size_t smem_optin) {
+  static std::mutex mu;
+  static std::map<std::pair<int, const void *>, size_t> configured;
+  int dev = 0;
+  H3D_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  size_t &have = configured[std::make_pair(dev, kernel)];
+  if (want <= have) return H3D_OK;
+  cudaFuncAttributes fa;
+  H3D_CUDA(cudaFuncGetAttributes(&fa, kernel));
+  if (smem_optin < fa.sharedSizeBytes) return fail(H3D_ERR_RANGE, "kernel's static shared memory exceeds the opt-in limit");
+  const size_t dyn_max = smem_optin - fa.sharedSizeBytes;   // the opt-in limit covers static + dynamic
+  if (want > dyn_max) return fail(H3D_ERR_RANGE, "dynamic shared memory request exceeds the device limit");
+  H3D_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max));
+  have = dyn_max;
+  return H3D_OK;
+}
+
 // ---- direction spaces (lib/hough.cpp:15-20: one global sphere) ---------------
 static std::mutex g_space_mu;
 static std::map<std::pair<int, unsigned>, std::shared_ptr<const Space>> g_spaces;   // (device, g)
@@ -305,15 +326,7 @@ template <int D, int ABLATE>
 static int launch_vote_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense,
                          int grid) {
   const size_t smem = (size_t)D * h->d.plane_stride * sizeof(unsigned);
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    cudaFuncAttributes fa;
-    H3D_CUDA(cudaFuncGetAttributes(&fa, vote_kernel<D, ABLATE>));
-    const size_t dyn_max = h->dev.smem_optin - fa.sharedSizeBytes;   // opt-in limit covers static + dynamic
-    H3D_CUDA(cudaFuncSetAttribute(vote_kernel<D, ABLATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)dyn_max));
-    configured = dyn_max;
-  }
+  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_kernel<D, ABLATE>), smem, h->dev.smem_optin));
   vote_kernel<D, ABLATE><<<grid, kVoteThreads, smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
   note_launches(1);
   H3D_CUDA(cudaGetLastError());
@@ -323,15 +336,7 @@ static int launch_vote_t(h3d_hough *h, const int *list, const int *count_ptr, in
 template <int P, int ABLATE>
 static int launch_resident_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm) {
   const size_t smem = ((size_t)2 * kResG * h->d.plane_stride + 4) * sizeof(unsigned);
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    cudaFuncAttributes fa;
-    H3D_CUDA(cudaFuncGetAttributes(&fa, vote_resident_kernel<P, ABLATE>));
-    const size_t dyn_max = h->dev.smem_optin - fa.sharedSizeBytes;
-    H3D_CUDA(cudaFuncSetAttribute(vote_resident_kernel<P, ABLATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)dyn_max));
-    configured = dyn_max;
-  }
+  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_resident_kernel<P, ABLATE>), smem, h->dev.smem_optin));
   vote_resident_kernel<P, ABLATE><<<h->dev.sm_count, kResThreads, smem, h->stream>>>(h->d, list, count_ptr,
                                                                                     count_imm);
   note_launches(1);
@@ -343,15 +348,7 @@ static int launch_resident_t(h3d_hough *h, const int *list, const int *count_ptr
 template <int P>
 static int launch_first_vote_t(h3d_hough *h, int grid) {
   const size_t smem = ((size_t)2 * kResG * h->d.plane_stride + 4) * sizeof(unsigned);
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    cudaFuncAttributes fa;
-    H3D_CUDA(cudaFuncGetAttributes(&fa, vote_resident_kernel<P, 0, true>));
-    const size_t dyn_max = h->dev.smem_optin - fa.sharedSizeBytes;
-    H3D_CUDA(cudaFuncSetAttribute(vote_resident_kernel<P, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)dyn_max));
-    configured = dyn_max;
-  }
+  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_resident_kernel<P, 0, true>), smem, h->dev.smem_optin));
   vote_resident_kernel<P, 0, true><<<grid, kResThreads, smem, h->stream>>>(h->d, nullptr, nullptr, h->d.dir_count);
   note_launches(1);
   H3D_CUDA(cudaGetLastError());
@@ -409,12 +406,7 @@ static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const i
       if (slices < min_slices) slices = min_slices;
       if (slices < 1) slices = 1;
       const size_t smem = (size_t)h->d.plane_stride * sizeof(unsigned);
-      static thread_local size_t configured = 0;
-      if (smem > configured) {
-        H3D_CUDA(cudaFuncSetAttribute(vote_sliced_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)(h->dev.smem_optin - 2048)));
-        configured = h->dev.smem_optin - 2048;
-      }
+      H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_sliced_kernel), smem, h->dev.smem_optin));
       vote_sliced_kernel<<<grid, kVoteThreads, smem, h->stream>>>(h->d, slices, h->gplanes);
       sliced_scan_kernel<<<h->d.dir_count, 256, 0, h->stream>>>(h->d, h->gplanes);
       note_launches(2);
@@ -1071,14 +1063,11 @@ int enqueue_segments(FrameCtx &f, size_t grid) {
 }
 
 static bool g_use_fused = true;
+static std::atomic<int> g_debug_poison{0};   // h3d_set_debug_poison: records start from 0xFFFFFFFF every frame
 static bool g_big_kernels = true;   // h3d_set_big_kernels: chunked K3 / removal kernels for large clouds
 
 int launch_fused(FrameCtx &f, const FusedArgs &args, size_t smem, int grid) {
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    H3D_CUDA(cudaFuncSetAttribute(fused_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(fused_loop_kernel), smem, f.hg->dev.smem_optin));
   void *params[] = {const_cast<FusedArgs *>(&args)};
   H3D_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(fused_loop_kernel), dim3(grid),
                                        dim3(kResThreads), params, smem, f.hg->stream));
@@ -1245,6 +1234,13 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
   f.big = n >= (size_t)kBigCloud && f.scr_cap >= n && g_big_kernels;
   f.big_n = n;
   int rc = H3D_OK;
+  if (g_debug_poison.load(std::memory_order_relaxed)) {
+    // debug aid: a record the first vote fails to write keeps 0xFFFFFFFF votes and wins every argmax,
+    // instead of silently holding the previous frame's maximum for that direction
+    const size_t nd = (size_t)(hd.dir_count > 0 ? hd.dir_count : 1);
+    H3D_CUDA(cudaMemsetAsync(hd.dvotes, 0xFF, nd * sizeof(unsigned), s));
+    H3D_CUDA(cudaMemsetAsync(hd.dcell, 0xFF, nd * sizeof(unsigned), s));
+  }
   // fast path: first vote + the whole loop in one persistent cooperative kernel
   bool fused = false;
   H3D_TRY(try_launch_fused(f, lb, opt_nlines, opt_dx, &fused));
@@ -1305,6 +1301,8 @@ int frame_run(FrameCtx &f, int opt_minvotes, int opt_nlines, double opt_dx, int 
 }
 
 }  // namespace
+
+static thread_local float g_last_call_us[4] = {0, 0, 0, 0};   // h3d_hough3dlines_timing
 
 extern "C" int h3d_hough3dlines(const double *xyz, size_t n, int granularity, double opt_dx, int opt_minvotes,
                                 int opt_nlines, int mode, h3d_iter *iters, size_t max_iters, uint32_t *pool,
@@ -1370,7 +1368,21 @@ extern "C" int h3d_hough3dlines_sharded(const double *xyz, size_t n, int granula
   f.comm = comm;
   const int rc = frame_run(f, opt_minvotes, opt_nlines, opt_dx, mode, iters, max_iters, pool, pool_cap, res);
   f.comm = nullptr;
+  for (auto &u : g_last_call_us) u = 0.0f;
+  if (rc == H3D_OK && f.timed) {
+    cudaEventElapsedTime(&g_last_call_us[0], f.ev[0], f.ev[1]);   // upload + NaN strip / bbox
+    cudaEventElapsedTime(&g_last_call_us[1], f.ev[4], f.ev[2]);   // Hough::add (the first vote)
+    cudaEventElapsedTime(&g_last_call_us[2], f.ev[2], f.ev[5]);   // the loop's kernels (+ in-stream all-reduces)
+    cudaEventElapsedTime(&g_last_call_us[3], f.ev[0], f.ev[3]);   // whole call on the device, result copies included
+    for (auto &u : g_last_call_us) u *= 1000.0f;
+  }
   return rc;
+}
+
+extern "C" int h3d_hough3dlines_timing(float us[4]) {
+  if (!us) return fail(H3D_ERR_ARG, "bad argument");
+  for (int k = 0; k < 4; ++k) us[k] = g_last_call_us[k];
+  return H3D_OK;
 }
 
 // =====================================================================================
@@ -2125,6 +2137,8 @@ extern "C" int h3d_set_fused(int on) {
   g_use_fused = on != 0;
   return old;
 }
+
+extern "C" int h3d_set_debug_poison(int on) { return g_debug_poison.exchange(on != 0 ? 1 : 0); }
 
 extern "C" int h3d_set_sliced_vote(int on) {
   const int old = g_sliced_vote ? 1 : 0;

@@ -479,7 +479,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
           const int r = rlist[s];
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
           const int i = Q.yidx[e];
-          if (vote_cell(h, make_fast(h.coef[j], h.inv_s), j, Q.x[i], Q.y[i], Q.z[i]) == rcell[r]) rstale[r] = 1;
+          if (vote_cell(h, make_fast(h.coef[j], h.inv_s), j, Q.x[i], Q.y[i], Q.z[i]) == rcell[r]) atomicExch(&rstale[r], 1u);   // several threads may hit one record
         }
       }
       __syncthreads();

@@ -445,10 +445,14 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
           sh.warp_best[slot ^ 1][g][warp] = ((unsigned long long)m[g] << 32) | (0xFFFFFFFFu - bcell[g]);
       }
     }
-    if (tid < G) cp_async_wait_all();
-    __syncthreads();   // votes of this group, scan of the previous one, staging of the next: done
+    // the previous group's direction numbers are read BEFORE the barrier: right after it lanes 0..G-1
+    // of warp 0 enter phase k+1 and stage() rewrites this very slot ((k+1)+1 == k+2 mod 3), so a read
+    // placed behind the barrier by a late warp 1..G-1 would race with it (a record stored under the
+    // wrong direction, or skipped and left holding the previous frame's maximum)
     int prev_l = -1;
     if (prev_any && warp < G) prev_l = sh.dir[dprev][warp];
+    if (tid < G) cp_async_wait_all();
+    __syncthreads();   // votes of this group, scan of the previous one, staging of the next: done
     if (prev_l >= 0) {
       unsigned long long key = lane < kResWarps ? sh.warp_best[slot ^ 1][warp][lane] : 0ull;
       key = warp_max_u64(key);
