@@ -244,10 +244,18 @@ def _cpu_worker(args):
     from pointcloud_segmentation_b200 import synth
     orc = O.Oracle()
     eng = O.Reference() if use_ref else orc
+    if use_ref:
+        eng.set_index_recovery(False)      # time the reference calls only: no flat-index scan, no index lists
     t0 = time.perf_counter()
     filt = orc.prefilter(frame, synth.WINDOW, float(synth.LEAF))
+    t1 = time.perf_counter()
     tr = eng.hough3dlines(filt.astype(np.float64), GRANULARITY, synth.OPT_DX, MINVOTES, NLINES, mode=0)
-    return time.perf_counter() - t0, tr.n_lines
+    t2 = time.perf_counter()
+    phases = np.concatenate([[t1 - t0], np.asarray(tr.timing_us) * 1e-6]) if tr.timing_us is not None else np.zeros(7)
+    return t2 - t0, tr.n_lines, phases
+
+
+CPU_PHASES = ("prefilter", "add", "subtract", "getLine", "pointsCloseToLine", "orthogonal_LSQ", "removePoints")
 
 
 def _cpu_init(use_ref):
@@ -282,10 +290,15 @@ def run_cpu_arm(args):
             pool.map(_cpu_worker, jobs)
         t0 = time.perf_counter()
         lines = 0
+        phases, busy = np.zeros(len(CPU_PHASES)), 0.0
         for _ in range(args.steps):
-            lines += sum(r[1] for r in pool.map(_cpu_worker, jobs))
+            for r in pool.map(_cpu_worker, jobs):
+                lines += r[1]; phases += r[2]; busy += r[0]
         dt = time.perf_counter() - t0
     value = workers * args.steps / dt
+    n_done = workers * args.steps
+    phase_ms = {k: 1e3 * float(v) / n_done for k, v in zip(CPU_PHASES, phases)}
+    phase_ms["other (Hough ctor zero-fill, copies into PointCloud, driver)"] = 1e3 * (busy - float(phases.sum())) / n_done
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
@@ -295,7 +308,11 @@ def run_cpu_arm(args):
                    "frames_per_step": workers, "parallelism": f"{workers} single-threaded processes, one per host core",
                    "lines_per_frame": lines / max(1, workers * args.steps)},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "reference" if use_ref else "port",
-                         "sample": f"{workers} frames per step, one single-threaded process per core"},
+                         "sample": f"{workers} frames per step, one single-threaded process per core",
+                         "ms_per_frame_by_phase": phase_ms,
+                         "timed": "reference calls only (add/subtract/getLine/pointsCloseToLine/removePoints of the "
+                                  "unmodified library; orthogonal_LSQ and the pre-filter are the stated restatements); "
+                                  "the shim's flat-index recovery scan and index lists are switched off"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(out), flush=True)
@@ -308,8 +325,9 @@ def cpu_baseline_sample(frames):
     use_ref = cpu_reference_available()
     if use_ref:
         _cpu_init(True)
-    dt, _ = _cpu_worker((frames[0], use_ref))
+    dt, _, phases = _cpu_worker((frames[0], use_ref))
     return {"value": 1.0 / dt, "unit": UNIT, "cores": 1, "kind": "reference" if use_ref else "port",
+            "ms_by_phase": {k: 1e3 * float(v) for k, v in zip(CPU_PHASES, phases)},
             "sample": "1 frame of the same workload, single thread (the reference is single-threaded); "
                       "sphere construction excluded"}
 
@@ -588,6 +606,115 @@ def run_gpu_arm(args):
                          "one-pipeline result of the same frame")
 
 
+# ---------------------------------------------------------------------------------------------
+# --workload c3: BASELINE.json configs[2] as written
+# ---------------------------------------------------------------------------------------------
+def _c3_frame(k):
+    from pointcloud_segmentation_b200 import synth
+    poses = synth.tower_trajectory(1000)
+    return synth.tof_frame(pose=tuple(poses[k]), seed=1000 + int(k)).astype(np.float32)
+
+
+def _c3_oracle(frame):
+    from oracle import oracle as O
+    from pointcloud_segmentation_b200 import synth
+    orc = O.Oracle()
+    filt = orc.prefilter(frame, synth.WINDOW, float(synth.LEAF))
+    tr = orc.hough3dlines(filt.astype(np.float64), GRANULARITY, synth.OPT_DX, MINVOTES, NLINES, mode=0)
+    return [(int(it.votes), int(it.argmax), int(it.status), np.asarray(it.inliers1, dtype=np.uint32).tobytes(),
+             np.asarray(it.inliers2, dtype=np.uint32).tobytes(), np.asarray(it.a2).tobytes(), np.asarray(it.b2).tobytes())
+            for it in tr.iters]
+
+
+def run_c3(args):
+    """configs[2]: batched replay of 1000 DISTINCT synthetic ToF frames along the tower trajectory, once, sharded
+    frame-parallel over the N GPUs (frame i -> rank i mod N, no collective on the data path).  Host frames in,
+    line records + inlier lists out (the e2e form); device time = CUDA events around every h3d_replay_run call,
+    summed, max over ranks.  Parity: 50 frames of rank 0 (every 20th of the trajectory) are recomputed by the CPU
+    oracle after the timed region and compared record for record."""
+    import ctypes
+    import multiprocessing as mp
+    import torch
+    import torch.distributed as dist
+    from pointcloud_segmentation_b200 import capi, sharding, synth
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libh3d.so has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    total = 1000
+    mine = sharding.frames_for_rank(total, rank, world)
+    with mp.get_context("spawn").Pool(max(1, min(16, (os.cpu_count() or 1) // world))) as pool:
+        frames = np.stack(pool.map(_c3_frame, mine, chunksize=8))
+    n_pts, stride = frames.shape[1], frames.shape[2]
+    pinned = torch.from_numpy(frames).pin_memory()
+    K, chunk = args.concurrency, 64
+    capi.set_wait_mode(2 if K > 1 else 0)
+    replay = capi.Replay(K, args.sm_share if K > 1 else 0, GRANULARITY, synth.WINDOW, synth.LEAF, synth.OPT_DX, MINVOTES,
+                         NLINES, n_pts, chunk)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    warm = [pinned[k % len(mine)].data_ptr() for k in range(chunk)]
+    for _ in range(2):
+        replay.run(warm, [n_pts] * chunk, stride, on_device=False)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms, lines, got = 0.0, 0, {}
+    for c0 in range(0, len(mine), chunk):
+        idx = list(range(c0, min(c0 + chunk, len(mine))))
+        torch.cuda.synchronize()
+        ev0.record()
+        res = replay.run([pinned[k].data_ptr() for k in idx], [n_pts] * len(idx), stride, on_device=False)
+        torch.cuda.synchronize()
+        ev1.record(); ev1.synchronize()
+        ms += ev0.elapsed_time(ev1)
+        for q, k in enumerate(idx):
+            lines += res[q].n_lines
+            if rank == 0 and mine[k] % 20 == 0:
+                its = replay.iters[q * replay.max_iters:(q + 1) * replay.max_iters]
+                plq = replay.pool[q * replay.pool_cap:(q + 1) * replay.pool_cap]
+                tr = capi.Trace(res[q], its, plq)
+                got[k] = [(it["votes"], it["argmax"], it["status"], it["inliers1"].tobytes(), it["inliers2"].tobytes(),
+                           it["a2"].tobytes(), it["b2"].tobytes()) for it in tr.iters]
+    replay.close()
+    t = torch.tensor([ms, float(lines)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        ms = float(tmax[0].item())
+    lines_total = int(t[1].item())
+    if rank == 0:
+        from concurrent.futures import ThreadPoolExecutor
+        from oracle import oracle as O
+        O.build(ref=False)
+        keys = sorted(got)
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(max_workers=min(len(keys), os.cpu_count() or 1)) as ex:
+            want = list(ex.map(_c3_oracle, [frames[k] for k in keys]))
+        cpu_s = time.perf_counter() - t0
+        mism = sum(1 for k, w in zip(keys, want) if got[k] != w)
+        out = {"metric": "frames/s (configs[2]: replay of 1000 distinct ToF frames, frame-parallel over the GPUs)",
+               "value": total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "frames": total, "ms_total": ms,
+               "higher_is_better": True, "scaling": "strong", "dtype": "f64", "data": "synthetic",
+               "config": {"workload": "configs[2]: 1000 distinct 224x172 ToF frames along the tower trajectory, each "
+                                      "PassThrough+VoxelGrid -> Hough g6, opt_nlines 20, opt_minvotes 12; frame i on rank i mod N",
+                          "frames_in_flight_per_gpu": K, "sms_per_frame": args.sm_share if K > 1 else "all",
+                          "host_frames": "pinned host memory; H2D of every frame and D2H of its records inside the timed region"},
+               "lines_per_frame": lines_total / total,
+               "parity_vs_oracle": {"frames": len(keys), "mismatches": mism, "oracle_cpu_s": cpu_s,
+                                    "checked": "every iteration record (votes, argmax, status, both inlier index lists, a, b) "
+                                               "of every 20th trajectory frame against oracle/h3d_oracle.c"}}
+        print(json.dumps(out), flush=True)
+        if mism:
+            raise SystemExit(f"bench.py --workload c3: {mism} of {len(keys)} sampled frames differ from the oracle")
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -602,9 +729,14 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10 s CPU sample (profiling runs)")
     ap.add_argument("--no-direction-sharded", action="store_true",
                     help="skip the configs[3] leg (1 M points, accumulator sharded by direction over the ranks)")
+    ap.add_argument("--workload", choices=("c2", "c3"), default="c2",
+                    help="c2 (default): BASELINE configs[1] frames, the contract line; c3: configs[2] as written, "
+                         "1000 distinct frames replayed once with an oracle parity sample (takes a few minutes)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_cpu_arm(args)
+    elif args.workload == "c3":
+        run_c3(args)
     else:
         run_gpu_arm(args)
 

@@ -418,6 +418,11 @@ class Reference(_Base):
         rc = self.lib.ref_read_from_file(path.encode(), C.c_char(delim.encode()), _dp(a), C.c_size_t(cap), C.byref(n))
         return rc, a[:n.value].copy()
 
+    def set_index_recovery(self, on):
+        """on = False: the loop driver runs the reference calls only (no flat-index recovery scan after getLine,
+        no inlier index lists) -- what bench.py times; records then carry argmax = 0 and empty index lists."""
+        return bool(self.lib.ref_set_index_recovery(C.c_int(1 if on else 0)))
+
     def hough3dlines(self, xyz, granularity, dx, minvotes, nlines, mode=0, max_iters=None):
         p, n = _pts(xyz)
         cap_it = max_iters or (nlines + 2 if nlines else n + 2)
