@@ -408,6 +408,13 @@ int h3d_set_big_kernels(int on);
  * Returns the previous setting.  Results are identical either way. */
 int h3d_set_sliced_vote(int on);
 
+/* frames of a pipeline with a pre-filter and a bounded line count run on the frame fast path: K0 + widening +
+ * bounding box + shift + Hough constructor in ONE thread-block-cluster launch, first vote, loop, post-tests and
+ * one export kernel that writes the results into mapped pinned host memory -- the host waits once per frame.
+ * on = 0 forces the general path (eleven K0/prep launches, Hough constructor on the host, three waits).
+ * Returns the previous setting.  Results are identical either way. */
+int h3d_set_fast_frames(int on);
+
 /* debug aid: on != 0 makes every frame start from per-direction records of 0xFFFFFFFF votes, so a
  * record the first vote fails to write wins every argmax instead of silently keeping the previous
  * frame's value (the parity tests of the frames-in-flight replay run with it).  Returns the previous

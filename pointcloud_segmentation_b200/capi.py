@@ -650,3 +650,9 @@ def set_debug_poison(on):
     """Start every frame from per-direction records of 0xFFFFFFFF votes (a record the first vote skips then
     wins every argmax); returns the previous setting."""
     return int(lib().h3d_set_debug_poison(C.c_int(1 if on else 0)))
+
+
+def set_fast_frames(on):
+    """Frame fast path of the pipelines (one cluster launch for K0 + prep + Hough ctor, one wait per frame);
+    returns the previous setting."""
+    return bool(lib().h3d_set_fast_frames(C.c_int(1 if on else 0)))

@@ -209,10 +209,6 @@ extern "C" int h3d_sphere(int g, double *vertices, size_t cap_v, size_t *n_v, un
 }
 
 // ---- Hough: lib/hough.cpp:26-135 ---------------------------------------------------
-static double round_to_nearest(double v) {   // lib/hough.cpp:22-24
-  return (v > 0.0) ? floor(v + 0.5) : ceil(v - 0.5);
-}
-
 static int ensure_points(h3d_hough *h, size_t need) {
   if (need <= h->cap) return H3D_OK;
   size_t cap = h->cap ? h->cap : 4096;
@@ -435,38 +431,19 @@ static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const i
 // Hough::Hough discretisation (lib/hough.cpp:32-40) into the device descriptor
 static int configure_hough(h3d_hough *h, const double minP[3], const double maxP[3], double var_dx) {
   const Space &sp = *h->space;
-  const double nmax = sqrt((maxP[0] * maxP[0]) + (maxP[1] * maxP[1]) + (maxP[2] * maxP[2]));
-  const double nmin = sqrt((minP[0] * minP[0]) + (minP[1] * minP[1]) + (minP[2] * minP[2]));
-  const double max_x = nmax < nmin ? nmin : nmax;
-  const double range_x = 2 * max_x;
-  double dx = var_dx;
-  if (dx == 0.0) dx = range_x / 64.0;
-  const double nxd = round_to_nearest(range_x / dx);
-  if (!(nxd >= 0.0) || nxd > 65535.0) return fail(H3D_ERR_RANGE, "num_x out of range");
-  const size_t num_x = (size_t)nxd;
-  const unsigned long long cells = (unsigned long long)num_x * num_x * sp.num_b;
-  if (cells >= (1ull << 32))
+  const HoughGeom g = hough_geometry(minP, maxP, var_dx, (unsigned long long)sp.num_b);   // h3d_frame.cuh: host == device
+  if (g.rc == 1) return fail(H3D_ERR_RANGE, "num_x out of range");
+  if (g.rc == 2)
     return fail(H3D_ERR_RANGE, "accumulator has >= 2^32 cells (the reference's unsigned argmax index wraps)");
   HoughDev &d = h->d;
-  d.num_x = (int)num_x;
-  d.plane_cells = (unsigned)(num_x * num_x);
-  d.plane_stride = (d.plane_cells + 2u * (unsigned)num_x + 4u + 3u) & ~3u;   // + slack cells (BOUNDED vote form)
+  d.num_x = g.num_x;
+  d.plane_cells = g.plane_cells;
+  d.plane_stride = g.plane_stride;
   d.num_b = (int)sp.num_b;
-  d.max_x = max_x; d.dx = dx;
-  d.inv_s = 0; d.kmagic = 0;
-  d.fast_ok = (num_x >= 1 && num_x <= 4000 && dx > 0.0 && std::isfinite(max_x)) ? 1 : 0;
-  if (d.fast_ok) {
-    const long double inv_s = ldexpl(1.0L / (long double)dx, 20);
-    d.inv_s = (double)inv_s;
-    const long double bias = roundl((long double)max_x * inv_s + 524288.0L);
-    d.kmagic = (double)(6755399441055744.0L + bias);   // 1.5 * 2^52 + bias
-    if (!(bias >= 0.0L && bias < 4294967296.0L)) d.fast_ok = 0;
-  }
-  // box symmetric about the origin (PointCloud::shiftToOrigin): with every point inside it,
-  // |x'| <= max_x (1 + 1e-9), so 0 <= x_i, y_i <= num_x + 1 and the fast path needs no range test
-  d.bounded = d.fast_ok && num_x < 2000;
-  for (int c = 0; c < 3; ++c)
-    if (!(fabs(minP[c] + maxP[c]) <= 1e-9 * max_x)) d.bounded = 0;
+  d.max_x = g.max_x; d.dx = g.dx;
+  d.inv_s = g.inv_s; d.kmagic = g.kmagic;
+  d.fast_ok = g.fast_ok;
+  d.bounded = g.bounded;
   d.coef = sp.coef_dev;
   return H3D_OK;
 }
@@ -859,6 +836,7 @@ struct FrameCtx {
   h3d_segment *seg_dev = nullptr, *seg_host = nullptr;   // iters_cap records each; host copy pinned
   size_t seg_cap = 0, seg_n = 0, seg_grid = 0;
   double seg_ns[3] = {0, 0, 0};          // what shiftToOrigin subtracted in the current frame
+  const double *seg_ns_dev = nullptr;    // frame fast path: the same three doubles in device memory (FrameDev::ns)
   unsigned seg_pool_cap = 0;
   double *seg_scr = nullptr;             // 5 * seg_scr_n doubles
   size_t seg_scr_n = 0;
@@ -1053,6 +1031,7 @@ int enqueue_segments(FrameCtx &f, size_t grid) {
   sa.iters = f.iters_dev; sa.n_iters = &f.st_dev->n_iters; sa.pool = f.pool_dev; sa.pool_cap = f.seg_pool_cap;
   sa.src = f.src; sa.stride = f.src_stride; sa.src_is_float = f.src_is_float;
   for (int c = 0; c < 3; ++c) { sa.ns[c] = f.seg_ns[c]; sa.shift[c] = f.seg_ns[c]; }   // X.shift = 0 + newshift
+  sa.ns_dev = f.seg_ns_dev;
   sa.cfg = f.seg_cfg; sa.scr = f.seg_scr; sa.scr_n = f.seg_scr_n; sa.out = f.seg_dev;
   sa.pose = f.seg_pose; sa.pose_on = f.seg_pose_on ? 1 : 0;
   segment_tests_kernel<<<(unsigned)grid, kSegThreads, 0, f.hg->stream>>>(sa);
@@ -1132,6 +1111,7 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   a.near_t = sqrt_le_threshold(opt_dx);
   a.cell_off = hd.max_x / hd.dx + 0.5;
   a.prof = f.prof_dev; a.prof_iters = f.prof_iters;
+  a.fd = nullptr;
   f.prof_grid = grid;
   if (f.prof_dev)
     H3D_CUDA(cudaMemsetAsync(f.prof_dev, 0, (size_t)f.prof_iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long), s));
@@ -1519,6 +1499,27 @@ extern "C" int h3d_prefilter(const float *xyz_in, size_t n, size_t stride, const
   return rc;
 }
 
+// Frame fast path (h3d_frame.cuh): K0 + prep + Hough ctor in one cluster launch, first vote, fused loop,
+// post-tests and ONE export kernel that writes the results into mapped pinned host memory; the host
+// waits once per frame.
+struct FastPath {
+  bool on = false;              // the pipeline qualifies (pre-filter with a finite window, bounded line count)
+  bool count_clean = false;     // pf.count is all zero (the fast path leaves it so; the general path does not)
+  bool last_was_fast = false;   // the last frame ran here (h3d_pipeline_filtered reads the count from the descriptor)
+  K0Grid grid{};
+  int2 *occ = nullptr;
+  int *tile_sums = nullptr;
+  FrameDev *fd_dev = nullptr;
+  size_t smem_vote = 0, smem_loop = 0;
+  // host staging (pinned, mapped): [FrameDev][LoopState][iters][pool]; the segment records go to f.seg_host
+  unsigned char *stage_host = nullptr, *stage_dev = nullptr;
+  size_t off_st = 0, off_iters = 0, off_pool = 0, pool_entries = 0, stage_bytes = 0;
+  void release() {
+    cudaFree(occ); cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
+    occ = nullptr; tile_sums = nullptr; fd_dev = nullptr; stage_host = stage_dev = nullptr; on = false;
+  }
+};
+
 struct h3d_pipeline {
   h3d_pipeline_config cfg;
   FrameCtx f;
@@ -1531,7 +1532,165 @@ struct h3d_pipeline {
   size_t raw_cap_floats = 0;
   unsigned char *msg_dev = nullptr;   // PointCloud2 byte buffer of the current frame (h3d_pipeline_run_cloud2)
   size_t msg_cap = 0;
+  FastPath fast;
 };
+
+static std::atomic<int> g_fast_frames{1};   // h3d_set_fast_frames
+
+// one-time set-up of the fast path for a pipeline; leaves fast.on = false when it does not qualify
+static int fast_path_setup(h3d_pipeline *p) {
+  FastPath &fp = p->fast;
+  FrameCtx &f = p->f;
+  if (!p->cfg.prefilter || p->cfg.opt_nlines <= 0 || !(p->cfg.opt_dx > 0.0)) return H3D_OK;
+  if (!make_window_grid(p->win, p->cfg.leaf, p->pf.grid_cap, &fp.grid)) return H3D_OK;
+  const DeviceFacts &dev = f.hg->dev;
+  if (dev.cc < 90) return H3D_OK;   // thread-block clusters
+  cudaFuncAttributes fa;
+  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_frame_kernel<12>));
+  if (dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
+  fp.smem_vote = ((dev.smem_optin - fa.sharedSizeBytes) / 16) * 16;
+  H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
+  if (dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
+  fp.smem_loop = ((dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;
+  const size_t n = p->cfg.max_raw_points;
+  H3D_CUDA(cudaMalloc(&fp.occ, n * sizeof(int2)));
+  H3D_CUDA(cudaMalloc(&fp.tile_sums, 2 * kK0Cluster * sizeof(int)));
+  H3D_CUDA(cudaMalloc(&fp.fd_dev, sizeof(FrameDev)));
+  fp.off_st = (sizeof(FrameDev) + 255) & ~(size_t)255;
+  fp.off_iters = fp.off_st + ((sizeof(LoopState) + 255) & ~(size_t)255);
+  fp.off_pool = fp.off_iters + ((f.iters_cap * sizeof(h3d_iter) + 255) & ~(size_t)255);
+  fp.pool_entries = 2 * f.iters_cap * (size_t)kFrameMaxPoints;
+  if (fp.pool_entries > f.pool_cap) fp.pool_entries = f.pool_cap;
+  fp.stage_bytes = fp.off_pool + fp.pool_entries * sizeof(unsigned);
+  H3D_CUDA(cudaHostAlloc(&fp.stage_host, fp.stage_bytes, cudaHostAllocMapped));
+  H3D_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void **>(&fp.stage_dev), fp.stage_host, 0));
+  memset(fp.stage_host, 0, fp.off_pool);
+  H3D_CUDA(cudaMemsetAsync(p->pf.count, 0, p->pf.grid_cap * sizeof(int), f.hg->stream));
+  fp.count_clean = true;
+  fp.on = true;
+  return H3D_OK;
+}
+
+// One frame on the fast path.  *done = false: the frame did not qualify (FrameDev::status 2) and must be
+// re-run on the general path (the raw frame is still where it was).
+static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
+                          uint32_t *pool, size_t pool_cap, h3d_result *res, bool *done) {
+  *done = false;
+  FastPath &fp = p->fast;
+  FrameCtx &f = p->f;
+  h3d_hough *h = f.hg;
+  cudaStream_t s = h->stream;
+  const int opt_nlines = p->cfg.opt_nlines;
+  const int grid = (f.fused_ctas > 0 && f.fused_ctas < h->dev.sm_count) ? f.fused_ctas : h->dev.sm_count;
+  HoughDev &hd = h->d;
+  hd.num_b = (int)h->space->num_b; hd.coef = h->space->coef_dev;
+  hd.dir_begin = 0; hd.dir_count = hd.num_b;
+  hd.n = 0; hd.n_dev = nullptr;
+  h->has_negative = false;
+  const int groups = (hd.dir_count + kResG - 1) / kResG;
+  const int n_own = ((groups + grid - 1) / grid) * kResG;
+  const size_t xchg_words = 2 * ((size_t)opt_nlines + 2);
+  if (xchg_words > f.gbest_cap) {
+    H3D_CUDA(cudaStreamSynchronize(s));
+    cudaFree(f.gbest); f.gbest = nullptr; f.gbest_cap = 0;
+    H3D_CUDA(cudaMalloc(&f.gbest, xchg_words * sizeof(unsigned long long)));
+    f.gbest_cap = xchg_words;
+  }
+  if (!fp.count_clean) {
+    H3D_CUDA(cudaMemsetAsync(p->pf.count, 0, p->pf.grid_cap * sizeof(int), s));
+    fp.count_clean = true;
+  }
+  const unsigned st_pool_cap = (unsigned)((pool_cap < f.pool_cap && !f.seg_on) ? pool_cap : f.pool_cap);
+  const size_t st_max_iters = p->cfg.max_iters < f.iters_cap ? p->cfg.max_iters : f.iters_cap;
+
+  FrameArgs fa;
+  fa.raw = raw_dev; fa.n = (int)n; fa.stride = (int)stride;
+  fa.win = p->win; fa.grid = fp.grid;
+  fa.count = p->pf.count; fa.start = p->pf.start; fa.members = p->pf.members; fa.occ = fp.occ; fa.tile_sums = fp.tile_sums;
+  fa.filt = p->filt_dev; fa.out_cap = (int)p->cfg.max_raw_points;
+  fa.px = h->px; fa.py = h->py; fa.pz = h->pz; fa.w = h->w; fa.orig = f.orig;
+  fa.fd = fp.fd_dev;
+  fa.opt_dx = p->cfg.opt_dx; fa.num_b = (unsigned long long)hd.num_b;
+  fa.st = f.st_dev; fa.minvotes = p->cfg.opt_minvotes; fa.nlines_max = opt_nlines; fa.max_iters = (int)st_max_iters;
+  fa.pool_cap = st_pool_cap;
+  fa.xchg = f.gbest; fa.xchg_words = (int)xchg_words; fa.bar = f.sync_dev;
+  fa.smem_loop = (unsigned)fp.smem_loop; fa.tables_bytes = (unsigned)n_own * 16u; fa.smem_vote = (unsigned)fp.smem_vote;
+  frame_prefilter_kernel<<<kK0Cluster, kK0Threads, 0, s>>>(fa);
+  H3D_CUDA(cudaGetLastError());
+  H3D_CUDA(cudaEventRecord(f.ev[1], s));
+  if (g_debug_poison.load(std::memory_order_relaxed)) {
+    const size_t nd = (size_t)(hd.dir_count > 0 ? hd.dir_count : 1);
+    H3D_CUDA(cudaMemsetAsync(hd.dvotes, 0xFF, nd * sizeof(unsigned), s));
+    H3D_CUDA(cudaMemsetAsync(hd.dcell, 0xFF, nd * sizeof(unsigned), s));
+  }
+  // Hough::add, wrap.h:228
+  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_frame_kernel<12>), fp.smem_vote, h->dev.smem_optin));
+  H3D_CUDA(cudaEventRecord(f.ev[4], s));
+  vote_frame_kernel<12><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
+  H3D_CUDA(cudaGetLastError());
+  H3D_CUDA(cudaEventRecord(f.ev[2], s));
+  // the loop, wrap.h:237-342
+  FusedArgs a;
+  memset(&a, 0, sizeof a);
+  a.h = hd;
+  a.st = f.st_dev; a.iters = f.iters_dev; a.pool = f.pool_dev; a.orig = f.orig; a.dirs = h->space->dirs_dev;
+  a.xchg = f.gbest; a.bar = f.sync_dev;
+  a.n_own_max = n_own;
+  a.near_t = sqrt_le_threshold(p->cfg.opt_dx);
+  a.prof = f.prof_dev; a.prof_iters = f.prof_iters;
+  a.fd = fp.fd_dev;
+  f.prof_grid = grid;
+  if (f.prof_dev)
+    H3D_CUDA(cudaMemsetAsync(f.prof_dev, 0, (size_t)f.prof_iters * f.prof_ctas * kProfSlots * sizeof(unsigned long long), s));
+  H3D_TRY(launch_fused(f, a, fp.smem_loop, grid));
+  H3D_CUDA(cudaEventRecord(f.ev[5], s));
+  // wrap.h:261-337 on every accepted line, then everything back to the host in one piece
+  f.src = p->filt_dev; f.src_stride = 3; f.src_is_float = 1;
+  f.seg_pool_cap = st_pool_cap; f.seg_grid = 0; f.seg_n = 0;
+  f.seg_ns_dev = &fp.fd_dev->ns[0];
+  hd.n = (int)p->cfg.max_raw_points;   // sizes the post-tests' scratch (the real count is on the device)
+  const int rc_seg = enqueue_segments(f, (size_t)opt_nlines);
+  f.seg_ns_dev = nullptr;
+  hd.n = 0;
+  if (rc_seg != H3D_OK) return rc_seg;
+  ExportArgs ea;
+  ea.fd = fp.fd_dev; ea.st = f.st_dev; ea.iters = f.iters_dev; ea.pool = f.pool_dev;
+  ea.segs = (f.seg_on && f.seg_grid) ? f.seg_dev : nullptr;
+  ea.max_iters = (int)st_max_iters; ea.seg_cap = (int)f.seg_grid;
+  ea.pool_host_cap = (unsigned)fp.pool_entries;
+  ea.fd_out = reinterpret_cast<FrameDev *>(fp.stage_dev);
+  ea.st_out = reinterpret_cast<LoopState *>(fp.stage_dev + fp.off_st);
+  ea.iters_out = reinterpret_cast<h3d_iter *>(fp.stage_dev + fp.off_iters);
+  ea.pool_out = reinterpret_cast<unsigned *>(fp.stage_dev + fp.off_pool);
+  ea.segs_out = nullptr;
+  if (ea.segs) H3D_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void **>(&ea.segs_out), f.seg_host, 0));
+  frame_export_kernel<<<8, 256, 0, s>>>(ea);
+  H3D_CUDA(cudaGetLastError());
+  note_launches(3);                       // K0 cluster, first vote, export (loop and post-tests count themselves)
+  H3D_CUDA(cudaEventRecord(f.ev[3], s));
+  H3D_CUDA(frame_wait(f));                // the frame's only wait
+  const FrameDev &F = *reinterpret_cast<const FrameDev *>(fp.stage_host);
+  const LoopState &fin = *reinterpret_cast<const LoopState *>(fp.stage_host + fp.off_st);
+  if (F.status == 2) return H3D_OK;       // *done stays false: the general path takes the frame
+  *done = true;
+  fp.last_was_fast = true;
+  f.timed = true; f.fused = true;
+  res->n_input = (uint32_t)F.n;
+  res->num_b = h->space->num_b;
+  res->d = F.d;
+  if (F.status == 1) { res->rc = 1; return H3D_OK; }
+  for (int c = 0; c < 3; ++c) { res->shift[c] = 0.0 + F.ns[c]; f.seg_ns[c] = F.ns[c]; }
+  res->dx = F.g.dx; res->max_x = F.g.max_x; res->num_x = (uint64_t)F.g.num_x;
+  res->n_iters = (uint32_t)fin.n_iters; res->n_lines = (uint32_t)fin.n_lines; res->pool_used = fin.pool_used;
+  res->votes_cast = (uint64_t)F.n * hd.dir_count + fin.votes_cast;
+  const size_t n_rec = (size_t)fin.n_iters < st_max_iters ? (size_t)fin.n_iters : st_max_iters;
+  if (n_rec && iters) memcpy(iters, fp.stage_host + fp.off_iters, n_rec * sizeof(h3d_iter));
+  size_t n_pool = (size_t)fin.pool_used < pool_cap ? (size_t)fin.pool_used : pool_cap;
+  if (n_pool > fp.pool_entries) n_pool = fp.pool_entries;
+  if (n_pool && pool) memcpy(pool, fp.stage_host + fp.off_pool, n_pool * sizeof(unsigned));
+  if (f.seg_on && n_rec) f.seg_n = n_rec < f.seg_grid ? n_rec : f.seg_grid;
+  return H3D_OK;
+}
 
 // packs x,y,z of a PointCloud2 byte buffer into (x,y,z,0) float quadruples, message order
 __global__ void cloud2_gather_kernel(const unsigned char *__restrict__ data, h3d_cloud2_layout L, float4 *out) {
@@ -1566,6 +1725,7 @@ extern "C" int h3d_pipeline_create(const h3d_pipeline_config *cfg, h3d_pipeline 
   }
   p->raw_cap_floats = n * 8;
   H3D_CUDA(cudaMalloc(&p->raw_dev, p->raw_cap_floats * sizeof(float)));
+  H3D_TRY(fast_path_setup(p));
   *out = guard.release();
   return H3D_OK;
 }
@@ -1574,6 +1734,7 @@ extern "C" void h3d_pipeline_destroy(h3d_pipeline *p) {
   if (!p) return;
   if (p->f.hg) cudaStreamSynchronize(p->f.hg->stream);
   cudaFree(p->raw_dev); cudaFree(p->filt_dev); cudaFree(p->msg_dev);
+  p->fast.release();
   delete p;
 }
 
@@ -1588,7 +1749,28 @@ extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_
   h3d_hough *h = f.hg;
   cudaStream_t s = h->stream;
   H3D_CUDA(cudaEventRecord(f.ev[0], s));
+  p->fast.last_was_fast = false;
+  if (p->fast.on && g_use_fused && g_fast_frames.load(std::memory_order_relaxed) && n > 0) {
+    bool done = false;
+    const int rc_fast = frame_run_fast(p, raw_dev, n, stride, iters, pool, pool_cap, res, &done);
+    if (rc_fast != H3D_OK) return rc_fast;
+    if (done) {
+      for (auto &u : f.us) u = 0.0f;
+      if (f.timed) {
+        cudaEventElapsedTime(&f.us[0], f.ev[0], f.ev[1]);   // pre-filter + prep + ctor (one cluster launch)
+        cudaEventElapsedTime(&f.us[1], f.ev[4], f.ev[2]);   // the first vote kernel alone (Hough::add)
+        cudaEventElapsedTime(&f.us[2], f.ev[2], f.ev[5]);   // the loop kernel
+        cudaEventElapsedTime(&f.us[3], f.ev[0], f.ev[3]);   // whole frame, results in host memory
+        for (auto &u : f.us) u *= 1000.0f;
+      }
+      return H3D_OK;
+    }
+    memset(res, 0, sizeof *res);            // FrameDev::status 2: the general path takes the frame
+    f.timed = false;
+    H3D_CUDA(cudaEventRecord(f.ev[0], s));
+  }
   if (p->cfg.prefilter) {
+    p->fast.count_clean = false;
     H3D_TRY(prefilter_phase1(p->pf, raw_dev, (int)n, (int)stride, p->win, p->cfg.leaf, h->dev.sm_count, s));
     H3D_TRY(prefilter_phase2(p->pf, raw_dev, (int)n, (int)stride, p->win, p->grid_cells, p->filt_dev, (int)p->cfg.max_raw_points, 3, h->dev.sm_count, s));
     // wrap.h:175-189: float -> double widening of the filtered cloud (+ NaN/Inf strip, bbox)
@@ -1695,6 +1877,7 @@ extern "C" int h3d_segment_test_pose(const double *y_xyz, size_t n, const double
     sa.iters = rec; sa.n_iters = nullptr; sa.pool = nullptr; sa.pool_cap = 0;
     sa.src = pts; sa.stride = 3; sa.src_is_float = 0;
     for (int c = 0; c < 3; ++c) { sa.ns[c] = 0.0; sa.shift[c] = shift[c]; }   // y - 0.0 == y
+    sa.ns_dev = nullptr;
     sa.cfg = *cfg; sa.scr = scr; sa.scr_n = n; sa.out = seg;
     sa.pose_on = pose ? 1 : 0;
     if (pose) sa.pose = *pose; else memset(&sa.pose, 0, sizeof sa.pose);
@@ -1748,9 +1931,14 @@ extern "C" int h3d_pipeline_filtered(h3d_pipeline *p, float *out_xyz, size_t cap
   if (!p || !n_out) return fail(H3D_ERR_ARG, "bad argument");
   if (!p->cfg.prefilter) return fail(H3D_ERR_ARG, "pipeline has no pre-filter stage");
   cudaStream_t s = p->f.hg->stream;
-  H3D_CUDA(cudaMemcpyAsync(p->pf.st_host, p->pf.st, sizeof(K0State), cudaMemcpyDeviceToHost, s));
-  H3D_CUDA(cudaStreamSynchronize(s));
-  *n_out = (size_t)p->pf.st_host->n_out;
+  if (p->fast.last_was_fast) {
+    H3D_CUDA(cudaStreamSynchronize(s));
+    *n_out = (size_t)reinterpret_cast<const FrameDev *>(p->fast.stage_host)->n;
+  } else {
+    H3D_CUDA(cudaMemcpyAsync(p->pf.st_host, p->pf.st, sizeof(K0State), cudaMemcpyDeviceToHost, s));
+    H3D_CUDA(cudaStreamSynchronize(s));
+    *n_out = (size_t)p->pf.st_host->n_out;
+  }
   const size_t n_copy = *n_out < cap ? *n_out : cap;
   if (n_copy && out_xyz) H3D_CUDA(cudaMemcpy(out_xyz, p->filt_dev, n_copy * 3 * sizeof(float), cudaMemcpyDeviceToHost));
   return H3D_OK;
@@ -2137,6 +2325,8 @@ extern "C" int h3d_set_fused(int on) {
   g_use_fused = on != 0;
   return old;
 }
+
+extern "C" int h3d_set_fast_frames(int on) { return g_fast_frames.exchange(on != 0 ? 1 : 0); }
 
 extern "C" int h3d_set_debug_poison(int on) { return g_debug_poison.exchange(on != 0 ? 1 : 0); }
 

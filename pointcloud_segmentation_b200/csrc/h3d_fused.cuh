@@ -29,7 +29,7 @@
 #ifndef H3D_FUSED_CUH_
 #define H3D_FUSED_CUH_
 
-#include "h3d_loop.cuh"
+#include "h3d_frame.cuh"
 
 namespace h3d {
 
@@ -49,6 +49,8 @@ struct FusedArgs {
   double cell_off;            // max_x/dx + 0.5: cell coordinate of x' = 0
   unsigned long long *prof;   // measurement hook (nullable): [it][cta][kProfSlots] globaltimer stamps
   int prof_iters;
+  const FrameDev *fd;         // frame fast path (nullable): geometry, point count and shared-memory layout come from
+                              // the descriptor the frame's first kernel wrote; h.n / nb_planes / n_cap / cell_off above are unused
 };
 constexpr int kProfSlots = 16;
 constexpr int kFusedMaxSlots = 12;
@@ -330,10 +332,16 @@ __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints
 __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(16) FusedShared sh;
+  __shared__ HoughDev hs;
   constexpr int G = kResG;
-  const HoughDev &h = A.h;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int cta = blockIdx.x, n_cta = gridDim.x;
+  if (A.fd && A.fd->status != 0) return;   // the frame ended before the vote (wrap.h:202-212) or takes the general path
+  if (tid == 0) { if (A.fd) patch_hough(hs, A.h, *A.fd); else hs = A.h; }
+  __syncthreads();
+  const HoughDev &h = hs;
+  const int n_cap = A.fd ? A.fd->n_cap : A.n_cap;
+  const double cell_off = A.fd ? A.fd->cell_off : A.cell_off;
   // per-CTA record tables first, then the planes (+ pad word); behind the planes of a re-vote
   // round (the first vote uses 2*G planes over the same area) the live points and the inlier list
   const int n_own = A.n_own_max;
@@ -345,12 +353,12 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   unsigned *planes = reinterpret_cast<unsigned *>(smem_raw + tables_bytes);
   const unsigned stride = h.plane_stride, quads = stride / 4;
   const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
-  const int nb = A.nb_planes;
+  const int nb = A.fd ? A.fd->nb_planes : A.nb_planes;
   const unsigned dummy_sa = planes_sa + (unsigned)nb * stride * 4u;      // pad word of the loop layout
   FusedPoints Q;
   Q.x = reinterpret_cast<double *>(planes + (size_t)nb * stride + 4);
-  Q.y = Q.x + A.n_cap; Q.z = Q.y + A.n_cap;
-  Q.yidx = reinterpret_cast<int *>(Q.z + A.n_cap);
+  Q.y = Q.x + n_cap; Q.z = Q.y + n_cap;
+  Q.yidx = reinterpret_cast<int *>(Q.z + n_cap);
 
   if (A.prof && tid == 0 && A.prof_iters > 0) A.prof[(size_t)cta * kProfSlots + 15] = globaltimer_ns();   // kernel start
   // hough->add(X) ran just before this kernel (vote_resident_kernel, BOUNDED form): the records of
@@ -467,7 +475,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
           // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
           if (cy == 0 || cy == num_x - 1 ||
-              strip_may_hit(make_fast(h.coef[j], h.inv_s), a, b, t0, t1, A.cell_off, reach2, cx, cy))
+              strip_may_hit(make_fast(h.coef[j], h.inv_s), a, b, t0, t1, cell_off, reach2, cx, cy))
             rlist[atomicAdd(&sh.ns, 1)] = r;
         }
         named_bar_sync(1, un);

@@ -42,6 +42,8 @@ struct SegArgs {
   int stride, src_is_float;
   double ns[3];              // what shiftToOrigin subtracted (lib/pointcloud.cpp:18-26)
   double shift[3];           // X.shift
+  const double *ns_dev;      // not null: both of the above are read from here (3 doubles in device memory,
+                             // FrameDev::ns of the frame fast path: the host never sees the bounding box)
   h3d_segment_config cfg;
   h3d_pose pose;             // drone -> world (node.cpp:429-470)
   int pose_on;
@@ -60,7 +62,8 @@ __device__ __forceinline__ void seg_point(const SegArgs &A, unsigned k, double p
   for (int c = 0; c < 3; ++c) {
     const size_t e = (size_t)k * A.stride + c;
     const double v = A.src_is_float ? (double)static_cast<const float *>(A.src)[e] : static_cast<const double *>(A.src)[e];
-    p[c] = __dadd_rn(__dsub_rn(v, A.ns[c]), A.shift[c]);
+    const double nsc = A.ns_dev ? A.ns_dev[c] : A.ns[c], shc = A.ns_dev ? __dadd_rn(0.0, A.ns_dev[c]) : A.shift[c];
+    p[c] = __dadd_rn(__dsub_rn(v, nsc), shc);
   }
 }
 
