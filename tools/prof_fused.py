@@ -4,9 +4,15 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from pointcloud_segmentation_b200 import capi, synth
 
-frame = synth.tof_frame()
-pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frame.shape[0])
 share = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+which = int(sys.argv[2]) if len(sys.argv) > 2 else -1        # bench frame 0..15 (bench.make_frames), -1: synth default
+if which >= 0:
+    poses = synth.tower_trajectory(1000)
+    k = int(np.linspace(0, 999, 16).astype(int)[which])
+    frame = synth.tof_frame(pose=tuple(poses[k]), seed=1000 + k).astype(np.float32)
+else:
+    frame = synth.tof_frame()
+pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frame.shape[0])
 pipe.set_sm_share(share)
 pipe.profile_enable(24)
 for _ in range(3):
