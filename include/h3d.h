@@ -408,6 +408,13 @@ int h3d_set_big_kernels(int on);
  * Returns the previous setting.  Results are identical either way. */
 int h3d_set_sliced_vote(int on);
 
+/* the streaming vote (clouds that do not fit the register-resident form: configs[3], the direction shards, the
+ * general loop) stages point tiles in shared memory with TMA bulk copies (cp.async.bulk + mbarrier, 2048 points per
+ * stage) and votes up to 8 directions per tile.  mode 1 (default): TMA tiles; 0: the same loop with plain LDGs;
+ * 2: the round-1 kernel (2 directions per work item, four LDGs per point).  Returns the previous mode.  Results are
+ * identical in every mode. */
+int h3d_set_stream_mode(int mode);
+
 /* frames of a pipeline with a pre-filter and a bounded line count run on the frame fast path: K0 + widening +
  * bounding box + shift + Hough constructor in ONE thread-block-cluster launch, first vote, loop, post-tests and
  * one export kernel that writes the results into mapped pinned host memory -- the host waits once per frame.

@@ -656,3 +656,9 @@ def set_fast_frames(on):
     """Frame fast path of the pipelines (one cluster launch for K0 + prep + Hough ctor, one wait per frame);
     returns the previous setting."""
     return bool(lib().h3d_set_fast_frames(C.c_int(1 if on else 0)))
+
+
+def set_stream_mode(mode):
+    """Streaming vote kernel: 1 = TMA-staged point tiles (default), 0 = same loop with LDGs, 2 = round-1 kernel;
+    returns the previous mode."""
+    return int(lib().h3d_set_stream_mode(C.c_int(int(mode))))

@@ -373,6 +373,55 @@ static int launch_resident(h3d_hough *h, int ablate, const int *list, const int 
   return fail(H3D_ERR_ARG, "too many points for the resident vote kernel");
 }
 
+// TMA-staged streaming vote (vote_stream_kernel): D <= 8 planes + the point-tile ring in shared memory
+static std::atomic<int> g_stream_mode{1};   // h3d_set_stream_mode: 1 TMA tiles (default), 0 same loop with LDGs, 2 round-1 vote_kernel
+
+template <int D, bool BOUNDED, bool TMA>
+static int launch_stream_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense, size_t smem) {
+  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_stream_kernel<D, BOUNDED, TMA>), smem, h->dev.smem_optin));
+  vote_stream_kernel<D, BOUNDED, TMA><<<h->dev.sm_count, kStreamThreads, smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
+  note_launches(1);
+  H3D_CUDA(cudaGetLastError());
+  return H3D_OK;
+}
+
+template <int D>
+static int launch_stream_d(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense, size_t smem, bool tma) {
+  if (h->d.bounded) return tma ? launch_stream_t<D, true, true>(h, list, count_ptr, count_imm, dense, smem)
+                               : launch_stream_t<D, true, false>(h, list, count_ptr, count_imm, dense, smem);
+  return tma ? launch_stream_t<D, false, true>(h, list, count_ptr, count_imm, dense, smem)
+             : launch_stream_t<D, false, false>(h, list, count_ptr, count_imm, dense, smem);
+}
+
+// returns H3D_OK with *launched = false when the planes do not fit beside the tile ring
+static int launch_stream(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense, bool tma,
+                         bool *launched) {
+  *launched = false;
+  cudaFuncAttributes fa;
+  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_stream_kernel<1, false, true>));
+  const size_t ring = (size_t)kStreamStages * 3 * kStreamTile * sizeof(double);
+  const size_t plane_bytes = (size_t)h->d.plane_stride * sizeof(unsigned);
+  if (h->dev.smem_optin < fa.sharedSizeBytes + 512 + ring + plane_bytes + 16) return H3D_OK;
+  const size_t room = h->dev.smem_optin - fa.sharedSizeBytes - 512 - ring - 16;
+  int D = (int)(room / plane_bytes);
+  if (D > kStreamMaxD) D = kStreamMaxD;
+  // no more planes than keep every SM busy: items = ceil(directions / D) >= 2 per CTA when possible
+  const int dirs = count_ptr ? h->d.dir_count : count_imm;
+  while (D > 1 && (dirs + D - 1) / D < 2 * h->dev.sm_count) --D;
+  const size_t smem = ring + (size_t)D * plane_bytes + 16;
+  *launched = true;
+  switch (D) {
+    case 1: return launch_stream_d<1>(h, list, count_ptr, count_imm, dense, smem, tma);
+    case 2: return launch_stream_d<2>(h, list, count_ptr, count_imm, dense, smem, tma);
+    case 3: return launch_stream_d<3>(h, list, count_ptr, count_imm, dense, smem, tma);
+    case 4: return launch_stream_d<4>(h, list, count_ptr, count_imm, dense, smem, tma);
+    case 5: return launch_stream_d<5>(h, list, count_ptr, count_imm, dense, smem, tma);
+    case 6: return launch_stream_d<6>(h, list, count_ptr, count_imm, dense, smem, tma);
+    case 7: return launch_stream_d<7>(h, list, count_ptr, count_imm, dense, smem, tma);
+    default: return launch_stream_d<8>(h, list, count_ptr, count_imm, dense, smem, tma);
+  }
+}
+
 // D planes per CTA, two CTAs per SM when they fit.  D == 0: pick the kernel form
 // (register-resident points when they fit, else streaming with D = 2).
 static bool g_sliced_vote = true;   // h3d_set_sliced_vote
@@ -408,6 +457,12 @@ static int launch_vote(h3d_hough *h, int D, int ablate, const int *list, const i
       note_launches(2);
       H3D_CUDA(cudaGetLastError());
       return H3D_OK;
+    }
+    const int mode = g_stream_mode.load(std::memory_order_relaxed);
+    if (mode != 2 && ablate == 0 && !h->has_negative) {   // unit weights: the TMA-staged streaming form
+      bool launched = false;
+      H3D_TRY(launch_stream(h, list, count_ptr, count_imm, dense, mode == 1, &launched));
+      if (launched) return H3D_OK;
     }
     D = 2;
   }
@@ -2329,6 +2384,8 @@ extern "C" int h3d_set_fused(int on) {
 extern "C" int h3d_set_fast_frames(int on) { return g_fast_frames.exchange(on != 0 ? 1 : 0); }
 
 extern "C" int h3d_set_debug_poison(int on) { return g_debug_poison.exchange(on != 0 ? 1 : 0); }
+
+extern "C" int h3d_set_stream_mode(int mode) { return g_stream_mode.exchange(mode == 0 ? 0 : mode == 2 ? 2 : 1); }
 
 extern "C" int h3d_set_sliced_vote(int on) {
   const int old = g_sliced_vote ? 1 : 0;

@@ -22,10 +22,16 @@ __device__ __forceinline__ unsigned long long scan_plane(const HoughDev &h, unsi
   uint4 *p4 = reinterpret_cast<uint4 *>(plane);
   unsigned best = 0, bcell = 0;
   for (unsigned q = t; q < h.plane_stride / 4; q += THREADS) {
-    const uint4 v = p4[q];
+    uint4 v = p4[q];
     if ((v.x | v.y | v.z | v.w) == 0) continue;
     p4[q] = make_uint4(0, 0, 0, 0);
     const unsigned c0 = 4 * q;
+    if (c0 + 3 >= h.plane_cells) {   // slack cells of the BOUNDED vote forms: zeroed, never counted
+      if (c0 >= h.plane_cells) v.x = 0;
+      if (c0 + 1 >= h.plane_cells) v.y = 0;
+      if (c0 + 2 >= h.plane_cells) v.z = 0;
+      v.w = 0;
+    }
     if (v.x > best) { best = v.x; bcell = c0; }
     if (v.y > best) { best = v.y; bcell = c0 + 1; }
     if (v.z > best) { best = v.z; bcell = c0 + 2; }
@@ -167,6 +173,192 @@ vote_kernel(const HoughDev h, const int *__restrict__ list, const int *__restric
   for (unsigned q = threadIdx.x; q < D * h.plane_stride / 4; q += kVoteThreads) p4[q] = make_uint4(0, 0, 0, 0);
   __syncthreads();
   vote_items<D, ABLATE>(h, list, count, dense, planes, warp_best, blockIdx.x, gridDim.x);
+}
+
+// ---------------------------------------------------------------------------
+// K1 (TMA-staged streaming form, any N, unit weights): the 1 M-point / direction-sharded kernel.
+//
+// The D = 2 streaming form above re-reads every point once per PAIR of directions with four LDGs per point
+// (ncu, round 1: 39.7 warp-instructions per warp-vote, LSU pipe 37.6 %, spills at D = 4).  Here
+//   * a work item is D <= 8 directions (planes in shared memory), so a point is fetched once per EIGHT directions;
+//   * the points arrive as TILES through the TMA: one elected thread issues three 1-D bulk copies
+//     (cp.async.bulk.shared.global, SASS UBLKCP) of kStreamTile x/y/z doubles per stage into a ring of
+//     kStreamStages stages, completion is counted on an mbarrier per stage; no thread spends an LDG or an
+//     address computation on a point;
+//   * a thread lifts its kStreamP points of the tile from shared memory into registers once (LDS.64, conflict
+//     free), the CTA barrier that follows frees the stage for the next bulk copy, and the D directions are then
+//     voted from registers with the scaled coefficients of one direction broadcast from shared memory;
+//   * all weights are +1 (compact live points), so the increment is the merging red.shared.add form.
+// TMA = false keeps the same loop with plain coalesced LDGs (the A/B of DESIGN.md).
+// ---------------------------------------------------------------------------
+constexpr int kStreamThreads = 512, kStreamWarps = kStreamThreads / 32;
+constexpr int kStreamP = 4;                                  // points per thread per tile
+constexpr int kStreamTile = kStreamThreads * kStreamP;       // 2048 points = 48 KB per stage
+constexpr int kStreamStages = 2;
+constexpr int kStreamMaxD = 8;
+
+__device__ __forceinline__ void mbar_init(unsigned bar_sa, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar_sa), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar_sa, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_sa), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar_sa, unsigned parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      :: "r"(bar_sa), "r"(parity) : "memory");
+}
+// 1-D bulk copy global -> shared through the TMA unit; bytes % 16 == 0, both addresses 16-byte aligned
+__device__ __forceinline__ void tma_load_1d(unsigned dst_sa, const void *src, unsigned bytes, unsigned bar_sa) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(dst_sa), "l"(src), "r"(bytes), "r"(bar_sa) : "memory");
+}
+
+struct StreamShared {
+  unsigned long long full[kStreamStages];            // mbarriers: the stage's three bulk copies have landed
+  unsigned long long warp_best[kStreamMaxD][kStreamWarps];
+  double coef[kStreamMaxD][6];                       // scaled coefficients (FastCoef) of the item's directions
+  int dir[kStreamMaxD];                              // local direction numbers of the item (-1: none)
+};
+
+template <int D, bool BOUNDED, bool TMA>
+__global__ void __launch_bounds__(kStreamThreads, 1)
+vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ list, const int *__restrict__ count_ptr,
+                   int count_imm, unsigned *__restrict__ dense) {
+  extern __shared__ __align__(128) unsigned char stream_smem[];
+  __shared__ __align__(16) StreamShared sh;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int count = count_ptr ? *count_ptr : count_imm;
+  const int n = point_count(h);
+  const unsigned stride = h.plane_stride;
+  // layout: [ring: stages x {x, y, z} x kStreamTile doubles][planes: D x stride u32][pad word]
+  double *ring = reinterpret_cast<double *>(stream_smem);
+  unsigned *planes = reinterpret_cast<unsigned *>(stream_smem + (size_t)kStreamStages * 3 * kStreamTile * sizeof(double));
+  const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
+  const unsigned dummy_sa = planes_sa + (unsigned)D * stride * 4u;
+  const unsigned ring_sa = (unsigned)__cvta_generic_to_shared(ring);
+  const unsigned full_sa = (unsigned)__cvta_generic_to_shared(&sh.full[0]);
+  const int n_items = (count + D - 1) / D;
+  const int my_items = blockIdx.x < n_items ? (n_items - blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int n_tiles = (n + kStreamTile - 1) / kStreamTile;
+  const long long total_fills = (long long)my_items * n_tiles;
+
+  {
+    uint4 *p4 = reinterpret_cast<uint4 *>(planes);
+    for (unsigned q = tid; q < (unsigned)D * stride / 4 + 1; q += kStreamThreads) p4[q] = make_uint4(0, 0, 0, 0);
+  }
+  if (TMA && tid == 0) {
+    for (int s = 0; s < kStreamStages; ++s) mbar_init(full_sa + 8u * s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  // fill k of this CTA = tile (k mod n_tiles) of the cloud into stage (k mod kStreamStages)
+  auto issue_fill = [&](long long k) {
+    const int t = (int)(k % n_tiles), st = (int)(k % kStreamStages);
+    const int i0 = t * kStreamTile;
+    const int cnt = min(kStreamTile, n - i0);
+    const unsigned bytes = (unsigned)(((cnt + 1) & ~1) * 8);   // 16-byte granules: one double past an odd end is read, never used
+    const unsigned bar = full_sa + 8u * st;
+    const unsigned dst = ring_sa + (unsigned)st * 3u * kStreamTile * 8u;
+    mbar_expect_tx(bar, 3u * bytes);
+    tma_load_1d(dst, h.px + i0, bytes, bar);
+    tma_load_1d(dst + kStreamTile * 8u, h.py + i0, bytes, bar);
+    tma_load_1d(dst + 2u * kStreamTile * 8u, h.pz + i0, bytes, bar);
+  };
+  if (TMA && tid == 0)
+    for (long long k = 0; k < kStreamStages && k < total_fills; ++k) issue_fill(k);
+
+  const double kmagic = h.kmagic;
+  const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells, row4 = 4u * (unsigned)h.num_x;
+  const bool no_fast = !h.fast_ok;
+  long long fill = 0;
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    if (tid < D) {
+      const int e = item * D + tid;
+      const int l = e < count ? (list ? list[e] : e) : -1;
+      sh.dir[tid] = l;
+      const FastCoef f = make_fast(h.coef[h.dir_begin + (l < 0 ? 0 : l)], h.inv_s);
+      sh.coef[tid][0] = f.c0s; sh.coef[tid][1] = f.c1n; sh.coef[tid][2] = f.c2s; sh.coef[tid][3] = f.bxn; sh.coef[tid][4] = f.byn;
+    }
+    __syncthreads();
+    for (int t = 0; t < n_tiles; ++t, ++fill) {
+      const int st = (int)(fill % kStreamStages);
+      const int i0 = t * kStreamTile;
+      double x[kStreamP], y[kStreamP], z[kStreamP];
+      unsigned live = 0;
+      if (TMA) {
+        mbar_wait(full_sa + 8u * st, (unsigned)((fill / kStreamStages) & 1));
+        const double *bx = ring + (size_t)st * 3 * kStreamTile, *by = bx + kStreamTile, *bz = by + kStreamTile;
+#pragma unroll
+        for (int p = 0; p < kStreamP; ++p) {
+          const int k = tid + p * kStreamThreads;
+          x[p] = bx[k]; y[p] = by[k]; z[p] = bz[k];
+          live |= (i0 + k < n) ? (1u << p) : 0u;
+        }
+        __syncthreads();                                   // every thread holds its points: the stage is free
+        if (tid == 0 && fill + kStreamStages < total_fills) issue_fill(fill + kStreamStages);
+      } else {
+#pragma unroll
+        for (int p = 0; p < kStreamP; ++p) {
+          const int i = i0 + tid + p * kStreamThreads;
+          const bool ok = i < n;
+          x[p] = ok ? h.px[i] : 0.0; y[p] = ok ? h.py[i] : 0.0; z[p] = ok ? h.pz[i] : 0.0;
+          live |= ok ? (1u << p) : 0u;
+        }
+      }
+      const bool full_tile = i0 + kStreamTile <= n;          // CTA-uniform
+#pragma unroll 1
+      for (int d = 0; d < D; ++d) {
+        const int l = sh.dir[d];
+        if (l < 0) break;
+        FastCoef f;
+        f.c0s = sh.coef[d][0]; f.c1n = sh.coef[d][1]; f.c2s = sh.coef[d][2]; f.bxn = sh.coef[d][3]; f.byn = sh.coef[d][4];
+        const unsigned mine_sa = planes_sa + (unsigned)d * stride * 4u;
+        const unsigned drop_off = dummy_sa - mine_sa;
+        unsigned off[kStreamP];
+        unsigned gmin = 0xFFFFFFFFu, hacc = 0;
+#pragma unroll
+        for (int p = 0; p < kStreamP; ++p) {
+          if (BOUNDED) off[p] = vote_off_bounded(f, kmagic, row4, x[p], y[p], z[p], gmin);
+          else off[p] = 4u * vote_cell_acc(f, kmagic, num_x, x[p], y[p], z[p], gmin, hacc);
+        }
+        if (batch_unsure(gmin, hacc) | no_fast) {            // rare: within 8e-6 cell of a boundary
+#pragma unroll
+          for (int p = 0; p < kStreamP; ++p) {
+            const unsigned cell = vote_cell_checked_h(&h, l, x[p], y[p], z[p]);
+            off[p] = cell < plane_cells ? 4u * cell : drop_off;
+          }
+        }
+#pragma unroll
+        for (int p = 0; p < kStreamP; ++p) {
+          bool in = BOUNDED ? true : off[p] < 4u * plane_cells;
+          if (!full_tile) in = in && ((live >> p) & 1u);
+          red_shared_inc(in ? mine_sa + off[p] : dummy_sa);
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      const int l = sh.dir[d];
+      if (l < 0) continue;   // uniform across the CTA
+      const unsigned long long k = scan_plane<kStreamThreads>(h, planes + (size_t)d * stride, tid, h.dir_begin + l, dense);
+      if (lane == 0) sh.warp_best[d][warp] = k;
+    }
+    __syncthreads();
+    if (warp < D && sh.dir[warp] >= 0) {
+      unsigned long long k = lane < kStreamWarps ? sh.warp_best[warp][lane] : 0ull;
+      k = warp_max_u64(k);
+      if (lane == 0) store_record(h, sh.dir[warp], k);
+    }
+    __syncthreads();           // sh.dir / sh.coef are rewritten by the next item
+  }
 }
 
 // ---------------------------------------------------------------------------
