@@ -283,14 +283,49 @@ __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
     // (the next batch is in flight while this one is added) and every lane adds them in order from
     // the shuffles, so only the 32 dependent DADDs remain per batch (a lone lane reading get(k)
     // paid two dependent L2 round trips per element: 2 ms for the 11 k inliers of a configs[3] line)
+    //
+    // Most batches do not even need the chain.  While the running sum S stays inside one binade
+    // [2^e, 2^(e+1)), every partial sum is a multiple of u = 2^(e-52), and fl(S + x) = S + rne_u(x) whenever
+    // x/u is not exactly half-way between two integers (adding the integer S/u does not move a non-tie
+    // rounding).  So the warp rounds its 32 values to multiples of u, prefix-sums them as int64 on top of
+    // S/u, and accepts the batch iff no value was a tie and every partial sum P_j stays STRICTLY inside
+    // (2^52, 2^53) in magnitude -- then every intermediate result of the sequential chain had spacing u and
+    // S + sum is the chain's result bit for bit.  Otherwise (binade crossings, ~log2(n) of them, the first
+    // batches, sums near zero) this batch runs the chain.  ~45 instructions instead of 32 dependent DADDs.
     sum = 0.0;
     double cur = lane < n ? get(lane) : 0.0;
     for (int k0 = 0; k0 < n; k0 += 32) {
       const int kn = k0 + 32 + lane;
       const double nxt = kn < n ? get(kn) : 0.0;
       const int m = n - k0 < 32 ? n - k0 : 32;
+      bool done = false;
+      const int es = (int)((__double_as_longlong(sum) >> 52) & 0x7FF);      // biased exponent of S (uniform)
+      if (es > 100 && es < 1900) {
+        const double inv_u = __longlong_as_double((long long)(1023 + 52 + 1023 - es) << 52);   // 2^(52-e)
+        const double q = __dmul_rn(cur, inv_u);                              // exact: a power of two, no underflow
+        const double r = rint(q);                                            // lanes >= m hold 0
+        // |q| < 2^60 (int64 range; also rejects Inf/NaN), not a tie (q - r is exact).  A q that underflows
+        // is far below 1/2 and rounds to 0, as the chain's addition does.
+        const bool lane_ok = fabs(q) < 1152921504606846976.0 && fabs(__dsub_rn(q, r)) != 0.5;
+        long long pj = (long long)r;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const long long up = __shfl_up_sync(0xFFFFFFFFu, pj, o);
+          if (lane >= o) pj += up;
+        }
+        pj += (long long)__dmul_rn(sum, inv_u);                              // S/u: an integer in (2^52, 2^53)
+        const long long mag = pj < 0 ? -pj : pj;
+        const bool inside = mag > 4503599627370496LL && mag < 9007199254740992LL;
+        if (__all_sync(0xFFFFFFFFu, lane_ok && inside)) {
+          const long long last = __shfl_sync(0xFFFFFFFFu, pj, 31);
+          sum = __dmul_rn((double)last, __longlong_as_double((long long)(es - 52) << 52));   // P * u, exact
+          done = true;
+        }
+      }
+      if (!done) {
 #pragma unroll 4
-      for (int j = 0; j < m; ++j) sum = __dadd_rn(sum, __shfl_sync(0xFFFFFFFFu, cur, j));
+        for (int j = 0; j < m; ++j) sum = __dadd_rn(sum, __shfl_sync(0xFFFFFFFFu, cur, j));
+      }
       cur = nxt;
     }
   }
