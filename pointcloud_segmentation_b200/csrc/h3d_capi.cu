@@ -1601,7 +1601,7 @@ static int fast_path_setup(h3d_pipeline *p) {
   const DeviceFacts &dev = f.hg->dev;
   if (dev.cc < 90) return H3D_OK;   // thread-block clusters
   cudaFuncAttributes fa;
-  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_frame_kernel<12>));
+  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_frame_kernel));
   if (dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   fp.smem_vote = ((dev.smem_optin - fa.sharedSizeBytes) / 16) * 16;
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
@@ -1679,9 +1679,9 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
     H3D_CUDA(cudaMemsetAsync(hd.dcell, 0xFF, nd * sizeof(unsigned), s));
   }
   // Hough::add, wrap.h:228
-  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_frame_kernel<12>), fp.smem_vote, h->dev.smem_optin));
+  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_frame_kernel), fp.smem_vote, h->dev.smem_optin));
   H3D_CUDA(cudaEventRecord(f.ev[4], s));
-  vote_frame_kernel<12><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
+  vote_frame_kernel<<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
   H3D_CUDA(cudaGetLastError());
   H3D_CUDA(cudaEventRecord(f.ev[2], s));
   // the loop, wrap.h:237-342

@@ -179,22 +179,53 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   for (int k = gtid; k < A.xchg_words; k += T) A.xchg[k] = 0ull;
   if (gtid < 4) A.bar[gtid] = 0u;
 
+  // Every phase is a handful of dependent L2 round trips per thread, so the loops are written in batches:
+  // all loads of a batch are issued before the first result is used (a rolled loop costs one ~0.7 us round
+  // trip per iteration: 65 us for the first version of this kernel).
+  constexpr int U = 5;   // points per thread per batch: 5 * 8192 threads cover a 224x172 frame in one batch
+
   // ---- phase A: PassThrough window + voxel histogram ---------------------------------------------------
-  for (int i = gtid; i < A.n; i += T) {
-    const float3 p = load_xyz(A.raw, i, A.stride);
-    if (in_window(p, A.win)) atomicAdd(&A.count[window_voxel_key(p, G)], 1);
+  for (int i0 = gtid; i0 < A.n; i0 += U * T) {
+    float3 p[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * T;
+      p[u] = i < A.n ? load_xyz(A.raw, i, A.stride) : make_float3(NAN, NAN, NAN);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (in_window(p[u], A.win)) atomicAdd(&A.count[window_voxel_key(p[u], G)], 1);
   }
   cluster.sync();
 
   // ---- phase B: exclusive scans over the grid (point offsets, output slots) ----------------------------
-  // CTA `rank` owns cells [t0, t1); warp w of it the chunk [c0, c1); a warp reads 32 consecutive cells per step
-  const int tile = (((G.cells + kK0Cluster - 1) / kK0Cluster) + 1023) & ~1023;
+  // CTA `rank` owns cells [t0, t1); warp w of it the chunk [c0, c1); a warp reads 128 consecutive cells per
+  // step, a lane four of them (one 16-byte load)
+  const int tile = (((G.cells + kK0Cluster - 1) / kK0Cluster) + 4095) & ~4095;
   const int t0 = min(rank * tile, G.cells), t1 = min(t0 + tile, G.cells);
-  const int chunk = tile / kK0Warps;                     // multiple of 32
+  const int chunk = tile / kK0Warps;                     // multiple of 128
   const int c0 = min(t0 + warp * chunk, t1), c1 = min(c0 + chunk, t1);
+  auto load4 = [&](int c) -> int4 {                      // cells c..c+3 of this warp's chunk (0 beyond its end)
+    if (c + 3 < c1) return *reinterpret_cast<const int4 *>(A.count + c);
+    int4 v = make_int4(0, 0, 0, 0);
+    if (c < c1) v.x = A.count[c];
+    if (c + 1 < c1) v.y = A.count[c + 1];
+    if (c + 2 < c1) v.z = A.count[c + 2];
+    return v;
+  };
+  constexpr int SB = 4;                                  // steps per batch
   {
     int sc = 0, sn = 0;
-    for (int c = c0 + lane; c < c1; c += 32) { const int v = A.count[c]; sc += v; sn += v > 0; }
+    for (int cb = c0; cb < c1; cb += SB * 128) {
+      int4 v[SB];
+#pragma unroll
+      for (int q = 0; q < SB; ++q) v[q] = load4(cb + q * 128 + 4 * lane);
+#pragma unroll
+      for (int q = 0; q < SB; ++q) {
+        sc += v[q].x + v[q].y + v[q].z + v[q].w;
+        sn += (v[q].x > 0) + (v[q].y > 0) + (v[q].z > 0) + (v[q].w > 0);
+      }
+    }
     sc = __reduce_add_sync(0xFFFFFFFFu, sc); sn = __reduce_add_sync(0xFFFFFFFFu, sn);
     if (lane == 0) wsum[warp] = make_int2(sc, sn);
   }
@@ -219,31 +250,51 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
       n_window += sc; n_out += sn;
     }
     int run_c = bc + wpre[warp].x, run_n = bn + wpre[warp].y;
-    const unsigned below = (1u << lane) - 1u;
-    for (int cb = c0; cb < c1; cb += 32) {
-      const int c = cb + lane;
-      const int v = c < c1 ? A.count[c] : 0;
-      const unsigned m = __ballot_sync(0xFFFFFFFFu, v > 0);
-      if (m == 0) continue;                                // most of the grid is empty
-      int inc = v;
-      for (int o = 1; o < 32; o <<= 1) { const int x = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= o) inc += x; }
-      if (v > 0) {
-        const int s = run_c + inc - v;
-        A.start[c] = s;
-        A.occ[run_n + __popc(m & below)] = make_int2(s, v);
+    for (int cb = c0; cb < c1; cb += SB * 128) {
+      int4 v[SB];
+#pragma unroll
+      for (int q = 0; q < SB; ++q) v[q] = load4(cb + q * 128 + 4 * lane);
+#pragma unroll
+      for (int q = 0; q < SB; ++q) {
+        const int s4 = v[q].x + v[q].y + v[q].z + v[q].w;
+        if (__ballot_sync(0xFFFFFFFFu, s4 > 0) == 0) continue;               // most of the grid is empty
+        const int n4 = (v[q].x > 0) + (v[q].y > 0) + (v[q].z > 0) + (v[q].w > 0);
+        int ic = s4, in = n4;
+        for (int o = 1; o < 32; o <<= 1) {
+          const int x = __shfl_up_sync(0xFFFFFFFFu, ic, o), y = __shfl_up_sync(0xFFFFFFFFu, in, o);
+          if (lane >= o) { ic += x; in += y; }
+        }
+        int sc = run_c + ic - s4, sn = run_n + in - n4;                      // exclusive prefixes of this lane's 4 cells
+        const int c = cb + q * 128 + 4 * lane;
+        const int vv[4] = {v[q].x, v[q].y, v[q].z, v[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          if (vv[e] > 0) {
+            A.start[c + e] = sc;
+            A.occ[sn] = make_int2(sc, vv[e]);
+            sc += vv[e]; ++sn;
+          }
+        }
+        run_c += __shfl_sync(0xFFFFFFFFu, ic, 31);
+        run_n += __shfl_sync(0xFFFFFFFFu, in, 31);
       }
-      run_c += __shfl_sync(0xFFFFFFFFu, inc, 31);
-      run_n += __popc(m);
     }
   }
   cluster.sync();
 
   // ---- phase C: scatter the raw indices into their voxel's list; the histogram goes back to zero -------
-  for (int i = gtid; i < A.n; i += T) {
-    const float3 p = load_xyz(A.raw, i, A.stride);
-    if (!in_window(p, A.win)) continue;
-    const int key = window_voxel_key(p, G);
-    A.members[A.start[key] + atomicSub(&A.count[key], 1) - 1] = i;
+  for (int i0 = gtid; i0 < A.n; i0 += U * T) {
+    int key[U], st[U], old[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * T;
+      const float3 p = i < A.n ? load_xyz(A.raw, i, A.stride) : make_float3(NAN, NAN, NAN);
+      key[u] = in_window(p, A.win) ? window_voxel_key(p, G) : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) if (key[u] >= 0) { st[u] = A.start[key[u]]; old[u] = atomicSub(&A.count[key[u]], 1); }
+#pragma unroll
+    for (int u = 0; u < U; ++u) if (key[u] >= 0) A.members[st[u] + old[u] - 1] = i0 + u * T;
   }
   cluster.sync();
 
@@ -251,20 +302,37 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   // order), sequential float sums, centroid; float bounding box of the centroids -------------------------
   const int n_keep = min(n_out, A.out_cap);
   {
+    constexpr int LM = 24;                                 // members sorted in local memory up to here
     int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
     for (int s = gtid; s < n_keep; s += T) {
       const int2 oc = A.occ[s];
       int *m = A.members + oc.x;
-      for (int a = 1; a < oc.y; ++a) {                     // insertion sort: lists are a handful of points long
-        const int key = m[a];
-        int b = a - 1;
-        while (b >= 0 && m[b] > key) { m[b + 1] = m[b]; --b; }
-        m[b + 1] = key;
-      }
       float cx = 0.0f, cy = 0.0f, cz = 0.0f;
-      for (int a = 0; a < oc.y; ++a) {
-        const float3 p = load_xyz(A.raw, m[a], A.stride);
-        cx = __fadd_rn(cx, p.x); cy = __fadd_rn(cy, p.y); cz = __fadd_rn(cz, p.z);
+      if (oc.y <= LM) {
+        int ml[LM];
+        float lx[LM], ly[LM], lz[LM];
+#pragma unroll 4
+        for (int a = 0; a < oc.y; ++a) ml[a] = m[a];
+        for (int a = 1; a < oc.y; ++a) {                   // insertion sort: lists are a handful of points long
+          const int key = ml[a];
+          int b = a - 1;
+          while (b >= 0 && ml[b] > key) { ml[b + 1] = ml[b]; --b; }
+          ml[b + 1] = key;
+        }
+#pragma unroll 4
+        for (int a = 0; a < oc.y; ++a) { const float3 p = load_xyz(A.raw, ml[a], A.stride); lx[a] = p.x; ly[a] = p.y; lz[a] = p.z; }
+        for (int a = 0; a < oc.y; ++a) { cx = __fadd_rn(cx, lx[a]); cy = __fadd_rn(cy, ly[a]); cz = __fadd_rn(cz, lz[a]); }
+      } else {
+        for (int a = 1; a < oc.y; ++a) {
+          const int key = m[a];
+          int b = a - 1;
+          while (b >= 0 && m[b] > key) { m[b + 1] = m[b]; --b; }
+          m[b + 1] = key;
+        }
+        for (int a = 0; a < oc.y; ++a) {
+          const float3 p = load_xyz(A.raw, m[a], A.stride);
+          cx = __fadd_rn(cx, p.x); cy = __fadd_rn(cy, p.y); cz = __fadd_rn(cz, p.z);
+        }
       }
       const float fc = (float)oc.y;
       cx = __fdiv_rn(cx, fc); cy = __fdiv_rn(cy, fc); cz = __fdiv_rn(cz, fc);
@@ -364,7 +432,9 @@ __device__ __forceinline__ void patch_hough(HoughDev &h, const HoughDev &fixed, 
 
 // Hough::add of a frame on the fast path: the BOUNDED resident vote with the widest slot count (the host
 // does not know the point count; a warp skips the slots it holds no point of), geometry from the descriptor.
-template <int P>
+// The slot count P = ceil(n / 512) is picked ON THE DEVICE: the kernel holds the twelve instantiations of the
+// vote loop and branches once (only the taken one occupies the instruction cache; the register allocation is
+// that of P = 12 either way, and one CTA per SM is resident regardless).
 __global__ void __launch_bounds__(kResThreads, 1)
 vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__restrict__ fd) {
   extern __shared__ __align__(16) unsigned planes[];
@@ -375,7 +445,21 @@ vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__rest
   __syncthreads();
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
   for (unsigned q = threadIdx.x; q < 2 * kResG * hs.plane_stride / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-  vote_resident<P, 0, true>(hs, nullptr, hs.dir_count, planes, sh, blockIdx.x, gridDim.x);
+  const int cta = blockIdx.x, n_cta = gridDim.x, count = hs.dir_count;
+  switch ((hs.n + kResThreads - 1) / kResThreads) {
+    case 0: case 1: vote_resident<1, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 2: vote_resident<2, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 3: vote_resident<3, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 4: vote_resident<4, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 5: vote_resident<5, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 6: vote_resident<6, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 7: vote_resident<7, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 8: vote_resident<8, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 9: vote_resident<9, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 10: vote_resident<10, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 11: vote_resident<11, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    default: vote_resident<12, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+  }
 }
 
 // ---- results to the host in one piece: written straight into mapped pinned host memory ----------------

@@ -303,7 +303,7 @@ __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints
                                             unsigned dummy_sa, unsigned &best0, unsigned &best1) {
   const double kmagic = h.kmagic;
   const unsigned row4 = 4u * (unsigned)h.num_x, plane_cells = h.plane_cells, lim = 4u * h.plane_cells;
-  const bool two = j1 >= 0;
+  const bool two = j1 >= 0, no_fast = !h.fast_ok;
   unsigned b0 = 0, b1 = 0;
 #pragma unroll 2
   for (int i = threadIdx.x; i < n_alive; i += kResThreads) {
@@ -311,7 +311,7 @@ __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints
     unsigned gmin = 0xFFFFFFFFu;
     unsigned o0 = vote_off_bounded(f0, kmagic, row4, x, y, z, gmin);
     unsigned o1 = vote_off_bounded(f1, kmagic, row4, x, y, z, gmin);
-    if ((gmin < 0x10000u) | !h.fast_ok) {   // rare: within 8e-6 cell of a boundary
+    if ((gmin < 0x10000u) | no_fast) {   // rare: within 8e-6 cell of a boundary
       const unsigned c0 = vote_cell_checked(h.coef + j0, h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
       o0 = c0 < plane_cells ? 4u * c0 : lim;
       if (two) {

@@ -545,6 +545,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
   __syncthreads();   // also orders the kernel's zero-fill of the planes
   const double kmagic = h.kmagic, inv_s = h.inv_s;
   const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells, row4 = 4u * (unsigned)h.num_x;
+  const bool no_fast = !h.fast_ok;   // in a register: h may live in shared memory, and the asm increments clobber memory
   unsigned sink = 0;
   bool prev_any = false;
   int k = 0;
@@ -579,7 +580,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
               else if (BOUNDED) off[c] = vote_off_bounded(f, kmagic, row4, px[p], py[p], pz[p], gmin);
               else off[c] = 4u * vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], gmin, hacc);
             }
-            if (ABLATE != 2 && (batch_unsure(gmin, hacc) | !h.fast_ok)) {   // rare: within 8e-6 cell of a boundary
+            if (ABLATE != 2 && (batch_unsure(gmin, hacc) | no_fast)) {   // rare: within 8e-6 cell of a boundary
 #pragma unroll
               for (int c = 0; c < CH; ++c) {   // unrolled: register arrays must not be indexed dynamically
                 const int p = p0 + c;
@@ -608,7 +609,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
               if (ABLATE == 2) o = 4u * (((unsigned)(tid + p * kResThreads) * 2654435761u + (unsigned)l * 40503u) % plane_cells);
               else if (BOUNDED) o = vote_off_bounded(f, kmagic, row4, px[p], py[p], pz[p], g1);
               else o = 4u * vote_cell_acc(f, kmagic, num_x, px[p], py[p], pz[p], g1, h1);
-              if (ABLATE != 2 && (batch_unsure(g1, h1) | !h.fast_ok)) {
+              if (ABLATE != 2 && (batch_unsure(g1, h1) | no_fast)) {
                 const unsigned cell = vote_cell_checked_h(&h, l, px[p], py[p], pz[p]);
                 o = cell < plane_cells ? 4u * cell : drop_off;
               }
