@@ -422,6 +422,11 @@ int h3d_set_stream_mode(int mode);
  * Returns the previous setting.  Results are identical either way. */
 int h3d_set_fast_frames(int on);
 
+/* first vote of the frame fast path: on = 1 (default) the shared-memory increment returns the old count and
+ * every thread tracks the maximum of its votes (no plane scan); on = 0 increments with the merging RED form and
+ * scans every plane.  Returns the previous setting.  Results are identical either way. */
+int h3d_set_vote_track(int on);
+
 /* debug aid: on != 0 makes every frame start from per-direction records of 0xFFFFFFFF votes, so a
  * record the first vote fails to write wins every argmax instead of silently keeping the previous
  * frame's value (the parity tests of the frames-in-flight replay run with it).  Returns the previous

@@ -662,3 +662,9 @@ def set_stream_mode(mode):
     """Streaming vote kernel: 1 = TMA-staged point tiles (default), 0 = same loop with LDGs, 2 = round-1 kernel;
     returns the previous mode."""
     return int(lib().h3d_set_stream_mode(C.c_int(int(mode))))
+
+
+def set_vote_track(on):
+    """First vote of the frame fast path: track maxima through the atomics' return values (True, default) or
+    scan the planes (False); returns the previous setting."""
+    return bool(lib().h3d_set_vote_track(C.c_int(1 if on else 0)))

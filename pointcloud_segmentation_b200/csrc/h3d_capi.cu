@@ -1591,6 +1591,7 @@ struct h3d_pipeline {
 };
 
 static std::atomic<int> g_fast_frames{1};   // h3d_set_fast_frames
+static std::atomic<int> g_vote_track{1};    // h3d_set_vote_track: first vote of the fast path tracks maxima instead of scanning planes
 
 // one-time set-up of the fast path for a pipeline; leaves fast.on = false when it does not qualify
 static int fast_path_setup(h3d_pipeline *p) {
@@ -1601,7 +1602,7 @@ static int fast_path_setup(h3d_pipeline *p) {
   const DeviceFacts &dev = f.hg->dev;
   if (dev.cc < 90) return H3D_OK;   // thread-block clusters
   cudaFuncAttributes fa;
-  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_frame_kernel));
+  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_frame_kernel<true>));
   if (dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   fp.smem_vote = ((dev.smem_optin - fa.sharedSizeBytes) / 16) * 16;
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
@@ -1679,9 +1680,12 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
     H3D_CUDA(cudaMemsetAsync(hd.dcell, 0xFF, nd * sizeof(unsigned), s));
   }
   // Hough::add, wrap.h:228
-  H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_frame_kernel), fp.smem_vote, h->dev.smem_optin));
+  const bool track = g_vote_track.load(std::memory_order_relaxed) != 0;
+  H3D_TRY(ensure_dyn_smem(track ? reinterpret_cast<const void *>(vote_frame_kernel<true>)
+                                : reinterpret_cast<const void *>(vote_frame_kernel<false>), fp.smem_vote, h->dev.smem_optin));
   H3D_CUDA(cudaEventRecord(f.ev[4], s));
-  vote_frame_kernel<<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
+  if (track) vote_frame_kernel<true><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
+  else vote_frame_kernel<false><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
   H3D_CUDA(cudaGetLastError());
   H3D_CUDA(cudaEventRecord(f.ev[2], s));
   // the loop, wrap.h:237-342
@@ -2380,6 +2384,8 @@ extern "C" int h3d_set_fused(int on) {
   g_use_fused = on != 0;
   return old;
 }
+
+extern "C" int h3d_set_vote_track(int on) { return g_vote_track.exchange(on != 0 ? 1 : 0); }
 
 extern "C" int h3d_set_fast_frames(int on) { return g_fast_frames.exchange(on != 0 ? 1 : 0); }
 

@@ -148,6 +148,13 @@ __device__ __forceinline__ bool batch_unsure(unsigned gmin, unsigned hacc) { ret
 __device__ __forceinline__ void red_shared_inc(unsigned addr) {
   asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(addr) : "memory");
 }
+// shared-memory increment that returns the old count (ATOMS.ADD): the last voter of a cell sees its final
+// count - 1, so max over all votes of (old + 1) is the plane maximum -- no scan of the plane needed
+__device__ __forceinline__ unsigned atom_shared_inc_ret(unsigned addr) {
+  unsigned old;
+  asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr) : "memory");
+  return old;
+}
 __device__ __forceinline__ void red_shared_add(unsigned addr, unsigned val, bool pred) {
   asm volatile(
       "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p red.shared.add.u32 [%0], %1;\n\t}"

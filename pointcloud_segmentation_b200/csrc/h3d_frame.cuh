@@ -435,6 +435,7 @@ __device__ __forceinline__ void patch_hough(HoughDev &h, const HoughDev &fixed, 
 // The slot count P = ceil(n / 512) is picked ON THE DEVICE: the kernel holds the twelve instantiations of the
 // vote loop and branches once (only the taken one occupies the instruction cache; the register allocation is
 // that of P = 12 either way, and one CTA per SM is resident regardless).
+template <bool TRACK>
 __global__ void __launch_bounds__(kResThreads, 1)
 vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__restrict__ fd) {
   extern __shared__ __align__(16) unsigned planes[];
@@ -446,20 +447,22 @@ vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__rest
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
   for (unsigned q = threadIdx.x; q < 2 * kResG * hs.plane_stride / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
   const int cta = blockIdx.x, n_cta = gridDim.x, count = hs.dir_count;
+#define H3D_FRAME_VOTE(PP) vote_resident<PP, 0, true, TRACK>(hs, nullptr, count, planes, sh, cta, n_cta); break;
   switch ((hs.n + kResThreads - 1) / kResThreads) {
-    case 0: case 1: vote_resident<1, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 2: vote_resident<2, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 3: vote_resident<3, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 4: vote_resident<4, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 5: vote_resident<5, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 6: vote_resident<6, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 7: vote_resident<7, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 8: vote_resident<8, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 9: vote_resident<9, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 10: vote_resident<10, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    case 11: vote_resident<11, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
-    default: vote_resident<12, 0, true>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+    case 0: case 1: H3D_FRAME_VOTE(1)
+    case 2: H3D_FRAME_VOTE(2)
+    case 3: H3D_FRAME_VOTE(3)
+    case 4: H3D_FRAME_VOTE(4)
+    case 5: H3D_FRAME_VOTE(5)
+    case 6: H3D_FRAME_VOTE(6)
+    case 7: H3D_FRAME_VOTE(7)
+    case 8: H3D_FRAME_VOTE(8)
+    case 9: H3D_FRAME_VOTE(9)
+    case 10: H3D_FRAME_VOTE(10)
+    case 11: H3D_FRAME_VOTE(11)
+    default: H3D_FRAME_VOTE(12)
   }
+#undef H3D_FRAME_VOTE
 }
 
 // ---- results to the host in one piece: written straight into mapped pinned host memory ----------------

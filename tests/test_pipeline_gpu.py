@@ -8,16 +8,18 @@ from test_loop_gpu import _compare
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["fast", "fused", "multikernel"])
+@pytest.fixture(autouse=True, params=["fast", "fast_scan", "fused", "multikernel"])
 def loop_form(request, h3d):
     """Every test runs on the frame fast path (one cluster launch for K0 + prep + Hough ctor, one wait), with
     the fused persistent loop kernel behind the eleven-launch K0 and the host-side ctor, and with the general
     multi-kernel loop."""
     old = h3d.set_fused(request.param != "multikernel")
-    old_fast = h3d.set_fast_frames(request.param == "fast")
+    old_fast = h3d.set_fast_frames(request.param.startswith("fast"))
+    old_track = h3d.set_vote_track(request.param != "fast_scan")   # fast_scan: first vote scans its planes (RED form)
     yield request.param
     h3d.set_fused(old)
     h3d.set_fast_frames(old_fast)
+    h3d.set_vote_track(old_track)
 
 
 def _frames():

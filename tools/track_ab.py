@@ -1,0 +1,27 @@
+"""A/B of the first vote of the frame fast path on the 16 bench frames: TRACK (atomics return the old count,
+maxima tracked per thread, planes only zero-filled) against SCAN (merging RED increments + plane scan)."""
+import os, sys, json
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from pointcloud_segmentation_b200 import capi, synth
+import bench
+
+frames = bench.make_frames(16)
+for share in (0, 18):
+    for track in (True, False):
+        capi.set_vote_track(track)
+        pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frames.shape[1])
+        pipe.set_sm_share(share)
+        us = []
+        for rep in range(4):
+            for k in range(16):
+                res = pipe.run(frames[k])
+                if rep:
+                    us.append((res.n_input, *pipe.timing_us()))
+        pipe.close()
+        a = np.array(us)
+        print(json.dumps({"share": share or 148, "vote": "track" if track else "scan", "k0_us": a[:, 1].mean(),
+                          "first_vote_us": a[:, 2].mean(), "loop_us": a[:, 3].mean(), "frame_us": a[:, 4].mean(),
+                          "gvotes_per_s": float((a[:, 0] * 20481 / a[:, 2] / 1e3).mean()),
+                          "first_vote_us_by_frame": [round(float(x), 1) for x in a[:16, 2]]}))
+capi.set_vote_track(True)
