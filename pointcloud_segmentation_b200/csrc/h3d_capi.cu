@@ -379,7 +379,7 @@ static std::atomic<int> g_stream_mode{1};   // h3d_set_stream_mode: 1 TMA tiles 
 template <int D, bool BOUNDED, bool TMA>
 static int launch_stream_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense, size_t smem) {
   H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_stream_kernel<D, BOUNDED, TMA>), smem, h->dev.smem_optin));
-  vote_stream_kernel<D, BOUNDED, TMA><<<h->dev.sm_count, kStreamThreads, smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
+  vote_stream_kernel<D, BOUNDED, TMA><<<h->dev.sm_count, kStreamThreads + (TMA ? 32 : 0), smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
   note_launches(1);
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;

@@ -221,13 +221,25 @@ __device__ __forceinline__ void tma_load_1d(unsigned dst_sa, const void *src, un
 
 struct StreamShared {
   unsigned long long full[kStreamStages];            // mbarriers: the stage's three bulk copies have landed
+  unsigned long long empty[kStreamStages];           // mbarriers: every consumer warp has lifted its points out of the stage
   unsigned long long warp_best[kStreamMaxD][kStreamWarps];
   double coef[kStreamMaxD][6];                       // scaled coefficients (FastCoef) of the item's directions
   int dir[kStreamMaxD];                              // local direction numbers of the item (-1: none)
 };
 
+__device__ __forceinline__ void mbar_arrive(unsigned bar_sa) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar_sa) : "memory");
+}
+__device__ __forceinline__ void consumer_bar() {     // the 512 voting threads only (the producer warp runs ahead)
+  asm volatile("bar.sync 1, %0;" :: "n"(kStreamThreads) : "memory");
+}
+
+// TMA = true: launched with kStreamThreads + 32 threads; warp 16 is the PRODUCER (one lane issues the bulk
+// copies, paced by the `empty` barriers), warps 0-15 vote and never wait for each other inside an item --
+// they meet only through the `full` barriers (the first version put a CTA barrier behind every tile to free
+// the stage and lost 25 % against plain LDGs: profiles/r02_stream_vote_ab_v1.txt).
 template <int D, bool BOUNDED, bool TMA>
-__global__ void __launch_bounds__(kStreamThreads, 1)
+__global__ void __launch_bounds__(TMA ? kStreamThreads + 32 : kStreamThreads, 1)
 vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ list, const int *__restrict__ count_ptr,
                    int count_imm, unsigned *__restrict__ dense) {
   extern __shared__ __align__(128) unsigned char stream_smem[];
@@ -243,36 +255,41 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
   const unsigned dummy_sa = planes_sa + (unsigned)D * stride * 4u;
   const unsigned ring_sa = (unsigned)__cvta_generic_to_shared(ring);
   const unsigned full_sa = (unsigned)__cvta_generic_to_shared(&sh.full[0]);
+  const unsigned empty_sa = (unsigned)__cvta_generic_to_shared(&sh.empty[0]);
   const int n_items = (count + D - 1) / D;
   const int my_items = blockIdx.x < n_items ? (n_items - blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   const int n_tiles = (n + kStreamTile - 1) / kStreamTile;
   const long long total_fills = (long long)my_items * n_tiles;
 
-  {
+  if (tid < kStreamThreads) {
     uint4 *p4 = reinterpret_cast<uint4 *>(planes);
     for (unsigned q = tid; q < (unsigned)D * stride / 4 + 1; q += kStreamThreads) p4[q] = make_uint4(0, 0, 0, 0);
   }
   if (TMA && tid == 0) {
-    for (int s = 0; s < kStreamStages; ++s) mbar_init(full_sa + 8u * s, 1);
+    for (int s = 0; s < kStreamStages; ++s) { mbar_init(full_sa + 8u * s, 1); mbar_init(empty_sa + 8u * s, kStreamWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   __syncthreads();
-  // fill k of this CTA = tile (k mod n_tiles) of the cloud into stage (k mod kStreamStages)
-  auto issue_fill = [&](long long k) {
-    const int t = (int)(k % n_tiles), st = (int)(k % kStreamStages);
-    const int i0 = t * kStreamTile;
-    const int cnt = min(kStreamTile, n - i0);
-    const unsigned bytes = (unsigned)(((cnt + 1) & ~1) * 8);   // 16-byte granules: one double past an odd end is read, never used
-    const unsigned bar = full_sa + 8u * st;
-    const unsigned dst = ring_sa + (unsigned)st * 3u * kStreamTile * 8u;
-    mbar_expect_tx(bar, 3u * bytes);
-    tma_load_1d(dst, h.px + i0, bytes, bar);
-    tma_load_1d(dst + kStreamTile * 8u, h.py + i0, bytes, bar);
-    tma_load_1d(dst + 2u * kStreamTile * 8u, h.pz + i0, bytes, bar);
-  };
-  if (TMA && tid == 0)
-    for (long long k = 0; k < kStreamStages && k < total_fills; ++k) issue_fill(k);
+  if (TMA && warp == kStreamWarps) {
+    // ---- producer: fill k = tile (k mod n_tiles) of the cloud into stage (k mod kStreamStages) ----------
+    if (lane == 0) {
+      for (long long k = 0; k < total_fills; ++k) {
+        const int st = (int)(k % kStreamStages);
+        if (k >= kStreamStages) mbar_wait(empty_sa + 8u * st, (unsigned)(((k / kStreamStages) - 1) & 1));
+        const int i0 = (int)(k % n_tiles) * kStreamTile;
+        const int cnt = min(kStreamTile, n - i0);
+        const unsigned bytes = (unsigned)(((cnt + 1) & ~1) * 8);   // 16-byte granules: one double past an odd end is read, never used
+        const unsigned bar = full_sa + 8u * st;
+        const unsigned dst = ring_sa + (unsigned)st * 3u * kStreamTile * 8u;
+        mbar_expect_tx(bar, 3u * bytes);
+        tma_load_1d(dst, h.px + i0, bytes, bar);
+        tma_load_1d(dst + kStreamTile * 8u, h.py + i0, bytes, bar);
+        tma_load_1d(dst + 2u * kStreamTile * 8u, h.pz + i0, bytes, bar);
+      }
+    }
+    return;
+  }
 
   const double kmagic = h.kmagic;
   const unsigned num_x = (unsigned)h.num_x, plane_cells = h.plane_cells, row4 = 4u * (unsigned)h.num_x;
@@ -286,7 +303,7 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
       const FastCoef f = make_fast(h.coef[h.dir_begin + (l < 0 ? 0 : l)], h.inv_s);
       sh.coef[tid][0] = f.c0s; sh.coef[tid][1] = f.c1n; sh.coef[tid][2] = f.c2s; sh.coef[tid][3] = f.bxn; sh.coef[tid][4] = f.byn;
     }
-    __syncthreads();
+    if (TMA) consumer_bar(); else __syncthreads();
     for (int t = 0; t < n_tiles; ++t, ++fill) {
       const int st = (int)(fill % kStreamStages);
       const int i0 = t * kStreamTile;
@@ -301,8 +318,8 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
           x[p] = bx[k]; y[p] = by[k]; z[p] = bz[k];
           live |= (i0 + k < n) ? (1u << p) : 0u;
         }
-        __syncthreads();                                   // every thread holds its points: the stage is free
-        if (tid == 0 && fill + kStreamStages < total_fills) issue_fill(fill + kStreamStages);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_sa + 8u * st);   // this warp's points are in registers: 16 arrivals free the stage
       } else {
 #pragma unroll
         for (int p = 0; p < kStreamP; ++p) {
@@ -343,7 +360,7 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
         }
       }
     }
-    __syncthreads();
+    if (TMA) consumer_bar(); else __syncthreads();
 #pragma unroll
     for (int d = 0; d < D; ++d) {
       const int l = sh.dir[d];
@@ -351,13 +368,13 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
       const unsigned long long k = scan_plane<kStreamThreads>(h, planes + (size_t)d * stride, tid, h.dir_begin + l, dense);
       if (lane == 0) sh.warp_best[d][warp] = k;
     }
-    __syncthreads();
+    if (TMA) consumer_bar(); else __syncthreads();
     if (warp < D && sh.dir[warp] >= 0) {
       unsigned long long k = lane < kStreamWarps ? sh.warp_best[warp][lane] : 0ull;
       k = warp_max_u64(k);
       if (lane == 0) store_record(h, sh.dir[warp], k);
     }
-    __syncthreads();           // sh.dir / sh.coef are rewritten by the next item
+    if (TMA) consumer_bar(); else __syncthreads();   // sh.dir / sh.coef are rewritten by the next item
   }
 }
 
