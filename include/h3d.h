@@ -422,10 +422,14 @@ int h3d_set_stream_mode(int mode);
  * Returns the previous setting.  Results are identical either way. */
 int h3d_set_fast_frames(int on);
 
-/* first vote of the frame fast path: on = 1 (default) the shared-memory increment returns the old count and
- * every thread tracks the maximum of its votes (no plane scan); on = 0 increments with the merging RED form and
- * scans every plane.  Returns the previous setting.  Results are identical either way. */
-int h3d_set_vote_track(int on);
+/* first vote of the frame fast path: mode 1 the shared-memory increment returns the old count and every thread
+ * tracks the maximum of its votes (no plane scan); mode 0 increments with the merging RED form and scans every
+ * plane; mode 2 (default) picks on the device: tracking up to 3072 points, scanning above.  Returns the previous
+ * mode.  Results are identical in every mode. */
+int h3d_set_vote_track(int mode);
+/* measurement hook: globaltimer stamps (ns) of the K0 cluster kernel of the pipeline's last fast-path frame:
+ * start, after each of its six cluster barriers, end */
+int h3d_pipeline_k0_stamps(h3d_pipeline *p, unsigned long long t_ns[8]);
 
 /* debug aid: on != 0 makes every frame start from per-direction records of 0xFFFFFFFF votes, so a
  * record the first vote fails to write wins every argmax instead of silently keeping the previous

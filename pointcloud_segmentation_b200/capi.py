@@ -375,6 +375,12 @@ class Pipeline:
         check(lib().h3d_pipeline_segments(self._p, segs, C.c_size_t(cap), C.byref(n), C.byref(rc_ref)))
         return rc_ref.value, [segs[k] for k in range(min(n.value, cap))]
 
+    def k0_stamps(self):
+        """globaltimer ns of the K0 cluster kernel's phases for the last (fast-path) frame"""
+        t = (C.c_ulonglong * 8)()
+        check(lib().h3d_pipeline_k0_stamps(self._p, t))
+        return list(t)
+
     def set_sm_share(self, n_ctas):
         """SMs the persistent loop kernel of this pipeline may use (0 = all)."""
         check(lib().h3d_pipeline_set_sm_share(self._p, C.c_int(n_ctas)))
@@ -664,7 +670,7 @@ def set_stream_mode(mode):
     return int(lib().h3d_set_stream_mode(C.c_int(int(mode))))
 
 
-def set_vote_track(on):
-    """First vote of the frame fast path: track maxima through the atomics' return values (True, default) or
-    scan the planes (False); returns the previous setting."""
-    return bool(lib().h3d_set_vote_track(C.c_int(1 if on else 0)))
+def set_vote_track(mode):
+    """First vote of the frame fast path: 1 / True = track maxima through the atomics' return values, 0 / False =
+    scan the planes, 2 = pick on the device by point count (default); returns the previous mode."""
+    return int(lib().h3d_set_vote_track(C.c_int(int(mode))))

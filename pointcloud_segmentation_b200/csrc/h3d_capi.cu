@@ -1591,7 +1591,7 @@ struct h3d_pipeline {
 };
 
 static std::atomic<int> g_fast_frames{1};   // h3d_set_fast_frames
-static std::atomic<int> g_vote_track{1};    // h3d_set_vote_track: first vote of the fast path tracks maxima instead of scanning planes
+static std::atomic<int> g_vote_track{2};    // h3d_set_vote_track: first vote of the fast path tracks maxima instead of scanning planes
 
 // one-time set-up of the fast path for a pipeline; leaves fast.on = false when it does not qualify
 static int fast_path_setup(h3d_pipeline *p) {
@@ -1602,7 +1602,7 @@ static int fast_path_setup(h3d_pipeline *p) {
   const DeviceFacts &dev = f.hg->dev;
   if (dev.cc < 90) return H3D_OK;   // thread-block clusters
   cudaFuncAttributes fa;
-  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_frame_kernel<true>));
+  H3D_CUDA(cudaFuncGetAttributes(&fa, vote_frame_kernel<2>));
   if (dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   fp.smem_vote = ((dev.smem_optin - fa.sharedSizeBytes) / 16) * 16;
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
@@ -1680,12 +1680,15 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
     H3D_CUDA(cudaMemsetAsync(hd.dcell, 0xFF, nd * sizeof(unsigned), s));
   }
   // Hough::add, wrap.h:228
-  const bool track = g_vote_track.load(std::memory_order_relaxed) != 0;
-  H3D_TRY(ensure_dyn_smem(track ? reinterpret_cast<const void *>(vote_frame_kernel<true>)
-                                : reinterpret_cast<const void *>(vote_frame_kernel<false>), fp.smem_vote, h->dev.smem_optin));
+  const int track = g_vote_track.load(std::memory_order_relaxed);
+  const void *vk = track == 0 ? reinterpret_cast<const void *>(vote_frame_kernel<0>)
+                 : track == 1 ? reinterpret_cast<const void *>(vote_frame_kernel<1>)
+                              : reinterpret_cast<const void *>(vote_frame_kernel<2>);
+  H3D_TRY(ensure_dyn_smem(vk, fp.smem_vote, h->dev.smem_optin));
   H3D_CUDA(cudaEventRecord(f.ev[4], s));
-  if (track) vote_frame_kernel<true><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
-  else vote_frame_kernel<false><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
+  if (track == 0) vote_frame_kernel<0><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
+  else if (track == 1) vote_frame_kernel<1><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
+  else vote_frame_kernel<2><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
   H3D_CUDA(cudaGetLastError());
   H3D_CUDA(cudaEventRecord(f.ev[2], s));
   // the loop, wrap.h:237-342
@@ -2385,7 +2388,17 @@ extern "C" int h3d_set_fused(int on) {
   return old;
 }
 
-extern "C" int h3d_set_vote_track(int on) { return g_vote_track.exchange(on != 0 ? 1 : 0); }
+extern "C" int h3d_set_vote_track(int mode) { return g_vote_track.exchange(mode == 0 ? 0 : mode == 1 ? 1 : 2); }
+
+// measurement: globaltimer stamps of the last fast-path frame's K0 cluster kernel (start, after each of its six
+// cluster barriers, end), nanoseconds
+extern "C" int h3d_pipeline_k0_stamps(h3d_pipeline *p, unsigned long long t_ns[8]) {
+  if (!p || !t_ns) return fail(H3D_ERR_ARG, "bad argument");
+  if (!p->fast.on || !p->fast.last_was_fast) return fail(H3D_ERR_ARG, "the last frame did not run on the fast path");
+  const FrameDev &F = *reinterpret_cast<const FrameDev *>(p->fast.stage_host);
+  for (int k = 0; k < 8; ++k) t_ns[k] = F.t_ns[k];
+  return H3D_OK;
+}
 
 extern "C" int h3d_set_fast_frames(int on) { return g_fast_frames.exchange(on != 0 ? 1 : 0); }
 

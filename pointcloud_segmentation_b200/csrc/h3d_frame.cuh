@@ -93,6 +93,7 @@ struct FrameDev {
   int nb_planes, n_cap;   // shared-memory layout of the loop kernel for this frame
   int bb[6];              // scratch: ordered-int float bounding box (min x,y,z, max x,y,z)
   int pad1[2];
+  unsigned long long t_ns[8];   // measurement: globaltimer at the start and after each phase of the K0 cluster kernel (thread 0)
 };
 
 // ---- the voxel grid of the window (host, once per pipeline) ------------------------------------------------
@@ -173,6 +174,9 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   const int rank = (int)cluster.block_rank();
   const int gtid = rank * kK0Threads + tid, T = kK0Cluster * kK0Threads;
   const K0Grid &G = A.grid;
+  int stamp_k = 0;
+  auto stamp = [&]() { if (gtid == 0 && stamp_k < 8) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); A.fd->t_ns[stamp_k] = t; } ++stamp_k; };
+  stamp();
 
   if (gtid < 6) A.fd->bb[gtid] = gtid < 3 ? INT_MAX : INT_MIN;
   if (tid < 6) bb_s[tid] = tid < 3 ? INT_MAX : INT_MIN;
@@ -197,6 +201,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
       if (in_window(p[u], A.win)) atomicAdd(&A.count[window_voxel_key(p[u], G)], 1);
   }
   cluster.sync();
+  stamp();
 
   // ---- phase B: exclusive scans over the grid (point offsets, output slots) ----------------------------
   // CTA `rank` owns cells [t0, t1); warp w of it the chunk [c0, c1); a warp reads 128 consecutive cells per
@@ -241,6 +246,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
     if (lane == 31) { A.tile_sums[2 * rank] = inc.x; A.tile_sums[2 * rank + 1] = inc.y; }
   }
   cluster.sync();
+  stamp();
   int n_window = 0, n_out = 0;
   {
     int bc = 0, bn = 0;
@@ -281,6 +287,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
     }
   }
   cluster.sync();
+  stamp();
 
   // ---- phase C: scatter the raw indices into their voxel's list; the histogram goes back to zero -------
   for (int i0 = gtid; i0 < A.n; i0 += U * T) {
@@ -297,6 +304,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
     for (int u = 0; u < U; ++u) if (key[u] >= 0) A.members[st[u] + old[u] - 1] = i0 + u * T;
   }
   cluster.sync();
+  stamp();
 
   // ---- phase D: one thread per occupied voxel: members back in input order (the canonical summation
   // order), sequential float sums, centroid; float bounding box of the centroids -------------------------
@@ -355,6 +363,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
     else if (tid < 6) atomicMax(&A.fd->bb[tid], bb_s[tid]);
   }
   cluster.sync();
+  stamp();
 
   // ---- phase E: widen (wrap.h:175-189; the centroids are finite, nothing to strip), getMinMax3D,
   // shiftToOrigin (lib/pointcloud.cpp:18-26), the guards of wrap.h:202-212 and the Hough ctor ------------
@@ -418,6 +427,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
     st.votes_cast = 0;
     *A.st = st;
   }
+  stamp();
 }
 
 // HoughDev of a frame on the fast path: the launch-time part (tables, buffers) + the geometry the frame's
@@ -435,7 +445,11 @@ __device__ __forceinline__ void patch_hough(HoughDev &h, const HoughDev &fixed, 
 // The slot count P = ceil(n / 512) is picked ON THE DEVICE: the kernel holds the twelve instantiations of the
 // vote loop and branches once (only the taken one occupies the instruction cache; the register allocation is
 // that of P = 12 either way, and one CTA per SM is resident regardless).
-template <bool TRACK>
+// MODE 0: RED increments + plane scan; 1: TRACK (atomics return the old count, no scan); 2 (default): TRACK up
+// to 6 slots (3072 points), scan above -- measured on the 16 bench frames (profiles/r02_track_ab.txt): TRACK
+// wins 88 vs 103 us at 1.3 k points and loses 195 vs 179 us at 4.9 k (ATOMS with a return value costs ~13 cycles
+// per warp-vote against ~9 for the merging RED form; the scan it saves is a fixed ~0.2 us per direction).
+template <int MODE>
 __global__ void __launch_bounds__(kResThreads, 1)
 vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__restrict__ fd) {
   extern __shared__ __align__(16) unsigned planes[];
@@ -447,7 +461,7 @@ vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__rest
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
   for (unsigned q = threadIdx.x; q < 2 * kResG * hs.plane_stride / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
   const int cta = blockIdx.x, n_cta = gridDim.x, count = hs.dir_count;
-#define H3D_FRAME_VOTE(PP) vote_resident<PP, 0, true, TRACK>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+#define H3D_FRAME_VOTE(PP) vote_resident<PP, 0, true, (MODE == 1 || (MODE == 2 && PP <= 6))>(hs, nullptr, count, planes, sh, cta, n_cta); break;
   switch ((hs.n + kResThreads - 1) / kResThreads) {
     case 0: case 1: H3D_FRAME_VOTE(1)
     case 2: H3D_FRAME_VOTE(2)

@@ -15,7 +15,7 @@ def loop_form(request, h3d):
     multi-kernel loop."""
     old = h3d.set_fused(request.param != "multikernel")
     old_fast = h3d.set_fast_frames(request.param.startswith("fast"))
-    old_track = h3d.set_vote_track(request.param != "fast_scan")   # fast_scan: first vote scans its planes (RED form)
+    old_track = h3d.set_vote_track(0 if request.param == "fast_scan" else 1)   # fast_scan: first vote scans its planes (RED form)
     yield request.param
     h3d.set_fused(old)
     h3d.set_fast_frames(old_fast)
