@@ -1140,11 +1140,11 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
   if (h->dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   const size_t smem = ((h->dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;   // everything the SM offers
-  // first vote: 2*G planes + pad; loop: nb planes + pad + the live points (24 B) + the inlier list (4 B)
+  // first vote: 2*G planes + pad; loop: nb planes + pad + the live points (24 B) + the inlier list (4 B) + its t values (4 B)
   if (tables + 2 * kResG * plane_bytes + 16 > smem) return H3D_OK;
   const size_t n_cap = ((size_t)hd.n + 1) & ~(size_t)1;
-  if (tables + 16 + 28 * n_cap + 2 * plane_bytes > smem) return H3D_OK;
-  size_t nb = (smem - tables - 16 - 28 * n_cap) / plane_bytes;
+  if (tables + 16 + 32 * n_cap + 2 * plane_bytes > smem) return H3D_OK;
+  size_t nb = (smem - tables - 16 - 32 * n_cap) / plane_bytes;
   if (nb > 2 * kResG) nb = 2 * kResG;
   nb &= ~(size_t)1;
   const size_t iters = (size_t)(opt_nlines > 0 ? opt_nlines : hd.n) + 2;
@@ -1563,6 +1563,7 @@ struct FastPath {
   bool last_was_fast = false;   // the last frame ran here (h3d_pipeline_filtered reads the count from the descriptor)
   K0Grid grid{};
   int2 *occ = nullptr;
+  int2 *dir_rows = nullptr;     // per direction: quads of its plane the current frame can touch
   int *tile_sums = nullptr;
   FrameDev *fd_dev = nullptr;
   size_t smem_vote = 0, smem_loop = 0;
@@ -1570,8 +1571,8 @@ struct FastPath {
   unsigned char *stage_host = nullptr, *stage_dev = nullptr;
   size_t off_st = 0, off_iters = 0, off_pool = 0, pool_entries = 0, stage_bytes = 0;
   void release() {
-    cudaFree(occ); cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
-    occ = nullptr; tile_sums = nullptr; fd_dev = nullptr; stage_host = stage_dev = nullptr; on = false;
+    cudaFree(occ); cudaFree(dir_rows); cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
+    occ = nullptr; dir_rows = nullptr; tile_sums = nullptr; fd_dev = nullptr; stage_host = stage_dev = nullptr; on = false;
   }
 };
 
@@ -1611,6 +1612,7 @@ static int fast_path_setup(h3d_pipeline *p) {
   const size_t n = p->cfg.max_raw_points;
   H3D_CUDA(cudaMalloc(&fp.occ, n * sizeof(int2)));
   H3D_CUDA(cudaMalloc(&fp.tile_sums, 2 * kK0Cluster * sizeof(int)));
+  H3D_CUDA(cudaMalloc(&fp.dir_rows, f.hg->space->num_b * sizeof(int2)));
   H3D_CUDA(cudaMalloc(&fp.fd_dev, sizeof(FrameDev)));
   fp.off_st = (sizeof(FrameDev) + 255) & ~(size_t)255;
   fp.off_iters = fp.off_st + ((sizeof(LoopState) + 255) & ~(size_t)255);
@@ -1671,7 +1673,18 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   fa.pool_cap = st_pool_cap;
   fa.xchg = f.gbest; fa.xchg_words = (int)xchg_words; fa.bar = f.sync_dev;
   fa.smem_loop = (unsigned)fp.smem_loop; fa.tables_bytes = (unsigned)n_own * 16u; fa.smem_vote = (unsigned)fp.smem_vote;
-  frame_prefilter_kernel<<<kK0Cluster, kK0Threads, 0, s>>>(fa);
+  fa.coef = h->space->coef_dev; fa.dir_rows = fp.dir_rows;
+  {
+    // cluster width: the whole GPU is this frame's -> 8 (latency); frames in flight beside it -> 2
+    const unsigned width = (grid >= h->dev.sm_count / 2) ? (unsigned)kK0Cluster : 2u;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(width); lc.blockDim = dim3(kK0Threads); lc.dynamicSmemBytes = 0; lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = width; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    lc.attrs = at; lc.numAttrs = 1;
+    H3D_CUDA(cudaLaunchKernelEx(&lc, frame_prefilter_kernel, fa));
+  }
   H3D_CUDA(cudaGetLastError());
   H3D_CUDA(cudaEventRecord(f.ev[1], s));
   if (g_debug_poison.load(std::memory_order_relaxed)) {
@@ -1680,6 +1693,7 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
     H3D_CUDA(cudaMemsetAsync(hd.dcell, 0xFF, nd * sizeof(unsigned), s));
   }
   // Hough::add, wrap.h:228
+  hd.dir_rows = fp.dir_rows;
   const int track = g_vote_track.load(std::memory_order_relaxed);
   const void *vk = track == 0 ? reinterpret_cast<const void *>(vote_frame_kernel<0>)
                  : track == 1 ? reinterpret_cast<const void *>(vote_frame_kernel<1>)
@@ -1690,6 +1704,7 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   else if (track == 1) vote_frame_kernel<1><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
   else vote_frame_kernel<2><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
   H3D_CUDA(cudaGetLastError());
+  hd.dir_rows = nullptr;
   H3D_CUDA(cudaEventRecord(f.ev[2], s));
   // the loop, wrap.h:237-342
   FusedArgs a;

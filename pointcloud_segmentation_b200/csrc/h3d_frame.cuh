@@ -158,12 +158,19 @@ struct FrameArgs {
   unsigned *bar;             // 4 words, zeroed here
   // shared-memory budget of the vote / loop kernels (fast-path eligibility, decided on the device)
   unsigned smem_loop, tables_bytes, smem_vote;
+  // per-direction rows of the projected bounding box (quad ranges of the planes), for the vote's scan / zero-fill
+  const DirCoef *coef;
+  int2 *dir_rows;            // num_b entries
 };
 
 // ---------------------------------------------------------------------------------------------------------
 // K0 + prep + Hough ctor: one cluster.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __cluster_dims__(kK0Cluster, 1, 1) __launch_bounds__(kK0Threads, 1)
+// Launched as ONE cluster of 1, 2, 4 or 8 CTAs (cudaLaunchAttributeClusterDimension): 8 for a frame that owns
+// the GPU (lowest latency), 2 when frames are in flight beside each other -- a cluster needs all its SMs free in
+// one GPC at the same time, and every CTA of the vote / loop kernels owns its SM's whole register file, so a
+// wide cluster would wait for other frames' kernels to end while a narrow one costs 50 us of two SMs.
+__global__ void __launch_bounds__(kK0Threads, 1)
 frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
@@ -171,8 +178,8 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   __shared__ int2 wpre[kK0Warps];
   __shared__ int bb_s[6];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int rank = (int)cluster.block_rank();
-  const int gtid = rank * kK0Threads + tid, T = kK0Cluster * kK0Threads;
+  const int rank = (int)cluster.block_rank(), n_blk = (int)cluster.num_blocks();   // n_blk <= kK0Cluster
+  const int gtid = rank * kK0Threads + tid, T = n_blk * kK0Threads;
   const K0Grid &G = A.grid;
   int stamp_k = 0;
   auto stamp = [&]() { if (gtid == 0 && stamp_k < 8) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); A.fd->t_ns[stamp_k] = t; } ++stamp_k; };
@@ -206,7 +213,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   // ---- phase B: exclusive scans over the grid (point offsets, output slots) ----------------------------
   // CTA `rank` owns cells [t0, t1); warp w of it the chunk [c0, c1); a warp reads 128 consecutive cells per
   // step, a lane four of them (one 16-byte load)
-  const int tile = (((G.cells + kK0Cluster - 1) / kK0Cluster) + 4095) & ~4095;
+  const int tile = (((G.cells + n_blk - 1) / n_blk) + 4095) & ~4095;
   const int t0 = min(rank * tile, G.cells), t1 = min(t0 + tile, G.cells);
   const int chunk = tile / kK0Warps;                     // multiple of 128
   const int c0 = min(t0 + warp * chunk, t1), c1 = min(c0 + chunk, t1);
@@ -250,7 +257,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   int n_window = 0, n_out = 0;
   {
     int bc = 0, bn = 0;
-    for (int q = 0; q < kK0Cluster; ++q) {
+    for (int q = 0; q < n_blk; ++q) {
       const int sc = A.tile_sums[2 * q], sn = A.tile_sums[2 * q + 1];
       if (q < rank) { bc += sc; bn += sn; }
       n_window += sc; n_out += sn;
@@ -381,6 +388,27 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
     A.w[s] = 1;
     A.orig[s] = (unsigned)s;
   }
+  {
+    // rows of every direction's plane that the cloud can reach: |x'| <= |c0| hx + |c1| hy + |bx| hz for a point
+    // inside the (centred) bounding box with half extents h (lib/hough.cpp:76-79 is linear in p), one row of margin
+    double minPs[3], maxPs[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { minPs[c] = lo[c] - ns[c]; maxPs[c] = hi[c] - ns[c]; }
+    const HoughGeom g = hough_geometry(minPs, maxPs, A.opt_dx, A.num_b);
+    if (g.rc == 0 && g.num_x > 0 && g.dx > 0.0) {
+      const double hx = fmax(fabs(minPs[0]), fabs(maxPs[0])), hy = fmax(fabs(minPs[1]), fabs(maxPs[1])),
+                   hz = fmax(fabs(minPs[2]), fabs(maxPs[2]));
+      const int rows_all = (int)(g.plane_stride / (unsigned)g.num_x) + 1, quads = (int)(g.plane_stride / 4u);
+      for (int j = gtid; j < (int)A.num_b; j += T) {
+        const DirCoef c = A.coef[j];
+        const double hr = fabs(c.c0) * hx + fabs(c.c1) * hy + fabs(c.bx) * hz;
+        int r0 = (int)floor((g.max_x - hr) / g.dx + 0.5) - 1, r1 = (int)floor((g.max_x + hr) / g.dx + 0.5) + 1;
+        r0 = max(r0, 0); r1 = min(r1, rows_all);
+        int q0 = (r0 * g.num_x) / 4, q1 = ((r1 + 1) * g.num_x + 3) / 4;
+        A.dir_rows[j] = make_int2(min(q0, quads), min(q1, quads));
+      }
+    }
+  }
   if (gtid == 0) {
     FrameDev &F = *A.fd;
     F.n = n_keep; F.n_in_window = n_window; F.status = 0;
@@ -408,10 +436,10 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
       bool ok = g.bounded && n_keep >= 1 && n_keep <= kFrameMaxPoints && g.plane_stride < 65536u;
       ok = ok && (2ull * kResG * plane_bytes + 16ull <= A.smem_vote);
       ok = ok && (A.tables_bytes + 2ull * kResG * plane_bytes + 16ull <= A.smem_loop);
-      ok = ok && (A.tables_bytes + 16ull + 28ull * n_cap + 2ull * plane_bytes <= A.smem_loop);
+      ok = ok && (A.tables_bytes + 16ull + 32ull * n_cap + 2ull * plane_bytes <= A.smem_loop);
       if (!ok) F.status = 2;
       else {
-        unsigned long long nb = (A.smem_loop - A.tables_bytes - 16ull - 28ull * n_cap) / plane_bytes;
+        unsigned long long nb = (A.smem_loop - A.tables_bytes - 16ull - 32ull * n_cap) / plane_bytes;
         if (nb > 2ull * kResG) nb = 2ull * kResG;
         nb &= ~1ull;
         F.nb_planes = (int)nb; F.n_cap = (int)n_cap;

@@ -78,6 +78,7 @@ struct FusedShared {
 struct FusedPoints {
   double *x, *y, *z;
   int *yidx;
+  float *yt;     // t = b * (p - a) of the inliers of the current pass, in list order (un-vote filter)
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
@@ -209,22 +210,30 @@ __device__ __forceinline__ void lsq_eig(FusedShared &sh) {
   sh.lsq.rc = (double)e.evals[2];
 }
 
-// Can a point of Y vote for cell (cx, cy) of the direction with scaled coefficients f?  Y lies in
-// the slab { a + t b + e : t in [t0, t1], |e| <= radius }, whose image in the (x', y') plane, in
-// cell units, is within `reach`/sqrt(2)-0.5 cells of the segment; the cell is reachable only if
-// its centre is within `reach` (Euclidean) of that segment.  Conservative, never exact.
-__device__ __forceinline__ bool strip_may_hit(const FastCoef &f, const double (&a)[3], const double (&b)[3], double t0,
-                                              double t1, double cell_off, double reach2, unsigned cx, unsigned cy) {
+// Which points of Y can vote for cell (cx, cy) of the direction with scaled coefficients f?  Y lies in the
+// slab { a + t b + e : |e| <= radius, e orthogonal to b }.  The map to the (x', y') plane is an orthogonal
+// projection, so in cell units a point of parameter t lands within radius/dx of P(t) = (xa + t gx, ya + t gy)
+// (relative to the cell's centre), and it votes for the cell only if it lands within sqrt(2)/2 of the centre:
+// |P(t)| <= reach, reach^2 = reach2 >= (sqrt(2)/2 + radius/dx)^2.  Returns false when no t qualifies, else the
+// interval [*tlo, *thi] (conservative, never exact; +-inf when the line is parallel to the direction).
+__device__ __forceinline__ bool strip_interval(const FastCoef &f, const double (&a)[3], const double (&b)[3],
+                                               double cell_off, double reach2, unsigned cx, unsigned cy, double *tlo,
+                                               double *thi) {
   const double s = 1.0 / 1048576.0;   // the coefficients carry 2^20/dx
   const double xa = (f.c0s * a[0] + f.c1n * a[1] + f.bxn * a[2]) * s + cell_off - ((double)cx + 0.5);
   const double ya = (f.c1n * a[0] + f.c2s * a[1] + f.byn * a[2]) * s + cell_off - ((double)cy + 0.5);
   const double gx = (f.c0s * b[0] + f.c1n * b[1] + f.bxn * b[2]) * s;
   const double gy = (f.c1n * b[0] + f.c2s * b[1] + f.byn * b[2]) * s;
-  const double gg = gx * gx + gy * gy;
-  double t = gg > 1e-30 ? -(xa * gx + ya * gy) / gg : t0;
-  t = fmin(fmax(t, t0), t1);
-  const double ex = xa + t * gx, ey = ya + t * gy;
-  return ex * ex + ey * ey <= reach2;
+  const double gg = gx * gx + gy * gy, bq = xa * gx + ya * gy, cq = xa * xa + ya * ya - reach2;
+  if (!(gg > 1e-12)) {                // the whole line projects (almost) to one spot
+    *tlo = -INFINITY; *thi = INFINITY;
+    return cq <= 1e-6;
+  }
+  const double disc = bq * bq - gg * cq;
+  if (disc < 0.0) return false;
+  const double sq = sqrt(disc);
+  *tlo = (-bq - sq) / gg; *thi = (-bq + sq) / gg;
+  return true;
 }
 
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
@@ -279,6 +288,10 @@ __device__ __forceinline__ unsigned inlier_pass(const FusedPoints &Q, int n_aliv
       const int pos = run + pre + __popc(bal & below);
       const int i = tid + p * kResThreads;
       Q.yidx[pos] = i;
+      if (track_t) {   // t = b * (p - a) again (same operations as the test above), kept for the un-vote's filter
+        const double ex = __dsub_rn(Q.x[i], a[0]), ey = __dsub_rn(Q.y[i], a[1]), ez = __dsub_rn(Q.z[i], a[2]);
+        Q.yt[pos] = (float)__dadd_rn(__dadd_rn(__dmul_rn(b[0], ex), __dmul_rn(b[1], ey)), __dmul_rn(b[2], ez));
+      }
       if (to_pool && pool_base + (unsigned)pos < pool_cap) pool[pool_base + pos] = orig[i];
     }
     run += tot;
@@ -355,6 +368,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   Q.x = reinterpret_cast<double *>(planes + (size_t)nb * stride + 4);
   Q.y = Q.x + n_cap; Q.z = Q.y + n_cap;
   Q.yidx = reinterpret_cast<int *>(Q.z + n_cap);
+  Q.yt = reinterpret_cast<float *>(Q.yidx + n_cap);
 
   if (A.prof && tid == 0 && A.prof_iters > 0) A.prof[(size_t)cta * kProfSlots + 15] = globaltimer_ns();   // kernel start
   // hough->add(X) ran just before this kernel (vote_resident_kernel, BOUNDED form): the records of
@@ -470,8 +484,9 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
           const unsigned cx = rcell[r] / num_x, cy = rcell[r] - cx * num_x;
           // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
+          double ilo, ihi;
           if (cy == 0 || cy == num_x - 1 ||
-              strip_may_hit(make_fast(h.coef[j], h.inv_s), a, b, t0, t1, cell_off, reach2, cx, cy))
+              (strip_interval(make_fast(h.coef[j], h.inv_s), a, b, cell_off, reach2, cx, cy, &ilo, &ihi) && ilo <= t1 && ihi >= t0))
             rlist[atomicAdd(&sh.ns, 1)] = r;
         }
         named_bar_sync(1, un);
@@ -485,11 +500,20 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
           const FastCoef fc = make_fast(h.coef[j], h.inv_s);
           const unsigned target = rcell[r];
+          // only inliers whose t puts them near the cell can vote for it: skip the others on their float t
+          // (edge cells reached through the reference's flat-index aliasing take every point)
+          const unsigned cx = target / num_x, cy = target - cx * num_x;
+          double ilo = -INFINITY, ihi = INFINITY;
+          if (cy != 0 && cy != num_x - 1) strip_interval(fc, a, b, cell_off, reach2, cx, cy, &ilo, &ihi);
+          const float flo = (float)(ilo - (fabs(ilo) * 1e-6 + 1e-6)), fhi = (float)(ihi + (fabs(ihi) * 1e-6 + 1e-6));
 #pragma unroll 1
           for (int e0 = 0; e0 < ny2; e0 += 32) {
             const int e = e0 + lane;
+            bool cand = false;
+            if (e < ny2) { const float te = Q.yt[e]; cand = te >= flo && te <= fhi; }
+            if (!__any_sync(0xFFFFFFFFu, cand)) continue;
             bool hit = false;
-            if (e < ny2) { const int i = Q.yidx[e]; hit = vote_cell(h, fc, j, Q.x[i], Q.y[i], Q.z[i]) == target; }
+            if (cand) { const int i = Q.yidx[e]; hit = vote_cell(h, fc, j, Q.x[i], Q.y[i], Q.z[i]) == target; }
             if (__any_sync(0xFFFFFFFFu, hit)) { if (lane == 0) rstale[r] = 1; break; }
           }
         }

@@ -479,11 +479,11 @@ constexpr int kResWarps = kResThreads / 32;
 // Quads are visited in ascending order and the update is strict, so bcell is the thread's first
 // maximum; the warp / CTA reductions of the caller keep the lowest cell among equal maxima.
 template <int THREADS>
-__device__ __forceinline__ void scan_plane_local(unsigned *plane, unsigned quads, int t, unsigned plane_cells,
+__device__ __forceinline__ void scan_plane_local(unsigned *plane, unsigned q_begin, unsigned quads, int t, unsigned plane_cells,
                                                  unsigned &best, unsigned &bcell) {
   uint4 *p4 = reinterpret_cast<uint4 *>(plane);
   best = 0; bcell = 0;
-  for (unsigned q0 = t; q0 < quads; q0 += 3 * THREADS) {
+  for (unsigned q0 = q_begin + t; q0 < quads; q0 += 3 * THREADS) {
     uint4 v[3];
 #pragma unroll
     for (int u = 0; u < 3; ++u) {
@@ -561,7 +561,9 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
       const double *src = reinterpret_cast<const double *>(h.coef + h.dir_begin + l);
 #pragma unroll
       for (int c = 0; c < 5; ++c) cp_async8(coef_sa + 48u * (unsigned)(slot * G + tid) + 8u * c, src + c);
+      if (h.dir_rows) cp_async8(coef_sa + 48u * (unsigned)(slot * G + tid) + 40u, h.dir_rows + h.dir_begin + l);
     }
+    if (!h.dir_rows || l < 0) *reinterpret_cast<int2 *>(&sh.coef[slot][tid][5]) = make_int2(0, 0x7FFFFFFF);
     sh.dir[dslot][tid] = l;
   };
   if (tid < G) { stage(cta, 0, 0); cp_async_wait_all(); }
@@ -660,8 +662,13 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
     }
     if (TRACK) {
       if (prev_any) {   // the previous group's planes back to zero (their maxima were tracked, not scanned)
-        uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)((slot ^ 1) * G) * stride);
-        for (unsigned q = tid; q < (unsigned)G * quads; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const int2 qr = *reinterpret_cast<const int2 *>(&sh.coef[slot ^ 1][g][5]);
+          uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)((slot ^ 1) * G + g) * stride);
+          const unsigned qe = min((unsigned)qr.y, quads);
+          for (unsigned q = (unsigned)qr.x + tid; q < qe; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
+        }
       }
       if (tid < G) cp_async_wait_all();
       __syncthreads();   // votes of this group and their per-warp maxima, zero-fill, staging of the next group: done
@@ -684,7 +691,11 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
       unsigned best[G], bcell[G];
 #pragma unroll
       for (int g = 0; g < G; ++g)
-        scan_plane_local<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, quads, tid, plane_cells, best[g], bcell[g]);
+      {
+        const int2 qr = *reinterpret_cast<const int2 *>(&sh.coef[slot ^ 1][g][5]);   // quads the frame's points can touch
+        scan_plane_local<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, (unsigned)qr.x, min((unsigned)qr.y, quads),
+                                      tid, plane_cells, best[g], bcell[g]);
+      }
       unsigned m[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) m[g] = __reduce_max_sync(0xFFFFFFFFu, best[g]);

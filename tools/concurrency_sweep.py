@@ -15,6 +15,7 @@ reps = int(sys.argv[1]) if len(sys.argv) > 1 else 6
 combos = [(1, 0), (4, 37), (5, 37), (6, 37), (8, 37), (5, 29), (6, 49), (4, 49), (3, 49), (8, 24)]
 if len(sys.argv) > 2:
     combos = [tuple(int(v) for v in c.split(":")) for c in sys.argv[2].split(",")]
+capi.set_wait_mode(2)   # poll + yield, what bench.py uses with frames in flight
 for K, share in combos:
     NF = 64
     rp = capi.Replay(K, share, 6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, n_pts, NF)

@@ -8,7 +8,7 @@ import bench
 
 frames = bench.make_frames(16)
 for share in (0, 18):
-    for track in (True, False):
+    for track in (2, 1, 0):
         capi.set_vote_track(track)
         pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frames.shape[1])
         pipe.set_sm_share(share)
@@ -18,10 +18,15 @@ for share in (0, 18):
                 res = pipe.run(frames[k])
                 if rep:
                     us.append((res.n_input, *pipe.timing_us()))
+        st = np.array(pipe.k0_stamps(), dtype=np.int64)
         pipe.close()
         a = np.array(us)
-        print(json.dumps({"share": share or 148, "vote": "track" if track else "scan", "k0_us": a[:, 1].mean(),
+        if track == 2:
+            print("K0 cluster kernel phases (us) on the last frame, share", share or 148, ":",
+                  dict(zip(("A_count", "B1_reduce", "B2_scan", "C_scatter", "D_centroid", "E_shift_ctor"),
+                           [round(float(x) / 1e3, 2) for x in np.diff(st[:7])])))
+        print(json.dumps({"share": share or 148, "vote": ("scan", "track", "auto")[track], "k0_us": a[:, 1].mean(),
                           "first_vote_us": a[:, 2].mean(), "loop_us": a[:, 3].mean(), "frame_us": a[:, 4].mean(),
                           "gvotes_per_s": float((a[:, 0] * 20481 / a[:, 2] / 1e3).mean()),
                           "first_vote_us_by_frame": [round(float(x), 1) for x in a[:16, 2]]}))
-capi.set_vote_track(True)
+capi.set_vote_track(2)
