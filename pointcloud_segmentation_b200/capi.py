@@ -665,8 +665,8 @@ def set_fast_frames(on):
 
 
 def set_stream_mode(mode):
-    """Streaming vote kernel: 1 = TMA-staged point tiles (default), 0 = same loop with LDGs, 2 = round-1 kernel;
-    returns the previous mode."""
+    """Streaming vote kernel: 0 = register tiles fetched with LDGs (default), 1 = TMA-staged tiles through a producer
+    warp, 2 = round-1 kernel; returns the previous mode."""
     return int(lib().h3d_set_stream_mode(C.c_int(int(mode))))
 
 

@@ -374,7 +374,11 @@ static int launch_resident(h3d_hough *h, int ablate, const int *list, const int 
 }
 
 // TMA-staged streaming vote (vote_stream_kernel): D <= 8 planes + the point-tile ring in shared memory
-static std::atomic<int> g_stream_mode{1};   // h3d_set_stream_mode: 1 TMA tiles (default), 0 same loop with LDGs, 2 round-1 vote_kernel
+// h3d_set_stream_mode: 0 (default) tile loop with coalesced LDGs, 1 the same loop fed by TMA bulk copies through a
+// producer warp, 2 the round-1 vote_kernel.  Measured on B200 (profiles/r02_stream_vote_ab_v2.txt, 1 M points, g6):
+// LDG 20.2 ms (1012 Gvotes/s), TMA 21.9 ms (935), round 1 32.9 ms (622): the kernel is bound by the shared-memory
+// pipe (the atomics), and staging tiles in shared memory adds their 24 B per point to that same pipe.
+static std::atomic<int> g_stream_mode{0};
 
 template <int D, bool BOUNDED, bool TMA>
 static int launch_stream_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense, size_t smem) {
@@ -2419,7 +2423,7 @@ extern "C" int h3d_set_fast_frames(int on) { return g_fast_frames.exchange(on !=
 
 extern "C" int h3d_set_debug_poison(int on) { return g_debug_poison.exchange(on != 0 ? 1 : 0); }
 
-extern "C" int h3d_set_stream_mode(int mode) { return g_stream_mode.exchange(mode == 0 ? 0 : mode == 2 ? 2 : 1); }
+extern "C" int h3d_set_stream_mode(int mode) { return g_stream_mode.exchange(mode == 1 ? 1 : mode == 2 ? 2 : 0); }
 
 extern "C" int h3d_set_sliced_vote(int on) {
   const int old = g_sliced_vote ? 1 : 0;

@@ -317,28 +317,37 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   // order), sequential float sums, centroid; float bounding box of the centroids -------------------------
   const int n_keep = min(n_out, A.out_cap);
   {
-    constexpr int LM = 24;                                 // members sorted in local memory up to here
+    constexpr int LM = 8;                                  // members ordered in REGISTERS up to here
     int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
     for (int s = gtid; s < n_keep; s += T) {
       const int2 oc = A.occ[s];
       int *m = A.members + oc.x;
       float cx = 0.0f, cy = 0.0f, cz = 0.0f;
       if (oc.y <= LM) {
-        int ml[LM];
-        float lx[LM], ly[LM], lz[LM];
-#pragma unroll 4
-        for (int a = 0; a < oc.y; ++a) ml[a] = m[a];
-        for (int a = 1; a < oc.y; ++a) {                   // insertion sort: lists are a handful of points long
-          const int key = ml[a];
-          int b = a - 1;
-          while (b >= 0 && ml[b] > key) { ml[b + 1] = ml[b]; --b; }
-          ml[b + 1] = key;
+        // every index is static (fully unrolled): the lists stay in registers.  (Per-thread local arrays of
+        // 24 entries made 393 KB per SM, more than the L1 holds: this phase alone took 24 us.)
+        int mi[LM];
+        float qx[LM], qy[LM], qz[LM];
+#pragma unroll
+        for (int a = 0; a < LM; ++a) mi[a] = a < oc.y ? m[a] : INT_MAX;
+#pragma unroll
+        for (int a = 0; a < LM; ++a) {
+          if (a < oc.y) { const float3 p = load_xyz(A.raw, mi[a], A.stride); qx[a] = p.x; qy[a] = p.y; qz[a] = p.z; }
+          else { qx[a] = 0.0f; qy[a] = 0.0f; qz[a] = 0.0f; }
         }
-#pragma unroll 4
-        for (int a = 0; a < oc.y; ++a) { const float3 p = load_xyz(A.raw, ml[a], A.stride); lx[a] = p.x; ly[a] = p.y; lz[a] = p.z; }
-        for (int a = 0; a < oc.y; ++a) { cx = __fadd_rn(cx, lx[a]); cy = __fadd_rn(cy, ly[a]); cz = __fadd_rn(cz, lz[a]); }
+#pragma unroll 1
+        for (int k = 0; k < oc.y; ++k) {                   // ascending raw index = the canonical summation order
+          int best = INT_MAX;
+#pragma unroll
+          for (int a = 0; a < LM; ++a) best = min(best, mi[a]);
+          float vx = 0.0f, vy = 0.0f, vz = 0.0f;
+#pragma unroll
+          for (int a = 0; a < LM; ++a)
+            if (mi[a] == best) { vx = qx[a]; vy = qy[a]; vz = qz[a]; mi[a] = INT_MAX; }
+          cx = __fadd_rn(cx, vx); cy = __fadd_rn(cy, vy); cz = __fadd_rn(cz, vz);
+        }
       } else {
-        for (int a = 1; a < oc.y; ++a) {
+        for (int a = 1; a < oc.y; ++a) {                   // insertion sort in place (rare: crowded voxels)
           const int key = m[a];
           int b = a - 1;
           while (b >= 0 && m[b] > key) { m[b + 1] = m[b]; --b; }

@@ -519,6 +519,9 @@ struct ResShared {
   double coef[2][kResG][6];   // raw DirCoef of the directions voted in phase k (slot k&1)
   int dir[3][kResG];          // local direction numbers of phase k (slot k%3; -1: none); the
                               // previous phase's numbers stay readable while the next are staged
+  int2 rows[3][kResG];        // same slots: quads [x, y) of the direction's plane that the points can touch (the
+                              // coef slots are only double-buffered: the previous group's are overwritten by the staging
+                              // of the next group in the very phase that scans the previous group's planes)
 };
 
 // TRACK form (needs plane_stride < 65536; N <= 6144 < 65536 always holds here): the increment returns the
@@ -534,6 +537,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
   const unsigned stride = h.plane_stride, quads = stride / 4;
   const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
   const unsigned coef_sa = (unsigned)__cvta_generic_to_shared(&sh.coef[0][0][0]);
+  const unsigned rows_sa = (unsigned)__cvta_generic_to_shared(&sh.rows[0][0]);
   // points are COMPACT here (every weight +1): slot p of thread t is point t + p*512, so all
   // slots below n/512 are full for every thread and only one slot is partially filled
   const int n = point_count(h);
@@ -561,9 +565,9 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
       const double *src = reinterpret_cast<const double *>(h.coef + h.dir_begin + l);
 #pragma unroll
       for (int c = 0; c < 5; ++c) cp_async8(coef_sa + 48u * (unsigned)(slot * G + tid) + 8u * c, src + c);
-      if (h.dir_rows) cp_async8(coef_sa + 48u * (unsigned)(slot * G + tid) + 40u, h.dir_rows + h.dir_begin + l);
+      if (h.dir_rows) cp_async8(rows_sa + 8u * (unsigned)(dslot * G + tid), h.dir_rows + h.dir_begin + l);
     }
-    if (!h.dir_rows || l < 0) *reinterpret_cast<int2 *>(&sh.coef[slot][tid][5]) = make_int2(0, 0x7FFFFFFF);
+    if (!h.dir_rows || l < 0) sh.rows[dslot][tid] = make_int2(0, 0x7FFFFFFF);
     sh.dir[dslot][tid] = l;
   };
   if (tid < G) { stage(cta, 0, 0); cp_async_wait_all(); }
@@ -664,7 +668,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
       if (prev_any) {   // the previous group's planes back to zero (their maxima were tracked, not scanned)
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-          const int2 qr = *reinterpret_cast<const int2 *>(&sh.coef[slot ^ 1][g][5]);
+          const int2 qr = sh.rows[dprev][g];
           uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)((slot ^ 1) * G + g) * stride);
           const unsigned qe = min((unsigned)qr.y, quads);
           for (unsigned q = (unsigned)qr.x + tid; q < qe; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
@@ -692,7 +696,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
 #pragma unroll
       for (int g = 0; g < G; ++g)
       {
-        const int2 qr = *reinterpret_cast<const int2 *>(&sh.coef[slot ^ 1][g][5]);   // quads the frame's points can touch
+        const int2 qr = sh.rows[dprev][g];   // quads the frame's points can touch
         scan_plane_local<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, (unsigned)qr.x, min((unsigned)qr.y, quads),
                                       tid, plane_cells, best[g], bcell[g]);
       }

@@ -30,4 +30,4 @@ for n in (38528, 200000, 1000000):
     row["same_winner"] = row["tma_key"] == row["ldg_key"] == row["round1_key"]
     out.append(row)
     print(json.dumps(row), flush=True)
-h3d.set_stream_mode(1)
+h3d.set_stream_mode(0)
