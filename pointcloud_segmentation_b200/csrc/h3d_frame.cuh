@@ -177,7 +177,11 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   __shared__ int2 wsum[kK0Warps];
   __shared__ int2 wpre[kK0Warps];
   __shared__ int bb_s[6];
+  constexpr int kBigList = 512, kBigPerLane = 4;     // crowded voxels (9..128 members) of this CTA, ordered by whole warps
+  __shared__ int big_list[kBigList];
+  __shared__ int big_n;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) big_n = 0;
   const int rank = (int)cluster.block_rank(), n_blk = (int)cluster.num_blocks();   // n_blk <= kK0Cluster
   const int gtid = rank * kK0Threads + tid, T = n_blk * kK0Threads;
   const K0Grid &G = A.grid;
@@ -346,8 +350,16 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
             if (mi[a] == best) { vx = qx[a]; vy = qy[a]; vz = qz[a]; mi[a] = INT_MAX; }
           cx = __fadd_rn(cx, vx); cy = __fadd_rn(cy, vy); cz = __fadd_rn(cz, vz);
         }
+      } else if (oc.y <= 32 * kBigPerLane) {
+        // a crowded voxel (a near surface: tens of pixels per voxel) is a WARP's job, below: a thread ordering
+        // 60 members by insertion in global memory made this phase 30 us long
+        const int slot = atomicAdd(&big_n, 1);
+        if (slot < kBigList) { big_list[slot] = s; continue; }
+        cx = cy = cz = 0.0f;
+        goto slow_path;
       } else {
-        for (int a = 1; a < oc.y; ++a) {                   // insertion sort in place (rare: crowded voxels)
+      slow_path:
+        for (int a = 1; a < oc.y; ++a) {                   // insertion sort in place (very rare: > 128 points in a voxel)
           const int key = m[a];
           int b = a - 1;
           while (b >= 0 && m[b] > key) { m[b + 1] = m[b]; --b; }
@@ -364,6 +376,52 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
       const int o[3] = {float_to_ordered(cx), float_to_ordered(cy), float_to_ordered(cz)};
 #pragma unroll
       for (int c = 0; c < 3; ++c) { mn[c] = min(mn[c], o[c]); mx[c] = max(mx[c], o[c]); }
+    }
+    __syncthreads();
+    // crowded voxels, one per warp: every lane holds up to kBigPerLane members; rank = number of smaller raw
+    // indices (they are distinct), then the sum runs in rank order with the points handed over by shuffles
+    for (int e = warp; e < min(big_n, kBigList); e += kK0Warps) {
+      const int s = big_list[e];
+      const int2 oc = A.occ[s];
+      const int *m = A.members + oc.x;
+      int mi[kBigPerLane], rk[kBigPerLane];
+      float qx[kBigPerLane], qy[kBigPerLane], qz[kBigPerLane];
+#pragma unroll
+      for (int k = 0; k < kBigPerLane; ++k) { const int a = lane + 32 * k; mi[k] = a < oc.y ? m[a] : INT_MAX; rk[k] = 0; }
+#pragma unroll
+      for (int k = 0; k < kBigPerLane; ++k) {
+        if (mi[k] != INT_MAX) { const float3 p = load_xyz(A.raw, mi[k], A.stride); qx[k] = p.x; qy[k] = p.y; qz[k] = p.z; }
+        else { qx[k] = 0.0f; qy[k] = 0.0f; qz[k] = 0.0f; }
+      }
+#pragma unroll
+      for (int k2 = 0; k2 < kBigPerLane; ++k2) {
+#pragma unroll 8
+        for (int src = 0; src < 32; ++src) {
+          const int v = __shfl_sync(0xFFFFFFFFu, mi[k2], src);
+#pragma unroll
+          for (int k = 0; k < kBigPerLane; ++k) rk[k] += v < mi[k];
+        }
+      }
+      float cx = 0.0f, cy = 0.0f, cz = 0.0f;
+#pragma unroll 1
+      for (int r = 0; r < oc.y; ++r) {
+        bool has = false;
+        float vx = 0.0f, vy = 0.0f, vz = 0.0f;
+#pragma unroll
+        for (int k = 0; k < kBigPerLane; ++k)
+          if (mi[k] != INT_MAX && rk[k] == r) { has = true; vx = qx[k]; vy = qy[k]; vz = qz[k]; }
+        const int src = __ffs(__ballot_sync(0xFFFFFFFFu, has)) - 1;
+        vx = __shfl_sync(0xFFFFFFFFu, vx, src); vy = __shfl_sync(0xFFFFFFFFu, vy, src); vz = __shfl_sync(0xFFFFFFFFu, vz, src);
+        cx = __fadd_rn(cx, vx); cy = __fadd_rn(cy, vy); cz = __fadd_rn(cz, vz);
+      }
+      if (lane == 0) {
+        const float fc = (float)oc.y;
+        cx = __fdiv_rn(cx, fc); cy = __fdiv_rn(cy, fc); cz = __fdiv_rn(cz, fc);
+        A.filt[3 * (size_t)s] = cx; A.filt[3 * (size_t)s + 1] = cy; A.filt[3 * (size_t)s + 2] = cz;
+        const int o[3] = {float_to_ordered(cx), float_to_ordered(cy), float_to_ordered(cz)};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { mn[c] = min(mn[c], o[c]); mx[c] = max(mx[c], o[c]); }
+      }
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -486,6 +544,13 @@ __device__ __forceinline__ void patch_hough(HoughDev &h, const HoughDev &fixed, 
 // to 6 slots (3072 points), scan above -- measured on the 16 bench frames (profiles/r02_track_ab.txt): TRACK
 // wins 88 vs 103 us at 1.3 k points and loses 195 vs 179 us at 4.9 k (ATOMS with a return value costs ~13 cycles
 // per warp-vote against ~9 for the merging RED form; the scan it saves is a fixed ~0.2 us per direction).
+// one out-of-line function per slot count: each gets its own register allocation (the P <= 7 loops need no
+// spill; inlined into one body, all twelve shared the allocation of the widest and spilled 76 bytes)
+template <int P, bool TRACK>
+__device__ __noinline__ void vote_frame_variant(const HoughDev *hs, unsigned *planes, ResShared *sh, int cta, int n_cta) {
+  vote_resident<P, 0, true, TRACK>(*hs, nullptr, hs->dir_count, planes, *sh, cta, n_cta);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(kResThreads, 1)
 vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__restrict__ fd) {
@@ -497,8 +562,8 @@ vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__rest
   __syncthreads();
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
   for (unsigned q = threadIdx.x; q < 2 * kResG * hs.plane_stride / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-  const int cta = blockIdx.x, n_cta = gridDim.x, count = hs.dir_count;
-#define H3D_FRAME_VOTE(PP) vote_resident<PP, 0, true, (MODE == 1 || (MODE == 2 && PP <= 6))>(hs, nullptr, count, planes, sh, cta, n_cta); break;
+  const int cta = blockIdx.x, n_cta = gridDim.x;
+#define H3D_FRAME_VOTE(PP) vote_frame_variant<PP, (MODE == 1 || (MODE == 2 && PP <= 6))>(&hs, planes, &sh, cta, n_cta); break;
   switch ((hs.n + kResThreads - 1) / kResThreads) {
     case 0: case 1: H3D_FRAME_VOTE(1)
     case 2: H3D_FRAME_VOTE(2)

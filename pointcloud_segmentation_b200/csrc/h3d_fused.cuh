@@ -479,26 +479,58 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
         const float tl = ordered_float(sh.tmin_i), th = ordered_float(sh.tmax_i);
         const double t0 = (double)tl - (fabs((double)tl) * 1e-6 + 1e-9), t1 = (double)th + (fabs((double)th) * 1e-6 + 1e-9);
         const unsigned num_x = (unsigned)h.num_x;
-        for (int r = ut; r < n_own; r += un) {
-          if (rstale[r] || rv[r] == 0) continue;
-          const unsigned cx = rcell[r] / num_x, cy = rcell[r] - cx * num_x;
-          // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
-          const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-          double ilo, ihi;
-          if (cy == 0 || cy == num_x - 1 ||
-              (strip_interval(make_fast(h.coef[j], h.inv_s), a, b, cell_off, reach2, cx, cy, &ilo, &ihi) && ilo <= t1 && ihi >= t0))
-            rlist[atomicAdd(&sh.ns, 1)] = r;
+        constexpr int SU = 3;   // records per thread per batch: their coefficient loads (L2) are issued together
+        for (int r0 = ut; r0 < n_own; r0 += SU * un) {
+          DirCoef cj[SU];
+          bool live[SU];
+#pragma unroll
+          for (int u = 0; u < SU; ++u) {
+            const int r = r0 + u * un;
+            live[u] = r < n_own && !rstale[r] && rv[r] != 0;
+            if (live[u]) cj[u] = h.coef[h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G)];
+          }
+#pragma unroll
+          for (int u = 0; u < SU; ++u) {
+            if (!live[u]) continue;
+            const int r = r0 + u * un;
+            const unsigned cx = rcell[r] / num_x, cy = rcell[r] - cx * num_x;
+            // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
+            double ilo, ihi;
+            if (cy == 0 || cy == num_x - 1 ||
+                (strip_interval(make_fast(cj[u], h.inv_s), a, b, cell_off, reach2, cx, cy, &ilo, &ihi) && ilo <= t1 && ihi >= t0))
+              rlist[atomicAdd(&sh.ns, 1)] = r;
+          }
         }
         named_bar_sync(1, un);
         // exact test of the surviving records, one WARP per record: 32 removed points per step, and the
         // record is done at its first hit (a record whose max cell lies on the removed line is hit within a
         // step or two; testing every (record, point) pair cost up to 200 us per iteration at 18 SMs per frame)
         const int ns = sh.ns;
+        // the coefficients of a record come from L2 (~0.7 us): lane q of the warp fetches those of the q-th record
+        // the warp will test, 32 records per round trip, and hands them over by shuffle (one dependent L2 load per
+        // record made this phase 40 us long with ~400 candidate records per CTA)
+        DirCoef pre = {0.0, 0.0, 0.0, 0.0, 0.0};
+        int pre_base = -1;
 #pragma unroll 1
-        for (int s = warp - 1; s < ns; s += kResWarps - 1) {
+        for (int s = warp - 1, q = 0; s < ns; s += kResWarps - 1, ++q) {
+          if ((q & 31) == 0) {
+            const int sq = s + lane * (kResWarps - 1);
+            if (sq < ns) {
+              const int rq = rlist[sq];
+              pre = h.coef[h.dir_begin + (cta + (rq / G) * n_cta) * G + (rq % G)];
+            }
+            pre_base = q;
+          }
           const int r = rlist[s];
           const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-          const FastCoef fc = make_fast(h.coef[j], h.inv_s);
+          DirCoef cj;
+          {
+            const int src = q - pre_base;
+            cj.c0 = __shfl_sync(0xFFFFFFFFu, pre.c0, src); cj.c1 = __shfl_sync(0xFFFFFFFFu, pre.c1, src);
+            cj.c2 = __shfl_sync(0xFFFFFFFFu, pre.c2, src); cj.bx = __shfl_sync(0xFFFFFFFFu, pre.bx, src);
+            cj.by = __shfl_sync(0xFFFFFFFFu, pre.by, src);
+          }
+          const FastCoef fc = make_fast(cj, h.inv_s);
           const unsigned target = rcell[r];
           // only inliers whose t puts them near the cell can vote for it: skip the others on their float t
           // (edge cells reached through the reference's flat-index aliasing take every point)

@@ -7,6 +7,21 @@ from pointcloud_segmentation_b200 import capi, synth
 import bench
 
 frames = bench.make_frames(16)
+# the round-1 path for comparison: eleven K0 launches, Hough ctor on the host, vote_resident_kernel<P> picked by the host
+capi.set_fast_frames(False)
+pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frames.shape[1])
+us = []
+for rep in range(4):
+    for k in range(16):
+        res = pipe.run(frames[k])
+        if rep:
+            us.append((res.n_input, *pipe.timing_us()))
+pipe.close()
+a = np.array(us)
+print(json.dumps({"share": 148, "path": "general (round 1)", "k0_us": a[:, 1].mean(), "first_vote_us": a[:, 2].mean(),
+                  "loop_us": a[:, 3].mean(), "frame_us": a[:, 4].mean(),
+                  "first_vote_us_by_frame": [round(float(x), 1) for x in a[:16, 2]]}))
+capi.set_fast_frames(True)
 for share in (0, 18):
     for track in (2, 1, 0):
         capi.set_vote_track(track)
