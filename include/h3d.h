@@ -429,8 +429,8 @@ int h3d_set_fast_frames(int on);
  * mode.  Results are identical in every mode. */
 int h3d_set_vote_track(int mode);
 /* measurement hook: globaltimer stamps (ns) of the K0 cluster kernel of the pipeline's last fast-path frame:
- * start, after each of its six cluster barriers, end */
-int h3d_pipeline_k0_stamps(h3d_pipeline *p, unsigned long long t_ns[8]);
+ * start, after each of its seven cluster barriers (count, reduce, scan, scatter, order, centroids, bbox), end */
+int h3d_pipeline_k0_stamps(h3d_pipeline *p, unsigned long long t_ns[10]);
 
 /* debug aid: on != 0 makes every frame start from per-direction records of 0xFFFFFFFF votes, so a
  * record the first vote fails to write wins every argmax instead of silently keeping the previous

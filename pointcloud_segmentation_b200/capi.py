@@ -377,7 +377,7 @@ class Pipeline:
 
     def k0_stamps(self):
         """globaltimer ns of the K0 cluster kernel's phases for the last (fast-path) frame"""
-        t = (C.c_ulonglong * 8)()
+        t = (C.c_ulonglong * 10)()
         check(lib().h3d_pipeline_k0_stamps(self._p, t))
         return list(t)
 

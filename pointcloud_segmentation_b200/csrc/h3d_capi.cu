@@ -1568,6 +1568,7 @@ struct FastPath {
   K0Grid grid{};
   int2 *occ = nullptr;
   int2 *dir_rows = nullptr;     // per direction: quads of its plane the current frame can touch
+  int *sorted = nullptr;        // voxel member lists in ascending raw index (max_raw_points ints)
   int *tile_sums = nullptr;
   FrameDev *fd_dev = nullptr;
   size_t smem_vote = 0, smem_loop = 0;
@@ -1575,7 +1576,7 @@ struct FastPath {
   unsigned char *stage_host = nullptr, *stage_dev = nullptr;
   size_t off_st = 0, off_iters = 0, off_pool = 0, pool_entries = 0, stage_bytes = 0;
   void release() {
-    cudaFree(occ); cudaFree(dir_rows); cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
+    cudaFree(occ); cudaFree(dir_rows); cudaFree(sorted); sorted = nullptr; cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
     occ = nullptr; dir_rows = nullptr; tile_sums = nullptr; fd_dev = nullptr; stage_host = stage_dev = nullptr; on = false;
   }
 };
@@ -1615,6 +1616,7 @@ static int fast_path_setup(h3d_pipeline *p) {
   fp.smem_loop = ((dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;
   const size_t n = p->cfg.max_raw_points;
   H3D_CUDA(cudaMalloc(&fp.occ, n * sizeof(int2)));
+  H3D_CUDA(cudaMalloc(&fp.sorted, n * sizeof(int)));
   H3D_CUDA(cudaMalloc(&fp.tile_sums, 2 * kK0Cluster * sizeof(int)));
   H3D_CUDA(cudaMalloc(&fp.dir_rows, f.hg->space->num_b * sizeof(int2)));
   H3D_CUDA(cudaMalloc(&fp.fd_dev, sizeof(FrameDev)));
@@ -1668,7 +1670,7 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   FrameArgs fa;
   fa.raw = raw_dev; fa.n = (int)n; fa.stride = (int)stride;
   fa.win = p->win; fa.grid = fp.grid;
-  fa.count = p->pf.count; fa.start = p->pf.start; fa.members = p->pf.members; fa.occ = fp.occ; fa.tile_sums = fp.tile_sums;
+  fa.count = p->pf.count; fa.start = p->pf.start; fa.ncell = p->pf.slot; fa.members = p->pf.members; fa.sorted = fp.sorted; fa.occ = fp.occ; fa.tile_sums = fp.tile_sums;
   fa.filt = p->filt_dev; fa.out_cap = (int)p->cfg.max_raw_points;
   fa.px = h->px; fa.py = h->py; fa.pz = h->pz; fa.w = h->w; fa.orig = f.orig;
   fa.fd = fp.fd_dev;
@@ -2411,11 +2413,11 @@ extern "C" int h3d_set_vote_track(int mode) { return g_vote_track.exchange(mode 
 
 // measurement: globaltimer stamps of the last fast-path frame's K0 cluster kernel (start, after each of its six
 // cluster barriers, end), nanoseconds
-extern "C" int h3d_pipeline_k0_stamps(h3d_pipeline *p, unsigned long long t_ns[8]) {
+extern "C" int h3d_pipeline_k0_stamps(h3d_pipeline *p, unsigned long long t_ns[10]) {
   if (!p || !t_ns) return fail(H3D_ERR_ARG, "bad argument");
   if (!p->fast.on || !p->fast.last_was_fast) return fail(H3D_ERR_ARG, "the last frame did not run on the fast path");
   const FrameDev &F = *reinterpret_cast<const FrameDev *>(p->fast.stage_host);
-  for (int k = 0; k < 8; ++k) t_ns[k] = F.t_ns[k];
+  for (int k = 0; k < 10; ++k) t_ns[k] = F.t_ns[k];
   return H3D_OK;
 }
 

@@ -93,7 +93,7 @@ struct FrameDev {
   int nb_planes, n_cap;   // shared-memory layout of the loop kernel for this frame
   int bb[6];              // scratch: ordered-int float bounding box (min x,y,z, max x,y,z)
   int pad1[2];
-  unsigned long long t_ns[8];   // measurement: globaltimer at the start and after each phase of the K0 cluster kernel (thread 0)
+  unsigned long long t_ns[10];   // measurement: globaltimer at the start and after each phase of the K0 cluster kernel (thread 0)
 };
 
 // ---- the voxel grid of the window (host, once per pipeline) ------------------------------------------------
@@ -137,8 +137,9 @@ struct FrameArgs {
   K0Window win;
   K0Grid grid;
   int *count;                // grid.cells ints: zero on entry, zero on exit
-  int *start;                // grid.cells ints (written for occupied voxels only)
-  int *members;              // >= n raw indices, grouped by voxel
+  int *start, *ncell;        // grid.cells ints each (written for occupied voxels only): list start, list length
+  int *members;              // >= n raw indices, grouped by voxel (scatter order)
+  int *sorted;               // >= n: the same lists in ascending raw index
   int2 *occ;                 // >= n: (start, count) of the occupied voxels in ascending voxel order
   int *tile_sums;            // 2 * kK0Cluster
   float *filt;               // 3 floats per centroid (the filtered cloud, kept for h3d_pipeline_filtered / post-tests)
@@ -177,7 +178,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   __shared__ int2 wsum[kK0Warps];
   __shared__ int2 wpre[kK0Warps];
   __shared__ int bb_s[6];
-  constexpr int kBigList = 512, kBigPerLane = 4;     // crowded voxels (9..128 members) of this CTA, ordered by whole warps
+  constexpr int kBigList = 1024, kBigVoxel = 32;     // voxels with more members than kBigVoxel are summed by whole warps
   __shared__ int big_list[kBigList];
   __shared__ int big_n;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -186,7 +187,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   const int gtid = rank * kK0Threads + tid, T = n_blk * kK0Threads;
   const K0Grid &G = A.grid;
   int stamp_k = 0;
-  auto stamp = [&]() { if (gtid == 0 && stamp_k < 8) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); A.fd->t_ns[stamp_k] = t; } ++stamp_k; };
+  auto stamp = [&]() { if (gtid == 0 && stamp_k < 10) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); A.fd->t_ns[stamp_k] = t; } ++stamp_k; };
   stamp();
 
   if (gtid < 6) A.fd->bb[gtid] = gtid < 3 ? INT_MAX : INT_MIN;
@@ -287,7 +288,7 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           if (vv[e] > 0) {
-            A.start[c + e] = sc;
+            A.start[c + e] = sc; A.ncell[c + e] = vv[e];
             A.occ[sn] = make_int2(sc, vv[e]);
             sc += vv[e]; ++sn;
           }
@@ -301,8 +302,12 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
   stamp();
 
   // ---- phase C: scatter the raw indices into their voxel's list; the histogram goes back to zero -------
+  // (a frame of up to U * T points is one batch: the keys / list starts / list lengths of a thread's points stay in
+  // registers for phase C'; larger frames recompute them there)
+  const bool one_batch = A.n <= U * T;
+  int key[U], st[U], nc[U];
   for (int i0 = gtid; i0 < A.n; i0 += U * T) {
-    int key[U], st[U], old[U];
+    int old[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int i = i0 + u * T;
@@ -310,118 +315,96 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
       key[u] = in_window(p, A.win) ? window_voxel_key(p, G) : -1;
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) if (key[u] >= 0) { st[u] = A.start[key[u]]; old[u] = atomicSub(&A.count[key[u]], 1); }
+    for (int u = 0; u < U; ++u)
+      if (key[u] >= 0) { st[u] = A.start[key[u]]; nc[u] = A.ncell[key[u]]; old[u] = atomicSub(&A.count[key[u]], 1); }
 #pragma unroll
     for (int u = 0; u < U; ++u) if (key[u] >= 0) A.members[st[u] + old[u] - 1] = i0 + u * T;
   }
   cluster.sync();
   stamp();
 
-  // ---- phase D: one thread per occupied voxel: members back in input order (the canonical summation
-  // order), sequential float sums, centroid; float bounding box of the centroids -------------------------
+  // ---- phase C': the lists in input order (the canonical summation order of the centroids): the rank of a
+  // point is the number of smaller raw indices in its voxel's list; one thread per POINT, a list is a few to a
+  // few tens of entries long and its loads are independent ------------------------------------------------
+  for (int i0 = gtid; i0 < A.n; i0 += U * T) {
+    if (!one_batch) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int i = i0 + u * T;
+        const float3 p = i < A.n ? load_xyz(A.raw, i, A.stride) : make_float3(NAN, NAN, NAN);
+        key[u] = in_window(p, A.win) ? window_voxel_key(p, G) : -1;
+        if (key[u] >= 0) { st[u] = A.start[key[u]]; nc[u] = A.ncell[key[u]]; }
+      }
+    }
+    int rk[U], cmax = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) { rk[u] = 0; if (key[u] < 0) nc[u] = 0; cmax = max(cmax, nc[u]); }
+    for (int a0 = 0; a0 < cmax; a0 += 4) {
+      int v[U][4];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) v[u][q] = a0 + q < nc[u] ? A.members[st[u] + a0 + q] : INT_MAX;
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) rk[u] += v[u][q] < i0 + u * T;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) if (key[u] >= 0) A.sorted[st[u] + rk[u]] = i0 + u * T;
+  }
+  cluster.sync();
+  stamp();
+
+  // ---- phase D: centroids: sequential float sums over the ordered lists; float bounding box -------------
+  // one thread per occupied voxel (8 list entries and 8 points in flight per trip); a crowded voxel (a near
+  // surface: a hundred pixels) is a warp's job: 32 loads per trip, the sum runs on lane 0's values by shuffle
   const int n_keep = min(n_out, A.out_cap);
   {
-    constexpr int LM = 8;                                  // members ordered in REGISTERS up to here
     int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
-    for (int s = gtid; s < n_keep; s += T) {
-      const int2 oc = A.occ[s];
-      int *m = A.members + oc.x;
-      float cx = 0.0f, cy = 0.0f, cz = 0.0f;
-      if (oc.y <= LM) {
-        // every index is static (fully unrolled): the lists stay in registers.  (Per-thread local arrays of
-        // 24 entries made 393 KB per SM, more than the L1 holds: this phase alone took 24 us.)
-        int mi[LM];
-        float qx[LM], qy[LM], qz[LM];
-#pragma unroll
-        for (int a = 0; a < LM; ++a) mi[a] = a < oc.y ? m[a] : INT_MAX;
-#pragma unroll
-        for (int a = 0; a < LM; ++a) {
-          if (a < oc.y) { const float3 p = load_xyz(A.raw, mi[a], A.stride); qx[a] = p.x; qy[a] = p.y; qz[a] = p.z; }
-          else { qx[a] = 0.0f; qy[a] = 0.0f; qz[a] = 0.0f; }
-        }
-#pragma unroll 1
-        for (int k = 0; k < oc.y; ++k) {                   // ascending raw index = the canonical summation order
-          int best = INT_MAX;
-#pragma unroll
-          for (int a = 0; a < LM; ++a) best = min(best, mi[a]);
-          float vx = 0.0f, vy = 0.0f, vz = 0.0f;
-#pragma unroll
-          for (int a = 0; a < LM; ++a)
-            if (mi[a] == best) { vx = qx[a]; vy = qy[a]; vz = qz[a]; mi[a] = INT_MAX; }
-          cx = __fadd_rn(cx, vx); cy = __fadd_rn(cy, vy); cz = __fadd_rn(cz, vz);
-        }
-      } else if (oc.y <= 32 * kBigPerLane) {
-        // a crowded voxel (a near surface: tens of pixels per voxel) is a WARP's job, below: a thread ordering
-        // 60 members by insertion in global memory made this phase 30 us long
-        const int slot = atomicAdd(&big_n, 1);
-        if (slot < kBigList) { big_list[slot] = s; continue; }
-        cx = cy = cz = 0.0f;
-        goto slow_path;
-      } else {
-      slow_path:
-        for (int a = 1; a < oc.y; ++a) {                   // insertion sort in place (very rare: > 128 points in a voxel)
-          const int key = m[a];
-          int b = a - 1;
-          while (b >= 0 && m[b] > key) { m[b + 1] = m[b]; --b; }
-          m[b + 1] = key;
-        }
-        for (int a = 0; a < oc.y; ++a) {
-          const float3 p = load_xyz(A.raw, m[a], A.stride);
-          cx = __fadd_rn(cx, p.x); cy = __fadd_rn(cy, p.y); cz = __fadd_rn(cz, p.z);
-        }
-      }
-      const float fc = (float)oc.y;
+    auto emit = [&](int s, float cx, float cy, float cz, int cnt) {
+      const float fc = (float)cnt;
       cx = __fdiv_rn(cx, fc); cy = __fdiv_rn(cy, fc); cz = __fdiv_rn(cz, fc);
       A.filt[3 * (size_t)s] = cx; A.filt[3 * (size_t)s + 1] = cy; A.filt[3 * (size_t)s + 2] = cz;
       const int o[3] = {float_to_ordered(cx), float_to_ordered(cy), float_to_ordered(cz)};
 #pragma unroll
       for (int c = 0; c < 3; ++c) { mn[c] = min(mn[c], o[c]); mx[c] = max(mx[c], o[c]); }
+    };
+    for (int s = gtid; s < n_keep; s += T) {
+      const int2 oc = A.occ[s];
+      if (oc.y > kBigVoxel) {
+        const int slot = atomicAdd(&big_n, 1);
+        if (slot < kBigList) { big_list[slot] = s; continue; }
+      }
+      const int *m = A.sorted + oc.x;
+      float cx = 0.0f, cy = 0.0f, cz = 0.0f;
+#pragma unroll 8
+      for (int a = 0; a < oc.y; ++a) {
+        const float3 p = load_xyz(A.raw, m[a], A.stride);
+        cx = __fadd_rn(cx, p.x); cy = __fadd_rn(cy, p.y); cz = __fadd_rn(cz, p.z);
+      }
+      emit(s, cx, cy, cz, oc.y);
     }
     __syncthreads();
-    // crowded voxels, one per warp: every lane holds up to kBigPerLane members; rank = number of smaller raw
-    // indices (they are distinct), then the sum runs in rank order with the points handed over by shuffles
     for (int e = warp; e < min(big_n, kBigList); e += kK0Warps) {
       const int s = big_list[e];
       const int2 oc = A.occ[s];
-      const int *m = A.members + oc.x;
-      int mi[kBigPerLane], rk[kBigPerLane];
-      float qx[kBigPerLane], qy[kBigPerLane], qz[kBigPerLane];
-#pragma unroll
-      for (int k = 0; k < kBigPerLane; ++k) { const int a = lane + 32 * k; mi[k] = a < oc.y ? m[a] : INT_MAX; rk[k] = 0; }
-#pragma unroll
-      for (int k = 0; k < kBigPerLane; ++k) {
-        if (mi[k] != INT_MAX) { const float3 p = load_xyz(A.raw, mi[k], A.stride); qx[k] = p.x; qy[k] = p.y; qz[k] = p.z; }
-        else { qx[k] = 0.0f; qy[k] = 0.0f; qz[k] = 0.0f; }
-      }
-#pragma unroll
-      for (int k2 = 0; k2 < kBigPerLane; ++k2) {
-#pragma unroll 8
-        for (int src = 0; src < 32; ++src) {
-          const int v = __shfl_sync(0xFFFFFFFFu, mi[k2], src);
-#pragma unroll
-          for (int k = 0; k < kBigPerLane; ++k) rk[k] += v < mi[k];
-        }
-      }
+      const int *m = A.sorted + oc.x;
       float cx = 0.0f, cy = 0.0f, cz = 0.0f;
-#pragma unroll 1
-      for (int r = 0; r < oc.y; ++r) {
-        bool has = false;
-        float vx = 0.0f, vy = 0.0f, vz = 0.0f;
-#pragma unroll
-        for (int k = 0; k < kBigPerLane; ++k)
-          if (mi[k] != INT_MAX && rk[k] == r) { has = true; vx = qx[k]; vy = qy[k]; vz = qz[k]; }
-        const int src = __ffs(__ballot_sync(0xFFFFFFFFu, has)) - 1;
-        vx = __shfl_sync(0xFFFFFFFFu, vx, src); vy = __shfl_sync(0xFFFFFFFFu, vy, src); vz = __shfl_sync(0xFFFFFFFFu, vz, src);
-        cx = __fadd_rn(cx, vx); cy = __fadd_rn(cy, vy); cz = __fadd_rn(cz, vz);
+      int idx = lane < oc.y ? m[lane] : -1;
+      for (int a0 = 0; a0 < oc.y; a0 += 32) {
+        const int nxt = a0 + 32 + lane < oc.y ? m[a0 + 32 + lane] : -1;     // next trip's entries, in flight
+        float3 p = make_float3(0.0f, 0.0f, 0.0f);
+        if (idx >= 0) p = load_xyz(A.raw, idx, A.stride);
+        const int cnt = min(32, oc.y - a0);
+        for (int q = 0; q < cnt; ++q) {
+          cx = __fadd_rn(cx, __shfl_sync(0xFFFFFFFFu, p.x, q));
+          cy = __fadd_rn(cy, __shfl_sync(0xFFFFFFFFu, p.y, q));
+          cz = __fadd_rn(cz, __shfl_sync(0xFFFFFFFFu, p.z, q));
+        }
+        idx = nxt;
       }
-      if (lane == 0) {
-        const float fc = (float)oc.y;
-        cx = __fdiv_rn(cx, fc); cy = __fdiv_rn(cy, fc); cz = __fdiv_rn(cz, fc);
-        A.filt[3 * (size_t)s] = cx; A.filt[3 * (size_t)s + 1] = cy; A.filt[3 * (size_t)s + 2] = cz;
-        const int o[3] = {float_to_ordered(cx), float_to_ordered(cy), float_to_ordered(cz)};
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { mn[c] = min(mn[c], o[c]); mx[c] = max(mx[c], o[c]); }
-      }
+      if (lane == 0) emit(s, cx, cy, cz, oc.y);
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) {

@@ -67,7 +67,8 @@ int PointCloud::readFromFile(const char *path, char delim) {
   if (!in) return 1;
   std::string line;
   while (std::getline(in, line)) {
-    if (line.empty() || line[0] == '#') continue;
+    if (!line.empty() && line[0] == '#') continue;
+    if (line.empty()) return 2;   // sscanf finds no number on an empty line: n != 3 (lib/pointcloud.cpp:72-77)
     std::stringstream ss(line);
     std::string field;
     double v[3];
@@ -138,15 +139,30 @@ double orthogonal_LSQ_b200(const PointCloud &pc, Vector3d *a, Vector3d *b) {
 // ---- fused loop ------------------------------------------------------------------------------
 int hough3dlines_b200(const double *xyz, size_t n, std::vector<Line3d> &lines, double opt_dx, int granularity,
                       int opt_minvotes, int opt_nlines, int &nblines_extracted) {
-  const size_t max_iters = opt_nlines > 0 ? (size_t)opt_nlines + 1 : 256;
-  std::vector<h3d_iter> iters(max_iters);
-  std::vector<uint32_t> pool(2 * max_iters * (n ? n : 1));
+  // opt_nlines == 0 means "until exhausted" (wrap.h:341-342): the record and index buffers start from a guess
+  // and the call is repeated with the sizes it reports when they were too small -- no line is ever dropped
+  size_t max_iters = opt_nlines > 0 ? (size_t)opt_nlines + 1 : 256;
+  size_t pool_cap = 2 * max_iters * (n ? n : 1);
+  const size_t pool_guess = (size_t)64 << 20;   // 256 MB of indices before the first answer is known
+  if (pool_cap > pool_guess) pool_cap = pool_guess > 4 * n ? pool_guess : 4 * (n ? n : 1);
+  std::vector<h3d_iter> iters;
+  std::vector<uint32_t> pool;
   h3d_result res;
-  if (h3d_hough3dlines(xyz, n, granularity, opt_dx, opt_minvotes, opt_nlines, 0, iters.data(), max_iters,
-                       pool.data(), pool.size(), &res) != H3D_OK)
-    return 1;
+  for (int attempt = 0; attempt < 3; ++attempt) {
+    iters.resize(max_iters);
+    pool.resize(pool_cap);
+    if (h3d_hough3dlines(xyz, n, granularity, opt_dx, opt_minvotes, opt_nlines, 0, iters.data(), max_iters,
+                         pool.data(), pool.size(), &res) != H3D_OK)
+      return 1;
+    if (res.rc != 0) break;
+    if (res.n_iters <= max_iters && res.pool_used <= pool_cap) break;
+    if (res.n_iters > max_iters) max_iters = (size_t)res.n_iters + 1;
+    // pool_used saturates at the capacity: when it filled up, size for the worst case of the iterations seen
+    if (res.pool_used >= pool_cap) pool_cap = 2 * max_iters * (n ? n : 1);
+  }
   nblines_extracted = 0;
   if (res.rc != 0) return 1;
+  if (res.n_iters > max_iters) return 1;   // did not converge to a consistent size (cannot happen: sizes only grow)
   const size_t n_rec = res.n_iters < max_iters ? res.n_iters : max_iters;
   for (size_t k = 0; k < n_rec; ++k) {
     const h3d_iter &it = iters[k];

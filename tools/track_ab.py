@@ -38,8 +38,8 @@ for share in (0, 18):
         a = np.array(us)
         if track == 2:
             print("K0 cluster kernel phases (us) on the last frame, share", share or 148, ":",
-                  dict(zip(("A_count", "B1_reduce", "B2_scan", "C_scatter", "D_centroid", "E_shift_ctor"),
-                           [round(float(x) / 1e3, 2) for x in np.diff(st[:7])])))
+                  dict(zip(("A_count", "B1_reduce", "B2_scan", "C_scatter", "C2_order", "D_centroid", "E_shift_ctor"),
+                           [round(float(x) / 1e3, 2) for x in np.diff(st[:8])])))
         print(json.dumps({"share": share or 148, "vote": ("scan", "track", "auto")[track], "k0_us": a[:, 1].mean(),
                           "first_vote_us": a[:, 2].mean(), "loop_us": a[:, 3].mean(), "frame_us": a[:, 4].mean(),
                           "gvotes_per_s": float((a[:, 0] * 20481 / a[:, 2] / 1e3).mean()),
