@@ -1716,6 +1716,7 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   FusedArgs a;
   memset(&a, 0, sizeof a);
   a.h = hd;
+  a.h.dir_rows = fp.dir_rows;   // reachable rows per direction, written by this frame's K0 kernel
   a.st = f.st_dev; a.iters = f.iters_dev; a.pool = f.pool_dev; a.orig = f.orig; a.dirs = h->space->dirs_dev;
   a.xchg = f.gbest; a.bar = f.sync_dev;
   a.n_own_max = n_own;

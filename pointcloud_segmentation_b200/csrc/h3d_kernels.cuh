@@ -519,6 +519,7 @@ struct ResShared {
   double coef[2][kResG][6];   // raw DirCoef of the directions voted in phase k (slot k&1)
   int dir[3][kResG];          // local direction numbers of phase k (slot k%3; -1: none); the
                               // previous phase's numbers stay readable while the next are staged
+  int zero_ctr[3];            // TRACK form: chunk counter of the zero-fill of phase k (slot k%3), reset two phases ahead
   int2 rows[3][kResG];        // same slots: quads [x, y) of the direction's plane that the points can touch (the
                               // coef slots are only double-buffered: the previous group's are overwritten by the staging
                               // of the next group in the very phase that scans the previous group's planes)
@@ -570,6 +571,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
     if (!h.dir_rows || l < 0) sh.rows[dslot][tid] = make_int2(0, 0x7FFFFFFF);
     sh.dir[dslot][tid] = l;
   };
+  if (tid == 0) { sh.zero_ctr[0] = 0; sh.zero_ctr[1] = 0; sh.zero_ctr[2] = 0; }
   if (tid < G) { stage(cta, 0, 0); cp_async_wait_all(); }
   __syncthreads();   // also orders the kernel's zero-fill of the planes
   const double kmagic = h.kmagic, inv_s = h.inv_s;
@@ -665,13 +667,23 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
       }
     }
     if (TRACK) {
-      if (prev_any) {   // the previous group's planes back to zero (their maxima were tracked, not scanned)
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
+      if (tid == 0) sh.zero_ctr[(k + 1) % 3] = 0;   // last used in phase k-2, next in phase k+1: no reader now
+      if (prev_any) {
+        // the previous group's planes back to zero (their maxima were tracked, not scanned).  The warps do not
+        // finish their votes together (5 or 6 slots of points each), so the zero-fill is handed out in chunks of
+        // kZeroChunk quads to whichever warp is free (ncu, round 2: 14 % of the samples waited at the phase barrier)
+        constexpr unsigned kZeroChunk = 128;            // 4 STS.128 per lane
+        const unsigned per_plane = (quads + kZeroChunk - 1) / kZeroChunk, n_chunks = per_plane * G;
+        for (;;) {
+          unsigned c = 0;
+          if (lane == 0) c = (unsigned)atomicAdd(&sh.zero_ctr[dslot], 1);
+          c = __shfl_sync(0xFFFFFFFFu, c, 0);
+          if (c >= n_chunks) break;
+          const unsigned g = c / per_plane, q0 = (c - g * per_plane) * kZeroChunk;
           const int2 qr = sh.rows[dprev][g];
+          const unsigned qb = max(q0, (unsigned)qr.x), qe = min(min(q0 + kZeroChunk, (unsigned)qr.y), quads);
           uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)((slot ^ 1) * G + g) * stride);
-          const unsigned qe = min((unsigned)qr.y, quads);
-          for (unsigned q = (unsigned)qr.x + tid; q < qe; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
+          for (unsigned q = qb + lane; q < qe; q += 32) p4[q] = make_uint4(0, 0, 0, 0);
         }
       }
       if (tid < G) cp_async_wait_all();
