@@ -1678,7 +1678,8 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   fa.st = f.st_dev; fa.minvotes = p->cfg.opt_minvotes; fa.nlines_max = opt_nlines; fa.max_iters = (int)st_max_iters;
   fa.pool_cap = st_pool_cap;
   fa.xchg = f.gbest; fa.xchg_words = (int)xchg_words; fa.bar = f.sync_dev;
-  fa.smem_loop = (unsigned)fp.smem_loop; fa.tables_bytes = (unsigned)n_own * 16u; fa.smem_vote = (unsigned)fp.smem_vote;
+  fa.smem_loop = (unsigned)fp.smem_loop; fa.tables_bytes = (unsigned)n_own * 16u;
+  fa.smem_vote = (unsigned)(fp.smem_vote - kVoteFramePlanesOff);   // what the planes get behind the kernel's header
   fa.coef = h->space->coef_dev; fa.dir_rows = fp.dir_rows;
   {
     // cluster width: the whole GPU is this frame's -> 8 (latency); frames in flight beside it -> 2
