@@ -1144,11 +1144,13 @@ int try_launch_fused(FrameCtx &f, const LoopBuffers &lb, int opt_nlines, double 
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
   if (h->dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   const size_t smem = ((h->dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;   // everything the SM offers
+  if (smem < kFusedHdr + 1024) return H3D_OK;
+  const size_t body = smem - kFusedHdr;            // behind the kernel's HoughDev + FusedShared header
   // first vote: 2*G planes + pad; loop: nb planes + pad + the live points (24 B) + the inlier list (4 B) + its t values (4 B)
-  if (tables + 2 * kResG * plane_bytes + 16 > smem) return H3D_OK;
+  if (tables + 2 * kResG * plane_bytes + 16 > body) return H3D_OK;
   const size_t n_cap = ((size_t)hd.n + 1) & ~(size_t)1;
-  if (tables + 16 + 32 * n_cap + 2 * plane_bytes > smem) return H3D_OK;
-  size_t nb = (smem - tables - 16 - 32 * n_cap) / plane_bytes;
+  if (tables + 16 + 32 * n_cap + 2 * plane_bytes > body) return H3D_OK;
+  size_t nb = (body - tables - 16 - 32 * n_cap) / plane_bytes;
   if (nb > 2 * kResG) nb = 2 * kResG;
   nb &= ~(size_t)1;
   const size_t iters = (size_t)(opt_nlines > 0 ? opt_nlines : hd.n) + 2;
@@ -1614,6 +1616,7 @@ static int fast_path_setup(h3d_pipeline *p) {
   H3D_CUDA(cudaFuncGetAttributes(&fa, fused_loop_kernel));
   if (dev.smem_optin < fa.sharedSizeBytes + 1024) return H3D_OK;
   fp.smem_loop = ((dev.smem_optin - fa.sharedSizeBytes - 256) / 16) * 16;
+  if (fp.smem_loop < kFusedHdr + 4096) return H3D_OK;
   const size_t n = p->cfg.max_raw_points;
   H3D_CUDA(cudaMalloc(&fp.occ, n * sizeof(int2)));
   H3D_CUDA(cudaMalloc(&fp.sorted, n * sizeof(int)));
@@ -1678,7 +1681,7 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   fa.st = f.st_dev; fa.minvotes = p->cfg.opt_minvotes; fa.nlines_max = opt_nlines; fa.max_iters = (int)st_max_iters;
   fa.pool_cap = st_pool_cap;
   fa.xchg = f.gbest; fa.xchg_words = (int)xchg_words; fa.bar = f.sync_dev;
-  fa.smem_loop = (unsigned)fp.smem_loop; fa.tables_bytes = (unsigned)n_own * 16u;
+  fa.smem_loop = (unsigned)(fp.smem_loop - kFusedHdr); fa.tables_bytes = (unsigned)n_own * 16u;   // the loop's body behind its header
   fa.smem_vote = (unsigned)(fp.smem_vote - kVoteFramePlanesOff);   // what the planes get behind the kernel's header
   fa.coef = h->space->coef_dev; fa.dir_rows = fp.dir_rows;
   {

@@ -339,37 +339,240 @@ __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints
   best0 = b0; best1 = b1;
 }
 
+// ---- shared-memory layout of the loop kernel ---------------------------------------------------------------
+// [HoughDev | FusedShared | record tables | planes (+ pad) | live points, inlier list, its t values], all carved
+// out of the one extern array so that the out-of-line phase functions below address it as SHARED memory (LDS /
+// STS / ATOMS) and get a register allocation of their own: inlined into one body, every hot loop of the kernel
+// shared 128 registers with everything else that was live and spilled (224 bytes with the re-vote prefetch).
+constexpr unsigned kFusedHoughBytes = 256;
+constexpr unsigned kFusedHdr = kFusedHoughBytes + (unsigned)((sizeof(FusedShared) + 255) / 256 * 256);
+static_assert(sizeof(HoughDev) <= kFusedHoughBytes, "HoughDev must fit its slot");
+
+struct FusedView {
+  const HoughDev *h;
+  FusedShared *sh;
+  unsigned *rv, *rcell, *rstale;   // per own record: max votes (bound when stale), first max cell, stale flag
+  int *rlist;
+  unsigned *planes;
+  unsigned planes_sa, dummy_sa, stride, quads;
+  FusedPoints Q;
+};
+__device__ __forceinline__ FusedView fused_view(int n_own, int nb, int n_cap) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FusedView V;
+  V.h = reinterpret_cast<const HoughDev *>(smem_raw);
+  V.sh = reinterpret_cast<FusedShared *>(smem_raw + kFusedHoughBytes);
+  unsigned char *body = smem_raw + kFusedHdr;
+  V.rv = reinterpret_cast<unsigned *>(body);
+  V.rcell = V.rv + n_own;
+  V.rstale = V.rcell + n_own;
+  V.rlist = reinterpret_cast<int *>(V.rstale + n_own);
+  V.planes = reinterpret_cast<unsigned *>(body + (size_t)n_own * 16u);   // n_own % 4 == 0 -> multiple of 16
+  V.stride = V.h->plane_stride; V.quads = V.stride / 4;
+  V.planes_sa = (unsigned)__cvta_generic_to_shared(V.planes);
+  V.dummy_sa = V.planes_sa + (unsigned)nb * V.stride * 4u;              // pad word of the loop layout
+  V.Q.x = reinterpret_cast<double *>(V.planes + (size_t)nb * V.stride + 4);
+  V.Q.y = V.Q.x + n_cap; V.Q.z = V.Q.y + n_cap;
+  V.Q.yidx = reinterpret_cast<int *>(V.Q.z + n_cap);
+  V.Q.yt = reinterpret_cast<float *>(V.Q.yidx + n_cap);
+  return V;
+}
+
+// K4 inside the loop: Hough::subtract(Y) for the CTA's own directions, run by warps 1..15 while warp 0 solves the
+// second eigen-problem.  Y (pass 2, ny2 points) lies within opt_dx of the line (a, b) of pass 2.
+__device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b)[3], int ny2, int n_own, int nb, int n_cap,
+                                          int cta, int n_cta, double cell_off, double reach2) {
+  constexpr int G = kResG;
+  const FusedView V = fused_view(n_own, nb, n_cap);
+  const HoughDev &h = *V.h;
+  FusedShared &sh = *V.sh;
+  unsigned *rv = V.rv, *rcell = V.rcell, *rstale = V.rstale;
+  int *rlist = V.rlist;
+  const FusedPoints &Q = V.Q;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        // Y (pass 2) lies within opt_dx of the line (a, b) of pass 2
+        const int ut = tid - 32, un = kResThreads - 32;
+        const float tl = ordered_float(sh.tmin_i), th = ordered_float(sh.tmax_i);
+        const double t0 = (double)tl - (fabs((double)tl) * 1e-6 + 1e-9), t1 = (double)th + (fabs((double)th) * 1e-6 + 1e-9);
+        const unsigned num_x = (unsigned)h.num_x;
+        constexpr int SU = 3;   // records per thread per batch: their coefficient loads (L2) are issued together
+        for (int r0 = ut; r0 < n_own; r0 += SU * un) {
+          DirCoef cj[SU];
+          bool live[SU];
+#pragma unroll
+          for (int u = 0; u < SU; ++u) {
+            const int r = r0 + u * un;
+            live[u] = r < n_own && !rstale[r] && rv[r] != 0;
+            if (live[u]) cj[u] = h.coef[h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G)];
+          }
+#pragma unroll
+          for (int u = 0; u < SU; ++u) {
+            if (!live[u]) continue;
+            const int r = r0 + u * un;
+            const unsigned cx = rcell[r] / num_x, cy = rcell[r] - cx * num_x;
+            // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
+            double ilo, ihi;
+            if (cy == 0 || cy == num_x - 1 ||
+                (strip_interval(make_fast(cj[u], h.inv_s), a, b, cell_off, reach2, cx, cy, &ilo, &ihi) && ilo <= t1 && ihi >= t0))
+              rlist[atomicAdd(&sh.ns, 1)] = r;
+          }
+        }
+        named_bar_sync(1, un);
+        // exact test of the surviving records, one WARP per record: 32 removed points per step, and the
+        // record is done at its first hit (a record whose max cell lies on the removed line is hit within a
+        // step or two; testing every (record, point) pair cost up to 200 us per iteration at 18 SMs per frame)
+        const int ns = sh.ns;
+        // the coefficients of a record come from L2 (~0.7 us): lane q of the warp fetches those of the q-th record
+        // the warp will test, 32 records per round trip, and hands them over by shuffle (one dependent L2 load per
+        // record made this phase 40 us long with ~400 candidate records per CTA)
+        DirCoef pre = {0.0, 0.0, 0.0, 0.0, 0.0};
+        int pre_base = -1;
+#pragma unroll 1
+        for (int s = warp - 1, q = 0; s < ns; s += kResWarps - 1, ++q) {
+          if ((q & 31) == 0) {
+            const int sq = s + lane * (kResWarps - 1);
+            if (sq < ns) {
+              const int rq = rlist[sq];
+              pre = h.coef[h.dir_begin + (cta + (rq / G) * n_cta) * G + (rq % G)];
+            }
+            pre_base = q;
+          }
+          const int r = rlist[s];
+          const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
+          DirCoef cj;
+          {
+            const int src = q - pre_base;
+            cj.c0 = __shfl_sync(0xFFFFFFFFu, pre.c0, src); cj.c1 = __shfl_sync(0xFFFFFFFFu, pre.c1, src);
+            cj.c2 = __shfl_sync(0xFFFFFFFFu, pre.c2, src); cj.bx = __shfl_sync(0xFFFFFFFFu, pre.bx, src);
+            cj.by = __shfl_sync(0xFFFFFFFFu, pre.by, src);
+          }
+          const FastCoef fc = make_fast(cj, h.inv_s);
+          const unsigned target = rcell[r];
+          // only inliers whose t puts them near the cell can vote for it: skip the others on their float t
+          // (edge cells reached through the reference's flat-index aliasing take every point)
+          const unsigned cx = target / num_x, cy = target - cx * num_x;
+          double ilo = -INFINITY, ihi = INFINITY;
+          if (cy != 0 && cy != num_x - 1) strip_interval(fc, a, b, cell_off, reach2, cx, cy, &ilo, &ihi);
+          const float flo = (float)(ilo - (fabs(ilo) * 1e-6 + 1e-6)), fhi = (float)(ihi + (fabs(ihi) * 1e-6 + 1e-6));
+#pragma unroll 1
+          for (int e0 = 0; e0 < ny2; e0 += 32) {
+            const int e = e0 + lane;
+            bool cand = false;
+            if (e < ny2) { const float te = Q.yt[e]; cand = te >= flo && te <= fhi; }
+            if (!__any_sync(0xFFFFFFFFu, cand)) continue;
+            bool hit = false;
+            if (cand) { const int i = Q.yidx[e]; hit = vote_cell(h, fc, j, Q.x[i], Q.y[i], Q.z[i]) == target; }
+            if (__any_sync(0xFFFFFFFFu, hit)) { if (lane == 0) rstale[r] = 1; break; }
+          }
+        }
+}
+
+// Re-vote of the stale records listed in rlist[0..nlist) (their bound reaches the best exact record).
+__device__ __noinline__ void fused_revote(int nlist, int n_alive, int n_own, int nb, int n_cap, int cta, int n_cta) {
+  constexpr int G = kResG;
+  const FusedView V = fused_view(n_own, nb, n_cap);
+  const HoughDev &h = *V.h;
+  FusedShared &sh = *V.sh;
+  unsigned *rv = V.rv, *rcell = V.rcell, *rstale = V.rstale;
+  int *rlist = V.rlist;
+  unsigned *planes = V.planes;
+  const unsigned planes_sa = V.planes_sa, dummy_sa = V.dummy_sa, stride = V.stride, quads = V.quads;
+  const FusedPoints &Q = V.Q;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // The coefficients of a round's planes come from L2 (~0.7 us): they are fetched one round AHEAD by the
+    // first 6 * nb threads into registers and parked in shared memory at the end of the round, so no vote ever
+    // waits for them (ncu, round 2: 7 % of the kernel's samples sat on this load, one per pair of planes; with
+    // 786 planes to rebuild per CTA that was most of a 310 us re-vote).  Slot [5] of a plane's entry holds the
+    // quad range of its rows that the cloud can reach (HoughDev::dir_rows): only those are zero-filled.
+    auto fetch_round = [&](int b0n) -> double {
+      const int cntn = min(nb, nlist - b0n);
+      const int pl = tid / 6, c = tid - pl * 6;
+      double v = 0.0;
+      if (b0n < nlist && pl < cntn) {
+        const int r = rlist[b0n + pl];
+        const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
+        if (c < 5) v = reinterpret_cast<const double *>(h.coef + j)[c];
+        else {
+          const int2 qr = h.dir_rows ? h.dir_rows[j] : make_int2(0, 0x7FFFFFFF);
+          v = __hiloint2double(qr.y, qr.x);
+        }
+      }
+      return v;
+    };
+    if (nlist > 0) {
+      const double v = fetch_round(0);
+      if (tid < 6 * nb) (&sh.rcoef[0][0][0])[tid] = v;
+      __syncthreads();
+    }
+    int rbuf = 0;
+#pragma unroll 1
+    for (int b0 = 0; b0 < nlist; b0 += nb, rbuf ^= 1) {
+      const int cnt = min(nb, nlist - b0);
+      const double vnext = fetch_round(b0 + nb);           // in flight during this round's votes
+#pragma unroll 1
+      for (int bi = 0; bi < cnt; bi += 2) {
+        const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
+        const int j0 = h.dir_begin + (cta + (r0 / G) * n_cta) * G + (r0 % G);
+        const int j1 = r1 >= 0 ? h.dir_begin + (cta + (r1 / G) * n_cta) * G + (r1 % G) : -1;
+        const int bj = r1 >= 0 ? bi + 1 : bi;
+        DirCoef c0, c1;
+        c0.c0 = sh.rcoef[rbuf][bi][0]; c0.c1 = sh.rcoef[rbuf][bi][1]; c0.c2 = sh.rcoef[rbuf][bi][2];
+        c0.bx = sh.rcoef[rbuf][bi][3]; c0.by = sh.rcoef[rbuf][bi][4];
+        c1.c0 = sh.rcoef[rbuf][bj][0]; c1.c1 = sh.rcoef[rbuf][bj][1]; c1.c2 = sh.rcoef[rbuf][bj][2];
+        c1.bx = sh.rcoef[rbuf][bj][3]; c1.by = sh.rcoef[rbuf][bj][4];
+        unsigned k0, k1;
+        revote_pair(h, Q, n_alive, make_fast(c0, h.inv_s), make_fast(c1, h.inv_s), j0, j1,
+                    planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa, k0, k1);
+        k0 = __reduce_max_sync(0xFFFFFFFFu, k0);
+        k1 = __reduce_max_sync(0xFFFFFFFFu, k1);
+        if (lane == 0) { sh.rv_best[bi][warp] = k0; sh.rv_best[bi + 1][warp] = k1; }
+      }
+      __syncthreads();
+      // the planes of this round back to zero (no scan: the keys already hold the maxima), reachable rows only
+#pragma unroll 1
+      for (int pl = 0; pl < cnt; ++pl) {
+        const double packed = sh.rcoef[rbuf][pl][5];
+        const unsigned q0 = (unsigned)__double2loint(packed), q1 = min((unsigned)__double2hiint(packed), quads);
+        uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)pl * stride);
+        for (unsigned q = q0 + tid; q < q1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
+      }
+      if (warp < cnt) {
+        unsigned k = lane < kResWarps ? sh.rv_best[warp][lane] : 0u;
+        k = __reduce_max_sync(0xFFFFFFFFu, k);
+        if (lane == 0) {
+          const int r = rlist[b0 + warp];
+          const unsigned v = k >> 16;
+          rv[r] = v; rcell[r] = v ? 0xFFFFu - (k & 0xFFFFu) : 0u; rstale[r] = 0;
+        }
+      }
+      if (tid < 6 * nb) (&sh.rcoef[rbuf ^ 1][0][0])[tid] = vnext;
+      __syncthreads();
+    }
+}
+
 __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ __align__(16) FusedShared sh;
-  __shared__ HoughDev hs;
+  HoughDev &hs = *reinterpret_cast<HoughDev *>(smem_raw);
   constexpr int G = kResG;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int cta = blockIdx.x, n_cta = gridDim.x;
   if (A.fd && A.fd->status != 0) return;   // the frame ended before the vote (wrap.h:202-212) or takes the general path
   if (tid == 0) { if (A.fd) patch_hough(hs, A.h, *A.fd); else hs = A.h; }
   __syncthreads();
-  const HoughDev &h = hs;
   const int n_cap = A.fd ? A.fd->n_cap : A.n_cap;
   const double cell_off = A.fd ? A.fd->cell_off : A.cell_off;
   // per-CTA record tables first, then the planes (+ pad word); behind the planes of a re-vote
   // round (the first vote uses 2*G planes over the same area) the live points and the inlier list
   const int n_own = A.n_own_max;
-  unsigned *rv = reinterpret_cast<unsigned *>(smem_raw);                 // max votes (bound when stale)
-  unsigned *rcell = rv + n_own;                                          // first max cell
-  unsigned *rstale = rcell + n_own;
-  int *rlist = reinterpret_cast<int *>(rstale + n_own);
-  const unsigned tables_bytes = (unsigned)n_own * 16u;                   // n_own % 4 == 0 -> multiple of 16
-  unsigned *planes = reinterpret_cast<unsigned *>(smem_raw + tables_bytes);
-  const unsigned stride = h.plane_stride, quads = stride / 4;
-  const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
   const int nb = A.fd ? A.fd->nb_planes : A.nb_planes;
-  const unsigned dummy_sa = planes_sa + (unsigned)nb * stride * 4u;      // pad word of the loop layout
-  FusedPoints Q;
-  Q.x = reinterpret_cast<double *>(planes + (size_t)nb * stride + 4);
-  Q.y = Q.x + n_cap; Q.z = Q.y + n_cap;
-  Q.yidx = reinterpret_cast<int *>(Q.z + n_cap);
-  Q.yt = reinterpret_cast<float *>(Q.yidx + n_cap);
+  const FusedView V = fused_view(n_own, nb, n_cap);
+  const HoughDev &h = *V.h;
+  FusedShared &sh = *V.sh;
+  unsigned *rv = V.rv, *rcell = V.rcell, *rstale = V.rstale;
+  int *rlist = V.rlist;
+  unsigned *planes = V.planes;
+  const unsigned quads = V.quads;
+  const FusedPoints Q = V.Q;
 
   if (A.prof && tid == 0 && A.prof_iters > 0) A.prof[(size_t)cta * kProfSlots + 15] = globaltimer_ns();   // kernel start
   // hough->add(X) ran just before this kernel (vote_resident_kernel, BOUNDED form): the records of
@@ -475,81 +678,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
         if (tid == 0) lsq_eig(sh);
       } else if (pass == 1 && !last) {
         // ---- hough->subtract(Y) for the own directions (K4), overlapped with the eigen-solve ----------
-        // Y (pass 2) lies within opt_dx of the line (a, b) of pass 2
-        const int ut = tid - 32, un = kResThreads - 32;
-        const float tl = ordered_float(sh.tmin_i), th = ordered_float(sh.tmax_i);
-        const double t0 = (double)tl - (fabs((double)tl) * 1e-6 + 1e-9), t1 = (double)th + (fabs((double)th) * 1e-6 + 1e-9);
-        const unsigned num_x = (unsigned)h.num_x;
-        constexpr int SU = 3;   // records per thread per batch: their coefficient loads (L2) are issued together
-        for (int r0 = ut; r0 < n_own; r0 += SU * un) {
-          DirCoef cj[SU];
-          bool live[SU];
-#pragma unroll
-          for (int u = 0; u < SU; ++u) {
-            const int r = r0 + u * un;
-            live[u] = r < n_own && !rstale[r] && rv[r] != 0;
-            if (live[u]) cj[u] = h.coef[h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G)];
-          }
-#pragma unroll
-          for (int u = 0; u < SU; ++u) {
-            if (!live[u]) continue;
-            const int r = r0 + u * un;
-            const unsigned cx = rcell[r] / num_x, cy = rcell[r] - cx * num_x;
-            // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
-            double ilo, ihi;
-            if (cy == 0 || cy == num_x - 1 ||
-                (strip_interval(make_fast(cj[u], h.inv_s), a, b, cell_off, reach2, cx, cy, &ilo, &ihi) && ilo <= t1 && ihi >= t0))
-              rlist[atomicAdd(&sh.ns, 1)] = r;
-          }
-        }
-        named_bar_sync(1, un);
-        // exact test of the surviving records, one WARP per record: 32 removed points per step, and the
-        // record is done at its first hit (a record whose max cell lies on the removed line is hit within a
-        // step or two; testing every (record, point) pair cost up to 200 us per iteration at 18 SMs per frame)
-        const int ns = sh.ns;
-        // the coefficients of a record come from L2 (~0.7 us): lane q of the warp fetches those of the q-th record
-        // the warp will test, 32 records per round trip, and hands them over by shuffle (one dependent L2 load per
-        // record made this phase 40 us long with ~400 candidate records per CTA)
-        DirCoef pre = {0.0, 0.0, 0.0, 0.0, 0.0};
-        int pre_base = -1;
-#pragma unroll 1
-        for (int s = warp - 1, q = 0; s < ns; s += kResWarps - 1, ++q) {
-          if ((q & 31) == 0) {
-            const int sq = s + lane * (kResWarps - 1);
-            if (sq < ns) {
-              const int rq = rlist[sq];
-              pre = h.coef[h.dir_begin + (cta + (rq / G) * n_cta) * G + (rq % G)];
-            }
-            pre_base = q;
-          }
-          const int r = rlist[s];
-          const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-          DirCoef cj;
-          {
-            const int src = q - pre_base;
-            cj.c0 = __shfl_sync(0xFFFFFFFFu, pre.c0, src); cj.c1 = __shfl_sync(0xFFFFFFFFu, pre.c1, src);
-            cj.c2 = __shfl_sync(0xFFFFFFFFu, pre.c2, src); cj.bx = __shfl_sync(0xFFFFFFFFu, pre.bx, src);
-            cj.by = __shfl_sync(0xFFFFFFFFu, pre.by, src);
-          }
-          const FastCoef fc = make_fast(cj, h.inv_s);
-          const unsigned target = rcell[r];
-          // only inliers whose t puts them near the cell can vote for it: skip the others on their float t
-          // (edge cells reached through the reference's flat-index aliasing take every point)
-          const unsigned cx = target / num_x, cy = target - cx * num_x;
-          double ilo = -INFINITY, ihi = INFINITY;
-          if (cy != 0 && cy != num_x - 1) strip_interval(fc, a, b, cell_off, reach2, cx, cy, &ilo, &ihi);
-          const float flo = (float)(ilo - (fabs(ilo) * 1e-6 + 1e-6)), fhi = (float)(ihi + (fabs(ihi) * 1e-6 + 1e-6));
-#pragma unroll 1
-          for (int e0 = 0; e0 < ny2; e0 += 32) {
-            const int e = e0 + lane;
-            bool cand = false;
-            if (e < ny2) { const float te = Q.yt[e]; cand = te >= flo && te <= fhi; }
-            if (!__any_sync(0xFFFFFFFFu, cand)) continue;
-            bool hit = false;
-            if (cand) { const int i = Q.yidx[e]; hit = vote_cell(h, fc, j, Q.x[i], Q.y[i], Q.z[i]) == target; }
-            if (__any_sync(0xFFFFFFFFu, hit)) { if (lane == 0) rstale[r] = 1; break; }
-          }
-        }
+        fused_unvote(a, b, ny2, n_own, nb, n_cap, cta, n_cta, cell_off, reach2);
       }
       __syncthreads();
       const double rc = sh.lsq.rc;
@@ -609,75 +738,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     const int nlist = sh.nlist;
     stamp(8, (unsigned long long)nlist + 1);
     revotes += (unsigned long long)nlist * (unsigned long long)n_alive;
-    // The coefficients of a round's planes come from L2 (~0.7 us): they are fetched one round AHEAD by the
-    // first 6 * nb threads into registers and parked in shared memory at the end of the round, so no vote ever
-    // waits for them (ncu, round 2: 7 % of the kernel's samples sat on this load, one per pair of planes; with
-    // 786 planes to rebuild per CTA that was most of a 310 us re-vote).  Slot [5] of a plane's entry holds the
-    // quad range of its rows that the cloud can reach (HoughDev::dir_rows): only those are zero-filled.
-    auto fetch_round = [&](int b0n) -> double {
-      const int cntn = min(nb, nlist - b0n);
-      const int pl = tid / 6, c = tid - pl * 6;
-      double v = 0.0;
-      if (b0n < nlist && pl < cntn) {
-        const int r = rlist[b0n + pl];
-        const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-        if (c < 5) v = reinterpret_cast<const double *>(h.coef + j)[c];
-        else {
-          const int2 qr = h.dir_rows ? h.dir_rows[j] : make_int2(0, 0x7FFFFFFF);
-          v = __hiloint2double(qr.y, qr.x);
-        }
-      }
-      return v;
-    };
-    if (nlist > 0) {
-      const double v = fetch_round(0);
-      if (tid < 6 * nb) (&sh.rcoef[0][0][0])[tid] = v;
-      __syncthreads();
-    }
-    int rbuf = 0;
-#pragma unroll 1
-    for (int b0 = 0; b0 < nlist; b0 += nb, rbuf ^= 1) {
-      const int cnt = min(nb, nlist - b0);
-      const double vnext = fetch_round(b0 + nb);           // in flight during this round's votes
-#pragma unroll 1
-      for (int bi = 0; bi < cnt; bi += 2) {
-        const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
-        const int j0 = h.dir_begin + (cta + (r0 / G) * n_cta) * G + (r0 % G);
-        const int j1 = r1 >= 0 ? h.dir_begin + (cta + (r1 / G) * n_cta) * G + (r1 % G) : -1;
-        const int bj = r1 >= 0 ? bi + 1 : bi;
-        DirCoef c0, c1;
-        c0.c0 = sh.rcoef[rbuf][bi][0]; c0.c1 = sh.rcoef[rbuf][bi][1]; c0.c2 = sh.rcoef[rbuf][bi][2];
-        c0.bx = sh.rcoef[rbuf][bi][3]; c0.by = sh.rcoef[rbuf][bi][4];
-        c1.c0 = sh.rcoef[rbuf][bj][0]; c1.c1 = sh.rcoef[rbuf][bj][1]; c1.c2 = sh.rcoef[rbuf][bj][2];
-        c1.bx = sh.rcoef[rbuf][bj][3]; c1.by = sh.rcoef[rbuf][bj][4];
-        unsigned k0, k1;
-        revote_pair(h, Q, n_alive, make_fast(c0, h.inv_s), make_fast(c1, h.inv_s), j0, j1,
-                    planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa, k0, k1);
-        k0 = __reduce_max_sync(0xFFFFFFFFu, k0);
-        k1 = __reduce_max_sync(0xFFFFFFFFu, k1);
-        if (lane == 0) { sh.rv_best[bi][warp] = k0; sh.rv_best[bi + 1][warp] = k1; }
-      }
-      __syncthreads();
-      // the planes of this round back to zero (no scan: the keys already hold the maxima), reachable rows only
-#pragma unroll 1
-      for (int pl = 0; pl < cnt; ++pl) {
-        const double packed = sh.rcoef[rbuf][pl][5];
-        const unsigned q0 = (unsigned)__double2loint(packed), q1 = min((unsigned)__double2hiint(packed), quads);
-        uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)pl * stride);
-        for (unsigned q = q0 + tid; q < q1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
-      }
-      if (warp < cnt) {
-        unsigned k = lane < kResWarps ? sh.rv_best[warp][lane] : 0u;
-        k = __reduce_max_sync(0xFFFFFFFFu, k);
-        if (lane == 0) {
-          const int r = rlist[b0 + warp];
-          const unsigned v = k >> 16;
-          rv[r] = v; rcell[r] = v ? 0xFFFFu - (k & 0xFFFFu) : 0u; rstale[r] = 0;
-        }
-      }
-      if (tid < 6 * nb) (&sh.rcoef[rbuf ^ 1][0][0])[tid] = vnext;
-      __syncthreads();
-    }
+    fused_revote(nlist, n_alive, n_own, nb, n_cap, cta, n_cta);
     stamp(9, 0);
     ++it;
   }
