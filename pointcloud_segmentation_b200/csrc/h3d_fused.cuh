@@ -72,7 +72,6 @@ struct FusedShared {
   int tmin_i, tmax_i;         // ordered-int encodings of float t bounds of Y
   int ns, nlist;
   unsigned rv_best[2 * kResG + 2][kResWarps];   // re-vote rounds: per-warp plane maxima
-  double rcoef[2][2 * kResG][6];                // re-vote rounds: raw DirCoef of the round's planes ([5]: int2 quad range)
 };
 
 // live points (compact, cloud order) and the current inlier list, all in shared memory
@@ -479,62 +478,28 @@ __device__ __noinline__ void fused_revote(int nlist, int n_alive, int n_own, int
   const unsigned planes_sa = V.planes_sa, dummy_sa = V.dummy_sa, stride = V.stride, quads = V.quads;
   const FusedPoints &Q = V.Q;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // The coefficients of a round's planes come from L2 (~0.7 us): they are fetched one round AHEAD by the
-    // first 6 * nb threads into registers and parked in shared memory at the end of the round, so no vote ever
-    // waits for them (ncu, round 2: 7 % of the kernel's samples sat on this load, one per pair of planes; with
-    // 786 planes to rebuild per CTA that was most of a 310 us re-vote).  Slot [5] of a plane's entry holds the
-    // quad range of its rows that the cloud can reach (HoughDev::dir_rows): only those are zero-filled.
-    auto fetch_round = [&](int b0n) -> double {
-      const int cntn = min(nb, nlist - b0n);
-      const int pl = tid / 6, c = tid - pl * 6;
-      double v = 0.0;
-      if (b0n < nlist && pl < cntn) {
-        const int r = rlist[b0n + pl];
-        const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-        if (c < 5) v = reinterpret_cast<const double *>(h.coef + j)[c];
-        else {
-          const int2 qr = h.dir_rows ? h.dir_rows[j] : make_int2(0, 0x7FFFFFFF);
-          v = __hiloint2double(qr.y, qr.x);
-        }
-      }
-      return v;
-    };
-    if (nlist > 0) {
-      const double v = fetch_round(0);
-      if (tid < 6 * nb) (&sh.rcoef[0][0][0])[tid] = v;
-      __syncthreads();
-    }
-    int rbuf = 0;
+    // (Fetching the coefficients a round ahead through shared memory and zero-filling only the reachable rows was
+    // tried and measured SLOWER -- 425 vs 365 us for a 786-plane rebuild at 18 SMs: the 16 warps already overlap
+    // the L2 latency of the two coefficient loads per pair, and the per-round bookkeeping cost more than it hid.)
 #pragma unroll 1
-    for (int b0 = 0; b0 < nlist; b0 += nb, rbuf ^= 1) {
+    for (int b0 = 0; b0 < nlist; b0 += nb) {
       const int cnt = min(nb, nlist - b0);
-      const double vnext = fetch_round(b0 + nb);           // in flight during this round's votes
 #pragma unroll 1
       for (int bi = 0; bi < cnt; bi += 2) {
         const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
         const int j0 = h.dir_begin + (cta + (r0 / G) * n_cta) * G + (r0 % G);
         const int j1 = r1 >= 0 ? h.dir_begin + (cta + (r1 / G) * n_cta) * G + (r1 % G) : -1;
-        const int bj = r1 >= 0 ? bi + 1 : bi;
-        DirCoef c0, c1;
-        c0.c0 = sh.rcoef[rbuf][bi][0]; c0.c1 = sh.rcoef[rbuf][bi][1]; c0.c2 = sh.rcoef[rbuf][bi][2];
-        c0.bx = sh.rcoef[rbuf][bi][3]; c0.by = sh.rcoef[rbuf][bi][4];
-        c1.c0 = sh.rcoef[rbuf][bj][0]; c1.c1 = sh.rcoef[rbuf][bj][1]; c1.c2 = sh.rcoef[rbuf][bj][2];
-        c1.bx = sh.rcoef[rbuf][bj][3]; c1.by = sh.rcoef[rbuf][bj][4];
         unsigned k0, k1;
-        revote_pair(h, Q, n_alive, make_fast(c0, h.inv_s), make_fast(c1, h.inv_s), j0, j1,
+        revote_pair(h, Q, n_alive, make_fast(h.coef[j0], h.inv_s), make_fast(h.coef[j1 >= 0 ? j1 : j0], h.inv_s), j0, j1,
                     planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa, k0, k1);
         k0 = __reduce_max_sync(0xFFFFFFFFu, k0);
         k1 = __reduce_max_sync(0xFFFFFFFFu, k1);
         if (lane == 0) { sh.rv_best[bi][warp] = k0; sh.rv_best[bi + 1][warp] = k1; }
       }
       __syncthreads();
-      // the planes of this round back to zero (no scan: the keys already hold the maxima), reachable rows only
-#pragma unroll 1
-      for (int pl = 0; pl < cnt; ++pl) {
-        const double packed = sh.rcoef[rbuf][pl][5];
-        const unsigned q0 = (unsigned)__double2loint(packed), q1 = min((unsigned)__double2hiint(packed), quads);
-        uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)pl * stride);
-        for (unsigned q = q0 + tid; q < q1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
+      {   // the planes of this round back to zero (no scan: the keys already hold the maxima)
+        uint4 *p4 = reinterpret_cast<uint4 *>(planes);
+        for (unsigned q = tid; q < (unsigned)cnt * quads; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
       }
       if (warp < cnt) {
         unsigned k = lane < kResWarps ? sh.rv_best[warp][lane] : 0u;
@@ -545,7 +510,6 @@ __device__ __noinline__ void fused_revote(int nlist, int n_alive, int n_own, int
           rv[r] = v; rcell[r] = v ? 0xFFFFu - (k & 0xFFFFu) : 0u; rstale[r] = 0;
         }
       }
-      if (tid < 6 * nb) (&sh.rcoef[rbuf ^ 1][0][0])[tid] = vnext;
       __syncthreads();
     }
 }
