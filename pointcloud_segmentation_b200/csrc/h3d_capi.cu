@@ -1569,7 +1569,6 @@ struct FastPath {
   bool last_was_fast = false;   // the last frame ran here (h3d_pipeline_filtered reads the count from the descriptor)
   K0Grid grid{};
   int2 *occ = nullptr;
-  int2 *dir_rows = nullptr;     // per direction: quads of its plane the current frame can touch
   int *sorted = nullptr;        // voxel member lists in ascending raw index (max_raw_points ints)
   int *tile_sums = nullptr;
   FrameDev *fd_dev = nullptr;
@@ -1578,8 +1577,8 @@ struct FastPath {
   unsigned char *stage_host = nullptr, *stage_dev = nullptr;
   size_t off_st = 0, off_iters = 0, off_pool = 0, pool_entries = 0, stage_bytes = 0;
   void release() {
-    cudaFree(occ); cudaFree(dir_rows); cudaFree(sorted); sorted = nullptr; cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
-    occ = nullptr; dir_rows = nullptr; tile_sums = nullptr; fd_dev = nullptr; stage_host = stage_dev = nullptr; on = false;
+    cudaFree(occ); cudaFree(sorted); sorted = nullptr; cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
+    occ = nullptr; tile_sums = nullptr; fd_dev = nullptr; stage_host = stage_dev = nullptr; on = false;
   }
 };
 
@@ -1621,7 +1620,6 @@ static int fast_path_setup(h3d_pipeline *p) {
   H3D_CUDA(cudaMalloc(&fp.occ, n * sizeof(int2)));
   H3D_CUDA(cudaMalloc(&fp.sorted, n * sizeof(int)));
   H3D_CUDA(cudaMalloc(&fp.tile_sums, 2 * kK0Cluster * sizeof(int)));
-  H3D_CUDA(cudaMalloc(&fp.dir_rows, f.hg->space->num_b * sizeof(int2)));
   H3D_CUDA(cudaMalloc(&fp.fd_dev, sizeof(FrameDev)));
   fp.off_st = (sizeof(FrameDev) + 255) & ~(size_t)255;
   fp.off_iters = fp.off_st + ((sizeof(LoopState) + 255) & ~(size_t)255);
@@ -1683,7 +1681,6 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   fa.xchg = f.gbest; fa.xchg_words = (int)xchg_words; fa.bar = f.sync_dev;
   fa.smem_loop = (unsigned)(fp.smem_loop - kFusedHdr); fa.tables_bytes = (unsigned)n_own * 16u;   // the loop's body behind its header
   fa.smem_vote = (unsigned)(fp.smem_vote - kVoteFramePlanesOff);   // what the planes get behind the kernel's header
-  fa.coef = h->space->coef_dev; fa.dir_rows = fp.dir_rows;
   {
     // cluster width: the whole GPU is this frame's -> 8 (latency); frames in flight beside it -> 2
     const unsigned width = (grid >= h->dev.sm_count / 2) ? (unsigned)kK0Cluster : 2u;
@@ -1703,7 +1700,6 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
     H3D_CUDA(cudaMemsetAsync(hd.dcell, 0xFF, nd * sizeof(unsigned), s));
   }
   // Hough::add, wrap.h:228
-  hd.dir_rows = fp.dir_rows;
   const int track = g_vote_track.load(std::memory_order_relaxed);
   const void *vk = track == 0 ? reinterpret_cast<const void *>(vote_frame_kernel<0>)
                  : track == 1 ? reinterpret_cast<const void *>(vote_frame_kernel<1>)
@@ -1714,13 +1710,11 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   else if (track == 1) vote_frame_kernel<1><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
   else vote_frame_kernel<2><<<grid, kResThreads, fp.smem_vote, s>>>(hd, fp.fd_dev);
   H3D_CUDA(cudaGetLastError());
-  hd.dir_rows = nullptr;
   H3D_CUDA(cudaEventRecord(f.ev[2], s));
   // the loop, wrap.h:237-342
   FusedArgs a;
   memset(&a, 0, sizeof a);
   a.h = hd;
-  a.h.dir_rows = fp.dir_rows;   // reachable rows per direction, written by this frame's K0 kernel
   a.st = f.st_dev; a.iters = f.iters_dev; a.pool = f.pool_dev; a.orig = f.orig; a.dirs = h->space->dirs_dev;
   a.xchg = f.gbest; a.bar = f.sync_dev;
   a.n_own_max = n_own;

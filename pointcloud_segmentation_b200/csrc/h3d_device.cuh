@@ -39,8 +39,6 @@ struct HoughDev {
   int bounded;            // box symmetric about the origin (shiftToOrigin) and num_x < 2000: with every point
                           // inside the box, 0 <= x_i, y_i <= num_x + 1 and the fast path needs no range test
   const DirCoef *coef;    // whole space, indexed by global direction
-  const int2 *dir_rows;   // nullable, whole space: quads [x, y) of a direction's plane that the frame's points can touch
-                          // (rows of the projected bounding box; written per frame by the K0 kernel of the fast path)
   // points (SoA, centred frame) and their weights: +1 added, -1 subtracted
   // without a matching added point, 0 removed
   const double *px, *py, *pz;

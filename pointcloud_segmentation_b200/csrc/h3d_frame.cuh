@@ -159,9 +159,6 @@ struct FrameArgs {
   unsigned *bar;             // 4 words, zeroed here
   // shared-memory budget of the vote / loop kernels (fast-path eligibility, decided on the device)
   unsigned smem_loop, tables_bytes, smem_vote;
-  // per-direction rows of the projected bounding box (quad ranges of the planes), for the vote's scan / zero-fill
-  const DirCoef *coef;
-  int2 *dir_rows;            // num_b entries
 };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -437,27 +434,6 @@ frame_prefilter_kernel(const __grid_constant__ FrameArgs A) {
     A.pz[s] = __dsub_rn((double)A.filt[3 * (size_t)s + 2], ns[2]);
     A.w[s] = 1;
     A.orig[s] = (unsigned)s;
-  }
-  {
-    // rows of every direction's plane that the cloud can reach: |x'| <= |c0| hx + |c1| hy + |bx| hz for a point
-    // inside the (centred) bounding box with half extents h (lib/hough.cpp:76-79 is linear in p), one row of margin
-    double minPs[3], maxPs[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) { minPs[c] = lo[c] - ns[c]; maxPs[c] = hi[c] - ns[c]; }
-    const HoughGeom g = hough_geometry(minPs, maxPs, A.opt_dx, A.num_b);
-    if (g.rc == 0 && g.num_x > 0 && g.dx > 0.0) {
-      const double hx = fmax(fabs(minPs[0]), fabs(maxPs[0])), hy = fmax(fabs(minPs[1]), fabs(maxPs[1])),
-                   hz = fmax(fabs(minPs[2]), fabs(maxPs[2]));
-      const int rows_all = (int)(g.plane_stride / (unsigned)g.num_x) + 1, quads = (int)(g.plane_stride / 4u);
-      for (int j = gtid; j < (int)A.num_b; j += T) {
-        const DirCoef c = A.coef[j];
-        const double hr = fabs(c.c0) * hx + fabs(c.c1) * hy + fabs(c.bx) * hz;
-        int r0 = (int)floor((g.max_x - hr) / g.dx + 0.5) - 1, r1 = (int)floor((g.max_x + hr) / g.dx + 0.5) + 1;
-        r0 = max(r0, 0); r1 = min(r1, rows_all);
-        int q0 = (r0 * g.num_x) / 4, q1 = ((r1 + 1) * g.num_x + 3) / 4;
-        A.dir_rows[j] = make_int2(min(q0, quads), min(q1, quads));
-      }
-    }
   }
   if (gtid == 0) {
     FrameDev &F = *A.fd;

@@ -520,9 +520,6 @@ struct ResShared {
   int dir[3][kResG];          // local direction numbers of phase k (slot k%3; -1: none); the
                               // previous phase's numbers stay readable while the next are staged
   int zero_ctr[3];            // TRACK form: chunk counter of the zero-fill of phase k (slot k%3), reset two phases ahead
-  int2 rows[3][kResG];        // same slots: quads [x, y) of the direction's plane that the points can touch (the
-                              // coef slots are only double-buffered: the previous group's are overwritten by the staging
-                              // of the next group in the very phase that scans the previous group's planes)
 };
 
 // TRACK form (needs plane_stride < 65536; N <= 6144 < 65536 always holds here): the increment returns the
@@ -538,7 +535,6 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
   const unsigned stride = h.plane_stride, quads = stride / 4;
   const unsigned planes_sa = (unsigned)__cvta_generic_to_shared(planes);
   const unsigned coef_sa = (unsigned)__cvta_generic_to_shared(&sh.coef[0][0][0]);
-  const unsigned rows_sa = (unsigned)__cvta_generic_to_shared(&sh.rows[0][0]);
   // points are COMPACT here (every weight +1): slot p of thread t is point t + p*512, so all
   // slots below n/512 are full for every thread and only one slot is partially filled
   const int n = point_count(h);
@@ -566,9 +562,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
       const double *src = reinterpret_cast<const double *>(h.coef + h.dir_begin + l);
 #pragma unroll
       for (int c = 0; c < 5; ++c) cp_async8(coef_sa + 48u * (unsigned)(slot * G + tid) + 8u * c, src + c);
-      if (h.dir_rows) cp_async8(rows_sa + 8u * (unsigned)(dslot * G + tid), h.dir_rows + h.dir_begin + l);
     }
-    if (!h.dir_rows || l < 0) sh.rows[dslot][tid] = make_int2(0, 0x7FFFFFFF);
     sh.dir[dslot][tid] = l;
   };
   if (tid == 0) { sh.zero_ctr[0] = 0; sh.zero_ctr[1] = 0; sh.zero_ctr[2] = 0; }
@@ -680,8 +674,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
           c = __shfl_sync(0xFFFFFFFFu, c, 0);
           if (c >= n_chunks) break;
           const unsigned g = c / per_plane, q0 = (c - g * per_plane) * kZeroChunk;
-          const int2 qr = sh.rows[dprev][g];
-          const unsigned qb = max(q0, (unsigned)qr.x), qe = min(min(q0 + kZeroChunk, (unsigned)qr.y), quads);
+          const unsigned qb = q0, qe = min(q0 + kZeroChunk, quads);
           uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)((slot ^ 1) * G + g) * stride);
           for (unsigned q = qb + lane; q < qe; q += 32) p4[q] = make_uint4(0, 0, 0, 0);
         }
@@ -707,11 +700,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
       unsigned best[G], bcell[G];
 #pragma unroll
       for (int g = 0; g < G; ++g)
-      {
-        const int2 qr = sh.rows[dprev][g];   // quads the frame's points can touch
-        scan_plane_local<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, (unsigned)qr.x, min((unsigned)qr.y, quads),
-                                      tid, plane_cells, best[g], bcell[g]);
-      }
+        scan_plane_local<kResThreads>(planes + (size_t)((slot ^ 1) * G + g) * stride, 0u, quads, tid, plane_cells, best[g], bcell[g]);
       unsigned m[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) m[g] = __reduce_max_sync(0xFFFFFFFFu, best[g]);
