@@ -194,6 +194,32 @@ __device__ __forceinline__ unsigned vote_cell(const HoughDev &h, const FastCoef 
   return cell;
 }
 
+// Which points of Y can vote for cell (cx, cy) of the direction with scaled coefficients f?  Y lies in the
+// slab { a + t b + e : |e| <= radius, e orthogonal to b }.  The map to the (x', y') plane is an orthogonal
+// projection, so in cell units a point of parameter t lands within radius/dx of P(t) = (xa + t gx, ya + t gy)
+// (relative to the cell's centre), and it votes for the cell only if it lands within sqrt(2)/2 of the centre:
+// |P(t)| <= reach, reach^2 = reach2 >= (sqrt(2)/2 + radius/dx)^2.  Returns false when no t qualifies, else the
+// interval [*tlo, *thi] (conservative, never exact; +-inf when the line is parallel to the direction).
+__device__ __forceinline__ bool strip_interval(const FastCoef &f, const double (&a)[3], const double (&b)[3],
+                                               double cell_off, double reach2, unsigned cx, unsigned cy, double *tlo,
+                                               double *thi) {
+  const double s = 1.0 / 1048576.0;   // the coefficients carry 2^20/dx
+  const double xa = (f.c0s * a[0] + f.c1n * a[1] + f.bxn * a[2]) * s + cell_off - ((double)cx + 0.5);
+  const double ya = (f.c1n * a[0] + f.c2s * a[1] + f.byn * a[2]) * s + cell_off - ((double)cy + 0.5);
+  const double gx = (f.c0s * b[0] + f.c1n * b[1] + f.bxn * b[2]) * s;
+  const double gy = (f.c1n * b[0] + f.c2s * b[1] + f.byn * b[2]) * s;
+  const double gg = gx * gx + gy * gy, bq = xa * gx + ya * gy, cq = xa * xa + ya * ya - reach2;
+  if (!(gg > 1e-12)) {                // the whole line projects (almost) to one spot
+    *tlo = -INFINITY; *thi = INFINITY;
+    return cq <= 1e-6;
+  }
+  const double disc = bq * bq - gg * cq;
+  if (disc < 0.0) return false;
+  const double sq = sqrt(disc);
+  *tlo = (-bq - sq) / gg; *thi = (-bq + sq) / gg;
+  return true;
+}
+
 // packed argmax key: larger votes first, then the LOWEST flat index
 // (lib/hough.cpp:107-112 strict `>` scan from index 0)
 __device__ __forceinline__ unsigned long long line_key(unsigned votes, unsigned cell, int j, int num_b) {

@@ -343,7 +343,8 @@ __device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *ou
   for (int q = warp; q < 6; q += nwarps) {
     if (q < 3) {                      // colwise().mean() of the float copy (wrap.h:129-137)
       float acc = 0.0f;
-      for (int k = lane; k < n; k += 32) acc = __fadd_rn(acc, (float)get(k, q));
+#pragma unroll 8
+      for (int k = lane; k < n; k += 32) acc = __fadd_rn(acc, (float)get(k, q));   // loads run ahead of the chain
       acc = tree32_combine(acc);
       if (lane == 0) s.mean[q] = __fdiv_rn(acc, (float)n);
     } else {                          // meanValue (lib/pointcloud.cpp:29-38)
@@ -358,6 +359,7 @@ __device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *ou
     const int c0 = q < 3 ? 0 : q < 5 ? 1 : 2, c1 = q < 3 ? q : q < 5 ? q - 2 : 2;
     const float m0 = s.mean[c0], m1 = s.mean[c1];
     float acc = 0.0f;
+#pragma unroll 8
     for (int k = lane; k < n; k += 32)
       acc = __fadd_rn(acc, __fmul_rn(__fsub_rn((float)get(k, c0), m0), __fsub_rn((float)get(k, c1), m1)));
     acc = tree32_combine(acc);

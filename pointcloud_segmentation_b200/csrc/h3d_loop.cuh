@@ -30,6 +30,7 @@ struct LoopState {
   unsigned long long fresh_key, best_key;
   double a[3], b[3];      // current line
   unsigned long long votes_cast;
+  double ua[3], ub[3];    // the line whose inlier test produced the set being removed (pass-1 fit): un-vote strip test
 };
 
 struct LoopBuffers {
@@ -66,12 +67,25 @@ __global__ void loop_unvote_kernel(const HoughDev h, LoopBuffers lb) {
   const int n_idx = s.ny_prev;
   const int n_chunks = (n_idx + kUnvoteChunk - 1) / kUnvoteChunk;
   const long long total = (long long)h.dir_count * n_chunks;
+  const double ua[3] = {s.ua[0], s.ua[1], s.ua[2]}, ub[3] = {s.ub[0], s.ub[1], s.ub[2]};
+  const double cell_off = h.max_x / h.dx + 0.5;
+  const double reach = 1.4142136 * (0.5 + s.opt_dx / h.dx + 0.02), reach2 = reach * reach;
   for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
        t += (long long)gridDim.x * blockDim.x) {
     const int l = (int)(t % h.dir_count), chunk = (int)(t / h.dir_count);
     if (h.dstale[l] || h.dvotes[l] == 0) continue;
     const unsigned target = h.dcell[l];
     const FastCoef c = make_fast(h.coef[h.dir_begin + l], h.inv_s);
+    {
+      // O(1) reject (as in the fused loop): the removed set lies within opt_dx of the line (ua, ub); a record whose
+      // max cell is farther than `reach` cells from that line's image in the plane cannot have lost a vote.  Edge
+      // cells, which the reference's flat-index aliasing can reach, are always tested.
+      const unsigned num_x = (unsigned)h.num_x, cx = target / num_x, cy = target - cx * num_x;
+      if (cy != 0 && cy != num_x - 1) {
+        double ilo, ihi;
+        if (!strip_interval(c, ua, ub, cell_off, reach2, cx, cy, &ilo, &ihi)) continue;
+      }
+    }
     const int e0 = chunk * kUnvoteChunk, e1 = min(e0 + kUnvoteChunk, n_idx);
     bool hit = false;
     for (int e = e0; e < e1; ++e) {
@@ -174,6 +188,7 @@ __global__ void __launch_bounds__(1024, 1) loop_compact_kernel(const HoughDev h,
     if (keep) {
       const int pos = off + __popc(bal & ((1u << lane) - 1u));
       lb.yidx[pos] = i;
+      lb.ypx[pos] = lb.px[i]; lb.ypy[pos] = lb.py[i]; lb.ypz[pos] = lb.pz[i];   // see big_scatter_kernel
       if (pool0 + (unsigned)pos < s.pool_cap) lb.pool[pool0 + pos] = lb.orig[i];
     }
     __syncthreads();
@@ -206,11 +221,9 @@ __global__ void __launch_bounds__(192, 1) loop_lsq_kernel(const HoughDev h, Loop
     if (threadIdx.x == 0) { if (r) r->status = 2; s.n_iters++; s.done = 1; }
     return;
   }
-  {
-    const int *idx = lb.yidx;
-    lsq_cta([&](int k, int c) { return (c == 0 ? h.px : c == 1 ? h.py : h.pz)[idx[k]]; }, s.ny, sh, &out);
-  }
+  lsq_cta([&](int k, int c) { return (c == 0 ? lb.ypx : c == 1 ? lb.ypy : lb.ypz)[k]; }, s.ny, sh, &out);   // compact Y
   if (threadIdx.x != 0) return;
+  if (pass == 2) for (int c = 0; c < 3; ++c) { s.ua[c] = s.a[c]; s.ub[c] = s.b[c]; }   // Y lies within opt_dx of THIS line
   for (int c = 0; c < 3; ++c) { s.a[c] = out.a[c]; s.b[c] = out.b[c]; }
   if (pass == 1) {
     if (r) { for (int c = 0; c < 3; ++c) { r->a1[c] = out.a[c]; r->b1[c] = out.b[c]; } r->rc1 = out.rc; }
@@ -354,6 +367,10 @@ __global__ void __launch_bounds__(kChunk) big_scatter_kernel(LoopBuffers lb) {
     if (keep) {
       const int pos = lb.coff[c] + r;
       lb.yidx[pos] = i;
+      // Y's coordinates, compact and in order: orthogonal_LSQ reads them coalesced (gathering px[yidx[k]] inside its
+      // reduction chains cost two dependent L2 round trips per element: 0.42 ms per fit of an 11 k-point line).
+      // The un-vote of this iteration has already consumed the previous Y from these arrays.
+      lb.ypx[pos] = lb.px[i]; lb.ypy[pos] = lb.py[i]; lb.ypz[pos] = lb.pz[i];
       if (pool0 + (unsigned)pos < s.pool_cap) lb.pool[pool0 + pos] = lb.orig[i];
     }
   }
