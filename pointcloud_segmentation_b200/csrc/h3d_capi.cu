@@ -158,6 +158,9 @@ struct h3d_hough {
   int vote_d = 1;                 // directions per work item of the full vote
   unsigned *gplanes = nullptr;    // sliced vote form: dir_count global planes (few directions, many points)
   size_t gplanes_cells = 0;
+  unsigned *rplanes = nullptr;    // point-sliced list re-votes of the streaming vote: rplanes_cap global planes, kept zero
+  int rplanes_cap = 0, *rflag = nullptr;
+  size_t rplanes_cells = 0;       // plane_cells the buffer was sized for
   uint64_t votes_cast = 0;
 };
 
@@ -380,11 +383,30 @@ static int launch_resident(h3d_hough *h, int ablate, const int *list, const int 
 // pipe (the atomics), and staging tiles in shared memory adds their 24 B per point to that same pipe.
 static std::atomic<int> g_stream_mode{0};
 
+constexpr int kStreamSlicePlanes = 2048;   // list re-votes of up to this many planes may be point-sliced (33 MB at num_x 64)
+
 template <int D, bool BOUNDED, bool TMA>
 static int launch_stream_t(h3d_hough *h, const int *list, const int *count_ptr, int count_imm, unsigned *dense, size_t smem) {
   H3D_TRY(ensure_dyn_smem(reinterpret_cast<const void *>(vote_stream_kernel<D, BOUNDED, TMA>), smem, h->dev.smem_optin));
-  vote_stream_kernel<D, BOUNDED, TMA><<<h->dev.sm_count, kStreamThreads + (TMA ? 32 : 0), smem, h->stream>>>(h->d, list, count_ptr, count_imm, dense);
+  // a re-vote LIST over a large cloud may be point-sliced on the device (see the kernel): global planes for it
+  const bool may_slice = !TMA && list && !dense && h->d.n >= 8 * kStreamTile;
+  if (may_slice && (h->rplanes_cells != h->d.plane_cells || !h->rplanes)) {
+    H3D_CUDA(cudaStreamSynchronize(h->stream));
+    cudaFree(h->rplanes); h->rplanes = nullptr; h->rplanes_cap = 0;
+    const size_t cells = (size_t)kStreamSlicePlanes * h->d.plane_cells;
+    H3D_CUDA(cudaMalloc(&h->rplanes, cells * sizeof(unsigned)));
+    H3D_CUDA(cudaMemsetAsync(h->rplanes, 0, cells * sizeof(unsigned), h->stream));
+    if (!h->rflag) H3D_CUDA(cudaMalloc(&h->rflag, sizeof(int)));
+    h->rplanes_cap = kStreamSlicePlanes; h->rplanes_cells = h->d.plane_cells;
+  }
+  vote_stream_kernel<D, BOUNDED, TMA><<<h->dev.sm_count, kStreamThreads + (TMA ? 32 : 0), smem, h->stream>>>(
+      h->d, list, count_ptr, count_imm, dense, may_slice ? h->rplanes : nullptr, may_slice ? h->rplanes_cap : 0,
+      may_slice ? h->rflag : nullptr);
   note_launches(1);
+  if (may_slice) {
+    stream_merge_kernel<<<h->dev.sm_count * 2, 256, 0, h->stream>>>(h->d, list, h->rplanes, h->rflag);
+    note_launches(1);
+  }
   H3D_CUDA(cudaGetLastError());
   return H3D_OK;
 }
@@ -563,7 +585,7 @@ extern "C" void h3d_destroy(h3d_hough *h) {
   cudaFree(h->px); cudaFree(h->py); cudaFree(h->pz); cudaFree(h->w);
   cudaFree(h->stage); cudaFree(h->idx);
   cudaFree(h->d.dvotes); cudaFree(h->d.dcell); cudaFree(h->d.dstale);
-  cudaFree(h->keys); cudaFree(h->list); cudaFree(h->count); cudaFree(h->gplanes);
+  cudaFree(h->keys); cudaFree(h->list); cudaFree(h->count); cudaFree(h->gplanes); cudaFree(h->rplanes); cudaFree(h->rflag);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }

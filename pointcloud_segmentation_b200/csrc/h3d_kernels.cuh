@@ -241,12 +241,26 @@ __device__ __forceinline__ void consumer_bar() {     // the 512 voting threads o
 template <int D, bool BOUNDED, bool TMA>
 __global__ void __launch_bounds__(TMA ? kStreamThreads + 32 : kStreamThreads, 1)
 vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ list, const int *__restrict__ count_ptr,
-                   int count_imm, unsigned *__restrict__ dense) {
+                   int count_imm, unsigned *__restrict__ dense, unsigned *__restrict__ gplanes, int gplanes_cap,
+                   int *__restrict__ sliced_flag) {
   extern __shared__ __align__(128) unsigned char stream_smem[];
   __shared__ __align__(16) StreamShared sh;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int count = count_ptr ? *count_ptr : count_imm;
   const int n = point_count(h);
+  // POINT SLICES (LDG form, re-vote lists): a list of a few hundred stale planes gives fewer work items than the GPU
+  // has SMs (40 planes of a direction shard: 6 items, each streaming the whole cloud).  Then an item becomes (group of
+  // D directions, slice of the point tiles): the CTA votes its slice, adds the non-zero cells of its planes to the
+  // group's planes in global memory, and stream_merge_kernel reduces those to the records.  Decided on the device
+  // (the host does not know the list length); *sliced_flag tells the merge kernel how many global planes to reduce.
+  const int n_groups_all = (count + D - 1) / D;
+  const int n_tiles_all = (n + kStreamTile - 1) / kStreamTile;
+  int slices = 1;
+  if (!TMA && gplanes && !dense && count > 0 && count <= gplanes_cap && n_groups_all < (int)gridDim.x && n_tiles_all >= 8) {
+    slices = (2 * (int)gridDim.x + n_groups_all - 1) / n_groups_all;
+    slices = min(slices, n_tiles_all / 4);             // at least 4 tiles (8192 points) per slice
+  }
+  if (sliced_flag && blockIdx.x == 0 && tid == 0) *sliced_flag = slices > 1 ? count : 0;
   const unsigned stride = h.plane_stride;
   // layout: [ring: stages x {x, y, z} x kStreamTile doubles][planes: D x stride u32][pad word]
   double *ring = reinterpret_cast<double *>(stream_smem);
@@ -256,10 +270,10 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
   const unsigned ring_sa = (unsigned)__cvta_generic_to_shared(ring);
   const unsigned full_sa = (unsigned)__cvta_generic_to_shared(&sh.full[0]);
   const unsigned empty_sa = (unsigned)__cvta_generic_to_shared(&sh.empty[0]);
-  const int n_items = (count + D - 1) / D;
+  const int n_items = n_groups_all * slices;
   const int my_items = blockIdx.x < n_items ? (n_items - blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-  const int n_tiles = (n + kStreamTile - 1) / kStreamTile;
-  const long long total_fills = (long long)my_items * n_tiles;
+  const int n_tiles = n_tiles_all;
+  const long long total_fills = (long long)my_items * n_tiles;   // TMA form only (never sliced)
 
   if (tid < kStreamThreads) {
     uint4 *p4 = reinterpret_cast<uint4 *>(planes);
@@ -296,15 +310,19 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
   const bool no_fast = !h.fast_ok;
   long long fill = 0;
   for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    // slice-major: CTAs running side by side vote the SAME tiles for different groups (the tiles come from L2 once)
+    const int group = slices > 1 ? item % n_groups_all : item, slice = slices > 1 ? item / n_groups_all : 0;
+    const int t_begin = slices > 1 ? (int)((long long)n_tiles * slice / slices) : 0;
+    const int t_end = slices > 1 ? (int)((long long)n_tiles * (slice + 1) / slices) : n_tiles;
     if (tid < D) {
-      const int e = item * D + tid;
+      const int e = group * D + tid;
       const int l = e < count ? (list ? list[e] : e) : -1;
       sh.dir[tid] = l;
       const FastCoef f = make_fast(h.coef[h.dir_begin + (l < 0 ? 0 : l)], h.inv_s);
       sh.coef[tid][0] = f.c0s; sh.coef[tid][1] = f.c1n; sh.coef[tid][2] = f.c2s; sh.coef[tid][3] = f.bxn; sh.coef[tid][4] = f.byn;
     }
     if (TMA) consumer_bar(); else __syncthreads();
-    for (int t = 0; t < n_tiles; ++t, ++fill) {
+    for (int t = t_begin; t < t_end; ++t, ++fill) {
       const int st = (int)(fill % kStreamStages);
       const int i0 = t * kStreamTile;
       double x[kStreamP], y[kStreamP], z[kStreamP];
@@ -361,6 +379,20 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
       }
     }
     if (TMA) consumer_bar(); else __syncthreads();
+    if (slices > 1) {        // partial planes of a slice: into the group's global planes, shared planes back to zero
+#pragma unroll 1
+      for (int d = 0; d < D; ++d) {
+        if (sh.dir[d] < 0) continue;
+        unsigned *g = gplanes + (size_t)(group * D + d) * plane_cells;
+        unsigned *pl = planes + (size_t)d * stride;
+        for (unsigned q = tid; q < stride; q += kStreamThreads) {
+          const unsigned v = pl[q];
+          if (v) { pl[q] = 0; if (q < plane_cells) atomicAdd(&g[q], v); }
+        }
+      }
+      __syncthreads();
+      continue;
+    }
 #pragma unroll
     for (int d = 0; d < D; ++d) {
       const int l = sh.dir[d];
@@ -375,6 +407,36 @@ vote_stream_kernel(const __grid_constant__ HoughDev h, const int *__restrict__ l
       if (lane == 0) store_record(h, sh.dir[warp], k);
     }
     if (TMA) consumer_bar(); else __syncthreads();   // sh.dir / sh.coef are rewritten by the next item
+  }
+}
+
+// second half of a point-sliced list re-vote: one CTA per listed plane reduces the global plane to its record and
+// zeroes it again (no-op when the vote kernel did not slice: *sliced_flag == 0)
+__global__ void __launch_bounds__(256) stream_merge_kernel(const HoughDev h, const int *__restrict__ list,
+                                                           unsigned *__restrict__ gplanes, const int *__restrict__ sliced_flag) {
+  __shared__ unsigned long long scratch[8];
+  const int count = *sliced_flag;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int e = blockIdx.x; e < count; e += gridDim.x) {
+    unsigned *g = gplanes + (size_t)e * h.plane_cells;
+    unsigned long long k = 0;
+    for (unsigned q = threadIdx.x; q < h.plane_cells; q += blockDim.x) {
+      const unsigned v = g[q];
+      if (v) {
+        g[q] = 0;
+        const unsigned long long kk = ((unsigned long long)v << 32) | (0xFFFFFFFFu - q);
+        k = kk > k ? kk : k;
+      }
+    }
+    k = warp_max_u64(k);
+    if (lane == 0) scratch[warp] = k;
+    __syncthreads();
+    if (warp == 0) {
+      k = lane < (int)(blockDim.x >> 5) ? scratch[lane] : 0ull;
+      k = warp_max_u64(k);
+      if (lane == 0) store_record(h, list ? list[e] : e, k);
+    }
+    __syncthreads();
   }
 }
 

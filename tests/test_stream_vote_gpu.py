@@ -44,8 +44,11 @@ def test_dense_accumulator_equals_oracle_in_every_mode(h3d, oracle, n, g, dx, bo
     ref.close()
 
 
-def test_subtract_and_revote_lists_through_the_streaming_kernel(h3d, oracle):
-    pts = synth.steel_tower(9000, seed=5)
+@pytest.mark.parametrize("n", [9000, 40000])
+def test_subtract_and_revote_lists_through_the_streaming_kernel(h3d, oracle, n):
+    """n = 40000: the re-vote lists are short and the cloud is large, so the kernel slices the POINTS over the CTAs
+    and merges partial planes in global memory (stream_merge_kernel)"""
+    pts = synth.steel_tower(n, seed=5)
     x, mn, mx = _centred(oracle, pts)
     g = 3
     ref = oracle.hough(g, mn, mx, 0.0)
