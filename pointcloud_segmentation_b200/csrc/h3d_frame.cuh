@@ -494,52 +494,38 @@ __device__ __forceinline__ void patch_hough(HoughDev &h, const HoughDev &fixed, 
   h.n = F.n; h.n_dev = nullptr;
 }
 
-// Hough::add of a frame on the fast path: the BOUNDED resident vote with the widest slot count (the host
-// does not know the point count; a warp skips the slots it holds no point of), geometry from the descriptor.
+// Hough::add of a frame on the fast path: the BOUNDED resident vote, geometry from the descriptor.
 // The slot count P = ceil(n / 512) is picked ON THE DEVICE: the kernel holds the twelve instantiations of the
 // vote loop and branches once (only the taken one occupies the instruction cache; the register allocation is
-// that of P = 12 either way, and one CTA per SM is resident regardless).
+// that of the widest, and only its path spills).
 // MODE 0: RED increments + plane scan; 1: TRACK (atomics return the old count, no scan); 2 (default): TRACK up
 // to 6 slots (3072 points), scan above -- measured on the 16 bench frames (profiles/r02_track_ab.txt): TRACK
 // wins 88 vs 103 us at 1.3 k points and loses 195 vs 179 us at 4.9 k (ATOMS with a return value costs ~13 cycles
 // per warp-vote against ~9 for the merging RED form; the scan it saves is a fixed ~0.2 us per direction).
-// Shared-memory layout of the frame vote kernel: [HoughDev | ResShared | planes ...], all carved out of the one
-// extern array, so that every function that touches them sees a __shared__ object (an out-of-line function that
-// received them as pointers addressed them through the generic space: LD instead of LDS on the hot loop's
-// coefficient and direction reads, 13 % slower than the host-dispatched kernel of the general path).
+// Shared-memory layout: [HoughDev | ResShared | planes ...], carved out of the one extern array.
 constexpr unsigned kVoteFrameHdr = 256;                                              // HoughDev
 constexpr unsigned kVoteFrameRes = (unsigned)((sizeof(ResShared) + 255) / 256 * 256);
 constexpr unsigned kVoteFramePlanesOff = kVoteFrameHdr + kVoteFrameRes;
 static_assert(sizeof(HoughDev) <= kVoteFrameHdr, "HoughDev must fit its slot");
 
-// one out-of-line function per slot count: each gets its own register allocation (the P <= 9 loops need no
-// spill; inlined into one body, all twelve shared the allocation of the widest and spilled 76 bytes)
-template <int P, bool TRACK>
-__device__ __noinline__ void vote_frame_variant(int cta, int n_cta) {
-  extern __shared__ __align__(16) unsigned char vf_smem[];
-  const HoughDev &hs = *reinterpret_cast<const HoughDev *>(vf_smem);
-  ResShared &sh = *reinterpret_cast<ResShared *>(vf_smem + kVoteFrameHdr);
-  unsigned *planes = reinterpret_cast<unsigned *>(vf_smem + kVoteFramePlanesOff);
-  vote_resident<P, 0, true, TRACK>(hs, nullptr, hs.dir_count, planes, sh, cta, n_cta);
-}
-
-// MODE 0: RED increments + plane scan; 1: TRACK (atomics return the old count, no scan); 2 (default): TRACK up
-// to 6 slots (3072 points), scan above -- measured on the 16 bench frames (profiles/r02_track_ab.txt): TRACK
-// wins 88 vs 103 us at 1.3 k points and loses 195 vs 179 us at 4.9 k (ATOMS with a return value costs ~13 cycles
-// per warp-vote against ~9 for the merging RED form; the scan it saves is a fixed ~0.2 us per direction).
 template <int MODE>
 __global__ void __launch_bounds__(kResThreads, 1)
 vote_frame_kernel(const __grid_constant__ HoughDev fixed, const FrameDev *__restrict__ fd) {
   extern __shared__ __align__(16) unsigned char vf_smem[];
   HoughDev &hs = *reinterpret_cast<HoughDev *>(vf_smem);
   unsigned *planes = reinterpret_cast<unsigned *>(vf_smem + kVoteFramePlanesOff);
+  ResShared &sh = *reinterpret_cast<ResShared *>(vf_smem + kVoteFrameHdr);
   if (fd->status != 0) return;
   if (threadIdx.x == 0) patch_hough(hs, fixed, *fd);
   __syncthreads();
   uint4 *p4 = reinterpret_cast<uint4 *>(planes);
   for (unsigned q = threadIdx.x; q < 2 * kResG * hs.plane_stride / 4 + 1; q += kResThreads) p4[q] = make_uint4(0, 0, 0, 0);
   const int cta = blockIdx.x, n_cta = gridDim.x;
-#define H3D_FRAME_VOTE(PP) vote_frame_variant<PP, (MODE == 1 || (MODE == 2 && PP <= 6))>(cta, n_cta); break;
+  // (One out-of-line function per slot count was tried for the sake of per-variant register allocation: ptxas then
+  // rebuilt the shared-window address -- S2UR SR_CgaCtaId / ULEA / IMAD -- in front of every shared access of the
+  // callee, +24 % instructions, 154 us against 132 us for the host-dispatched kernel; ncu, round 2.  Inlined, the
+  // variants share the register allocation of the widest one and only its path spills.)
+#define H3D_FRAME_VOTE(PP) vote_resident<PP, 0, true, (MODE == 1 || (MODE == 2 && PP <= 6))>(hs, nullptr, hs.dir_count, planes, sh, cta, n_cta); break;
   switch ((hs.n + kResThreads - 1) / kResThreads) {
     case 0: case 1: H3D_FRAME_VOTE(1)
     case 2: H3D_FRAME_VOTE(2)
