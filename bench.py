@@ -11,8 +11,8 @@ A step is one pass of the hot path over a batch of FRAMES_PER_STEP synthetic fra
 (poses along the tower trajectory).  Frames are independent (one Hough per frame) and the loop of
 one frame is latency-bound, so a GPU keeps K frames in flight: K pipelines driven by K host
 threads of the library (h3d_replay_run), each limited to a share of the SMs for its persistent loop
-kernel (--concurrency 12 x --sm-share 18 by default; the shares may oversubscribe the GPU, a
-kernel then waits for free SMs while its pipeline pre-filters the next frame).
+kernels (--concurrency 16 x --sm-share 9 by default = 144 of the 148 SMs; shares that oversubscribe the GPU also
+work, a cooperative kernel then waits for free SMs).
 `value` is timed with the frames resident in HBM (h3d_pipeline_run_dev), `e2e` through
 h3d_pipeline_run with pinned HOST frames: H2D of the raw frame and D2H of the line records and
 inlier lists are inside the timed region.  A step is bracketed by device synchronisation and a pair
@@ -43,8 +43,9 @@ sys.path.insert(0, ROOT)
 
 FRAMES_PER_STEP = 64          # frames per step: 4 passes over DISTINCT_FRAMES different frames
 DISTINCT_FRAMES = 16
-FRAMES_IN_FLIGHT = 12          # pipelines (host threads) per GPU ...
-SM_SHARE = 18                  # ... each limited to this many SMs for its persistent loop kernel
+FRAMES_IN_FLIGHT = 16          # pipelines (host threads) per GPU ...
+SM_SHARE = 9                   # ... each limited to this many SMs for its vote and persistent loop kernels
+                               # (16 x 9 = 144 of 148 SMs; sweep on B200: profiles/r02_concurrency_sweep_final.txt)
 GRANULARITY = 6
 NLINES = 20
 MINVOTES = 12

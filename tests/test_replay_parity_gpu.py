@@ -21,7 +21,9 @@ pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_golden_g56.npz")
 FIELDS = ("votes", "argmax", "status", "n1", "n2", "inl1", "inl2", "a2", "b2")
-K_PIPES, SM_SHARE = 12, 18      # bench.py FRAMES_IN_FLIGHT x SM_SHARE
+# (pipelines, SMs per pipeline): round 1's oversubscribed bench configuration (216 > 148 SMs: cooperative kernels
+# queue for SMs) and bench.py's current FRAMES_IN_FLIGHT x SM_SHARE
+SHAPES = [(12, 18), (16, 9)]
 
 
 def _sha(a):
@@ -90,9 +92,10 @@ def test_single_frames_match_the_reference_at_g6(h3d, tof):
     assert sum(int(w["n_lines"]) for w in want) == 257 or "oracle" in tof[3]
 
 
+@pytest.mark.parametrize("shape", SHAPES, ids=["12x18", "16x9"])
 @pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("on_device", [False, True])
-def test_oversubscribed_replay_matches_the_reference(h3d, tof, fused, on_device):
+def test_oversubscribed_replay_matches_the_reference(h3d, tof, fused, on_device, shape):
     """64 frames over 12 pipelines x 18 SMs (oversubscribed), the three host wait modes: every frame's trace
     equals the reference's, whatever runs beside it"""
     import torch
@@ -102,7 +105,7 @@ def test_oversubscribed_replay_matches_the_reference(h3d, tof, fused, on_device)
     stack = torch.from_numpy(np.stack(frames)).pin_memory()
     dev = stack.cuda() if on_device else None
     ptrs = [(dev if on_device else stack)[k % len(frames)].data_ptr() for k in range(n_frames)]
-    rp = h3d.Replay(K_PIPES, SM_SHARE, g, synth.WINDOW, synth.LEAF, synth.OPT_DX, minvotes, nlines, n_pts, n_frames)
+    rp = h3d.Replay(shape[0], shape[1], g, synth.WINDOW, synth.LEAF, synth.OPT_DX, minvotes, nlines, n_pts, n_frames)
     old_poison = h3d.set_debug_poison(1)
     h3d.set_fused(fused)
     try:
