@@ -95,6 +95,23 @@ int h3d_points_close_to_line(const double *xyz, size_t n, const double a[3], con
                              double dx, uint32_t *idx_out, size_t *n_out);
 /* removePoints (:109-128): ordered set difference by exact ==, compacts x in place */
 int h3d_remove_points(double *x_xyz, size_t nx, const double *y_xyz, size_t ny, size_t *n_out);
+/* pointsCloseToLine WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same result as h3d_points_close_to_line (bit-exact: same expression tree, same order), but
+ *   - xyz_dev (n x 3 doubles), idx_out_dev (>= n uint32) and n_out_dev (one int) are DEVICE pointers owned by
+ *     the caller; a[3], b[3] are host arrays read before the call returns;
+ *   - the one-byte-per-point inlier flags live in a file-scope __device__ array of H3D_NOALLOC_MAX_POINTS
+ *     bytes (1 MiB, held by every GPU that loads the library until the process exits); n beyond that is
+ *     rejected with H3D_ERR_RANGE and a message in h3d_last_error();
+ *   - the two kernels are launched on `stream` (a cudaStream_t, NULL = default stream) and the call returns
+ *     without synchronising; it calls no cudaMalloc / cudaFree / allocating library routine.  The first call
+ *     on each device looks the array's address up (cudaGetSymbolAddress): make it outside stream capture.
+ * Every call on a device shares the array (it keeps the last call's contents; nothing in it needs clearing,
+ * each call writes flags[0, n) before reading them): calls that OVERLAP on the GPU race -- keep them on one
+ * stream or order them with events. */
+#define H3D_NOALLOC_MAX_POINTS 1048576
+int h3d_points_close_to_line_noalloc(const double *xyz_dev, size_t n, const double a[3], const double b[3],
+                                     double dx, uint32_t *idx_out_dev, int *n_out_dev, void *stream);
 /* orthogonal_LSQ (wrap.h:121-150): anchor = f64 mean, direction = top eigenvector
  * of the f32 centred scatter, *rc = top eigenvalue */
 int h3d_orthogonal_lsq(const double *xyz, size_t n, double a[3], double b[3], double *rc);

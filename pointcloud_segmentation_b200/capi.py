@@ -515,6 +515,17 @@ def points_close_to_line(xyz, a_, b_, dx):
     return idx[: n_out.value].copy()
 
 
+NOALLOC_MAX_POINTS = 1048576   # H3D_NOALLOC_MAX_POINTS (include/h3d.h)
+
+
+def points_close_to_line_noalloc(xyz_dev_ptr, n, a_, b_, dx, idx_out_dev_ptr, n_out_dev_ptr, stream=0):
+    """h3d_points_close_to_line_noalloc: DEVICE pointers (ints) in and out, launches on `stream`, no
+    synchronisation and no allocation -- the caller owns every buffer (include/h3d.h)."""
+    check(lib().h3d_points_close_to_line_noalloc(C.c_void_p(xyz_dev_ptr), C.c_size_t(n), _d3(a_), _d3(b_),
+                                                 C.c_double(dx), C.c_void_p(idx_out_dev_ptr),
+                                                 C.c_void_p(n_out_dev_ptr), C.c_void_p(stream)))
+
+
 def remove_points(x, y):
     xa = np.array(x, dtype=np.float64).reshape(-1, 3)
     ya, yp, ny = _pts(y)
