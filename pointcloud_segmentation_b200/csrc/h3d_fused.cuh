@@ -353,6 +353,18 @@ __device__ __forceinline__ FusedView fused_view(int n_own, int nb, int n_cap) {
 
 // K4 inside the loop: Hough::subtract(Y) for the CTA's own directions, run by warps 1..15 while warp 0 solves the
 // second eigen-problem.  Y (pass 2, ny2 points) lies within opt_dx of the line (a, b) of pass 2.
+//
+// A record turns stale iff some point e of Y votes for its max cell.  Only points whose parameter t_e along the
+// line falls into the record's strip interval can (strip_interval), so Y is first bucketed by t (counting sort
+// into kUvBuckets buckets; the scratch is the head of the plane area, which is all zero between re-vote rounds
+// and is zeroed again here) and every record then looks at the few points of its bucket range only:
+//   stage 1  one THREAD per record: interval, bucket range; up to kUvInline candidates are tested on the spot
+//            (exact cell arithmetic, first hit ends the record), longer ranges go to a list;
+//   stage 2  one WARP per listed record, 32 candidates per step.
+// Before (every surviving record took a warp that walked all of Y with a float-t filter) the phase cost 20-90 us
+// per iteration with 2276 records per CTA (9 SMs per frame), most of it per-record overhead of stage 2.
+constexpr int kUvBuckets = 128, kUvInline = 16;
+
 __device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b)[3], int ny2, int n_own, int nb, int n_cap,
                                           int cta, int n_cta, double cell_off, double reach2) {
   constexpr int G = kResG;
@@ -363,81 +375,152 @@ __device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b
   int *rlist = V.rlist;
   const FusedPoints &Q = V.Q;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-        // Y (pass 2) lies within opt_dx of the line (a, b) of pass 2
-        const int ut = tid - 32, un = kResThreads - 32;
-        const float tl = ordered_float(sh.tmin_i), th = ordered_float(sh.tmax_i);
-        const double t0 = (double)tl - (fabs((double)tl) * 1e-6 + 1e-9), t1 = (double)th + (fabs((double)th) * 1e-6 + 1e-9);
-        const unsigned num_x = (unsigned)h.num_x;
-        constexpr int SU = 3;   // records per thread per batch: their coefficient loads (L2) are issued together
-        for (int r0 = ut; r0 < n_own; r0 += SU * un) {
-          DirCoef cj[SU];
-          bool live[SU];
+  const int ut = tid - 32, un = kResThreads - 32;
+  const float tl = ordered_float(sh.tmin_i), th = ordered_float(sh.tmax_i);
+  const double t0 = (double)tl - (fabs((double)tl) * 1e-6 + 1e-9), t1 = (double)th + (fabs((double)th) * 1e-6 + 1e-9);
+  const unsigned num_x = (unsigned)h.num_x;
+
+  // ---- Y bucketed by t: start[0..kUvBuckets] | fill[kUvBuckets] | sidx[ny2] | st[ny2] in the (zero) plane area ----
+  int *start = reinterpret_cast<int *>(V.planes);
+  int *fill = start + kUvBuckets + 1;
+  int *sidx = fill + kUvBuckets;
+  float *st = reinterpret_cast<float *>(sidx + ny2);
+  const unsigned scratch_words = 2u * kUvBuckets + 1u + 2u * (unsigned)ny2;
+  // uniform.  Not with few records per CTA (a frame on all SMs: the three barriers of the bucketing would cost more
+  // than they save, and the phase hides behind the eigen-solve anyway) or tiny planes with a huge Y.
+  const bool bucketed = n_own >= 512 && scratch_words <= (unsigned)nb * V.stride;
+  const float bscale = th > tl ? (float)kUvBuckets / (th - tl) : 0.0f;
+  // monotonic in t (float subtraction, multiplication by a positive constant, truncation, clamp): a point with
+  // flo <= t_e <= fhi lies in a bucket of [bucket_of(flo), bucket_of(fhi)]
+  auto bucket_of = [&](float t) {
+    const float v = (t - tl) * bscale;
+    return v >= (float)(kUvBuckets - 1) ? kUvBuckets - 1 : (v > 0.0f ? (int)v : 0);
+  };
+  if (bucketed) {
+    for (int e = ut; e < ny2; e += un) atomicAdd(&start[bucket_of(Q.yt[e]) + 1], 1);
+    named_bar_sync(1, un);
+    if (warp == 1) {   // inclusive scan of the counts: start[k] = points in buckets below k
+      constexpr int PER = kUvBuckets / 32;
+      int c[PER], tot = 0;
 #pragma unroll
-          for (int u = 0; u < SU; ++u) {
-            const int r = r0 + u * un;
-            live[u] = r < n_own && !rstale[r] && rv[r] != 0;
-            if (live[u]) cj[u] = h.coef[h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G)];
-          }
+      for (int q = 0; q < PER; ++q) { c[q] = start[1 + lane * PER + q]; tot += c[q]; }
+      int incl = tot;
 #pragma unroll
-          for (int u = 0; u < SU; ++u) {
-            if (!live[u]) continue;
-            const int r = r0 + u * un;
-            const unsigned cx = rcell[r] / num_x, cy = rcell[r] - cx * num_x;
-            // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92)
-            double ilo, ihi;
-            if (cy == 0 || cy == num_x - 1 ||
-                (strip_interval(make_fast(cj[u], h.inv_s), a, b, cell_off, reach2, cx, cy, &ilo, &ihi) && ilo <= t1 && ihi >= t0))
-              rlist[atomicAdd(&sh.ns, 1)] = r;
-          }
-        }
-        named_bar_sync(1, un);
-        // exact test of the surviving records, one WARP per record: 32 removed points per step, and the
-        // record is done at its first hit (a record whose max cell lies on the removed line is hit within a
-        // step or two; testing every (record, point) pair cost up to 200 us per iteration at 18 SMs per frame)
-        const int ns = sh.ns;
-        // the coefficients of a record come from L2 (~0.7 us): lane q of the warp fetches those of the q-th record
-        // the warp will test, 32 records per round trip, and hands them over by shuffle (one dependent L2 load per
-        // record made this phase 40 us long with ~400 candidate records per CTA)
-        DirCoef pre = {0.0, 0.0, 0.0, 0.0, 0.0};
-        int pre_base = -1;
+      for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= o) incl += v; }
+      int run = incl - tot;
+#pragma unroll
+      for (int q = 0; q < PER; ++q) { run += c[q]; start[1 + lane * PER + q] = run; }
+    }
+    named_bar_sync(1, un);
+    for (int e = ut; e < ny2; e += un) {
+      const float te = Q.yt[e];
+      const int bk = bucket_of(te);
+      const int pos = start[bk] + atomicAdd(&fill[bk], 1);
+      sidx[pos] = Q.yidx[e]; st[pos] = te;
+    }
+    named_bar_sync(1, un);
+  }
+
+  // ---- stage 1: one thread per record ----
+  constexpr int SU = 3;   // records per thread per batch: their coefficient loads (L2) are issued together
+  for (int r0 = ut; r0 < n_own; r0 += SU * un) {
+    DirCoef cj[SU];
+    bool live[SU];
+#pragma unroll
+    for (int u = 0; u < SU; ++u) {
+      const int r = r0 + u * un;
+      live[u] = r < n_own && !rstale[r] && rv[r] != 0;
+      if (live[u]) cj[u] = h.coef[h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G)];
+    }
+#pragma unroll
+    for (int u = 0; u < SU; ++u) {
+      if (!live[u]) continue;
+      const int r = r0 + u * un;
+      const unsigned target = rcell[r];
+      const unsigned cx = target / num_x, cy = target - cx * num_x;
+      // y_i == num_x or -1 aliases into a neighbouring row (flat bound only, lib/hough.cpp:90-92): edge cells take
+      // every point of Y
+      const bool edge = cy == 0 || cy == num_x - 1;
+      const FastCoef fc = make_fast(cj[u], h.inv_s);
+      double ilo = -INFINITY, ihi = INFINITY;
+      if (!edge && !(strip_interval(fc, a, b, cell_off, reach2, cx, cy, &ilo, &ihi) && ilo <= t1 && ihi >= t0)) continue;
+      if (!bucketed) { rlist[atomicAdd(&sh.ns, 1)] = r; continue; }
+      const float flo = (float)(ilo - (fabs(ilo) * 1e-6 + 1e-6)), fhi = (float)(ihi + (fabs(ihi) * 1e-6 + 1e-6));
+      const int e0 = start[bucket_of(flo)], e1 = start[bucket_of(fhi) + 1];
+      const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
+      // middle-out over the sorted range: a vote for the cell needs P(t) within half a cell of its centre, i.e.
+      // t in the central third of the interval, so a record whose max cell lies ON the removed line (almost
+      // every record when a dominant line goes) is hit within the first few tests
+      const int len = e1 - e0, tries = min(len, kUvInline);
+      int hi_i = e0 + (len >> 1);
+      if (ihi - ilo < 1e30) {   // start at the bucket of the interval's centre (the range may be clipped at an end of Y)
+        const int bc = bucket_of((float)(0.5 * (ilo + ihi)));
+        hi_i = min(max((start[bc] + start[bc + 1]) >> 1, e0), max(e1 - 1, e0));
+      }
+      int lo_i = hi_i - 1;
+      bool hit = false;
 #pragma unroll 1
-        for (int s = warp - 1, q = 0; s < ns; s += kResWarps - 1, ++q) {
-          if ((q & 31) == 0) {
-            const int sq = s + lane * (kResWarps - 1);
-            if (sq < ns) {
-              const int rq = rlist[sq];
-              pre = h.coef[h.dir_begin + (cta + (rq / G) * n_cta) * G + (rq % G)];
-            }
-            pre_base = q;
-          }
-          const int r = rlist[s];
-          const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
-          DirCoef cj;
-          {
-            const int src = q - pre_base;
-            cj.c0 = __shfl_sync(0xFFFFFFFFu, pre.c0, src); cj.c1 = __shfl_sync(0xFFFFFFFFu, pre.c1, src);
-            cj.c2 = __shfl_sync(0xFFFFFFFFu, pre.c2, src); cj.bx = __shfl_sync(0xFFFFFFFFu, pre.bx, src);
-            cj.by = __shfl_sync(0xFFFFFFFFu, pre.by, src);
-          }
-          const FastCoef fc = make_fast(cj, h.inv_s);
-          const unsigned target = rcell[r];
-          // only inliers whose t puts them near the cell can vote for it: skip the others on their float t
-          // (edge cells reached through the reference's flat-index aliasing take every point)
-          const unsigned cx = target / num_x, cy = target - cx * num_x;
-          double ilo = -INFINITY, ihi = INFINITY;
-          if (cy != 0 && cy != num_x - 1) strip_interval(fc, a, b, cell_off, reach2, cx, cy, &ilo, &ihi);
-          const float flo = (float)(ilo - (fabs(ilo) * 1e-6 + 1e-6)), fhi = (float)(ihi + (fabs(ihi) * 1e-6 + 1e-6));
+      for (int q = 0; q < tries; ++q) {   // hi, lo, hi, lo, ... while both sides last, then the side that is left
+        const bool up = (q & 1) == 0 ? hi_i < e1 : lo_i < e0;
+        const int e = up ? hi_i++ : lo_i--;
+        const float te = st[e];
+        if (!(te >= flo && te <= fhi)) continue;
+        const int i = sidx[e];
+        if (vote_cell(h, fc, j, Q.x[i], Q.y[i], Q.z[i]) == target) { hit = true; break; }
+      }
+      if (hit) rstale[r] = 1;
+      else if (len > kUvInline) rlist[atomicAdd(&sh.ns, 1)] = r;   // the rest of a long range: a warp takes it
+    }
+  }
+  named_bar_sync(1, un);
+
+  // ---- stage 2: one WARP per listed record, 32 candidates per step, done at the first hit ----
+  const int ns = sh.ns;
+  // the coefficients of a record come from L2 (~0.7 us): lane q of the warp fetches those of the q-th record
+  // the warp will test, 32 records per round trip, and hands them over by shuffle
+  DirCoef pre = {0.0, 0.0, 0.0, 0.0, 0.0};
+  int pre_base = -1;
 #pragma unroll 1
-          for (int e0 = 0; e0 < ny2; e0 += 32) {
-            const int e = e0 + lane;
-            bool cand = false;
-            if (e < ny2) { const float te = Q.yt[e]; cand = te >= flo && te <= fhi; }
-            if (!__any_sync(0xFFFFFFFFu, cand)) continue;
-            bool hit = false;
-            if (cand) { const int i = Q.yidx[e]; hit = vote_cell(h, fc, j, Q.x[i], Q.y[i], Q.z[i]) == target; }
-            if (__any_sync(0xFFFFFFFFu, hit)) { if (lane == 0) rstale[r] = 1; break; }
-          }
-        }
+  for (int s = warp - 1, q = 0; s < ns; s += kResWarps - 1, ++q) {
+    if ((q & 31) == 0) {
+      const int sq = s + lane * (kResWarps - 1);
+      if (sq < ns) {
+        const int rq = rlist[sq];
+        pre = h.coef[h.dir_begin + (cta + (rq / G) * n_cta) * G + (rq % G)];
+      }
+      pre_base = q;
+    }
+    const int r = rlist[s];
+    const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
+    DirCoef cj;
+    {
+      const int src = q - pre_base;
+      cj.c0 = __shfl_sync(0xFFFFFFFFu, pre.c0, src); cj.c1 = __shfl_sync(0xFFFFFFFFu, pre.c1, src);
+      cj.c2 = __shfl_sync(0xFFFFFFFFu, pre.c2, src); cj.bx = __shfl_sync(0xFFFFFFFFu, pre.bx, src);
+      cj.by = __shfl_sync(0xFFFFFFFFu, pre.by, src);
+    }
+    const FastCoef fc = make_fast(cj, h.inv_s);
+    const unsigned target = rcell[r];
+    const unsigned cx = target / num_x, cy = target - cx * num_x;
+    double ilo = -INFINITY, ihi = INFINITY;
+    if (cy != 0 && cy != num_x - 1) strip_interval(fc, a, b, cell_off, reach2, cx, cy, &ilo, &ihi);
+    const float flo = (float)(ilo - (fabs(ilo) * 1e-6 + 1e-6)), fhi = (float)(ihi + (fabs(ihi) * 1e-6 + 1e-6));
+    const int e_begin = bucketed ? start[bucket_of(flo)] : 0, e_end = bucketed ? start[bucket_of(fhi) + 1] : ny2;
+#pragma unroll 1
+    for (int e0 = e_begin; e0 < e_end; e0 += 32) {
+      const int e = e0 + lane;
+      bool cand = false;
+      if (e < e_end) { const float te = bucketed ? st[e] : Q.yt[e]; cand = te >= flo && te <= fhi; }
+      if (!__any_sync(0xFFFFFFFFu, cand)) continue;
+      bool hit = false;
+      if (cand) { const int i = bucketed ? sidx[e] : Q.yidx[e]; hit = vote_cell(h, fc, j, Q.x[i], Q.y[i], Q.z[i]) == target; }
+      if (__any_sync(0xFFFFFFFFu, hit)) { if (lane == 0) rstale[r] = 1; break; }
+    }
+  }
+  if (bucketed) {   // the scratch back to zero: the re-vote rounds count on an all-zero plane area
+    named_bar_sync(1, un);
+    for (unsigned w = (unsigned)ut; w < scratch_words; w += (unsigned)un) V.planes[w] = 0u;
+  }
 }
 
 // Re-vote of the stale records listed in rlist[0..nlist) (their bound reaches the best exact record).
@@ -619,6 +702,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
         fused_unvote(a, b, ny2, n_own, nb, n_cap, cta, n_cta, cell_off, reach2);
       }
       __syncthreads();
+      if (pass == 1) stamp(14, (unsigned long long)sh.ns + 1);   // measurement: records the un-vote handed to its warp stage
       const double rc = sh.lsq.rc;
       if (rec) {
         if (pass == 0) { for (int c = 0; c < 3; ++c) { R->a1[c] = sh.lsq.a[c]; R->b1[c] = sh.lsq.b[c]; } R->rc1 = rc; }

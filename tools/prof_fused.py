@@ -29,7 +29,8 @@ for it in range(t.shape[0]):
     c0 = a[0]
     seg = [c0[k + 1] - c0[k] for k in range(7)]
     line = f"it {it:2d} cta0 us: " + " ".join(f"{n}={v/1e3:5.1f}" for n, v in zip(names, seg))
-    line += f" [line {(c0[14]-c0[2])/1e3:.1f} mask1 {(c0[12]-c0[14])/1e3:.1f} eig1+mask2 {(c0[13]-c0[4])/1e3:.1f}]"
+    uv2 = a[:, 14][a[:, 14] > 0] - 1   # records per CTA that the un-vote handed to its warp-per-record stage
+    line += f" [unvote warp-stage records/CTA max {uv2.max() if len(uv2) else 0} mean {uv2.mean() if len(uv2) else 0:.1f}; eig1+mask2 {(c0[13]-c0[4])/1e3:.1f}]"
     if a[0, 9]:
         nl = a[:, 8] - 1
         rv = (a[:, 9] - a[:, 11]) / 1e3
