@@ -303,9 +303,11 @@ __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints
       }
     }
     const bool in0 = o0 < lim, in1 = two & (o1 < lim);
-    const unsigned old0 = atom_shared_inc_ret(in0 ? plane0_sa + o0 : dummy_sa);
-    const unsigned old1 = atom_shared_inc_ret(in1 ? plane1_sa + o1 : dummy_sa);
-    const unsigned k0 = ((old0 + 1u) << 16) | (0xFFFFu - (o0 >> 2)), k1 = ((old1 + 1u) << 16) | (0xFFFFu - (o1 >> 2));
+    // BOUNDED form: a vote that is not counted still lands inside its plane's stride (slack cells; `lim` on the exact
+    // path), so plane 0 needs no redirect; plane 1 does not exist when the pair is a single record
+    const unsigned old0 = atom_shared_inc_ret(plane0_sa + o0);
+    const unsigned old1 = atom_shared_inc_ret(two ? plane1_sa + o1 : dummy_sa);
+    const unsigned k0 = ((old0 + 1u) << 16) | ((o0 >> 2) ^ 0xFFFFu), k1 = ((old1 + 1u) << 16) | ((o1 >> 2) ^ 0xFFFFu);
     b0 = max(b0, in0 ? k0 : 0u);
     b1 = max(b1, in1 ? k1 : 0u);
   }

@@ -652,9 +652,11 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
         const unsigned mine_sa = planes_sa + (unsigned)(slot * G + g) * stride * 4u;
         unsigned tbest = 0;     // TRACK: this thread's best (count, ~cell) key of direction g
         const unsigned lim4 = 4u * plane_cells;
-        auto track = [&](unsigned off, bool counted) {
-          const unsigned old = atom_shared_inc_ret(counted ? mine_sa + off : dummy_sa);
-          const unsigned key = ((old + 1u) << 16) | (0xFFFFu - (off >> 2));
+        // in_plane: the increment may land where `off` says even when it is not counted (BOUNDED form with every
+        // lane live: a dropped vote falls into the slack cells or, on the exact path, onto the pad word)
+        auto track = [&](unsigned off, bool counted, bool in_plane) {
+          const unsigned old = atom_shared_inc_ret((in_plane || counted) ? mine_sa + off : dummy_sa);
+          const unsigned key = ((old + 1u) << 16) | ((off >> 2) ^ 0xFFFFu);   // == 0xFFFF - cell for a counted vote
           tbest = max(tbest, counted ? key : 0u);
         };
         constexpr int CH = 4;   // votes per batch: 8 independent DFMA chains, 4 cell registers
@@ -690,7 +692,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
             for (int c = 0; c < CH; ++c) {
               if (p0 + c >= P) continue;
               if (ABLATE == 1) sink ^= off[c];
-              else if (TRACK) track(off[c], off[c] < lim4);
+              else if (TRACK) track(off[c], off[c] < lim4, BOUNDED);
               else if (BOUNDED) red_shared_inc(mine_sa + off[c]);
               else red_shared_inc(off[c] < 4u * plane_cells ? mine_sa + off[c] : dummy_sa);
             }
@@ -710,7 +712,7 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
               }
               // an empty lane of a partly filled slot votes into the pad word
               if (ABLATE == 1) sink ^= o;
-              else if (TRACK) track(o, (o < lim4) & ((live >> p) & 1u));
+              else if (TRACK) track(o, (o < lim4) & ((live >> p) & 1u), false);
               else if (BOUNDED) red_shared_inc(((live >> p) & 1u) ? mine_sa + o : dummy_sa);
               else red_shared_inc(((o < 4u * plane_cells) & ((live >> p) & 1u)) ? mine_sa + o : dummy_sa);
             }
@@ -728,17 +730,21 @@ __device__ __forceinline__ void vote_resident(const HoughDev &h, const int *__re
         // the previous group's planes back to zero (their maxima were tracked, not scanned).  The warps do not
         // finish their votes together (5 or 6 slots of points each), so the zero-fill is handed out in chunks of
         // kZeroChunk quads to whichever warp is free (ncu, round 2: 14 % of the samples waited at the phase barrier)
-        constexpr unsigned kZeroChunk = 128;            // 4 STS.128 per lane
-        const unsigned per_plane = (quads + kZeroChunk - 1) / kZeroChunk, n_chunks = per_plane * G;
+        // The G planes of a slot are contiguous; a chunk is 8 STS.128 per lane.  (ncu, round 2: with 128-quad chunks
+        // addressed as (plane, offset) the bookkeeping -- a division, 64-bit address arithmetic, a rolled store
+        // loop -- made the zero-fill 21 % of the kernel's instructions, 920 per direction for 49 useful stores.)
+        constexpr unsigned kZeroChunk = 256;
+        const unsigned total_q = (unsigned)G * quads;
+        uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)((slot ^ 1) * G) * stride);
         for (;;) {
           unsigned c = 0;
           if (lane == 0) c = (unsigned)atomicAdd(&sh.zero_ctr[dslot], 1);
           c = __shfl_sync(0xFFFFFFFFu, c, 0);
-          if (c >= n_chunks) break;
-          const unsigned g = c / per_plane, q0 = (c - g * per_plane) * kZeroChunk;
-          const unsigned qb = q0, qe = min(q0 + kZeroChunk, quads);
-          uint4 *p4 = reinterpret_cast<uint4 *>(planes + (size_t)((slot ^ 1) * G + g) * stride);
-          for (unsigned q = qb + lane; q < qe; q += 32) p4[q] = make_uint4(0, 0, 0, 0);
+          const unsigned q0 = c * kZeroChunk + lane;
+          if (q0 - lane >= total_q) break;
+#pragma unroll
+          for (unsigned u = 0; u < kZeroChunk / 32; ++u)
+            if (q0 + u * 32 < total_q) p4[q0 + u * 32] = make_uint4(0, 0, 0, 0);
         }
       }
       if (tid < G) cp_async_wait_all();
