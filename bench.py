@@ -372,6 +372,12 @@ def run_gpu_arm(args):
     # (3.31 k vs 3.31 k frames/s at 1 GPU / 16 cores), far ahead of it when they are not
     wait_mode = {"spin": 0, "block": 1, "yield": 2}.get(args.wait, 2 if K > 1 else 0)
     capi.set_wait_mode(wait_mode)
+    # fewer cores than ranks x K: each host thread drives several pipelines in split phase (submit, poll, complete)
+    cores_per_rank = max(1, host_cores // world)
+    # (measured at N = 1 on 16 cores: 16 / 8 / 4 / 2 threads for 16 pipelines -> 3763 / 3783 / 3784 / 3772 frames/s:
+    # a frame costs the host ~30 us of launches and one copy, so a few threads are enough on any box)
+    replay_threads = args.replay_threads if args.replay_threads >= 0 else min(K, max(2, min(4, cores_per_rank - 1)))
+    capi.set_replay_threads(replay_threads)
     share = 0 if K == 1 else (args.sm_share if args.sm_share > 0 else max(1, sm_count // K))
 
     def new_pipe(sm_share):
@@ -579,7 +585,8 @@ def run_gpu_arm(args):
                        "parallelism": (f"frame-parallel x{world} GPUs, " if world > 1 else "single GPU, ") +
                                       f"{K} frames in flight per GPU",
                        "sm_count": sm_count, "host_cores": host_cores,
-                       "host_wait": ("spin", "blocking events", "poll + yield")[wait_mode]},
+                       "host_wait": ("spin", "blocking events", "poll + yield")[wait_mode],
+                       "host_threads_per_rank": replay_threads or K},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": frame_bytes * FRAMES_PER_STEP,
                     "d2h_bytes_per_step": int(e2e["d2h"] / args.steps), "ms_per_step": e2e["ms"] / args.steps,
                     "lines_per_frame": e2e["lines"] / n_frames_rank},
@@ -671,6 +678,11 @@ def run_c3(args):
     pinned = torch.from_numpy(frames).pin_memory()
     K, chunk = args.concurrency, 64
     capi.set_wait_mode(2 if K > 1 else 0)
+    try:
+        cores_per_rank = max(1, len(os.sched_getaffinity(0)) // world)
+    except AttributeError:
+        cores_per_rank = max(1, (os.cpu_count() or 1) // world)
+    capi.set_replay_threads(args.replay_threads if args.replay_threads >= 0 else min(K, max(2, min(4, cores_per_rank - 1))))
     replay = capi.Replay(K, args.sm_share if K > 1 else 0, GRANULARITY, synth.WINDOW, synth.LEAF, synth.OPT_DX, MINVOTES,
                          NLINES, n_pts, chunk)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -743,6 +755,9 @@ def main():
                     help="frames in flight per GPU (K pipelines, K host threads); 1 = lowest latency")
     ap.add_argument("--wait", choices=("auto", "spin", "block", "yield"), default="auto",
                     help="how the K host threads wait for the device (auto: poll + yield when frames are in flight)")
+    ap.add_argument("--replay-threads", type=int, default=-1,
+                    help="host threads per rank driving the frames in flight (-1: one per frame in flight while the "
+                         "box has the cores, fewer otherwise)")
     ap.add_argument("--sm-share", type=int, default=SM_SHARE, help="SMs per frame in flight (0: sm_count / concurrency)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10 s CPU sample (profiling runs)")
     ap.add_argument("--no-direction-sharded", action="store_true",

@@ -324,6 +324,10 @@ int h3d_replay_run(h3d_pipeline *const *pipes, size_t n_pipes, const float *cons
  * are in flight than the host has cores (several GPUs x frames in flight); 2 = poll an event and
  * yield the core between polls.  Process-wide; returns the previous setting. */
 int h3d_set_wait_mode(int mode);
+/* Host threads of h3d_replay_run*: 0 (default) = one per pipeline; 0 < n < pipelines = n threads, each driving
+ * several pipelines in split phase (submit a frame, poll, complete) -- for boxes with fewer host cores than
+ * ranks x pipelines (node.cpp has one callback thread; this is replay plumbing).  Returns the previous value. */
+int h3d_set_replay_threads(int n);
 
 /* same, also collecting the segment records of every frame (the pipelines must have
  * h3d_pipeline_enable_segments on): segments + i*max_segments, n_segments[i] (may exceed

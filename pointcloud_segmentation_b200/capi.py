@@ -642,6 +642,11 @@ class World:
         check(lib().h3d_world_save_csv(self._w, enc(segments_path), enc(intersections_path)))
 
 
+def set_replay_threads(n):
+    """host threads of a replay (0 = one per pipeline); returns the previous setting"""
+    return lib().h3d_set_replay_threads(C.c_int(n))
+
+
 def set_wait_mode(mode):
     """0: host threads spin on their stream (lowest latency); 1: they sleep on a blocking event;
     2: they poll an event and yield the core between polls."""

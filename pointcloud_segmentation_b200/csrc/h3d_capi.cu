@@ -959,6 +959,7 @@ struct FrameCtx {
 // latency), 1 = a blocking event (the thread sleeps: for more pipelines than host cores),
 // 2 = event polling with sched_yield between polls
 std::atomic<int> g_wait_mode{0};
+std::atomic<int> g_replay_threads{0};   // h3d_set_replay_threads
 
 cudaError_t frame_wait(FrameCtx &f) {
   cudaStream_t s = f.hg->stream;
@@ -1598,6 +1599,7 @@ struct FastPath {
   // host staging (pinned, mapped): [FrameDev][LoopState][iters][pool]; the segment records go to f.seg_host
   unsigned char *stage_host = nullptr, *stage_dev = nullptr;
   size_t off_st = 0, off_iters = 0, off_pool = 0, pool_entries = 0, stage_bytes = 0;
+  size_t sub_max_iters = 0;     // of the frame in flight (frame_submit_fast -> frame_complete_fast)
   void release() {
     cudaFree(occ); cudaFree(sorted); sorted = nullptr; cudaFree(tile_sums); cudaFree(fd_dev); cudaFreeHost(stage_host);
     occ = nullptr; tile_sums = nullptr; fd_dev = nullptr; stage_host = stage_dev = nullptr; on = false;
@@ -1660,9 +1662,10 @@ static int fast_path_setup(h3d_pipeline *p) {
 
 // One frame on the fast path.  *done = false: the frame did not qualify (FrameDev::status 2) and must be
 // re-run on the general path (the raw frame is still where it was).
-static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
-                          uint32_t *pool, size_t pool_cap, h3d_result *res, bool *done) {
-  *done = false;
+// The fast path in two halves, so that one host thread can keep several pipelines busy (replay_impl): the first
+// enqueues the whole frame on the pipeline's stream and returns, the second waits (unless the caller saw the
+// frame's last event complete) and copies the results out of the mapped staging area.
+static int frame_submit_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, size_t pool_cap) {
   FastPath &fp = p->fast;
   FrameCtx &f = p->f;
   h3d_hough *h = f.hg;
@@ -1772,7 +1775,19 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   H3D_CUDA(cudaGetLastError());
   note_launches(3);                       // K0 cluster, first vote, export (loop and post-tests count themselves)
   H3D_CUDA(cudaEventRecord(f.ev[3], s));
-  H3D_CUDA(frame_wait(f));                // the frame's only wait
+  fp.sub_max_iters = st_max_iters;
+  return H3D_OK;
+}
+
+static int frame_complete_fast(h3d_pipeline *p, h3d_iter *iters, uint32_t *pool, size_t pool_cap, h3d_result *res,
+                               bool *done, bool already_complete) {
+  *done = false;
+  FastPath &fp = p->fast;
+  FrameCtx &f = p->f;
+  h3d_hough *h = f.hg;
+  const HoughDev &hd = h->d;
+  const size_t st_max_iters = fp.sub_max_iters;
+  if (!already_complete) H3D_CUDA(frame_wait(f));   // the frame's only wait
   const FrameDev &F = *reinterpret_cast<const FrameDev *>(fp.stage_host);
   const LoopState &fin = *reinterpret_cast<const LoopState *>(fp.stage_host + fp.off_st);
   if (F.status == 2) return H3D_OK;       // *done stays false: the general path takes the frame
@@ -1794,6 +1809,13 @@ static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_
   if (n_pool && pool) memcpy(pool, fp.stage_host + fp.off_pool, n_pool * sizeof(unsigned));
   if (f.seg_on && n_rec) f.seg_n = n_rec < f.seg_grid ? n_rec : f.seg_grid;
   return H3D_OK;
+}
+
+static int frame_run_fast(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
+                          uint32_t *pool, size_t pool_cap, h3d_result *res, bool *done) {
+  *done = false;
+  H3D_TRY(frame_submit_fast(p, raw_dev, n, stride, pool_cap));
+  return frame_complete_fast(p, iters, pool, pool_cap, res, done, false);
 }
 
 // packs x,y,z of a PointCloud2 byte buffer into (x,y,z,0) float quadruples, message order
@@ -1842,37 +1864,23 @@ extern "C" void h3d_pipeline_destroy(h3d_pipeline *p) {
   delete p;
 }
 
-extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
-                                    uint32_t *pool, size_t pool_cap, h3d_result *res) {
-  if (!p || !res || (!raw_dev && n) || stride < 3) return fail(H3D_ERR_ARG, "bad argument");
-  if (n > p->cfg.max_raw_points) return fail(H3D_ERR_ARG, "frame larger than max_raw_points");
-  H3D_CUDA(cudaSetDevice(p->device));   // the calling thread may be a fresh one (current device 0)
-  memset(res, 0, sizeof *res);
+static void pipeline_fast_timing(FrameCtx &f) {
+  for (auto &u : f.us) u = 0.0f;
+  if (f.timed) {
+    cudaEventElapsedTime(&f.us[0], f.ev[0], f.ev[1]);   // pre-filter + prep + ctor (one cluster launch)
+    cudaEventElapsedTime(&f.us[1], f.ev[4], f.ev[2]);   // the first vote kernel alone (Hough::add)
+    cudaEventElapsedTime(&f.us[2], f.ev[2], f.ev[5]);   // the loop kernel
+    cudaEventElapsedTime(&f.us[3], f.ev[0], f.ev[3]);   // whole frame, results in host memory
+    for (auto &u : f.us) u *= 1000.0f;
+  }
+}
+
+// the general path of a frame: K0 kernels, widening, host-side Hough constructor, frame_run
+static int pipeline_run_general(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
+                                uint32_t *pool, size_t pool_cap, h3d_result *res) {
   FrameCtx &f = p->f;
-  f.timed = false;
   h3d_hough *h = f.hg;
   cudaStream_t s = h->stream;
-  H3D_CUDA(cudaEventRecord(f.ev[0], s));
-  p->fast.last_was_fast = false;
-  if (p->fast.on && g_use_fused && g_fast_frames.load(std::memory_order_relaxed) && n > 0) {
-    bool done = false;
-    const int rc_fast = frame_run_fast(p, raw_dev, n, stride, iters, pool, pool_cap, res, &done);
-    if (rc_fast != H3D_OK) return rc_fast;
-    if (done) {
-      for (auto &u : f.us) u = 0.0f;
-      if (f.timed) {
-        cudaEventElapsedTime(&f.us[0], f.ev[0], f.ev[1]);   // pre-filter + prep + ctor (one cluster launch)
-        cudaEventElapsedTime(&f.us[1], f.ev[4], f.ev[2]);   // the first vote kernel alone (Hough::add)
-        cudaEventElapsedTime(&f.us[2], f.ev[2], f.ev[5]);   // the loop kernel
-        cudaEventElapsedTime(&f.us[3], f.ev[0], f.ev[3]);   // whole frame, results in host memory
-        for (auto &u : f.us) u *= 1000.0f;
-      }
-      return H3D_OK;
-    }
-    memset(res, 0, sizeof *res);            // FrameDev::status 2: the general path takes the frame
-    f.timed = false;
-    H3D_CUDA(cudaEventRecord(f.ev[0], s));
-  }
   if (p->cfg.prefilter) {
     p->fast.count_clean = false;
     H3D_TRY(prefilter_phase1(p->pf, raw_dev, (int)n, (int)stride, p->win, p->cfg.leaf, h->dev.sm_count, s));
@@ -1896,6 +1904,79 @@ extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_
     for (auto &u : f.us) u *= 1000.0f;
   }
   return rc;
+}
+
+static bool pipeline_fast_eligible(const h3d_pipeline *p, size_t n) {
+  return p->fast.on && g_use_fused && g_fast_frames.load(std::memory_order_relaxed) && n > 0;
+}
+
+extern "C" int h3d_pipeline_run_dev(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
+                                    uint32_t *pool, size_t pool_cap, h3d_result *res) {
+  if (!p || !res || (!raw_dev && n) || stride < 3) return fail(H3D_ERR_ARG, "bad argument");
+  if (n > p->cfg.max_raw_points) return fail(H3D_ERR_ARG, "frame larger than max_raw_points");
+  H3D_CUDA(cudaSetDevice(p->device));   // the calling thread may be a fresh one (current device 0)
+  memset(res, 0, sizeof *res);
+  FrameCtx &f = p->f;
+  f.timed = false;
+  cudaStream_t s = f.hg->stream;
+  H3D_CUDA(cudaEventRecord(f.ev[0], s));
+  p->fast.last_was_fast = false;
+  if (pipeline_fast_eligible(p, n)) {
+    bool done = false;
+    const int rc_fast = frame_run_fast(p, raw_dev, n, stride, iters, pool, pool_cap, res, &done);
+    if (rc_fast != H3D_OK) return rc_fast;
+    if (done) { pipeline_fast_timing(f); return H3D_OK; }
+    memset(res, 0, sizeof *res);            // FrameDev::status 2: the general path takes the frame
+    f.timed = false;
+    H3D_CUDA(cudaEventRecord(f.ev[0], s));
+  }
+  return pipeline_run_general(p, raw_dev, n, stride, iters, pool, pool_cap, res);
+}
+
+// ---- split-phase form for the replay: submit a frame, later complete it ------------------------------------
+// *async = false: the pipeline does not qualify for the fast path; the caller runs the frame synchronously.
+static int pipeline_submit(h3d_pipeline *p, const float *raw, int on_device, size_t n, size_t stride, size_t pool_cap,
+                           const float **raw_dev_out, bool *async) {
+  *async = false;
+  if (!p || (!raw && n) || stride < 3) return fail(H3D_ERR_ARG, "bad argument");
+  if (n > p->cfg.max_raw_points) return fail(H3D_ERR_ARG, "frame larger than max_raw_points");
+  if (!on_device && n * stride > p->raw_cap_floats) return fail(H3D_ERR_ARG, "frame larger than the pipeline's raw buffer");
+  if (!pipeline_fast_eligible(p, n)) return H3D_OK;
+  H3D_CUDA(cudaSetDevice(p->device));
+  FrameCtx &f = p->f;
+  cudaStream_t s = f.hg->stream;
+  const float *raw_dev = raw;
+  if (!on_device) {
+    H3D_CUDA(cudaMemcpyAsync(p->raw_dev, raw, n * stride * sizeof(float), cudaMemcpyHostToDevice, s));
+    raw_dev = p->raw_dev;
+  }
+  *raw_dev_out = raw_dev;
+  f.timed = false;
+  H3D_CUDA(cudaEventRecord(f.ev[0], s));
+  p->fast.last_was_fast = false;
+  H3D_TRY(frame_submit_fast(p, raw_dev, n, stride, pool_cap));
+  *async = true;
+  return H3D_OK;
+}
+
+// 0: still running; 1: the frame's last event has completed; -1: the query failed (the completion's wait reports it)
+static int pipeline_ready(h3d_pipeline *p) {
+  const cudaError_t e = cudaEventQuery(p->f.ev[3]);
+  return e == cudaErrorNotReady ? 0 : e == cudaSuccess ? 1 : -1;
+}
+
+static int pipeline_complete(h3d_pipeline *p, const float *raw_dev, size_t n, size_t stride, h3d_iter *iters,
+                             uint32_t *pool, size_t pool_cap, h3d_result *res, bool already_complete) {
+  H3D_CUDA(cudaSetDevice(p->device));
+  memset(res, 0, sizeof *res);
+  FrameCtx &f = p->f;
+  bool done = false;
+  H3D_TRY(frame_complete_fast(p, iters, pool, pool_cap, res, &done, already_complete));
+  if (done) { pipeline_fast_timing(f); return H3D_OK; }
+  memset(res, 0, sizeof *res);              // FrameDev::status 2: the general path takes the frame
+  f.timed = false;
+  H3D_CUDA(cudaEventRecord(f.ev[0], f.hg->stream));
+  return pipeline_run_general(p, raw_dev, n, stride, iters, pool, pool_cap, res);
 }
 
 extern "C" int h3d_pipeline_run(h3d_pipeline *p, const float *raw, size_t n, size_t stride, h3d_iter *iters,
@@ -2153,14 +2234,93 @@ static int replay_impl(h3d_pipeline *const *pipes, size_t n_pipes, const float *
       }
     }
   };
+  // Fewer host threads than pipelines (h3d_set_replay_threads; several ranks on a box with few cores): thread t
+  // drives pipelines t, t + T, ...  It submits a frame on each (the fast path enqueues a whole frame without
+  // waiting), then polls their last events and completes / refills whichever is done.
+  auto report = [&](int rc) {
+    int expected = H3D_OK;
+    if (first_rc.compare_exchange_strong(expected, rc)) {
+      std::lock_guard<std::mutex> lock(err_mu);
+      err_text = h3d_last_error();
+    }
+  };
+  auto worker_mux = [&](size_t t, size_t T) {
+    struct Slot { h3d_pipeline *p; size_t frame; const float *raw_dev; bool busy; };
+    std::vector<Slot> slots;
+    for (size_t q = t; q < n_pipes; q += T) slots.push_back(Slot{pipes[q], 0, nullptr, false});
+    size_t active = 0;
+    bool feed = true;
+    auto finish = [&](Slot &sl, size_t i) -> int {   // what follows a frame's results
+      if (!segments) return H3D_OK;
+      size_t m = 0;
+      int ref = 0;
+      const int rc = h3d_pipeline_segments(sl.p, segments + i * max_segments, max_segments, &m, &ref);
+      n_segments[i] = (uint32_t)m;
+      if (rc_ref) rc_ref[i] = ref;
+      return rc;
+    };
+    auto refill = [&](Slot &sl) -> int {
+      while (feed) {
+        const size_t i = next.fetch_add(1);
+        if (i >= n_frames || first_rc.load() != H3D_OK) { feed = false; break; }
+        h3d_iter *it = iters ? iters + i * max_iters : nullptr;
+        uint32_t *pl = pool ? pool + i * pool_cap : nullptr;
+        if (poses) h3d_pipeline_set_pose(sl.p, &poses[i]);
+        bool async = false;
+        int rc = pipeline_submit(sl.p, raw[i], frames_on_device, n_points[i], stride, pool ? pool_cap : 0, &sl.raw_dev, &async);
+        if (rc != H3D_OK) return rc;
+        if (async) { sl.frame = i; sl.busy = true; ++active; return H3D_OK; }
+        rc = frames_on_device
+                 ? h3d_pipeline_run_dev(sl.p, raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i])
+                 : h3d_pipeline_run(sl.p, raw[i], n_points[i], stride, it, pl, pool ? pool_cap : 0, &results[i]);
+        if (rc == H3D_OK) rc = finish(sl, i);
+        if (rc != H3D_OK) return rc;
+      }
+      return H3D_OK;
+    };
+    int rc = H3D_OK;
+    for (auto &sl : slots) if ((rc = refill(sl)) != H3D_OK) break;
+    const bool spin = g_wait_mode.load(std::memory_order_relaxed) == 0;
+    while (rc == H3D_OK && active) {
+      bool progressed = false;
+      for (auto &sl : slots) {
+        if (!sl.busy) continue;
+        const int ready = pipeline_ready(sl.p);
+        if (ready == 0) continue;
+        const size_t i = sl.frame;
+        sl.busy = false; --active; progressed = true;
+        rc = pipeline_complete(sl.p, sl.raw_dev, n_points[i], stride, iters ? iters + i * max_iters : nullptr,
+                               pool ? pool + i * pool_cap : nullptr, pool ? pool_cap : 0, &results[i], ready == 1);
+        if (rc == H3D_OK) rc = finish(sl, i);
+        if (rc == H3D_OK) rc = refill(sl);
+        if (rc != H3D_OK) break;
+      }
+      if (!progressed && !spin) std::this_thread::yield();
+    }
+    if (rc != H3D_OK) {
+      report(rc);
+      for (auto &sl : slots) if (sl.busy) cudaStreamSynchronize(sl.p->f.hg->stream);   // nothing left in flight
+    }
+  };
+  size_t T = (size_t)g_replay_threads.load(std::memory_order_relaxed);
   std::vector<std::thread> threads;
-  threads.reserve(n_pipes);
-  for (size_t t = 1; t < n_pipes; ++t) threads.emplace_back(worker, t);
-  worker(0);
+  if (T == 0 || T >= n_pipes) {
+    threads.reserve(n_pipes);
+    for (size_t t = 1; t < n_pipes; ++t) threads.emplace_back(worker, t);
+    worker(0);
+  } else {
+    threads.reserve(T);
+    for (size_t t = 1; t < T; ++t) threads.emplace_back(worker_mux, t, T);
+    worker_mux(0, T);
+  }
   for (auto &th : threads) th.join();
   if (first_rc.load() != H3D_OK) { set_error(err_text); return first_rc.load(); }
   return H3D_OK;
 }
+
+// Host threads of a replay: 0 = one per pipeline (default); n < pipelines = n threads, each driving several
+// pipelines (for boxes with fewer cores than ranks x pipelines).  Returns the previous setting.
+extern "C" int h3d_set_replay_threads(int n) { return g_replay_threads.exchange(n > 0 ? n : 0); }
 
 extern "C" int h3d_set_wait_mode(int mode) {
   return g_wait_mode.exchange(mode == 1 ? 1 : mode == 2 ? 2 : 0);

@@ -129,6 +129,43 @@ def test_oversubscribed_replay_matches_the_reference(h3d, tof, fused, on_device,
         rp.close()
 
 
+@pytest.mark.parametrize("threads", [3, 8, 15])
+@pytest.mark.parametrize("on_device", [False, True])
+def test_multiplexed_replay_matches_the_reference(h3d, tof, threads, on_device):
+    """16 pipelines x 9 SMs driven by FEWER host threads (h3d_set_replay_threads: each thread submits frames on its
+    pipelines, polls their last events and completes / refills whichever is done): every frame's trace equals the
+    reference's; with h3d_set_fast_frames(0) the same workers take the synchronous path"""
+    import torch
+    frames, want, (g, minvotes, nlines), src = tof
+    n_frames = 64
+    n_pts, stride = frames[0].shape
+    stack = torch.from_numpy(np.stack(frames)).pin_memory()
+    dev = stack.cuda() if on_device else None
+    ptrs = [(dev if on_device else stack)[k % len(frames)].data_ptr() for k in range(n_frames)]
+    rp = h3d.Replay(16, 9, g, synth.WINDOW, synth.LEAF, synth.OPT_DX, minvotes, nlines, n_pts, n_frames)
+    old_poison = h3d.set_debug_poison(1)
+    old_threads = h3d.set_replay_threads(threads)
+    try:
+        for fast in (1, 0):
+            h3d.set_fast_frames(fast)
+            for mode in ((0, 2) if fast else (2,)):
+                h3d.set_wait_mode(mode)
+                for rep in range(2 if fast else 1):
+                    res = rp.run(ptrs, [n_pts] * n_frames, stride, on_device=on_device)
+                    torch.cuda.synchronize()
+                    for k in range(n_frames):
+                        its = rp.iters[k * rp.max_iters:(k + 1) * rp.max_iters]
+                        pool = rp.pool[k * rp.pool_cap:(k + 1) * rp.pool_cap]
+                        _same(_digest(h3d.Trace(res[k], its, pool)), want[k % len(frames)],
+                              f"frame {k} threads={threads} fast={fast} wait={mode} rep={rep} on_device={on_device} ({src})")
+    finally:
+        h3d.set_wait_mode(0)
+        h3d.set_fast_frames(1)
+        h3d.set_replay_threads(old_threads)
+        h3d.set_debug_poison(old_poison)
+        rp.close()
+
+
 @pytest.mark.parametrize("key", ["synthetic_b_g5", "testdata_g6", "attpc_c_g6"])
 def test_reference_fixtures_at_g5_g6(h3d, key):
     """the reference's own fixtures at granularity 5 and 6: full traces recorded from oracle/_ref"""

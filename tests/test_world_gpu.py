@@ -58,6 +58,17 @@ def test_replay_world_matches_oracle_chain(h3d, oracle, oracle_mod, tmp_path):
     rep.run_world([f.ctypes.data for f in frames], [f.shape[0] for f in frames], frames[0].shape[1], False,
                   [_pose(h3d, p) for p in poses], world)
     _same_world(world, want)
+    # the same replay with two host threads for the three pipelines (split-phase workers): poses and segment
+    # records must follow their frames
+    old_threads = h3d.set_replay_threads(2)
+    try:
+        world_mux = h3d.World(DIAG, MIN_W)
+        rep.run_world([f.ctypes.data for f in frames], [f.shape[0] for f in frames], frames[0].shape[1], False,
+                      [_pose(h3d, p) for p in poses], world_mux)
+        _same_world(world_mux, want)
+        world_mux.close()
+    finally:
+        h3d.set_replay_threads(old_threads)
     seg_csv, int_csv = tmp_path / "segments.csv", tmp_path / "intersections.csv"
     world.save_csv(str(seg_csv), str(int_csv))
     assert (seg_csv.read_text(), int_csv.read_text()) == want.csv()
