@@ -41,7 +41,11 @@ os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-FRAMES_PER_STEP = 64          # frames per step: 4 passes over DISTINCT_FRAMES different frames
+FRAMES_PER_STEP = int(os.environ.get("H3D_FRAMES_PER_STEP", "256"))   # frames per step: 16 passes over the DISTINCT_FRAMES frames.
+                              # Every step ends by draining the pipelines (the last frames run with idle SMs beside
+                              # them); with 64 frames = 4 per pipeline that tail was worth 13 % of the step and
+                              # depended on the ORDER of the frames (measured: the same frames rotated by 5 on a
+                              # second rank ran 13 % slower than the heaviest-first order of rank 0)
 DISTINCT_FRAMES = 16
 FRAMES_IN_FLIGHT = 16          # pipelines (host threads) per GPU ...
 SM_SHARE = 9                   # ... each limited to this many SMs for its vote and persistent loop kernels
@@ -116,7 +120,7 @@ class ClockSampler:
 
 
 def check_against_golden(frames, lines):
-    """rank 0's frames are the ones tests/golden/reference_golden_g56.npz holds reference traces of (recorded
+    """the bench frames are the ones tests/golden/reference_golden_g56.npz holds reference traces of (recorded
     from oracle/_ref by tests/golden/make_golden_g56.py): compare the per-frame line counts when the raw frames
     regenerated here are bit-identical to the recorded ones."""
     path = os.path.join(ROOT, "tests", "golden", "reference_golden_g56.npz")
@@ -349,9 +353,18 @@ def run_gpu_arm(args):
         raise SystemExit("bench.py needs a CUDA device: libh3d.so has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        if os.environ.get("H3D_BENCH_BACKEND") == "gloo":      # experiment switch (tools/): plumbing without NCCL
+            dist.init_process_group("gloo")
+        elif os.environ.get("H3D_BENCH_BACKEND") == "nccl-lazy":
+            dist.init_process_group("nccl")
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    frames = make_frames(DISTINCT_FRAMES, rank)
+    # every rank replays the SAME 16 frames in the same order (weak scaling: per-GPU work fixed as N grows; with a
+    # frame set or an order of its own per rank the slowest rank's drain tail set the step time: 0.89 "efficiency"
+    # at N = 2 that was data, not the machine -- profiles/r02_n2_efficiency_experiments.txt)
+    frames = make_frames(DISTINCT_FRAMES, 0)
+    rot = 0
     n_pts, stride = frames.shape[1], frames.shape[2]
     pinned = torch.from_numpy(frames).pin_memory()
     on_dev = pinned.cuda()
@@ -390,8 +403,8 @@ def run_gpu_arm(args):
     # frame's loop is latency-bound, so the GPU is filled with frames in flight
     replay = capi.Replay(K, share, GRANULARITY, synth.WINDOW, synth.LEAF, synth.OPT_DX, MINVOTES, NLINES, n_pts,
                          FRAMES_PER_STEP)
-    host_ptrs = [pinned[k % DISTINCT_FRAMES].data_ptr() for k in range(FRAMES_PER_STEP)]
-    dev_ptrs = [on_dev[k % DISTINCT_FRAMES].data_ptr() for k in range(FRAMES_PER_STEP)]
+    host_ptrs = [pinned[(k + rot) % DISTINCT_FRAMES].data_ptr() for k in range(FRAMES_PER_STEP)]
+    dev_ptrs = [on_dev[(k + rot) % DISTINCT_FRAMES].data_ptr() for k in range(FRAMES_PER_STEP)]
     counts = [n_pts] * FRAMES_PER_STEP
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
@@ -415,7 +428,7 @@ def run_gpu_arm(args):
         want_digest.append(frame_digest(r, ctypes.addressof(ref_pipe.iters), ref_pipe.pool, 0, ref_pipe.max_iters))
         want_lines.append(int(r.n_lines))
     ref_pipe.close()
-    golden = check_against_golden(frames, want_lines) if rank == 0 else None
+    golden = check_against_golden(frames, want_lines)   # every rank holds the golden frames
 
     def one_step(e2e):
         """one batch of FRAMES_PER_STEP frames over the K pipelines; device time of the whole batch (ms)"""
@@ -436,7 +449,7 @@ def run_gpu_arm(args):
             # parity inside the timed legs: the frame's complete result against the one-pipeline run of the same frame
             got = frame_digest(r, base + k * replay.max_iters * iter_bytes, replay.pool, k * replay.pool_cap, replay.max_iters)
             out["checked"] += 1
-            out["mismatches"] += got != want_digest[k % DISTINCT_FRAMES]
+            out["mismatches"] += got != want_digest[(k + rot) % DISTINCT_FRAMES]
         out["ms"] = ev0.elapsed_time(ev1)
         return out
 
@@ -556,7 +569,8 @@ def run_gpu_arm(args):
             sharded = {"error": f"{type(exc).__name__}: {exc}"}
     n_frames_rank = FRAMES_PER_STEP * args.steps
     total_frames = n_frames_rank * world
-    parity = torch.tensor([dev["checked"] + e2e["checked"], dev["mismatches"] + e2e["mismatches"]],
+    golden_bad = int(golden.get("line_count_mismatches", 0)) if isinstance(golden, dict) else 0   # this rank's GPU vs the reference's line counts
+    parity = torch.tensor([dev["checked"] + e2e["checked"], dev["mismatches"] + e2e["mismatches"] + golden_bad],
                           dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(parity, op=dist.ReduceOp.SUM)
