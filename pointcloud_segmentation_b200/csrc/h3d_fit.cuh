@@ -251,10 +251,14 @@ __device__ __forceinline__ float tree32_combine(float acc) {
 
 // meanValue of axis values get(k) (k = 0..n-1 in cloud order) by one warp: the reference's
 // sequential double sum, via the exact int64 route when it is provably identical
-template <class GetAxis>
+// U: batches of 32 values fetched together (U loads in flight per lane).  1 when get() reads shared memory; 8 when it
+// reads global memory: with one batch of look-ahead every batch of the chain waited for an L2 round trip (~0.35 us),
+// 202 us per call for the 11 k inliers of a configs[3] line (ncu launch list, round 2).
+template <int U = 1, class GetAxis>
 __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
   int lo = 0x7FFFFFFF, hi = -0x7FFFFFFF;
   bool bad = false;
+#pragma unroll U
   for (int k = lane; k < n; k += 32) {
     const long long bits = __double_as_longlong(get(k));
     const int e = (int)((bits >> 52) & 0x7FF);
@@ -274,6 +278,7 @@ __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
   } else if (!bad && hi + 1 - lo + (32 - __clz(n)) <= 53 && lo > -900 && hi < 900) {
     const double scale = __longlong_as_double((long long)(1023 - lo) << 52);   // 2^-lo
     long long acc = 0;
+#pragma unroll U
     for (int k = lane; k < n; k += 32) acc += __double2ll_rn(__dmul_rn(get(k), scale));
 #pragma unroll
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
@@ -293,40 +298,91 @@ __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
     // S + sum is the chain's result bit for bit.  Otherwise (binade crossings, ~log2(n) of them, the first
     // batches, sums near zero) this batch runs the chain.  ~45 instructions instead of 32 dependent DADDs.
     sum = 0.0;
-    double cur = lane < n ? get(lane) : 0.0;
-    for (int k0 = 0; k0 < n; k0 += 32) {
-      const int kn = k0 + 32 + lane;
-      const double nxt = kn < n ? get(kn) : 0.0;
-      const int m = n - k0 < 32 ? n - k0 : 32;
-      bool done = false;
-      const int es = (int)((__double_as_longlong(sum) >> 52) & 0x7FF);      // biased exponent of S (uniform)
-      if (es > 100 && es < 1900) {
-        const double inv_u = __longlong_as_double((long long)(1023 + 52 + 1023 - es) << 52);   // 2^(52-e)
-        const double q = __dmul_rn(cur, inv_u);                              // exact: a power of two, no underflow
-        const double r = rint(q);                                            // lanes >= m hold 0
-        // |q| < 2^60 (int64 range; also rejects Inf/NaN), not a tie (q - r is exact).  A q that underflows
-        // is far below 1/2 and rounds to 0, as the chain's addition does.
-        const bool lane_ok = fabs(q) < 1152921504606846976.0 && fabs(__dsub_rn(q, r)) != 0.5;
-        long long pj = (long long)r;
+    double buf[U];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const long long up = __shfl_up_sync(0xFFFFFFFFu, pj, o);
-          if (lane >= o) pj += up;
-        }
-        pj += (long long)__dmul_rn(sum, inv_u);                              // S/u: an integer in (2^52, 2^53)
-        const long long mag = pj < 0 ? -pj : pj;
-        const bool inside = mag > 4503599627370496LL && mag < 9007199254740992LL;
-        if (__all_sync(0xFFFFFFFFu, lane_ok && inside)) {
-          const long long last = __shfl_sync(0xFFFFFFFFu, pj, 31);
-          sum = __dmul_rn((double)last, __longlong_as_double((long long)(es - 52) << 52));   // P * u, exact
-          done = true;
+    for (int u = 0; u < U; ++u) { const int k = u * 32 + lane; buf[u] = k < n ? get(k) : 0.0; }
+    for (int k0 = 0; k0 < n; k0 += 32 * U) {
+      double nbuf[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) { const int k = k0 + (U + u) * 32 + lane; nbuf[u] = k < n ? get(k) : 0.0; }
+      // U batches at once under the same argument: if all 32*U partial sums stay strictly inside the binade S is
+      // in when the group starts (and no value is a tie), the whole chain through the group had spacing u.  The U
+      // warp scans are independent (one batch at a time, each batch waited for the previous one's S: ~400 cycles of
+      // dependent conversions, shuffles and a vote per batch, 70 us for 11 k values).
+      bool group_done = false;
+      if (U > 1) {
+        const int es = (int)((__double_as_longlong(sum) >> 52) & 0x7FF);
+        if (es > 100 && es < 1900) {
+          const double inv_u = __longlong_as_double((long long)(1023 + 52 + 1023 - es) << 52);
+          long long pj[U];
+          bool ok = true;
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const double q = __dmul_rn(buf[u], inv_u), r = rint(q);
+            ok = ok && fabs(q) < 1152921504606846976.0 && fabs(__dsub_rn(q, r)) != 0.5;
+            pj[u] = (long long)r;
+          }
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const long long up = __shfl_up_sync(0xFFFFFFFFu, pj[u], o);
+              if (lane >= o) pj[u] += up;
+            }
+          }
+          long long tot[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) tot[u] = __shfl_sync(0xFFFFFFFFu, pj[u], 31);
+          long long base = (long long)__dmul_rn(sum, inv_u);                   // S/u: an integer in (2^52, 2^53)
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const long long v = pj[u] + base, mag = v < 0 ? -v : v;
+            ok = ok && mag > 4503599627370496LL && mag < 9007199254740992LL;
+            base += tot[u];
+          }
+          if (__all_sync(0xFFFFFFFFu, ok)) {
+            sum = __dmul_rn((double)base, __longlong_as_double((long long)(es - 52) << 52));   // P * u, exact
+            group_done = true;
+          }
         }
       }
-      if (!done) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int kb = k0 + u * 32;
+        if (group_done || kb >= n) break;                                      // uniform
+        const double cur = buf[u];
+        const int m = n - kb < 32 ? n - kb : 32;
+        bool done = false;
+        const int es = (int)((__double_as_longlong(sum) >> 52) & 0x7FF);      // biased exponent of S (uniform)
+        if (es > 100 && es < 1900) {
+          const double inv_u = __longlong_as_double((long long)(1023 + 52 + 1023 - es) << 52);   // 2^(52-e)
+          const double q = __dmul_rn(cur, inv_u);                              // exact: a power of two, no underflow
+          const double r = rint(q);                                            // lanes >= m hold 0
+          // |q| < 2^60 (int64 range; also rejects Inf/NaN), not a tie (q - r is exact).  A q that underflows
+          // is far below 1/2 and rounds to 0, as the chain's addition does.
+          const bool lane_ok = fabs(q) < 1152921504606846976.0 && fabs(__dsub_rn(q, r)) != 0.5;
+          long long pj = (long long)r;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const long long up = __shfl_up_sync(0xFFFFFFFFu, pj, o);
+            if (lane >= o) pj += up;
+          }
+          pj += (long long)__dmul_rn(sum, inv_u);                              // S/u: an integer in (2^52, 2^53)
+          const long long mag = pj < 0 ? -pj : pj;
+          const bool inside = mag > 4503599627370496LL && mag < 9007199254740992LL;
+          if (__all_sync(0xFFFFFFFFu, lane_ok && inside)) {
+            const long long last = __shfl_sync(0xFFFFFFFFu, pj, 31);
+            sum = __dmul_rn((double)last, __longlong_as_double((long long)(es - 52) << 52));   // P * u, exact
+            done = true;
+          }
+        }
+        if (!done) {
 #pragma unroll 4
-        for (int j = 0; j < m; ++j) sum = __dadd_rn(sum, __shfl_sync(0xFFFFFFFFu, cur, j));
+          for (int j = 0; j < m; ++j) sum = __dadd_rn(sum, __shfl_sync(0xFFFFFFFFu, cur, j));
+        }
       }
-      cur = nxt;
+#pragma unroll
+      for (int u = 0; u < U; ++u) buf[u] = nbuf[u];
     }
   }
   return n > 0 ? __ddiv_rn(sum, (double)n) : sum;
@@ -349,7 +405,7 @@ __device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *ou
       if (lane == 0) s.mean[q] = __fdiv_rn(acc, (float)n);
     } else {                          // meanValue (lib/pointcloud.cpp:29-38)
       const int c = q - 3;
-      const double m = mean_axis_warp([&](int k) { return get(k, c); }, n, lane);
+      const double m = mean_axis_warp<8>([&](int k) { return get(k, c); }, n, lane);
       if (lane == 0) out->a[c] = m;
     }
   }
