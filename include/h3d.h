@@ -465,6 +465,9 @@ int h3d_set_debug_poison(int on);
  * 1 = projection math only (no shared atomics), 2 = shared atomics only;
  * bits 8..15 of `ablate` optionally give the directions per work item (1,2,4; 0 = automatic: register-resident points when they fit). */
 int h3d_bench_vote(h3d_hough *h, int reps, int ablate, float *us_per_launch);
+/* one orthogonal_LSQ call (wrap.h:121-150) on a host cloud: device time of its phases in microseconds
+ * (us[0] means incl. the sequential anchor, us[1] scatter sums, us[2] eigen-solve), globaltimer stamps */
+int h3d_bench_lsq(const double *xyz, size_t n, float us[3]);
 
 #ifdef __cplusplus
 }

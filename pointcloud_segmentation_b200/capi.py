@@ -535,6 +535,14 @@ def remove_points(x, y):
     return xa[: n_out.value].copy()
 
 
+def bench_lsq(xyz):
+    """device time (us) of the phases of one orthogonal_LSQ call: means (incl. the sequential anchor), scatter sums, eig"""
+    a, p, n = _pts(xyz)
+    us = (C.c_float * 3)()
+    check(lib().h3d_bench_lsq(p, n, us))
+    return list(us)
+
+
 def orthogonal_lsq(xyz):
     a, p, n = _pts(xyz)
     aa, bb, rc = (C.c_double * 3)(), (C.c_double * 3)(), C.c_double()
