@@ -258,24 +258,34 @@ template <int U = 1, class GetAxis>
 __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
   int lo = 0x7FFFFFFF, hi = -0x7FFFFFFF;
   bool bad = false;
-#pragma unroll U
-  for (int k = lane; k < n; k += 32) {
-    const long long bits = __double_as_longlong(get(k));
-    const int e = (int)((bits >> 52) & 0x7FF);
-    const long long mant = bits & 0xFFFFFFFFFFFFFLL;
-    if (e == 0x7FF || (e == 0 && mant != 0)) bad = true;          // Inf/NaN/subnormal: sequential path
-    else if (e != 0) {
-      lo = min(lo, e - 1075 + (__ffsll(mant | 0x10000000000000LL) - 1));
-      hi = max(hi, e - 1023);
+  const int nbits = 32 - __clz(n);
+  // The exact-int64 route needs hi + 1 - lo + bits(n) <= 53 over ALL values; lo only falls and hi only rises, so
+  // the scan stops at the first group of 32*U values that already rules the route out (doubles with full
+  // mantissas do so at once: the scan was a quarter of the kernel's time for nothing).
+  for (int k0 = 0; k0 < n && !bad; k0 += 32 * U) {
+    double v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) { const int k = k0 + u * 32 + lane; v[u] = k < n ? get(k) : 0.0; }   // loads together
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long bits = __double_as_longlong(v[u]);
+      const int e = (int)((bits >> 52) & 0x7FF);
+      const long long mant = bits & 0xFFFFFFFFFFFFFLL;
+      if (e == 0x7FF || (e == 0 && mant != 0)) bad = true;          // Inf/NaN/subnormal: sequential path
+      else if (e != 0) {                                            // (+-0, also the padding of the last group: no constraint)
+        lo = min(lo, e - 1075 + (__ffsll(mant | 0x10000000000000LL) - 1));
+        hi = max(hi, e - 1023);
+      }
     }
+    const int glo = __reduce_min_sync(0xFFFFFFFFu, lo), ghi = __reduce_max_sync(0xFFFFFFFFu, hi);
+    bad = __any_sync(0xFFFFFFFFu, bad) || (glo != 0x7FFFFFFF && !(ghi + 1 - glo + nbits <= 53 && glo > -900 && ghi < 900));
   }
   lo = __reduce_min_sync(0xFFFFFFFFu, lo);
   hi = __reduce_max_sync(0xFFFFFFFFu, hi);
-  bad = __any_sync(0xFFFFFFFFu, bad);
   double sum;
   if (lo == 0x7FFFFFFF && !bad) {
     sum = 0.0;                                                     // all zero (or n == 0)
-  } else if (!bad && hi + 1 - lo + (32 - __clz(n)) <= 53 && lo > -900 && hi < 900) {
+  } else if (!bad && hi + 1 - lo + nbits <= 53 && lo > -900 && hi < 900) {
     const double scale = __longlong_as_double((long long)(1023 - lo) << 52);   // 2^-lo
     long long acc = 0;
 #pragma unroll U
@@ -388,36 +398,57 @@ __device__ __forceinline__ double mean_axis_warp(GetAxis get, int n, int lane) {
   return n > 0 ? __ddiv_rn(sum, (double)n) : sum;
 }
 
-// get(k, c): coordinate c of the k-th point of the cloud.  blockDim.x a multiple of 32; all
-// threads of the CTA call it; ends with a barrier (out and s are shared memory).
-template <class Get>
-__device__ __forceinline__ void lsq_cta(Get get, int n, LsqShared &s, LsqOut *out, unsigned long long *dbg = nullptr) {
+// x, y, z: the cloud's coordinate arrays (n values each, global memory).  blockDim.x a multiple of 32; all threads
+// of the CTA call it; ends with a barrier (out and s are shared memory).
+// The axis of a task is picked ONCE, outside the loops: with an accessor get(k, c) and a run-time c the compiler
+// turned the choice of the array into branches inside the loop body, the loads of an unrolled body could no
+// longer be issued together, and every element paid its own L2 round trip (ncu SASS, round 2: the scatter sums
+// took 124 us for 11 k points, 700 cycles per element).
+// stage / cap: shared memory for 3 * cap floats (nullptr / 0: none).  The warps that sum the float columns keep
+// the converted values of the first `cap` points there, and the six scatter sums read them back instead of
+// converting every coordinate four more times inside their dependent chains (F2F.F32.F64 on inexact values
+// made those chains 3x slower than on float-exact data: 78 vs 38 us for 11 k points, tools/lsq_bench.py).
+constexpr int kLsqStageCap = 16384;
+__device__ __forceinline__ void lsq_cta(const double *__restrict__ x, const double *__restrict__ y,
+                                        const double *__restrict__ z, int n, LsqShared &s, LsqOut *out,
+                                        unsigned long long *dbg = nullptr, float *stage = nullptr, int cap = 0) {
   auto dbg_stamp = [&](int k) {
-    if (dbg && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); dbg[k] = t; }
+    if (dbg && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t) : : "memory"); dbg[k] = t; }
   };
+  auto axis = [&](int c) { return c == 0 ? x : c == 1 ? y : z; };
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   for (int q = warp; q < 6; q += nwarps) {
     if (q < 3) {                      // colwise().mean() of the float copy (wrap.h:129-137)
+      const double *__restrict__ p = axis(q);
+      const int ns = n < cap ? n : cap;          // staged part (a multiple of 32 or all of n: lane order is kept)
+      float *__restrict__ sq = stage + (size_t)q * cap;
       float acc = 0.0f;
 #pragma unroll 8
-      for (int k = lane; k < n; k += 32) acc = __fadd_rn(acc, (float)get(k, q));   // loads run ahead of the chain
+      for (int k = lane; k < ns; k += 32) { const float v = (float)p[k]; sq[k] = v; acc = __fadd_rn(acc, v); }
+#pragma unroll 8
+      for (int k = ns + lane; k < n; k += 32) acc = __fadd_rn(acc, (float)p[k]);   // loads run ahead of the chain
       acc = tree32_combine(acc);
       if (lane == 0) s.mean[q] = __fdiv_rn(acc, (float)n);
     } else {                          // meanValue (lib/pointcloud.cpp:29-38)
-      const int c = q - 3;
-      const double m = mean_axis_warp<8>([&](int k) { return get(k, c); }, n, lane);
-      if (lane == 0) out->a[c] = m;
+      const double *__restrict__ p = axis(q - 3);
+      const double m = mean_axis_warp<8>([&](int k) { return p[k]; }, n, lane);
+      if (lane == 0) out->a[q - 3] = m;
     }
   }
   __syncthreads();
   dbg_stamp(0);
   for (int q = warp; q < 6; q += nwarps) {   // centred^T * centred (wrap.h:137-138)
     const int c0 = q < 3 ? 0 : q < 5 ? 1 : 2, c1 = q < 3 ? q : q < 5 ? q - 2 : 2;
+    const double *__restrict__ p0 = axis(c0), *__restrict__ p1 = axis(c1);
     const float m0 = s.mean[c0], m1 = s.mean[c1];
+    const int ns = n < cap ? n : cap;
+    const float *__restrict__ s0 = stage + (size_t)c0 * cap, *__restrict__ s1 = stage + (size_t)c1 * cap;
     float acc = 0.0f;
 #pragma unroll 8
-    for (int k = lane; k < n; k += 32)
-      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn((float)get(k, c0), m0), __fsub_rn((float)get(k, c1), m1)));
+    for (int k = lane; k < ns; k += 32) acc = __fadd_rn(acc, __fmul_rn(__fsub_rn(s0[k], m0), __fsub_rn(s1[k], m1)));
+#pragma unroll 8
+    for (int k = ns + lane; k < n; k += 32)
+      acc = __fadd_rn(acc, __fmul_rn(__fsub_rn((float)p0[k], m0), __fsub_rn((float)p1[k], m1)));
     acc = tree32_combine(acc);
     if (lane == 0) s.sc[q] = acc;
   }

@@ -221,7 +221,8 @@ __global__ void __launch_bounds__(192, 1) loop_lsq_kernel(const HoughDev h, Loop
     if (threadIdx.x == 0) { if (r) r->status = 2; s.n_iters++; s.done = 1; }
     return;
   }
-  lsq_cta([&](int k, int c) { return (c == 0 ? lb.ypx : c == 1 ? lb.ypy : lb.ypz)[k]; }, s.ny, sh, &out);   // compact Y
+  extern __shared__ __align__(16) float lsq_stage[];   // 3 * kLsqStageCap floats
+  lsq_cta(lb.ypx, lb.ypy, lb.ypz, s.ny, sh, &out, nullptr, lsq_stage, kLsqStageCap);   // compact Y
   if (threadIdx.x != 0) return;
   if (pass == 2) for (int c = 0; c < 3; ++c) { s.ua[c] = s.a[c]; s.ub[c] = s.b[c]; }   // Y lies within opt_dx of THIS line
   for (int c = 0; c < 3; ++c) { s.a[c] = out.a[c]; s.b[c] = out.b[c]; }

@@ -11,7 +11,8 @@ for n in (300, 3000, 11000, 50000):
     t = rng.uniform(-20.0, 20.0, n)
     b = np.array([0.6, -0.3, 0.74]); b /= np.linalg.norm(b)
     pts = np.array([3.0, -7.0, 2.5]) + t[:, None] * b + rng.normal(0, 0.02, (n, 3))
-    for name, p in (("f64", pts), ("widened f32", pts.astype(np.float32).astype(np.float64))):
+    w = pts.astype(np.float32).astype(np.float64)
+    for name, p in (("f64", pts), ("widened f32", w), ("f64 again", pts), ("widened+1e-9", w + 1e-9), ("f64 rounded 1e-6", np.round(pts, 6))):
         capi.bench_lsq(p)
         us = capi.bench_lsq(p)
-        print(f"n={n:6d} {name:12s} means {us[0]:7.1f} us  scatter {us[1]:7.1f} us  eig {us[2]:6.1f} us  total {sum(us):7.1f} us")
+        print(f"n={n:6d} {name:18s} means {us[0]:7.1f} us  scatter {us[1]:7.1f} us  eig {us[2]:6.1f} us  total {sum(us):7.1f} us")
