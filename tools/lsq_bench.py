@@ -15,4 +15,4 @@ for n in (300, 3000, 11000, 50000):
     for name, p in (("f64", pts), ("widened f32", w), ("f64 again", pts), ("widened+1e-9", w + 1e-9), ("f64 rounded 1e-6", np.round(pts, 6))):
         capi.bench_lsq(p)
         us = capi.bench_lsq(p)
-        print(f"n={n:6d} {name:18s} means {us[0]:7.1f} us  scatter {us[1]:7.1f} us  eig {us[2]:6.1f} us  total {sum(us):7.1f} us")
+        print(f"n={n:6d} {name:18s} to barrier 1 {us[0]:7.1f} us  to barrier 2 {us[1]:7.1f} us  eig {us[2]:6.1f} us  total {sum(us):7.1f} us")
