@@ -396,6 +396,17 @@ int h3d_check_connections(const h3d_world_segment *s1, const h3d_world_segment *
 /* saveSegmentsToFile / saveIntersectionsToFile (node.cpp:850-897): same columns,
  * default ostream formatting (%g, 6 significant digits).  Either path may be NULL. */
 int h3d_world_save_csv(const h3d_world *w, const char *segments_path, const char *intersections_path);
+/* The node's verbosity levels (node.cpp:23 enum verbose {NONE, INFO, WARN}, /verbose_level): above NONE the
+ * callback time of every frame is printed, above INFO also the warnings, the intersection matrix and the segment
+ * list (node.cpp:296-346); ROS_INFO / ROS_WARN become "[ INFO] ..." / "[ WARN] ..." lines on stderr.
+ * Returns the previous level. */
+int h3d_set_verbosity(int level);
+/* The tail of the node's callback for one frame (node.cpp:308-346): logs by verbosity and appends the frame's
+ * callback_info {wall_time, callback_time, world_segments.size(), nblines} (microseconds).  h3d_replay_run_world
+ * calls it for every frame. */
+int h3d_world_note_frame(h3d_world *w, int wall_time_us, int callback_time_us, int nblines, int hough_rc);
+/* saveProcessingTimeToFile (node.cpp:905-919): "wall_time,processing_time,seg_vec_size,nblines" + one row per frame */
+int h3d_world_save_processing_time(const h3d_world *w, const char *path);
 
 /* ROS-free replay of node.cpp:286-306 for n_frames frames: hough3dlines with the post-tests,
  * drone2WorldSeg + heighSegmentCutoff with poses[i] (the pipelines must have

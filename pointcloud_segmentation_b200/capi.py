@@ -600,6 +600,11 @@ def check_connections(s1, s2, cfg):
     return bool(con.value), tuple(sol)
 
 
+def set_verbosity(level):
+    """node.cpp:23 verbosity (0 NONE, 1 INFO, 2 WARN) of the stderr logger; returns the previous level"""
+    return lib().h3d_set_verbosity(C.c_int(level))
+
+
 class World:
     """world_segments + intersection_matrix kept across frames (node.cpp:136-138, segFiltering node.cpp:479-542)."""
 
@@ -644,6 +649,14 @@ class World:
             check(lib().h3d_world_intersections(self._w, buf.ctypes.data_as(C.POINTER(C.c_double)), C.c_size_t(m * m),
                                                 C.byref(n)))
         return buf
+
+    def note_frame(self, wall_time_us, callback_time_us, nblines, hough_rc=0):
+        """node.cpp:331-346: log by verbosity, append the frame's callback_info"""
+        check(lib().h3d_world_note_frame(self._w, C.c_int(wall_time_us), C.c_int(callback_time_us), C.c_int(nblines), C.c_int(hough_rc)))
+
+    def save_processing_time(self, path):
+        """saveProcessingTimeToFile, node.cpp:905-919"""
+        check(lib().h3d_world_save_processing_time(self._w, path.encode()))
 
     def save_csv(self, segments_path=None, intersections_path=None):
         enc = lambda p: p.encode() if p is not None else None

@@ -13,6 +13,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <atomic>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -212,11 +213,24 @@ bool check_connections(const h3d_world_segment &s1, const h3d_world_segment &s2,
 
 }  // namespace
 
+// callback_info (node.cpp:46-51): one record per processed frame, written by saveProcessingTimeToFile
+struct CallbackInfo {
+  int wall_time, callback_time;   // microseconds since the start of the run / spent on this frame
+  size_t seg_vec_size;            // world_segments.size() after the frame
+  int nblines;                    // lines the Hough loop extracted from the frame
+};
+
 struct h3d_world {
   h3d_world_config cfg;
   std::vector<h3d_world_segment> segs;              // world_segments
   std::vector<std::vector<double>> inter;           // intersection_matrix, rows of (t1, t2) pairs
+  std::vector<CallbackInfo> callbacks;              // callback_info_vec
 };
+
+// The node's three verbosity levels (node.cpp:23: NONE, INFO, WARN; /verbose_level): a level above NONE prints
+// the callback time, a level above INFO also the warnings, the intersection matrix and the segment list
+// (node.cpp:296-346).  ROS_INFO / ROS_WARN become lines on stderr.
+static std::atomic<int> g_verbosity{0};
 
 namespace {
 
@@ -344,6 +358,44 @@ int h3d_check_connections(const h3d_world_segment *s1, const h3d_world_segment *
   if (!s1 || !s2 || !cfg || !sol || !connected)
     return h3d::set_error("h3d_check_connections: null argument"), H3D_ERR_ARG;
   *connected = check_connections(*s1, *s2, *cfg, sol) ? 1 : 0;
+  return H3D_OK;
+}
+
+int h3d_set_verbosity(int level) { return g_verbosity.exchange(level < 0 ? 0 : level > 2 ? 2 : level); }
+
+// The tail of the node's callback (node.cpp:308-346) for one frame: log according to the verbosity level and keep
+// the callback_info record.  hough_rc: what hough3dlines() returned for the frame.
+int h3d_world_note_frame(h3d_world *w, int wall_time_us, int callback_time_us, int nblines, int hough_rc) {
+  if (!w) return h3d::set_error("h3d_world_note_frame: null argument"), H3D_ERR_ARG;
+  const int level = g_verbosity.load(std::memory_order_relaxed);
+  if (hough_rc != 0 && level > 1) std::fprintf(stderr, "[ WARN] Unable to perform the Hough transform\n");
+  if (level > 1) {
+    std::fprintf(stderr, "[ INFO] Intersection matrix:\n");
+    for (size_t i = 0; i < w->inter.size(); i++)
+      for (size_t j = 0; j < i; j++)
+        std::fprintf(stderr, "[ INFO] intersection_matrix[%zu][%zu] = (%f, %f)\n", i, j, w->inter[i][2 * j], w->inter[i][2 * j + 1]);
+    std::fprintf(stderr, "[ INFO] Number of segments: %zu\n", w->segs.size());
+    for (size_t i = 0; i < w->segs.size(); i++)
+      std::fprintf(stderr, "[ INFO] Segment %zu: a = (%f, %f, %f), t_min = %f, t_max = %f\n", i, w->segs[i].a[0],
+                   w->segs[i].a[1], w->segs[i].a[2], w->segs[i].t_min, w->segs[i].t_max);
+  }
+  try {
+    w->callbacks.push_back(CallbackInfo{wall_time_us, callback_time_us, w->segs.size(), nblines});
+  } catch (const std::bad_alloc &) {
+    return h3d::set_error("h3d_world_note_frame: out of memory"), H3D_ERR_NOMEM;
+  }
+  if (level > 0) std::fprintf(stderr, "[ INFO] Callback execution time: %d us\n", callback_time_us);
+  return H3D_OK;
+}
+
+// saveProcessingTimeToFile (node.cpp:905-919): processing_time.csv, same header and column order
+int h3d_world_save_processing_time(const h3d_world *w, const char *path) {
+  if (!w || !path) return h3d::set_error("h3d_world_save_processing_time: null argument"), H3D_ERR_ARG;
+  FILE *f = std::fopen(path, "w");
+  if (!f) return h3d::set_error(std::string("h3d_world_save_processing_time: cannot open ") + path), H3D_ERR_ARG;
+  std::fprintf(f, "wall_time,processing_time,seg_vec_size,nblines\n");
+  for (const CallbackInfo &c : w->callbacks) std::fprintf(f, "%d,%d,%zu,%d\n", c.wall_time, c.callback_time, c.seg_vec_size, c.nblines);
+  std::fclose(f);
   return H3D_OK;
 }
 

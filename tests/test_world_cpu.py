@@ -236,3 +236,39 @@ def test_update_frame_takes_kept_world_segments(h3d):
     assert tuple(segs[0].pca_eigenvalues) == (1.0, 0.5, 1.0 / 3)
     assert w.update_frame([]) == 0
     w.close()
+
+
+def test_verbosity_levels_and_processing_time_csv(h3d, tmp_path, capfd):
+    """node.cpp:23, 296-346 (what each verbosity level prints) and saveProcessingTimeToFile (node.cpp:905-919):
+    header, column order, one row per frame with world_segments.size() after the frame"""
+    w = h3d.World(DIAG, MIN_W)
+    segs = [h3d.WorldSegment.make((0, 0, 1.0 + k), (1, 0, 0), t_min=-1.0, t_max=1.0, radius=0.05, points_size=50,
+                                  pca_coeff=0.99, pca_eigenvalues=(1.0, 0.01, 0.01)) for k in range(2)]
+    old = h3d.set_verbosity(0)
+    try:
+        w.update(segs[:1]); w.note_frame(1000, 400, 3)                       # NONE: nothing on stderr
+        assert capfd.readouterr().err == ""
+        h3d.set_verbosity(1)
+        w.update(segs); w.note_frame(2500, 600, 5, hough_rc=1)               # INFO: the callback time only
+        err = capfd.readouterr().err
+        assert err == "[ INFO] Callback execution time: 600 us\n"
+        h3d.set_verbosity(2)
+        w.note_frame(4000, 700, 0, hough_rc=1)                               # WARN: warning, matrix, segments, time
+        err = capfd.readouterr().err.splitlines()
+        assert err[0] == "[ WARN] Unable to perform the Hough transform"
+        assert err[1] == "[ INFO] Intersection matrix:"
+        n = len(w.segments())
+        assert f"[ INFO] Number of segments: {n}" in err
+        assert sum(l.startswith("[ INFO] Segment ") for l in err) == n
+        assert sum(l.startswith("[ INFO] intersection_matrix[") for l in err) == n * (n - 1) // 2
+        assert err[-1] == "[ INFO] Callback execution time: 700 us"
+    finally:
+        h3d.set_verbosity(old)
+    path = tmp_path / "processing_time.csv"
+    w.save_processing_time(str(path))
+    rows = path.read_text().splitlines()
+    assert rows[0] == "wall_time,processing_time,seg_vec_size,nblines"
+    assert rows[1] == "1000,400,1,3"
+    assert rows[2].split(",")[:2] == ["2500", "600"] and rows[2].split(",")[3] == "5"
+    assert rows[3] == f"4000,700,{len(w.segments())},0" and len(rows) == 4
+    w.close()
