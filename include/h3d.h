@@ -477,8 +477,10 @@ int h3d_set_debug_poison(int on);
  * bits 8..15 of `ablate` optionally give the directions per work item (1,2,4; 0 = automatic: register-resident points when they fit). */
 int h3d_bench_vote(h3d_hough *h, int reps, int ablate, float *us_per_launch);
 /* one orthogonal_LSQ call (wrap.h:121-150) on a host cloud: device time of its phases in microseconds
- * (us[0] means incl. the sequential anchor, us[1] scatter sums, us[2] eigen-solve), globaltimer stamps */
-int h3d_bench_lsq(const double *xyz, size_t n, float us[3]);
+ * (us[0] to the barrier after the column means and the sequential anchor, us[1] scatter sums, us[2] eigen-solve;
+ * us[3] / us[4]: when warp 0 had its float mean / warp 3 its sequential double mean, from the kernel's start),
+ * globaltimer stamps */
+int h3d_bench_lsq(const double *xyz, size_t n, float us[5]);
 
 #ifdef __cplusplus
 }

@@ -538,7 +538,7 @@ def remove_points(x, y):
 def bench_lsq(xyz):
     """device time (us) of the phases of one orthogonal_LSQ call: means (incl. the sequential anchor), scatter sums, eig"""
     a, p, n = _pts(xyz)
-    us = (C.c_float * 3)()
+    us = (C.c_float * 5)()
     check(lib().h3d_bench_lsq(p, n, us))
     return list(us)
 

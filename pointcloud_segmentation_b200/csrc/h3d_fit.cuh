@@ -429,10 +429,12 @@ __device__ __forceinline__ void lsq_cta(const double *__restrict__ x, const doub
       for (int k = ns + lane; k < n; k += 32) acc = __fadd_rn(acc, (float)p[k]);   // loads run ahead of the chain
       acc = tree32_combine(acc);
       if (lane == 0) s.mean[q] = __fdiv_rn(acc, (float)n);
+      if (dbg && q == 0 && lane == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t) : : "memory"); dbg[5] = t; }
     } else {                          // meanValue (lib/pointcloud.cpp:29-38)
       const double *__restrict__ p = axis(q - 3);
       const double m = mean_axis_warp<8>([&](int k) { return p[k]; }, n, lane);
       if (lane == 0) out->a[q - 3] = m;
+      if (dbg && q == 3 && lane == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t) : : "memory"); dbg[4] = t; }
     }
   }
   __syncthreads();
