@@ -55,9 +55,14 @@ struct FusedArgs {
 constexpr int kProfSlots = 16;
 constexpr int kFusedMaxSlots = 12;
 
+// A timer read placed right after __syncthreads() is NOT held back by the barrier (BAR.SYNC.DEFER_BLOCKING lets the
+// warp run on until it touches memory): the volatile shared-memory load in front of it is, and instructions of a
+// warp issue in order, so the stamp is taken once the barrier has completed.
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  unsigned probe;
+  asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(probe) : "r"(0u) : "memory");
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t) : "r"(probe) : "memory");
   return t;
 }
 
