@@ -9,15 +9,18 @@ granularity 6, opt_nlines 20, opt_minvotes 12, dx = sqrt(3)*leaf.
 
 A step is one pass of the hot path over a batch of FRAMES_PER_STEP synthetic frames (DISTINCT_FRAMES different ones, cycled)
 (poses along the tower trajectory).  Frames are independent (one Hough per frame) and the loop of
-one frame is latency-bound, so a GPU keeps K frames in flight: K pipelines driven by K host
-threads of the library (h3d_replay_run), each limited to a share of the SMs for its persistent loop
+one frame is latency-bound, so a GPU keeps K frames in flight: K pipelines driven by a few host
+threads of the library (h3d_replay_run, split-phase workers: --replay-threads), each limited to a share of the SMs for its persistent loop
 kernels (--concurrency 16 x --sm-share 9 by default = 144 of the 148 SMs; shares that oversubscribe the GPU also
 work, a cooperative kernel then waits for free SMs).
 `value` is timed with the frames resident in HBM (h3d_pipeline_run_dev), `e2e` through
 h3d_pipeline_run with pinned HOST frames: H2D of the raw frame and D2H of the line records and
 inlier lists are inside the timed region.  A step is bracketed by device synchronisation and a pair
-of CUDA events (all pipeline streams drained on both sides); for N > 1 every rank replays its own
-frames (frame-parallel, no collective on the data path) and the maximum over ranks is reported.
+of CUDA events (all pipeline streams drained on both sides); for N > 1 every rank replays the same
+frames in the same order (frame-parallel, no collective on the data path) and the maximum over ranks is
+reported.  Every frame's complete result is hashed in both timed legs and compared with the same frame run alone
+(`parity_in_timed_region`; a mismatch makes the run fail), and a `direction_sharded` leg runs configs[3]
+(1 M points, accumulator sharded by direction over the ranks, one 8-byte NCCL all-reduce per iteration).
 A third leg runs one frame at a time on all SMs: `single_frame_latency` (the < 1 ms target of
 BASELINE.json's north_star) and the `roofline` of the frame's one kernel, timed alone.
 Only the cpu_baseline leg and --impl reference execute anything under oracle/.
