@@ -370,7 +370,7 @@ __device__ __forceinline__ FusedView fused_view(int n_own, int nb, int n_cap) {
 //   stage 2  one WARP per listed record, 32 candidates per step.
 // Before (every surviving record took a warp that walked all of Y with a float-t filter) the phase cost 20-90 us
 // per iteration with 2276 records per CTA (9 SMs per frame), most of it per-record overhead of stage 2.
-constexpr int kUvBuckets = 128, kUvInline = 16;
+constexpr int kUvBuckets = 256, kUvInline = 8;
 
 __device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b)[3], int ny2, int n_own, int nb, int n_cap,
                                           int cta, int n_cta, double cell_off, double reach2) {
