@@ -406,6 +406,10 @@ def run_gpu_arm(args):
     # frame's loop is latency-bound, so the GPU is filled with frames in flight
     replay = capi.Replay(K, share, GRANULARITY, synth.WINDOW, synth.LEAF, synth.OPT_DX, MINVOTES, NLINES, n_pts,
                          FRAMES_PER_STEP)
+    # SMs left over by K x share (148 - 16 x 9 = 4) go to the first pipelines, one each
+    spare = sm_count - K * share if (K > 1 and share > 0 and not args.no_spare_sms) else 0
+    for k in range(max(0, min(spare, K))):
+        replay.pipes[k].set_sm_share(share + 1)
     host_ptrs = [pinned[(k + rot) % DISTINCT_FRAMES].data_ptr() for k in range(FRAMES_PER_STEP)]
     dev_ptrs = [on_dev[(k + rot) % DISTINCT_FRAMES].data_ptr() for k in range(FRAMES_PER_STEP)]
     counts = [n_pts] * FRAMES_PER_STEP
@@ -598,7 +602,7 @@ def run_gpu_arm(args):
                                    "Hough g6 (20481 directions), dx=sqrt(3)*leaf, opt_nlines 20, opt_minvotes 12",
                        "frames_per_step": FRAMES_PER_STEP, "filtered_points_per_frame": round(dev["nf"] / n_frames_rank, 1),
                        "lines_per_frame": dev["lines"] / n_frames_rank, "l2": "flushed between steps (256 MiB write)",
-                       "distinct_frames": DISTINCT_FRAMES, "frames_in_flight_per_gpu": K, "sms_per_frame": share or sm_count,
+                       "distinct_frames": DISTINCT_FRAMES, "frames_in_flight_per_gpu": K, "sms_per_frame": share or sm_count, "pipelines_with_one_more_sm": max(0, min(spare, K)),
                        "parallelism": (f"frame-parallel x{world} GPUs, " if world > 1 else "single GPU, ") +
                                       f"{K} frames in flight per GPU",
                        "sm_count": sm_count, "host_cores": host_cores,
@@ -772,6 +776,7 @@ def main():
                     help="frames in flight per GPU (K pipelines, K host threads); 1 = lowest latency")
     ap.add_argument("--wait", choices=("auto", "spin", "block", "yield"), default="auto",
                     help="how the K host threads wait for the device (auto: poll + yield when frames are in flight)")
+    ap.add_argument("--no-spare-sms", action="store_true", help="do not hand the SMs left over by K x share to the first pipelines")
     ap.add_argument("--replay-threads", type=int, default=-1,
                     help="host threads per rank driving the frames in flight (-1: one per frame in flight while the "
                          "box has the cores, fewer otherwise)")
