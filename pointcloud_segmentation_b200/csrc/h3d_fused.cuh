@@ -319,6 +319,43 @@ __device__ __forceinline__ void revote_pair(const HoughDev &h, const FusedPoints
   best0 = b0; best1 = b1;
 }
 
+// The same for FOUR directions per pass over the points (records j[k] < 0: none): the three coordinate loads, the
+// loop overhead and the fixed cost of a pass (coefficient fetch from L2, key reductions) are shared by four
+// planes instead of two.  Used when the frame's layout has at least four planes.
+__device__ __forceinline__ void revote_quad(const HoughDev &h, const FusedPoints &Q, int n_alive, const FastCoef (&f)[4],
+                                            const int (&j)[4], unsigned plane0_sa, unsigned plane_bytes, unsigned dummy_sa,
+                                            unsigned (&best)[4]) {
+  const double kmagic = h.kmagic;
+  const unsigned row4 = 4u * (unsigned)h.num_x, plane_cells = h.plane_cells, lim = 4u * h.plane_cells;
+  const bool no_fast = !h.fast_ok;
+  unsigned b[4] = {0u, 0u, 0u, 0u};
+#pragma unroll 1
+  for (int i = threadIdx.x; i < n_alive; i += kResThreads) {
+    const double x = Q.x[i], y = Q.y[i], z = Q.z[i];
+    unsigned gmin = 0xFFFFFFFFu;
+    unsigned o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = vote_off_bounded(f[k], kmagic, row4, x, y, z, gmin);
+    if ((gmin < 0x10000u) | no_fast) {   // rare: within 8e-6 cell of a boundary
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (j[k] < 0) continue;
+        const unsigned c = vote_cell_checked(h.coef + j[k], h.inv_s, kmagic, h.max_x, h.dx, h.num_x, h.fast_ok, x, y, z);
+        o[k] = c < plane_cells ? 4u * c : lim;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const bool have = j[k] >= 0, in = have & (o[k] < lim);
+      const unsigned old = atom_shared_inc_ret(have ? plane0_sa + (unsigned)k * plane_bytes + o[k] : dummy_sa);
+      const unsigned key = ((old + 1u) << 16) | ((o[k] >> 2) ^ 0xFFFFu);
+      b[k] = max(b[k], in ? key : 0u);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) best[k] = b[k];
+}
+
 // ---- shared-memory layout of the loop kernel ---------------------------------------------------------------
 // [HoughDev | FusedShared | record tables | planes (+ pad) | live points, inlier list, its t values], all carved
 // out of the one extern array so that the out-of-line phase functions below address it as SHARED memory (LDS /
@@ -548,6 +585,27 @@ __device__ __noinline__ void fused_revote(int nlist, int n_alive, int n_own, int
 #pragma unroll 1
     for (int b0 = 0; b0 < nlist; b0 += nb) {
       const int cnt = min(nb, nlist - b0);
+      if (nb >= 4) {
+#pragma unroll 1
+        for (int bi = 0; bi < cnt; bi += 4) {
+          int j[4];
+          FastCoef f[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int r = bi + k < cnt ? rlist[b0 + bi + k] : -1;
+            j[k] = r >= 0 ? h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G) : -1;
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) f[k] = make_fast(h.coef[j[k] >= 0 ? j[k] : j[0]], h.inv_s);
+          unsigned key[4];
+          revote_quad(h, Q, n_alive, f, j, planes_sa + (unsigned)bi * stride * 4u, stride * 4u, dummy_sa, key);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const unsigned kk = __reduce_max_sync(0xFFFFFFFFu, key[k]);
+            if (lane == 0) sh.rv_best[bi + k][warp] = kk;
+          }
+        }
+      } else {
 #pragma unroll 1
       for (int bi = 0; bi < cnt; bi += 2) {
         const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
@@ -559,6 +617,7 @@ __device__ __noinline__ void fused_revote(int nlist, int n_alive, int n_own, int
         k0 = __reduce_max_sync(0xFFFFFFFFu, k0);
         k1 = __reduce_max_sync(0xFFFFFFFFu, k1);
         if (lane == 0) { sh.rv_best[bi][warp] = k0; sh.rv_best[bi + 1][warp] = k1; }
+      }
       }
       __syncthreads();
       {   // the planes of this round back to zero (no scan: the keys already hold the maxima)
