@@ -66,14 +66,19 @@ def make_frames(count, rank=0):
     from pointcloud_segmentation_b200 import synth
     cache = f"/tmp/h3d_frames_{count}_{rank}.npy"
     if os.path.exists(cache):
-        f = np.load(cache)
-        if f.shape == (count, synth.TOF_W * synth.TOF_H, 4):
-            return f
+        try:
+            f = np.load(cache)
+            if f.shape == (count, synth.TOF_W * synth.TOF_H, 4):
+                return f
+        except Exception:   # another rank may be writing it (every rank uses the same frames): regenerate
+            pass
     poses = synth.tower_trajectory(1000)
     pick = np.linspace(0, 999, count).astype(int) if rank == 0 else (np.arange(count) * 37 + 101 * rank) % 1000
     frames = np.stack([synth.tof_frame(pose=tuple(poses[k]), seed=1000 + int(k)) for k in pick]).astype(np.float32)
-    try:
-        np.save(cache, frames)
+    try:                    # atomic: a reader never sees a half-written file
+        tmp = f"{cache}.{os.getpid()}.tmp.npy"
+        np.save(tmp, frames)
+        os.replace(tmp, cache)
     except OSError:
         pass
     return frames
