@@ -11,8 +11,8 @@ A step is one pass of the hot path over a batch of FRAMES_PER_STEP synthetic fra
 (poses along the tower trajectory).  Frames are independent (one Hough per frame) and the loop of
 one frame is latency-bound, so a GPU keeps K frames in flight: K pipelines driven by a few host
 threads of the library (h3d_replay_run, split-phase workers: --replay-threads), each limited to a share of the SMs for its persistent loop
-kernels (--concurrency 16 x --sm-share 9 by default = 144 of the 148 SMs; shares that oversubscribe the GPU also
-work, a cooperative kernel then waits for free SMs).
+kernels (--concurrency 24 x --sm-share 9 by default = 216 > 148 SMs, oversubscribed on purpose: a cooperative
+kernel then waits for free SMs while other pipelines' kernels fill the gaps).
 `value` is timed with the frames resident in HBM (h3d_pipeline_run_dev), `e2e` through
 h3d_pipeline_run with pinned HOST frames: H2D of the raw frame and D2H of the line records and
 inlier lists are inside the timed region.  A step is bracketed by device synchronisation and a pair
@@ -50,9 +50,12 @@ FRAMES_PER_STEP = int(os.environ.get("H3D_FRAMES_PER_STEP", "256"))   # frames p
                               # depended on the ORDER of the frames (measured: the same frames rotated by 5 on a
                               # second rank ran 13 % slower than the heaviest-first order of rank 0)
 DISTINCT_FRAMES = 16
-FRAMES_IN_FLIGHT = 16          # pipelines (host threads) per GPU ...
+FRAMES_IN_FLIGHT = 24          # pipelines per GPU ...
 SM_SHARE = 9                   # ... each limited to this many SMs for its vote and persistent loop kernels
-                               # (16 x 9 = 144 of 148 SMs; sweep on B200: profiles/r02_concurrency_sweep_final.txt)
+                               # (24 x 9 = 216 > 148 SMs, oversubscribed on purpose: a cooperative loop kernel waits for
+                               # 9 free SMs while the other pipelines' K0 / vote kernels and drain tails fill the gaps;
+                               # sweep on B200, profiles/r02_concurrency_sweep_final.txt: 16x9 (+4 spare SMs) 4056,
+                               # 20x9 4108, 24x9 4109, 28x9 4116, 16x10 4001, 18x8 3750 frames/s)
 GRANULARITY = 6
 NLINES = 20
 MINVOTES = 12

@@ -23,7 +23,7 @@ GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "refer
 FIELDS = ("votes", "argmax", "status", "n1", "n2", "inl1", "inl2", "a2", "b2")
 # (pipelines, SMs per pipeline): round 1's oversubscribed bench configuration (216 > 148 SMs: cooperative kernels
 # queue for SMs) and bench.py's current FRAMES_IN_FLIGHT x SM_SHARE
-SHAPES = [(12, 18), (16, 9)]
+SHAPES = [(12, 18), (16, 9), (24, 9)]
 
 
 def _sha(a):
@@ -92,7 +92,7 @@ def test_single_frames_match_the_reference_at_g6(h3d, tof):
     assert sum(int(w["n_lines"]) for w in want) == 257 or "oracle" in tof[3]
 
 
-@pytest.mark.parametrize("shape", SHAPES, ids=["12x18", "16x9"])
+@pytest.mark.parametrize("shape", SHAPES, ids=["12x18", "16x9", "24x9"])
 @pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("on_device", [False, True])
 def test_oversubscribed_replay_matches_the_reference(h3d, tof, fused, on_device, shape):
