@@ -705,7 +705,7 @@ def run_c3(args):
         frames = np.stack(pool.map(_c3_frame, mine, chunksize=8))
     n_pts, stride = frames.shape[1], frames.shape[2]
     pinned = torch.from_numpy(frames).pin_memory()
-    K, chunk = args.concurrency, 64
+    K, chunk = args.concurrency, 250   # frames per timed call: the drain tail of a call is one frame time
     capi.set_wait_mode(2 if K > 1 else 0)
     try:
         cores_per_rank = max(1, len(os.sched_getaffinity(0)) // world)
