@@ -1,3 +1,4 @@
+"""One orthogonal_LSQ call on 11 k points (full-mantissa doubles, then widened floats): the command ncu captures."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
