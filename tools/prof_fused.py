@@ -1,4 +1,5 @@
-"""Phase breakdown of the fused loop kernel (globaltimer stamps, h3d_pipeline_profile)."""
+"""Phase breakdown of the fused loop kernel (globaltimer stamps, h3d_pipeline_profile).
+argv: [sm_share] [bench frame 0..15 | -1] [cold]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -15,7 +16,12 @@ else:
 pipe = capi.Pipeline(6, synth.WINDOW, synth.LEAF, synth.OPT_DX, 12, 20, max_raw_points=frame.shape[0])
 pipe.set_sm_share(share)
 pipe.profile_enable(24)
+cold = len(sys.argv) > 3 and sys.argv[3] == "cold"     # flush L2 (256 MiB write) before the measured frame, as bench.py does
 for _ in range(3):
+    if cold:
+        import torch
+        torch.empty(256 << 20, dtype=torch.uint8, device="cuda").fill_(1)
+        torch.cuda.synchronize()
     res = pipe.run(frame)
 print(res.n_input, res.n_lines, [round(u, 1) for u in pipe.timing_us()])
 t = pipe.profile_read().astype(np.int64)
