@@ -395,6 +395,15 @@ __device__ __forceinline__ FusedView fused_view(int n_own, int nb, int n_cap) {
   return V;
 }
 
+// Which direction (index inside the instance's slice) is record r of CTA `cta`.  With few CTAs (frames in flight, 9-18
+// SMs each) groups of G consecutive directions stay together (their coefficients share cache lines).  With the whole
+// GPU on one frame the map is a pure interleave: directions next to each other on the sphere turn stale together, and
+// with 140 records per CTA a clump of them on one CTA made every other CTA wait at the next barrier for its re-votes.
+__device__ __forceinline__ int own_dir(int r, int cta, int n_cta) {
+  constexpr int G = kResG;
+  return n_cta >= 64 ? r * n_cta + cta : (cta + (r / G) * n_cta) * G + (r % G);
+}
+
 // K4 inside the loop: Hough::subtract(Y) for the CTA's own directions, run by warps 1..15 while warp 0 solves the
 // second eigen-problem.  Y (pass 2, ny2 points) lies within opt_dx of the line (a, b) of pass 2.
 //
@@ -430,9 +439,10 @@ __device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b
   int *sidx = fill + kUvBuckets;
   float *st = reinterpret_cast<float *>(sidx + ny2);
   const unsigned scratch_words = 2u * kUvBuckets + 1u + 2u * (unsigned)ny2;
-  // uniform.  Not with few records per CTA (a frame on all SMs: the three barriers of the bucketing would cost more
-  // than they save, and the phase hides behind the eigen-solve anyway) or tiny planes with a huge Y.
-  const bool bucketed = n_own >= 512 && scratch_words <= (unsigned)nb * V.stride;
+  // uniform.  Not with few records per CTA AND a short Y (a frame on all SMs: the three barriers of the bucketing
+  // would cost more than they save, and the phase hides behind the eigen-solve anyway; with a long Y the warp stage
+  // walked 400 inliers for each of ~140 records, 10 us on the critical path) or tiny planes with a huge Y.
+  const bool bucketed = (n_own >= 512 || ny2 >= 128) && scratch_words <= (unsigned)nb * V.stride;
   const float bscale = th > tl ? (float)kUvBuckets / (th - tl) : 0.0f;
   // monotonic in t (float subtraction, multiplication by a positive constant, truncation, clamp): a point with
   // flo <= t_e <= fhi lies in a bucket of [bucket_of(flo), bucket_of(fhi)]
@@ -474,7 +484,7 @@ __device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b
     for (int u = 0; u < SU; ++u) {
       const int r = r0 + u * un;
       live[u] = r < n_own && !rstale[r] && rv[r] != 0;
-      if (live[u]) cj[u] = h.coef[h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G)];
+      if (live[u]) cj[u] = h.coef[h.dir_begin + own_dir(r, cta, n_cta)];
     }
 #pragma unroll
     for (int u = 0; u < SU; ++u) {
@@ -491,7 +501,7 @@ __device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b
       if (!bucketed) { rlist[atomicAdd(&sh.ns, 1)] = r; continue; }
       const float flo = (float)(ilo - (fabs(ilo) * 1e-6 + 1e-6)), fhi = (float)(ihi + (fabs(ihi) * 1e-6 + 1e-6));
       const int e0 = start[bucket_of(flo)], e1 = start[bucket_of(fhi) + 1];
-      const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
+      const int j = h.dir_begin + own_dir(r, cta, n_cta);
       // middle-out over the sorted range: a vote for the cell needs P(t) within half a cell of its centre, i.e.
       // t in the central third of the interval, so a record whose max cell lies ON the removed line (almost
       // every record when a dominant line goes) is hit within the first few tests
@@ -530,12 +540,12 @@ __device__ __noinline__ void fused_unvote(const double (&a)[3], const double (&b
       const int sq = s + lane * (kResWarps - 1);
       if (sq < ns) {
         const int rq = rlist[sq];
-        pre = h.coef[h.dir_begin + (cta + (rq / G) * n_cta) * G + (rq % G)];
+        pre = h.coef[h.dir_begin + own_dir(rq, cta, n_cta)];
       }
       pre_base = q;
     }
     const int r = rlist[s];
-    const int j = h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G);
+    const int j = h.dir_begin + own_dir(r, cta, n_cta);
     DirCoef cj;
     {
       const int src = q - pre_base;
@@ -593,7 +603,7 @@ __device__ __noinline__ void fused_revote(int nlist, int n_alive, int n_own, int
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             const int r = bi + k < cnt ? rlist[b0 + bi + k] : -1;
-            j[k] = r >= 0 ? h.dir_begin + (cta + (r / G) * n_cta) * G + (r % G) : -1;
+            j[k] = r >= 0 ? h.dir_begin + own_dir(r, cta, n_cta) : -1;
           }
 #pragma unroll
           for (int k = 0; k < 4; ++k) f[k] = make_fast(h.coef[j[k] >= 0 ? j[k] : j[0]], h.inv_s);
@@ -609,8 +619,8 @@ __device__ __noinline__ void fused_revote(int nlist, int n_alive, int n_own, int
 #pragma unroll 1
       for (int bi = 0; bi < cnt; bi += 2) {
         const int r0 = rlist[b0 + bi], r1 = bi + 1 < cnt ? rlist[b0 + bi + 1] : -1;
-        const int j0 = h.dir_begin + (cta + (r0 / G) * n_cta) * G + (r0 % G);
-        const int j1 = r1 >= 0 ? h.dir_begin + (cta + (r1 / G) * n_cta) * G + (r1 % G) : -1;
+        const int j0 = h.dir_begin + own_dir(r0, cta, n_cta);
+        const int j1 = r1 >= 0 ? h.dir_begin + own_dir(r1, cta, n_cta) : -1;
         unsigned k0, k1;
         revote_pair(h, Q, n_alive, make_fast(h.coef[j0], h.inv_s), make_fast(h.coef[j1 >= 0 ? j1 : j0], h.inv_s), j0, j1,
                     planes_sa + (unsigned)bi * stride * 4u, planes_sa + (unsigned)(bi + 1) * stride * 4u, dummy_sa, k0, k1);
@@ -670,7 +680,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
   }
   // own records: entry r = k*G + g is direction (cta + k*n_cta)*G + g
   for (int r = tid; r < n_own; r += kResThreads) {
-    const int l = (cta + (r / G) * n_cta) * G + (r % G);
+    const int l = own_dir(r, cta, n_cta);
     if (l < h.dir_count) {
       rv[r] = h.dvotes[l]; rcell[r] = h.dcell[l];
     } else { rv[r] = 0; rcell[r] = 0; }
@@ -715,7 +725,7 @@ __global__ void __launch_bounds__(kResThreads, 1) fused_loop_kernel(const FusedA
     {
       unsigned long long k = 0;
       for (int r = tid; r < n_own; r += kResThreads) {
-        const int l = (cta + (r / G) * n_cta) * G + (r % G);
+        const int l = own_dir(r, cta, n_cta);
         if (l < h.dir_count) { const unsigned long long kk = line_key(rv[r], rcell[r], h.dir_begin + l, h.num_b); k = kk > k ? kk : k; }
       }
       k = block_max_u64(k, sh.warp_key);
