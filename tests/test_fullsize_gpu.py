@@ -100,7 +100,11 @@ def test_big_cloud_kernels_match_one_cta_kernels_and_oracle(h3d, oracle):
     """Clouds >= 32 768 points take the chunked multi-CTA compaction / removal kernels: same records as the
     one-CTA kernels of the frame loop, and both equal to the oracle (40 k-point tower, g4; a ragged last chunk)."""
     pts = synth.steel_tower(40000 + 77, seed=8)
+    # non-finite points are stripped in order (wrap.h:175-189): in the first and the last chunk, a whole run of
+    # them across a chunk border, and scattered ones -- the chunked prep kernels must keep order and indices
+    pts[0, 0] = np.nan; pts[1023:1030, 1] = np.inf; pts[-1, 2] = -np.inf; pts[5000:39000:977, 0] = np.nan
     want = oracle.hough3dlines(pts, 4, 0.0, 10, 14, mode=1)
+    assert want.n_input == len(pts) - int((~np.isfinite(pts).all(axis=1)).sum()) < len(pts)
     runs = []
     for on in (1, 0):
         old = h3d.set_big_kernels(on)
@@ -108,6 +112,7 @@ def test_big_cloud_kernels_match_one_cta_kernels_and_oracle(h3d, oracle):
         h3d.set_big_kernels(old)
     for got in runs:
         assert (got.rc, got.n_lines, len(got.iters)) == (want.rc, want.n_lines, len(want.iters))
+        assert got.n_input == want.n_input and np.array_equal(got.shift, want.shift) and got.d == want.d
         for g, w in zip(got.iters, want.iters):
             assert (g["votes"], g["argmax"], g["status"]) == (w.votes, w.argmax, w.status)
             assert np.array_equal(g["inliers1"], w.inliers1) and np.array_equal(g["inliers2"], w.inliers2)
