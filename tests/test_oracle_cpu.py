@@ -195,6 +195,18 @@ def test_product_fails_loudly_without_gpu(h3d):
         h3d.hough3dlines(np.random.default_rng(0).standard_normal((10, 3)), 2, 0.1, 2, 2)
 
 
+def test_noalloc_entry_point_checks_its_arguments_before_touching_cuda(h3d):
+    """h3d_points_close_to_line_noalloc: a cloud beyond the fixed scratch is refused with H3D_ERR_RANGE and a
+    message that names the limit; null pointers with H3D_ERR_ARG -- both without a device (no compute call is made)"""
+    dummy = 4096                                       # never dereferenced: the checks come first
+    with pytest.raises(h3d.H3dError) as err:
+        h3d.points_close_to_line_noalloc(dummy, h3d.NOALLOC_MAX_POINTS + 1, (0, 0, 0), (0, 0, 1), 0.1, dummy, dummy)
+    assert err.value.code == 4 and "H3D_NOALLOC_MAX_POINTS" in str(err.value)
+    with pytest.raises(h3d.H3dError) as err:
+        h3d.points_close_to_line_noalloc(0, 10, (0, 0, 0), (0, 0, 1), 0.1, dummy, dummy)
+    assert err.value.code == 1
+
+
 def test_product_eigensolver_matches_oracle_on_host(tmp_path):
     """eig3f of the product (csrc/h3d_fit.cuh, its __host__ side) vs the oracle's h3do_eig3f."""
     import shutil
